@@ -1,0 +1,91 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference (imported from
+/root/reference, build container only) on the seeded weights/inputs of
+zipvoice_b200.synth.  Run:  python -m oracle.make_golden
+The fixtures pin the oracle restatement (tests/test_oracle_golden.py) and are the
+known-answer vectors for the CUDA path (tests/test_gpu_parity.py).
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+REF = "/root/reference"
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def _ref_model(kind, cfg, sd):
+    sys.path.insert(0, REF)
+    from zipvoice.models.zipvoice import ZipVoice
+    from zipvoice.models.zipvoice_dialog import ZipVoiceDialog
+    from zipvoice.models.zipvoice_distill import ZipVoiceDistill
+    from zipvoice_b200 import synth
+    cls = {"zipvoice": ZipVoice, "distill": ZipVoiceDistill, "dialog": ZipVoiceDialog}[kind]
+    kw = dict(cfg, vocab_size=synth.VOCAB_SIZE, pad_id=synth.PAD_ID)
+    if kind == "dialog":
+        kw.update(spk_a_id=synth.SPK_A_ID, spk_b_id=synth.SPK_B_ID)
+    m = cls(**kw).eval()
+    m.load_state_dict(sd, strict=True)
+    return m
+
+
+from tests.cases import case_inputs  # noqa: E402  (same seeded inputs as the tests)
+
+
+@torch.inference_mode()
+def main():
+    from zipvoice_b200 import synth
+    os.makedirs(OUT, exist_ok=True)
+    torch.set_num_threads(8)
+    small = synth.small_model_cfg()
+
+    # 1. one fm_decoder NFE, stress weights, ragged mask
+    sd = synth.make_state_dict(small, seed=1, stress=True)
+    m = _ref_model("zipvoice", small, sd)
+    x0, text, speech, mask = case_inputs(2, 37, 11, seed=10)
+    v = m.forward_fm_decoder(torch.tensor(0.3), x0, text, speech, mask)
+    np.savez(os.path.join(OUT, "velocity_small_stress.npz"), v=v.numpy())
+
+    # 2. Euler + CFG, both t>0.5 branches, stress weights
+    x1 = m.solver.sample(x=x0, text_condition=text, speech_condition=speech, padding_mask=mask,
+                         num_step=4, guidance_scale=1.0, t_shift=0.5)
+    x1b = m.solver.sample(x=x0, text_condition=text, speech_condition=speech, padding_mask=mask,
+                          num_step=3, guidance_scale=0.0, t_shift=0.7)
+    np.savez(os.path.join(OUT, "euler_small_stress.npz"), x1_cfg=x1.numpy(), x1_nocfg=x1b.numpy())
+
+    # 3. distill: guidance embedded, no doubling
+    sdd = synth.make_state_dict(small, seed=2, distill=True, stress=True)
+    md = _ref_model("distill", small, sdd)
+    x1d = md.solver.sample(x=x0, text_condition=text, speech_condition=speech, padding_mask=mask,
+                           num_step=2, guidance_scale=3.0, t_shift=0.5)
+    np.savez(os.path.join(OUT, "euler_small_distill.npz"), x1=x1d.numpy())
+
+    # 4. ZipVoice.sample end to end (text encoder + condition + solver + prompt strip)
+    tokens, prompt_tokens = synth.make_tokens(2, n_prompt=9, n_text=21, seed=5, ragged=True)
+    pf, pfl = synth.make_prompt_features(2, 14, seed=6, ragged=True)
+    torch.manual_seed(666)
+    out = m.sample(tokens=tokens, prompt_tokens=prompt_tokens, prompt_features=pf, prompt_features_lens=pfl,
+                   speed=1.3, t_shift=0.5, duration="predict", num_step=3, guidance_scale=1.0)
+    emb, tl = m.forward_text_embed([p + t for p, t in zip(prompt_tokens, tokens)])
+    np.savez(os.path.join(OUT, "sample_small_stress.npz"), x1_wo=out[0].numpy(), wo_lens=out[1].numpy(),
+             x1_prompt=out[2].numpy(), text_embed=emb.numpy())
+
+    # 5. dialog text embed (speaker rows)
+    sdg = synth.make_state_dict(small, seed=3, dialog=True, stress=True)
+    mg = _ref_model("dialog", small, sdg)
+    dt, dp = synth.make_tokens(2, n_prompt=30, n_text=60, seed=8, dialog=True, ragged=True)
+    embg, _ = mg.forward_text_embed([p + t for p, t in zip(dp, dt)])
+    np.savez(os.path.join(OUT, "dialog_text_embed.npz"), text_embed=embg.numpy())
+
+    # 6. full 123 M base config, init-like weights, one CFG velocity through DiffusionModel
+    sdb = synth.make_state_dict(synth.BASE_MODEL_CFG, seed=0)
+    mb = _ref_model("zipvoice", synth.BASE_MODEL_CFG, sdb)
+    xb, tb, sb, mkb = case_inputs(2, 50, 15, seed=11)
+    vb = mb.solver.model(t=torch.tensor(0.7), x=xb, text_condition=tb, speech_condition=sb, padding_mask=mkb,
+                         guidance_scale=1.5)
+    np.savez(os.path.join(OUT, "velocity_base_cfg.npz"), v=vb.numpy())
+    print("golden written to", OUT)
+
+
+if __name__ == "__main__":
+    main()

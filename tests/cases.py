@@ -1,0 +1,24 @@
+"""Seeded solver-level inputs shared by oracle/make_golden.py and the tests."""
+import torch
+
+
+def case_inputs(B, T, prompt, seed, ragged=True):
+    g = torch.Generator().manual_seed(seed)
+    x0 = torch.randn(B, T, 100, generator=g)
+    text = torch.randn(B, T, 100, generator=g) * 0.5
+    speech = torch.randn(B, T, 100, generator=g) * 0.5 - 0.5
+    speech[:, prompt:] = 0
+    lens = torch.full((B,), T, dtype=torch.int64)
+    if ragged and B > 1:
+        lens[1:] = torch.randint(T // 2, T, (B - 1,), generator=g)
+    mask = torch.arange(T)[None] >= lens[:, None]
+    return x0, text, speech, mask
+
+
+def rel_l2(a, b):
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def valid_rel_l2(a, b, mask):
+    keep = (~mask).unsqueeze(-1).to(a.dtype)
+    return rel_l2(a * keep, b * keep)

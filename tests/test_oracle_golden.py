@@ -1,0 +1,79 @@
+"""The oracle restatement against outputs of the unmodified reference (tests/golden,
+produced by oracle/make_golden.py).  CPU only."""
+import os
+
+import numpy as np
+import torch
+
+from oracle import zipvoice_oracle as O
+from zipvoice_b200 import synth
+from tests.cases import case_inputs, rel_l2, valid_rel_l2
+from tests.conftest import GOLDEN
+
+TOL = 2e-5  # fp32 vs fp32, different summation order only
+
+
+def _g(name):
+    return {k: torch.from_numpy(v) for k, v in np.load(os.path.join(GOLDEN, name)).items()}
+
+
+def test_velocity_small_stress():
+    cfg = synth.small_model_cfg()
+    sd = synth.make_state_dict(cfg, seed=1, stress=True)
+    x0, text, speech, mask = case_inputs(2, 37, 11, seed=10)
+    v = O.forward_fm_decoder(sd, cfg, torch.tensor(0.3), x0, text, speech, mask)
+    assert valid_rel_l2(v, _g("velocity_small_stress.npz")["v"], mask) < TOL
+
+
+def test_euler_cfg_and_nocfg():
+    cfg = synth.small_model_cfg()
+    sd = synth.make_state_dict(cfg, seed=1, stress=True)
+    x0, text, speech, mask = case_inputs(2, 37, 11, seed=10)
+    g = _g("euler_small_stress.npz")
+    x1 = O.euler_sample(sd, cfg, x0, text, speech, mask, num_step=4, guidance_scale=1.0, t_shift=0.5)
+    assert valid_rel_l2(x1, g["x1_cfg"], mask) < TOL
+    x1 = O.euler_sample(sd, cfg, x0, text, speech, mask, num_step=3, guidance_scale=0.0, t_shift=0.7)
+    assert valid_rel_l2(x1, g["x1_nocfg"], mask) < TOL
+
+
+def test_euler_distill():
+    cfg = synth.small_model_cfg()
+    sd = synth.make_state_dict(cfg, seed=2, distill=True, stress=True)
+    x0, text, speech, mask = case_inputs(2, 37, 11, seed=10)
+    x1 = O.euler_sample(sd, cfg, x0, text, speech, mask, num_step=2, guidance_scale=3.0, t_shift=0.5, distill=True)
+    assert valid_rel_l2(x1, _g("euler_small_distill.npz")["x1"], mask) < TOL
+
+
+def test_sample_end_to_end():
+    cfg = synth.small_model_cfg()
+    sd = synth.make_state_dict(cfg, seed=1, stress=True)
+    tokens, prompt_tokens = synth.make_tokens(2, n_prompt=9, n_text=21, seed=5, ragged=True)
+    pf, pfl = synth.make_prompt_features(2, 14, seed=6, ragged=True)
+    g = _g("sample_small_stress.npz")
+    emb, _ = O.forward_text_embed(sd, cfg, [p + t for p, t in zip(prompt_tokens, tokens)])
+    assert rel_l2(emb, g["text_embed"]) < TOL
+    ptl = torch.tensor([len(t) for t in prompt_tokens])
+    tl = torch.tensor([len(t) for t in tokens])
+    T = int(O.predict_features_lens(pfl, ptl, tl, 1.3).max())
+    torch.manual_seed(666)
+    x0 = torch.randn(2, T, 100)
+    out = O.sample(sd, cfg, tokens, prompt_tokens, pf, pfl, speed=1.3, t_shift=0.5, duration="predict",
+                   num_step=3, guidance_scale=1.0, x0=x0)
+    assert torch.equal(out[1], g["wo_lens"])
+    assert rel_l2(out[0], g["x1_wo"]) < TOL
+    assert rel_l2(out[2], g["x1_prompt"]) < TOL
+
+
+def test_dialog_text_embed():
+    cfg = synth.small_model_cfg()
+    sd = synth.make_state_dict(cfg, seed=3, dialog=True, stress=True)
+    dt, dp = synth.make_tokens(2, n_prompt=30, n_text=60, seed=8, dialog=True, ragged=True)
+    emb, _ = O.forward_text_embed(sd, cfg, [p + t for p, t in zip(dp, dt)], dialog=(synth.SPK_A_ID, synth.SPK_B_ID))
+    assert rel_l2(emb, _g("dialog_text_embed.npz")["text_embed"]) < TOL
+
+
+def test_velocity_base_cfg():
+    sd = synth.make_state_dict(synth.BASE_MODEL_CFG, seed=0)
+    x, t, s, mk = case_inputs(2, 50, 15, seed=11)
+    v = O.cfg_velocity(sd, synth.BASE_MODEL_CFG, torch.tensor(0.7), x, t, s, mk, guidance_scale=1.5)
+    assert valid_rel_l2(v, _g("velocity_base_cfg.npz")["v"], mk) < TOL
