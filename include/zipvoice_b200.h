@@ -1,0 +1,106 @@
+/* zipvoice_b200 -- C ABI of the B200-native ZipVoice hot path (libzipvoice_b200.so).
+ *
+ * Conventions: every function returns 0 on success, non-zero error code otherwise (never throws);
+ * zv_last_error() gives the text.  All tensor pointers are DEVICE pointers to contiguous fp32 /
+ * uint8 / int64 data unless stated; calls are asynchronous on `stream` (a cudaStream_t passed as
+ * void*).  A handle is bound to the current CUDA device and is not thread-safe.
+ * Citations are file:line in the reference repository (winlaic/ZipVoice).
+ */
+#ifndef ZIPVOICE_B200_H
+#define ZIPVOICE_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ZV_MAX_STACKS 8
+
+/* Model hyper-parameters: the "model" section of model.json (egs/zipvoice/conf/zipvoice_base.json:1-25)
+ * = the keyword arguments of ZipVoice.__init__ (zipvoice/models/zipvoice.py:38-60). */
+typedef struct zv_config {
+  int feat_dim;
+  int fm_num_stacks;
+  int fm_downsampling_factor[ZV_MAX_STACKS];
+  int fm_num_layers[ZV_MAX_STACKS];
+  int fm_cnn_module_kernel[ZV_MAX_STACKS];
+  int fm_feedforward_dim, fm_num_heads, fm_dim;
+  int text_num_layers, text_feedforward_dim, text_cnn_module_kernel, text_num_heads, text_dim;
+  int query_head_dim, value_head_dim, pos_head_dim, pos_dim;
+  int time_embed_dim, text_embed_dim;
+  int vocab_size, pad_id;
+  int use_guidance_scale_embed; /* 1 for ZipVoiceDistill (zipvoice_distill.py:52-67) */
+  int dialog;                   /* 1 for ZipVoiceDialog: spk_embed rows added (zipvoice_dialog.py:127-159) */
+  int spk_a_id, spk_b_id;
+} zv_config;
+
+/* Replaces ZipVoice.__init__ (zipvoice.py:38-133): builds the fm_decoder + text_encoder skeleton. */
+int zv_create(const zv_config* cfg, void** handle);
+void zv_destroy(void* handle);
+const char* zv_last_error(void* handle);
+
+/* Weights enter by state_dict name (torch nn.Module.load_state_dict equivalent,
+ * bin/infer_zipvoice.py:561-566).  `data` is fp32, host (on_device=0) or device (on_device=1). */
+int zv_set_weight(void* handle, const char* name, const float* data, const int64_t* shape, int ndim, int on_device);
+/* Packs weights into the device arena (bf16 GEMM operands, permuted GLU / gate layouts, folded
+ * time-embedding projections).  Fails if a tensor of the architecture is missing. */
+int zv_finalize_weights(void* handle);
+
+/* options: "gemm_impl" 0 = tcgen05 kernel (default), 1 = SIMT checker kernel (tests only). */
+int zv_set_option(void* handle, const char* key, int value);
+
+/* get_time_steps (models/modules/solver.py:256-281), fp32 arithmetic identical to torch
+ * (python-double scalars, fp32 tensor ops, FMA linspace); host output. */
+int zv_time_steps(double t_start, double t_end, int num_step, double t_shift, float* out_host /* num_step+1 */);
+
+/* One call of DiffusionModel.forward (variant 0, solver.py:40-110: CFG batch doubling, the t>0.5
+ * branch, (1+g) cond - g uncond) or DistillDiffusionModel.forward (variant 1, solver.py:127-165)
+ * around ZipVoice.forward_fm_decoder (zipvoice.py:135-185) -> TTSZipformer.forward
+ * (zipformer.py:242-293).  x,text,speech,v_out: (B,T,feat_dim) fp32; padding_mask (B,T) uint8,
+ * 1 = padded, may be NULL; guidance: HOST floats, guidance_len 1 or B. */
+int zv_velocity(void* handle, int variant, float t, const float* x, const float* text_condition,
+                const float* speech_condition, const uint8_t* padding_mask, int B, int T, const float* guidance,
+                int guidance_len, float* v_out, void* stream);
+
+/* EulerSolver.sample / DistillEulerSolver.sample (solver.py:182-240).  x0 is not modified; x1 receives
+ * the solution at t_end.  No host synchronisation inside. */
+int zv_sample(void* handle, int variant, const float* x0, const float* text_condition,
+              const float* speech_condition, const uint8_t* padding_mask, int B, int T, int num_step,
+              const float* guidance, int guidance_len, double t_start, double t_end, double t_shift, float* x1,
+              void* stream);
+
+/* ZipVoice.forward_text_embed (zipvoice.py:187-212; dialog variant zipvoice_dialog.py:127-159):
+ * tokens_padded (B,S) int64 as produced by pad_labels (utils/common.py:255-268), tokens_lens (B) int64
+ * -> embed (B,S,feat_dim). */
+int zv_text_embed(void* handle, const int64_t* tokens_padded, const int64_t* tokens_lens, int B, int S,
+                  float* embed_out, void* stream);
+/* ZipVoice.forward_text_condition (zipvoice.py:214-251) with prepare_avg_tokens_durations /
+ * get_tokens_index (utils/common.py:246-295) evaluated on the device.  Also writes the padding
+ * mask (B,T) uint8 (make_pad_mask, utils/common.py:395-420). */
+int zv_text_condition(void* handle, const float* embed, const int64_t* tokens_lens, const int64_t* features_lens,
+                      int B, int S, int T, float* text_condition_out, uint8_t* padding_mask_out, void* stream);
+
+/* VocosFbank.extract / _feature_fn (zipvoice/utils/feature.py:56-116): wav (B,N) fp32 24 kHz mono,
+ * lens (B) int64 valid samples -> log-mel (B, T, 100), T = (N + 128) / 256 frames. */
+int zv_fbank(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out, void* stream);
+
+/* Vocos.decode (third-party `vocos`; call site bin/infer_zipvoice.py:378): mel (B,100,T) -> wav (B, 256*(T-1)).
+ * Weights are set through zv_set_weight with the "vocoder." prefix. */
+int zv_vocos_decode(void* handle, const float* mel, int B, int T, float* wav_out, void* stream);
+
+/* Test / bench hooks (not part of the reference-facing surface). */
+int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int gate_cols, const float* A_f32,
+                  const float* W_f32, const float* bias, const float* rowbias, const float* res, const float* resbias,
+                  const float* orig, const float* bypass_scale, const uint8_t* mask, float* out_f32, float* out2_f32,
+                  void* stream);
+int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp_f32, int ldq, const float* E,
+                       const uint8_t* mask, const float* V_f32, int ldv, const float* gate_f32, float* out_f32,
+                       void* stream);
+int zv_debug_pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E_out, void* stream);
+/* Launch counters: kernels launched by this library since the last reset. */
+long long zv_launch_count(void);
+void zv_launch_count_reset(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,174 @@
+"""Unit parity of single CUDA kernels through the C ABI debug hooks (GPU only).
+Reference = plain torch fp32 on the bf16-rounded operands (these are floating-point kernels)."""
+import ctypes as C
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+EPI_BIAS, EPI_SWOOSHL, EPI_GLU, EPI_NONLIN, EPI_RESIDUAL, EPI_F32 = range(6)
+
+
+def _lib():
+    from zipvoice_b200 import _lib
+    return _lib.load()
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def swoosh_l(x):
+    return torch.logaddexp(torch.zeros_like(x), x - 4.0) - 0.08 * x - 0.035
+
+
+def run_gemm(mode, impl, A, W, bias, L=1, gate_cols=0, rowbias=None, res=None, resbias=None, orig=None, bscale=None,
+             mask=None):
+    M, K = A.shape
+    N = W.shape[0]
+    n_out = N // 2 if mode == EPI_GLU else (gate_cols // 2 if mode == EPI_NONLIN else N)
+    out = torch.zeros(M, n_out, device="cuda")
+    out2 = torch.zeros(M, max(N - gate_cols, 1) if mode == EPI_NONLIN else N, device="cuda")
+    rc = _lib().zv_debug_gemm(mode, impl, M, N, K, L, gate_cols, _p(A), _p(W), _p(bias), _p(rowbias), _p(res),
+                              _p(resbias), _p(orig), _p(bscale), _p(mask), _p(out), _p(out2), None)
+    assert rc == 0, f"zv_debug_gemm rc={rc}"
+    return out, out2
+
+
+def ref_gemm(mode, A, W, bias, L=1, gate_cols=0, rowbias=None, res=None, resbias=None, orig=None, bscale=None,
+             mask=None):
+    M = A.shape[0]
+    acc = A.bfloat16().float() @ W.bfloat16().float().T + bias
+    b = torch.arange(M, device="cuda") // L
+    if rowbias is not None and mode != EPI_RESIDUAL:
+        acc = acc + rowbias[b]
+    if mode == EPI_BIAS or mode == EPI_F32:
+        return acc, None
+    if mode == EPI_SWOOSHL:
+        return swoosh_l(acc), None
+    if mode == EPI_GLU:
+        g = acc.reshape(M, -1, 2, 16)
+        o = (g[:, :, 0] * torch.sigmoid(g[:, :, 1])).reshape(M, -1)
+        if mask is not None:
+            o = o * (1 - mask.reshape(-1).float())[:, None]
+        return o, None
+    if mode == EPI_NONLIN:
+        g = acc[:, :gate_cols].reshape(M, -1, 2, 16)
+        return (g[:, :, 1] * torch.tanh(g[:, :, 0])).reshape(M, -1), acc[:, gate_cols:]
+    if mode == EPI_RESIDUAL:
+        v = acc + res
+        if resbias is not None:
+            v = v + resbias[b]
+        if orig is not None:
+            v = orig + (v - orig) * bscale
+        return v, v
+    raise AssertionError
+
+
+def rel(a, b):
+    return float((a - b).norm() / b.norm().clamp_min(1e-20))
+
+
+CASES = [
+    # mode, M, N, K, extra
+    (EPI_F32, 300, 512, 320, {}),
+    (EPI_F32, 257, 100, 512, {}),
+    (EPI_BIAS, 1000, 272, 512, {}),
+    (EPI_BIAS, 130, 48, 512, {}),
+    (EPI_SWOOSHL, 777, 1152, 512, {"rowbias": True, "L": 111}),
+    (EPI_SWOOSHL, 640, 1920, 512, {}),
+    (EPI_GLU, 500, 1024, 512, {"mask": True, "L": 125}),
+    (EPI_GLU, 200, 384, 192, {}),
+    (EPI_NONLIN, 400, 1152, 512, {"gate_cols": 768}),
+    (EPI_NONLIN, 150, 432, 192, {"gate_cols": 288}),
+    (EPI_RESIDUAL, 900, 512, 1536, {"resbias": True, "orig": True, "L": 300}),
+    (EPI_RESIDUAL, 333, 512, 48, {}),
+    (EPI_RESIDUAL, 129, 192, 640, {}),
+    (EPI_RESIDUAL, 20000, 512, 384, {"resbias": True, "L": 1219}),
+]
+
+
+@pytest.mark.parametrize("impl", [1, 0], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("case", CASES, ids=lambda c: f"m{c[0]}_{c[1]}x{c[2]}x{c[3]}")
+def test_gemm(case, impl):
+    mode, M, N, K, ex = case
+    if impl == 1 and M * N * K > 3e9:
+        pytest.skip("SIMT checker kept to small shapes")
+    g = torch.Generator(device="cuda").manual_seed(mode * 1000 + M)
+    rn = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    A, W, bias = rn(M, K), rn(N, K) / math.sqrt(K), rn(N) * 0.5
+    L = ex.get("L", M)
+    nb = (M + L - 1) // L
+    kw = dict(L=L, gate_cols=ex.get("gate_cols", 0))
+    if ex.get("rowbias"):
+        kw["rowbias"] = rn(nb, N)
+    if mode == EPI_RESIDUAL:
+        kw["res"] = rn(M, N)
+        if ex.get("resbias"):
+            kw["resbias"] = rn(nb, N)
+        if ex.get("orig"):
+            kw["orig"], kw["bscale"] = rn(M, N), torch.rand(N, device="cuda", generator=g)
+    if ex.get("mask"):
+        kw["mask"] = (torch.rand(nb * L, device="cuda", generator=g) < 0.3).to(torch.uint8)[: nb * L].contiguous()
+    out, out2 = run_gemm(mode, impl, A, W, bias, **kw)
+    want, want2 = ref_gemm(mode, A, W, bias, **kw)
+    tol = 2e-5 if mode in (EPI_F32, EPI_RESIDUAL) else 6e-3  # bf16 outputs: 2^-9 rounding
+    assert rel(out, want) < tol, f"rel-L2 {rel(out, want):.3e} max-abs {float((out - want).abs().max()):.3e}"
+    if mode == EPI_NONLIN:
+        assert rel(out2, want2) < 6e-3, f"out2 rel-L2 {rel(out2, want2):.3e}"
+    if mode == EPI_RESIDUAL:
+        assert rel(out2, want2) < 6e-3, f"bf16 shadow rel-L2 {rel(out2, want2):.3e}"
+
+
+def test_pos_table():
+    from oracle import zipformer_oracle as zo
+    for L in (5, 64, 305, 1219):
+        W = torch.randn(16, 48, generator=torch.Generator().manual_seed(L)) * 0.3
+        want = (zo.rel_pos_encoding(L, 48) @ W.T).reshape(2 * L - 1, 4, 4).permute(1, 0, 2).contiguous()
+        E = torch.zeros(4, 2 * L - 1, 4, device="cuda")
+        rc = _lib().zv_debug_pos_table(_p(W.cuda()), 4, 4, 48, L, _p(E), None)
+        assert rc == 0
+        err = float((E.cpu() - want).abs().max())
+        assert err < 2e-5, f"L={L} max-abs {err:.3e}"
+
+
+def ref_attention(qkp, E, mask, V, gate, H, heads, dv):
+    nb, L, _ = qkp.shape
+    q = qkp[..., : H * 32].reshape(nb, L, H, 32).permute(2, 0, 1, 3)
+    k = qkp[..., H * 32: 2 * H * 32].reshape(nb, L, H, 32).permute(2, 0, 1, 3)
+    p = qkp[..., 2 * H * 32: 2 * H * 32 + 4 * H].reshape(nb, L, H, 4).permute(2, 0, 1, 3)
+    s = q @ k.transpose(-1, -2)
+    ps = p @ E.permute(0, 2, 1)[:, None]  # (H, nb, L, 2L-1)
+    idx = (L - 1) - torch.arange(L, device="cuda")[:, None] + torch.arange(L, device="cuda")[None, :]
+    s = s + torch.gather(ps, 3, idx[None, None].expand(H, nb, L, L))
+    if mask is not None:
+        s = s.masked_fill(mask.bool()[None, :, None, :], -1000.0)
+    a = s.softmax(-1)[:heads]
+    v = V[..., : heads * dv].reshape(nb, L, heads, dv).permute(2, 0, 1, 3)
+    o = (a @ v).permute(1, 2, 0, 3).reshape(nb, L, heads * dv)
+    return o * gate[..., : heads * dv] if gate is not None else o
+
+
+@pytest.mark.parametrize("L", [1, 37, 64, 130, 611])
+@pytest.mark.parametrize("kind", ["self", "nonlin384", "nonlin144"])
+def test_attention(L, kind):
+    H, nb = 4, 3
+    g = torch.Generator(device="cuda").manual_seed(L)
+    rn = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    qkp = (rn(nb, L, 288) * 0.7).bfloat16().float()
+    E = rn(H, 2 * L - 1, 4).contiguous()
+    lens = torch.tensor([L, max(1, L // 2), max(1, L - 3)], device="cuda")
+    mask = (torch.arange(L, device="cuda")[None] >= lens[:, None]).to(torch.uint8).contiguous()
+    heads, dv = (4, 12) if kind == "self" else (1, int(kind[6:]))
+    ldv = heads * dv
+    V = rn(nb, L, ldv).bfloat16().float()
+    gate = None if kind == "self" else rn(nb, L, ldv).bfloat16().float()
+    out = torch.zeros(nb, L, ldv, device="cuda")
+    rc = _lib().zv_debug_attention(nb, L, H, heads, dv, _p(qkp), 288, _p(E), _p(mask), _p(V), ldv, _p(gate), _p(out),
+                                   None)
+    assert rc == 0
+    want = ref_attention(qkp, E, mask, V, gate, H, heads, dv)
+    r = rel(out, want)
+    assert r < 8e-3, f"rel-L2 {r:.3e} max-abs {float((out - want).abs().max()):.3e}"

@@ -1,0 +1,64 @@
+"""CPU-only checks of the host side: the C-ABI library loads and exports every symbol declared in
+include/zipvoice_b200.h, pure-host entry points agree with torch, and the product fails loudly
+without a GPU (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+import torch
+
+from tests.conftest import ROOT
+
+
+def test_library_exports_every_declared_symbol():
+    from zipvoice_b200 import _lib
+    lib = _lib.load()
+    hdr = open(os.path.join(ROOT, "include", "zipvoice_b200.h")).read()
+    declared = set(re.findall(r"\b(zv_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in include/zipvoice_b200.h but not exported"
+    assert declared == set(_lib.EXPORTS), declared ^ set(_lib.EXPORTS)
+
+
+def test_time_steps_match_torch():
+    from oracle import zipvoice_oracle as O
+    from zipvoice_b200.solver import get_time_steps
+    for n, s, a, b in [(16, 0.5, 0.0, 1.0), (4, 0.7, 0.0, 1.0), (7, 1.0, 0.2, 0.9), (1, 0.5, 0.0, 1.0),
+                       (8, 0.3, 0.0, 1.0), (33, 0.9, 0.1, 0.7)]:
+        assert torch.equal(get_time_steps(a, b, n, s), O.get_time_steps(a, b, n, s)), (n, s, a, b)
+
+
+def test_config_struct_matches_header():
+    from zipvoice_b200 import _lib, synth
+    from zipvoice_b200.engine import make_config
+    c = make_config(synth.BASE_MODEL_CFG, synth.VOCAB_SIZE, synth.PAD_ID, distill=True)
+    assert list(c.fm_downsampling_factor)[:5] == [1, 2, 4, 2, 1] and c.fm_num_stacks == 5
+    assert c.use_guidance_scale_embed == 1 and c.vocab_size == 364
+    hdr = open(os.path.join(ROOT, "include", "zipvoice_b200.h")).read()
+    body = hdr[hdr.index("typedef struct zv_config {"):hdr.index("} zv_config;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = re.findall(r"\b([a-z_0-9]+)(?:\[[A-Z_]+\])?\s*[,;]", body)
+    assert names == [f[0] for f in _lib.ZvConfig._fields_], names
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback():
+    from zipvoice_b200 import synth
+    from zipvoice_b200.engine import Engine, ZvError
+    with pytest.raises(ZvError):
+        Engine(synth.small_model_cfg(), {}, synth.VOCAB_SIZE)
+    from zipvoice_b200 import _lib
+    h = C.c_void_p()
+    cfg = _lib.ZvConfig()
+    assert _lib.load().zv_create(C.byref(cfg), C.byref(h)) != 0
+
+
+def test_synth_state_dict_is_deterministic():
+    from zipvoice_b200 import synth
+    a = synth.make_state_dict(synth.small_model_cfg(), seed=3, stress=True)
+    b = synth.make_state_dict(synth.small_model_cfg(), seed=3, stress=True)
+    assert a.keys() == b.keys() and all(torch.equal(a[k], b[k]) for k in a)
+    full = synth.make_state_dict(distill=True)
+    assert len(full) == 890 and abs(sum(v.numel() for v in full.values()) / 1e6 - 122.7) < 0.1

@@ -1,0 +1,106 @@
+// Test hooks: run a single GEMM / attention / position-table kernel on fp32 inputs supplied by the
+// caller (converted to the bf16 operand layout here).  Used by tests/ only.
+#include <vector>
+
+#include "zv_common.cuh"
+#include "zv_engine.h"
+
+using namespace zv;
+
+__global__ void cvt_pad_kernel(const float* __restrict__ in, int rows, int cols, int ld_in, __nv_bfloat16* out,
+                               int ld_out) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)rows * ld_out) return;
+  const int c = (int)(gid % ld_out);
+  const size_t r = gid / ld_out;
+  out[gid] = __float2bfloat16(c < cols ? in[r * ld_in + c] : 0.f);
+}
+__global__ void cvt_back_kernel(const __nv_bfloat16* __restrict__ in, size_t n, float* out) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid < n) out[gid] = __bfloat162float(in[gid]);
+}
+static void cvt_pad(const float* in, int rows, int cols, int ld_in, __nv_bfloat16* out, int ld_out, cudaStream_t s) {
+  const size_t n = (size_t)rows * ld_out;
+  cvt_pad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, rows, cols, ld_in, out, ld_out);
+}
+static void cvt_back(const __nv_bfloat16* in, size_t n, float* out, cudaStream_t s) {
+  cvt_back_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, n, out);
+}
+
+extern "C" int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int gate_cols, const float* A_f32,
+                             const float* W_f32, const float* bias, const float* rowbias, const float* res,
+                             const float* resbias, const float* orig, const float* bypass_scale, const uint8_t* mask,
+                             float* out_f32, float* out2_f32, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  const int block_n = gemm_pick_block_n(N, mode, gate_cols);
+  const int N_pad = (N + block_n - 1) / block_n * block_n;
+  const int ld = (K + 63) / 64 * 64;
+  const int n_out = (mode == EPI_GLU_BF16) ? N / 2 : (mode == EPI_NONLIN_BF16 ? gate_cols / 2 : N);
+  const int n_out2 = mode == EPI_NONLIN_BF16 ? N - gate_cols : 0;
+  __nv_bfloat16 *A = nullptr, *W = nullptr, *ob = nullptr, *ob2 = nullptr;
+  float* of = nullptr;
+  cudaMalloc(&A, (size_t)M * ld * 2);
+  cudaMalloc(&W, (size_t)N_pad * ld * 2);
+  cudaMalloc(&ob, (size_t)M * (n_out + 8) * 2);
+  cudaMalloc(&ob2, (size_t)M * (n_out2 + 8) * 2);
+  cudaMalloc(&of, (size_t)M * N * 4);
+  cudaMemsetAsync(W, 0, (size_t)N_pad * ld * 2, s);
+  cvt_pad(A_f32, M, K, K, A, ld, s);
+  cvt_pad(W_f32, N, K, K, W, ld, s);
+  GemmPlan p;
+  p.M = M, p.N_pad = N_pad, p.K = K, p.lda = ld, p.ldw = ld, p.block_n = block_n;
+  EpiParams ep;
+  ep.mode = mode, ep.M = M, ep.N = N, ep.L = L, ep.gate_cols = gate_cols, ep.bias = bias, ep.rowbias = rowbias;
+  ep.bias_ld = N, ep.out_bf16 = ob, ep.ld_bf16 = n_out, ep.out2_bf16 = ob2, ep.ld2_bf16 = n_out2;
+  ep.out_f32 = of, ep.ld_f32 = N, ep.res = res, ep.resbias = resbias, ep.orig = orig, ep.bypass_scale = bypass_scale;
+  ep.mask = mask;
+  if (mode == EPI_F32) ep.out_bf16 = nullptr;
+  int rc = gemm_launch(A, W, p, ep, impl, s);
+  if (!rc) {
+    if (mode == EPI_RESIDUAL || mode == EPI_F32) {
+      cudaMemcpyAsync(out_f32, of, (size_t)M * N * 4, cudaMemcpyDeviceToDevice, s);
+      if (mode == EPI_RESIDUAL && out2_f32) cvt_back(ob, (size_t)M * N, out2_f32, s);
+    } else {
+      cvt_back(ob, (size_t)M * n_out, out_f32, s);
+      if (n_out2) cvt_back(ob2, (size_t)M * n_out2, out2_f32, s);
+    }
+    rc = (int)cudaStreamSynchronize(s);
+  }
+  cudaFree(A), cudaFree(W), cudaFree(ob), cudaFree(ob2), cudaFree(of);
+  return rc;
+}
+
+extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp_f32, int ldq,
+                                  const float* E, const uint8_t* mask, const float* V_f32, int ldv,
+                                  const float* gate_f32, float* out_f32, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t rows = (size_t)nb * L;
+  __nv_bfloat16 *q = nullptr, *v = nullptr, *g = nullptr, *o = nullptr;
+  cudaMalloc(&q, rows * ldq * 2);
+  cudaMalloc(&v, rows * ldv * 2);
+  cudaMalloc(&o, rows * ldv * 2);
+  cvt_pad(qkp_f32, (int)rows, ldq, ldq, q, ldq, s);
+  cvt_pad(V_f32, (int)rows, ldv, ldv, v, ldv, s);
+  if (gate_f32) {
+    cudaMalloc(&g, rows * ldv * 2);
+    cvt_pad(gate_f32, (int)rows, ldv, ldv, g, ldv, s);
+  }
+  cudaMemsetAsync(o, 0, rows * ldv * 2, s);
+  AttnParams a;
+  a.qkp = q, a.ldq = ldq, a.E = E, a.mask = mask, a.V = v, a.ldv = ldv, a.gate = g, a.ldg = ldv, a.out = o, a.ldo = ldv;
+  a.nb = nb, a.L = L, a.H = H, a.heads = heads, a.dv = dv;
+  int rc = attention(a, s);
+  if (!rc) {
+    cvt_back(o, rows * ldv, out_f32, s);
+    rc = (int)cudaStreamSynchronize(s);
+  }
+  cudaFree(q), cudaFree(v), cudaFree(o);
+  if (g) cudaFree(g);
+  return rc;
+}
+
+extern "C" int zv_debug_pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E_out, void* stream) {
+  int rc = pos_table(W, H, dp, pos_dim, L, E_out, (cudaStream_t)stream);
+  if (!rc) rc = (int)cudaStreamSynchronize((cudaStream_t)stream);
+  return rc;
+}

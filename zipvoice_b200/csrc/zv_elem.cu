@@ -1,0 +1,276 @@
+// Bandwidth-bound kernels of the Zipformer layer: coalesced, 128-bit vectorised where the
+// layout allows, shared-memory staged where there is reuse (depthwise conv), warp-shuffle
+// reductions (BiasNorm).  Grids are sized from the data; all launches are asynchronous.
+#include "zv_common.cuh"
+#include "zv_kernels.h"
+
+namespace zv {
+
+static inline unsigned blocks_for(size_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+// ------------------------------------------------------------------ input packing (+ CFG doubling)
+__global__ void pack_input_kernel(const float* __restrict__ x, const float* __restrict__ text,
+                                  const float* __restrict__ speech, const uint8_t* __restrict__ mask, int B, int T,
+                                  int F, int cfg, int zero_speech_uncond, bf16* __restrict__ out, int ldo,
+                                  uint8_t* __restrict__ mask_out) {
+  // one thread per (row, pair of output columns)
+  const int half = ldo >> 1;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int nb = cfg ? 2 * B : B;
+  if (gid >= (size_t)nb * T * half) return;
+  const int c = (int)(gid % half) * 2;
+  const size_t row = gid / half;
+  const int t = (int)(row % T);
+  const int bo = (int)(row / T);
+  const int b = cfg ? (bo % B) : bo;
+  const bool uncond = cfg && bo < B;
+  const size_t src = ((size_t)b * T + t) * F;
+  float v[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int cc = c + i;
+    float val = 0.f;
+    if (cc < F) val = x[src + cc];
+    else if (cc < 2 * F) val = uncond ? 0.f : text[src + cc - F];
+    else if (cc < 3 * F) val = (uncond && zero_speech_uncond) ? 0.f : speech[src + cc - 2 * F];
+    v[i] = val;
+  }
+  *reinterpret_cast<uint32_t*>(out + row * ldo + c) = pack_bf16x2(v[0], v[1]);
+  if (c == 0 && mask_out) mask_out[row] = mask ? mask[(size_t)b * T + t] : 0;
+}
+
+int pack_input(const float* x, const float* text, const float* speech, const uint8_t* mask, int B, int T, int F,
+               int cfg, int zero_speech_uncond, bf16* out, int ldo, uint8_t* mask_out, cudaStream_t s) {
+  const size_t n = (size_t)(cfg ? 2 * B : B) * T * (ldo / 2);
+  pack_input_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, text, speech, mask, B, T, F, cfg, zero_speech_uncond, out,
+                                                       ldo, mask_out);
+  return (int)cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ CFG combine + Euler update
+__global__ void cfg_euler_kernel(float* __restrict__ x, const float* __restrict__ v,
+                                 const float* __restrict__ guidance, int guidance_len, float g_mult, int B,
+                                 size_t per_b, int cfg, float dt, float* __restrict__ v_out) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)B * per_b) return;
+  float vel;
+  if (cfg) {
+    const int b = (int)(gid / per_b);
+    const float g = guidance[guidance_len == 1 ? 0 : b] * g_mult;
+    const float u = v[gid], c = v[gid + (size_t)B * per_b];
+    vel = (1.f + g) * c - g * u;
+  } else {
+    vel = v[gid];
+  }
+  if (v_out) v_out[gid] = vel;
+  if (x) x[gid] = x[gid] + vel * dt;
+}
+
+int cfg_euler_update(float* x, const float* v, const float* guidance, int guidance_len, float g_mult, int B, int T,
+                     int F, int cfg, float dt, float* v_out, cudaStream_t s) {
+  const size_t per_b = (size_t)T * F;
+  cfg_euler_kernel<<<blocks_for((size_t)B * per_b, 256), 256, 0, s>>>(x, v, guidance, guidance_len, g_mult, B, per_b,
+                                                                      cfg, dt, v_out);
+  return (int)cudaGetLastError();
+}
+
+__global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, size_t n) {
+  const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i + 3 < n) {
+    const float4 v = *reinterpret_cast<const float4*>(in + i);
+    *reinterpret_cast<uint2*>(out + i) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+  } else {
+    for (size_t j = i; j < n; ++j) out[j] = __float2bfloat16(in[j]);
+  }
+}
+int f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t s) {
+  f32_to_bf16_kernel<<<blocks_for((n + 3) / 4, 256), 256, 0, s>>>(in, out, n);
+  return (int)cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ depthwise conv + SwooshR
+// Block = (sequence b, 64-frame tile, 256-channel chunk).  The input tile plus a (K-1)-frame halo
+// is staged in shared memory (bf16x2 per thread-column, conflict-free), taps live in registers,
+// and every thread produces 4 consecutive frames x 2 channels per step so each shared-memory
+// word is read once per 4 outputs.
+template <int K>
+__global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in, const float* __restrict__ w,
+                                                     const float* __restrict__ bias, int L, int C,
+                                                     bf16* __restrict__ out) {
+  constexpr int TT = 64, PAD = K / 2, ROWS = TT + K - 1;
+  __shared__ uint32_t tile[ROWS][128];
+  const int cp = threadIdx.x;                 // channel pair within chunk
+  const int c = blockIdx.y * 256 + cp * 2;    // first channel
+  const int b = blockIdx.z;
+  const int t0 = blockIdx.x * TT;
+  const bool active = c < C;
+  const bf16* src = in + (size_t)b * L * C;
+  for (int r = threadIdx.y; r < ROWS; r += blockDim.y) {
+    const int t = t0 - PAD + r;
+    uint32_t v = 0;
+    if (active && t >= 0 && t < L) v = *reinterpret_cast<const uint32_t*>(src + (size_t)t * C + c);
+    tile[r][cp] = v;
+  }
+  __syncthreads();
+  if (!active) return;
+  float w0[K], w1[K];
+#pragma unroll
+  for (int j = 0; j < K; ++j) w0[j] = __ldg(w + (size_t)c * K + j), w1[j] = __ldg(w + (size_t)(c + 1) * K + j);
+  const float b0 = __ldg(bias + c), b1 = __ldg(bias + c + 1);
+  bf16* dst = out + (size_t)b * L * C;
+  const int per_y = TT / 2;
+  for (int tt = threadIdx.y * per_y; tt < (threadIdx.y + 1) * per_y; tt += 4) {
+    float a0[4] = {b0, b0, b0, b0}, a1[4] = {b1, b1, b1, b1};
+#pragma unroll
+    for (int j = 0; j < K + 3; ++j) {
+      const uint32_t xv = tile[tt + j][cp];
+      const float x0 = bf16_lo(xv), x1 = bf16_hi(xv);
+#pragma unroll
+      for (int o = 0; o < 4; ++o) {
+        const int tap = j - o;
+        if (tap >= 0 && tap < K) a0[o] = fmaf(w0[tap], x0, a0[o]), a1[o] = fmaf(w1[tap], x1, a1[o]);
+      }
+    }
+#pragma unroll
+    for (int o = 0; o < 4; ++o) {
+      const int t = t0 + tt + o;
+      if (t < L)
+        *reinterpret_cast<uint32_t*>(dst + (size_t)t * C + c) = pack_bf16x2(swoosh_r(a0[o]), swoosh_r(a1[o]));
+    }
+  }
+}
+
+int dwconv_swooshr(const bf16* in, const float* w, const float* bias, int nb, int L, int C, int k, bf16* out,
+                   cudaStream_t s) {
+  dim3 grid((L + 63) / 64, (C + 255) / 256, nb), block(128, 2);
+  switch (k) {
+    case 7: dwconv_kernel<7><<<grid, block, 0, s>>>(in, w, bias, L, C, out); break;
+    case 9: dwconv_kernel<9><<<grid, block, 0, s>>>(in, w, bias, L, C, out); break;
+    case 15: dwconv_kernel<15><<<grid, block, 0, s>>>(in, w, bias, L, C, out); break;
+    case 31: dwconv_kernel<31><<<grid, block, 0, s>>>(in, w, bias, L, C, out); break;
+    default: return 910;
+  }
+  return (int)cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ BiasNorm + bypass (one warp per row)
+__global__ void biasnorm_bypass_kernel(const float* __restrict__ src, const float* __restrict__ orig,
+                                       const float* __restrict__ nbias, float scale_exp,
+                                       const float* __restrict__ bscale, int M, int D, float* __restrict__ out,
+                                       bf16* __restrict__ out_bf16) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const float* s = src + (size_t)row * D;
+  const float* o = orig + (size_t)row * D;
+  float4 v[4];  // up to D = 512: 4 float4 per lane
+  float ss = 0.f;
+  const int nvec = D >> 7;  // float4 groups per lane (D multiple of 128... handled below for 192)
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int col = (i * 32 + lane) * 4;
+    if (col < D) {
+      v[i] = *reinterpret_cast<const float4*>(s + col);
+      const float4 nb = *reinterpret_cast<const float4*>(nbias + col);
+      const float d0 = v[i].x - nb.x, d1 = v[i].y - nb.y, d2 = v[i].z - nb.z, d3 = v[i].w - nb.w;
+      ss += d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
+    }
+  }
+  (void)nvec;
+  ss = warp_sum(ss);
+  const float sc = rsqrtf(ss / (float)D) * scale_exp;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int col = (i * 32 + lane) * 4;
+    if (col < D) {
+      const float4 og = *reinterpret_cast<const float4*>(o + col);
+      const float4 bs = *reinterpret_cast<const float4*>(bscale + col);
+      float4 r;
+      r.x = og.x + (v[i].x * sc - og.x) * bs.x;
+      r.y = og.y + (v[i].y * sc - og.y) * bs.y;
+      r.z = og.z + (v[i].z * sc - og.z) * bs.z;
+      r.w = og.w + (v[i].w * sc - og.w) * bs.w;
+      *reinterpret_cast<float4*>(out + (size_t)row * D + col) = r;
+      *reinterpret_cast<uint2*>(out_bf16 + (size_t)row * D + col) =
+          make_uint2(pack_bf16x2(r.x, r.y), pack_bf16x2(r.z, r.w));
+    }
+  }
+}
+
+int biasnorm_bypass(const float* src, const float* orig, const float* nbias, float log_scale, const float* bscale,
+                    int M, int D, float* out, bf16* out_bf16, cudaStream_t s) {
+  if (D > 512 || (D & 3)) return 911;
+  const int warps = 8;
+  biasnorm_bypass_kernel<<<(M + warps - 1) / warps, warps * 32, 0, s>>>(src, orig, nbias, expf(log_scale), bscale, M,
+                                                                        D, out, out_bf16);
+  return (int)cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ SimpleDownsample / SimpleUpsample
+__global__ void downsample_kernel(const float* __restrict__ src, float4 w, int L, int L2, int D, int ds,
+                                  float* __restrict__ out, bf16* __restrict__ out_bf16, size_t total4) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= total4) return;
+  const int d4 = D >> 2;
+  const int c = (int)(gid % d4) * 4;
+  const size_t row = gid / d4;  // b * L2 + j
+  const int j = (int)(row % L2);
+  const int b = (int)(row / L2);
+  const float ws[4] = {w.x, w.y, w.z, w.w};
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int k = 0; k < ds; ++k) {
+    const int t = min(j * ds + k, L - 1);
+    const float4 v = *reinterpret_cast<const float4*>(src + ((size_t)b * L + t) * D + c);
+    acc.x += v.x * ws[k], acc.y += v.y * ws[k], acc.z += v.z * ws[k], acc.w += v.w * ws[k];
+  }
+  *reinterpret_cast<float4*>(out + row * D + c) = acc;
+  *reinterpret_cast<uint2*>(out_bf16 + row * D + c) =
+      make_uint2(pack_bf16x2(acc.x, acc.y), pack_bf16x2(acc.z, acc.w));
+}
+__global__ void mask_subsample_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int nb, int L, int L2,
+                                      int ds) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= nb * L2) return;
+  const int b = gid / L2, j = gid % L2;
+  out[gid] = in[(size_t)b * L + j * ds];  // padding_mask[..., ::ds] (zipformer.py:857-858)
+}
+
+int downsample(const float* src, const float* w, int nb, int L, int D, int ds, float* out, bf16* out_bf16,
+               uint8_t* mask_out, const uint8_t* mask_in, cudaStream_t s) {
+  if (ds > 4 || (D & 3)) return 912;
+  const int L2 = (L + ds - 1) / ds;
+  float4 wv = make_float4(w[0], ds > 1 ? w[1] : 0.f, ds > 2 ? w[2] : 0.f, ds > 3 ? w[3] : 0.f);
+  const size_t total4 = (size_t)nb * L2 * (D >> 2);
+  downsample_kernel<<<blocks_for(total4, 256), 256, 0, s>>>(src, wv, L, L2, D, ds, out, out_bf16, total4);
+  if (mask_out) mask_subsample_kernel<<<blocks_for((size_t)nb * L2, 256), 256, 0, s>>>(mask_in, mask_out, nb, L, L2, ds);
+  return (int)cudaGetLastError();
+}
+
+__global__ void upsample_combine_kernel(float* __restrict__ orig, const float* __restrict__ y,
+                                        const float* __restrict__ bscale, int L, int L2, int D, int ds,
+                                        bf16* __restrict__ out_bf16, size_t total4) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= total4) return;
+  const int d4 = D >> 2;
+  const int c = (int)(gid % d4) * 4;
+  const size_t row = gid / d4;  // b * L + t
+  const int t = (int)(row % L);
+  const int b = (int)(row / L);
+  const float4 o = *reinterpret_cast<const float4*>(orig + row * D + c);
+  const float4 v = *reinterpret_cast<const float4*>(y + ((size_t)b * L2 + t / ds) * D + c);
+  const float4 sc = *reinterpret_cast<const float4*>(bscale + c);
+  float4 r;
+  r.x = o.x + (v.x - o.x) * sc.x, r.y = o.y + (v.y - o.y) * sc.y;
+  r.z = o.z + (v.z - o.z) * sc.z, r.w = o.w + (v.w - o.w) * sc.w;
+  *reinterpret_cast<float4*>(orig + row * D + c) = r;
+  *reinterpret_cast<uint2*>(out_bf16 + row * D + c) = make_uint2(pack_bf16x2(r.x, r.y), pack_bf16x2(r.z, r.w));
+}
+
+int upsample_combine(float* orig, const float* y, const float* bscale, int nb, int L, int L2, int D, int ds,
+                     bf16* out_bf16, cudaStream_t s) {
+  const size_t total4 = (size_t)nb * L * (D >> 2);
+  upsample_combine_kernel<<<blocks_for(total4, 256), 256, 0, s>>>(orig, y, bscale, L, L2, D, ds, out_bf16, total4);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace zv

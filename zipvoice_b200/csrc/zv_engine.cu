@@ -1,0 +1,434 @@
+// Weight packing (finalize) and the per-NFE launch schedule of the TTSZipformer
+// (reference: zipvoice/models/modules/zipformer.py:242-293, 489-642, 702-744, 850-870).
+#include "zv_engine.h"
+
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+namespace zv {
+
+long long g_launch_count = 0;
+
+#define ZV_TRY(expr)                                                                  \
+  do {                                                                                \
+    int _rc = (expr);                                                                 \
+    if (_rc) {                                                                        \
+      char _b[640];                                                                   \
+      snprintf(_b, sizeof(_b), "%s failed with %d at %s:%d", #expr, _rc, __FILE__, __LINE__); \
+      e.err = _b;                                                                     \
+      return _rc;                                                                     \
+    }                                                                                 \
+  } while (0)
+#define ZV_K(expr)      \
+  do {                  \
+    ++g_launch_count;   \
+    ZV_TRY(expr);       \
+  } while (0)
+
+static int dev_alloc(Engine& e, std::vector<void*>& pool, void** p, size_t bytes) {
+  if (bytes == 0) bytes = 16;
+  cudaError_t rc = cudaMalloc(p, bytes);
+  if (rc != cudaSuccess) {
+    e.err = std::string("cudaMalloc failed: ") + cudaGetErrorString(rc);
+    return (int)rc;
+  }
+  pool.push_back(*p);
+  return 0;
+}
+
+static const HostTensor* find(Engine& e, const std::string& name) {
+  auto it = e.raw.find(name);
+  if (it == e.raw.end()) {
+    e.err = "missing weight: " + name;
+    return nullptr;
+  }
+  return &it->second;
+}
+
+static int upload_f32(Engine& e, const std::vector<float>& v, float** out) {
+  ZV_TRY(dev_alloc(e, e.weight_allocs, (void**)out, v.size() * sizeof(float)));
+  ZV_TRY((int)cudaMemcpy(*out, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice));
+  return 0;
+}
+static int upload_named(Engine& e, const std::string& name, float** out) {
+  const HostTensor* t = find(e, name);
+  if (!t) return 940;
+  return upload_f32(e, t->data, out);
+}
+
+// Row permutation applied to the (out_features) axis for the fused epilogues.
+//   GLU     (conv in_proj, rows = [x (D) | s (D)])           -> groups of 32 = [16 x | 16 s]
+//   NONLIN  (nonlin in_proj, rows = [s (h) | x (h) | y (h)])  -> groups of 32 = [16 s | 16 x], then y
+static std::vector<int> row_perm(int mode, int N) {
+  std::vector<int> p(N);
+  if (mode == EPI_GLU_BF16) {
+    const int D = N / 2;
+    for (int g = 0; g < D / 16; ++g)
+      for (int i = 0; i < 16; ++i) p[g * 32 + i] = g * 16 + i, p[g * 32 + 16 + i] = D + g * 16 + i;
+  } else if (mode == EPI_NONLIN_BF16) {
+    const int h = N / 3;
+    for (int g = 0; g < h / 16; ++g)
+      for (int i = 0; i < 16; ++i) p[g * 32 + i] = g * 16 + i, p[g * 32 + 16 + i] = h + g * 16 + i;
+    for (int i = 0; i < h; ++i) p[2 * h + i] = 2 * h + i;
+  } else {
+    for (int i = 0; i < N; ++i) p[i] = i;
+  }
+  return p;
+}
+
+static inline uint16_t f2bf(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;
+  u += 0x7fffu + ((u >> 16) & 1u);  // round to nearest even
+  return (uint16_t)(u >> 16);
+}
+
+static int pack_linear(Engine& e, const std::string& name, int mode, Lin* lin, int k_pad_to = 0) {
+  const HostTensor* w = find(e, name + ".weight");
+  if (!w) return 940;
+  const int N = (int)w->shape[0], K = (int)w->shape[1];
+  lin->N = N, lin->K = k_pad_to ? k_pad_to : K, lin->mode = mode;
+  lin->gate_cols = mode == EPI_NONLIN_BF16 ? 2 * (N / 3) : 0;
+  if ((mode == EPI_GLU_BF16 && (N / 2) % 16) || (mode == EPI_NONLIN_BF16 && (N / 3) % 16)) {
+    e.err = "fused epilogue needs channel counts that are multiples of 16: " + name;
+    return 941;
+  }
+  lin->block_n = gemm_pick_block_n(N, mode, lin->gate_cols);
+  lin->N_pad = (N + lin->block_n - 1) / lin->block_n * lin->block_n;
+  lin->ldw = (lin->K + 63) / 64 * 64;
+  const std::vector<int> perm = row_perm(mode, N);
+  std::vector<uint16_t> wb((size_t)lin->N_pad * lin->ldw, 0);
+  for (int n = 0; n < N; ++n) {
+    const float* src = w->data.data() + (size_t)perm[n] * K;
+    uint16_t* dst = wb.data() + (size_t)n * lin->ldw;
+    for (int k = 0; k < K; ++k) dst[k] = f2bf(src[k]);
+  }
+  ZV_TRY(dev_alloc(e, e.weight_allocs, (void**)&lin->w, wb.size() * 2));
+  ZV_TRY((int)cudaMemcpy(lin->w, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
+  std::vector<float> bias(N, 0.f);
+  auto it = e.raw.find(name + ".bias");
+  if (it != e.raw.end())
+    for (int n = 0; n < N; ++n) bias[n] = it->second.data[perm[n]];
+  ZV_TRY(upload_f32(e, bias, &lin->bias));
+  return 0;
+}
+
+static int build_layer(Engine& e, Net& net, const std::string& p, int kernel, Layer* L) {
+  ZV_TRY(pack_linear(e, p + ".self_attn_weights.in_proj", EPI_BIAS_BF16, &L->attn_in));
+  ZV_TRY(upload_named(e, p + ".self_attn_weights.linear_pos.weight", &L->w_pos));
+  for (int i = 0; i < 3; ++i) {
+    const std::string f = p + ".feed_forward" + std::to_string(i + 1);
+    ZV_TRY(pack_linear(e, f + ".in_proj", EPI_SWOOSHL_BF16, &L->ff_in[i]));
+    ZV_TRY(pack_linear(e, f + ".out_proj", EPI_RESIDUAL, &L->ff_out[i]));
+  }
+  ZV_TRY(pack_linear(e, p + ".nonlin_attention.in_proj", EPI_NONLIN_BF16, &L->na_in));
+  ZV_TRY(pack_linear(e, p + ".nonlin_attention.out_proj", EPI_RESIDUAL, &L->na_out));
+  for (int i = 0; i < 2; ++i) {
+    const std::string a = p + ".self_attn" + std::to_string(i + 1);
+    ZV_TRY(pack_linear(e, a + ".in_proj", EPI_BIAS_BF16, &L->sa_in[i]));
+    ZV_TRY(pack_linear(e, a + ".out_proj", EPI_RESIDUAL, &L->sa_out[i]));
+    const std::string c = p + ".conv_module" + std::to_string(i + 1);
+    ZV_TRY(pack_linear(e, c + ".in_proj", EPI_GLU_BF16, &L->conv_in[i]));
+    ZV_TRY(pack_linear(e, c + ".out_proj", EPI_RESIDUAL, &L->conv_out[i]));
+    ZV_TRY(upload_named(e, c + ".depthwise_conv.weight", &L->dw_w[i]));
+    ZV_TRY(upload_named(e, c + ".depthwise_conv.bias", &L->dw_b[i]));
+    const HostTensor* dw = find(e, c + ".depthwise_conv.weight");
+    if ((int)dw->shape[2] != kernel) {
+      e.err = "depthwise kernel size mismatch at " + c;
+      return 942;
+    }
+  }
+  ZV_TRY(upload_named(e, p + ".norm.bias", &L->norm_bias));
+  const HostTensor* ls = find(e, p + ".norm.log_scale");
+  if (!ls) return 940;
+  L->log_scale = ls->data[0];
+  ZV_TRY(upload_named(e, p + ".bypass.bypass_scale", &L->bypass_scale));
+  ZV_TRY(upload_named(e, p + ".bypass_mid.bypass_scale", &L->bypass_mid_scale));
+  (void)net;
+  return 0;
+}
+
+static int build_net(Engine& e, Net& net, const std::string& prefix, int in_dim, int out_dim, int D, int F, int H,
+                     int n_stacks, const int* ds, const int* nl, const int* kern, bool use_time, bool use_guidance) {
+  const zv_config& c = e.cfg;
+  net.prefix = prefix, net.in_dim = in_dim, net.out_dim = out_dim, net.D = D, net.F = F, net.H = H;
+  net.hidden_na = 3 * D / 4;
+  net.in_pad = (in_dim + 63) / 64 * 64;
+  net.use_time = use_time, net.use_guidance = use_guidance;
+  if (c.query_head_dim != 32 || c.pos_head_dim != 4 || c.value_head_dim != 12 || H * c.pos_head_dim > 16) {
+    e.err = "attention kernel is specialised for query_head_dim 32, pos_head_dim 4, value_head_dim 12, <=4 heads";
+    return 943;
+  }
+  if (D % 64 || D > 512) {
+    e.err = "encoder dim must be a multiple of 64 and <= 512";
+    return 943;
+  }
+  ZV_TRY(pack_linear(e, prefix + ".in_proj", EPI_F32, &net.in_proj, net.in_pad));
+  ZV_TRY(pack_linear(e, prefix + ".out_proj", EPI_F32, &net.out_proj));
+  const int td = c.time_embed_dim;
+  if (use_time) {
+    ZV_TRY(upload_named(e, prefix + ".time_embed.0.weight", &net.te_w0));
+    ZV_TRY(upload_named(e, prefix + ".time_embed.0.bias", &net.te_b0));
+    ZV_TRY(upload_named(e, prefix + ".time_embed.2.weight", &net.te_w2));
+    ZV_TRY(upload_named(e, prefix + ".time_embed.2.bias", &net.te_b2));
+    if (use_guidance) ZV_TRY(upload_named(e, prefix + ".guidance_scale_embed.weight", &net.te_wg));
+  }
+  net.stacks.resize(n_stacks);
+  size_t te_cols = 0;
+  for (int i = 0; i < n_stacks; ++i) {
+    Stack& st = net.stacks[i];
+    st.ds = ds[i], st.kernel = kern[i];
+    const std::string sp = prefix + ".encoders." + std::to_string(i);
+    const std::string ep = st.ds == 1 ? sp : sp + ".encoder";
+    if (st.ds != 1) {
+      if (st.ds > 4) {
+        e.err = "downsampling factor > 4 unsupported";
+        return 943;
+      }
+      const HostTensor* b = find(e, sp + ".downsample.bias");
+      if (!b) return 940;
+      float mx = -1e30f, sum = 0.f;
+      for (int k = 0; k < st.ds; ++k) mx = fmaxf(mx, b->data[k]);
+      for (int k = 0; k < st.ds; ++k) sum += expf(b->data[k] - mx);
+      for (int k = 0; k < st.ds; ++k) st.ds_w[k] = expf(b->data[k] - mx) / sum;
+      ZV_TRY(upload_named(e, sp + ".out_combiner.bypass_scale", &st.out_comb_scale));
+    }
+    st.layers.resize(nl[i]);
+    if (use_time) st.te_off = te_cols, te_cols += D;
+    for (int j = 0; j < nl[i]; ++j) {
+      ZV_TRY(build_layer(e, net, ep + ".layers." + std::to_string(j), st.kernel, &st.layers[j]));
+      if (use_time) st.layers[j].te_off_ff1 = te_cols, te_cols += st.layers[j].ff_in[0].N;
+    }
+  }
+  net.N_te = (int)te_cols;
+  if (use_time) {
+    // Fold: te_stack = Ws a + bs (zipformer.py:677-680), FF1 row-bias = Wff1 te_stack (in_proj is linear,
+    // so in_proj(src + te) = in_proj(src) + Wff1 te).  Rows are stored in projection-column order.
+    ZV_TRY(dev_alloc(e, e.weight_allocs, (void**)&net.te_proj_w, te_cols * td * sizeof(float)));
+    ZV_TRY(dev_alloc(e, e.weight_allocs, (void**)&net.te_proj_b, te_cols * sizeof(float)));
+    for (int i = 0; i < n_stacks; ++i) {
+      Stack& st = net.stacks[i];
+      const std::string sp = prefix + ".encoders." + std::to_string(i);
+      const std::string ep = st.ds == 1 ? sp : sp + ".encoder";
+      const HostTensor* ws = find(e, ep + ".time_emb.1.weight");
+      const HostTensor* bs = find(e, ep + ".time_emb.1.bias");
+      if (!ws || !bs) return 940;
+      ZV_TRY((int)cudaMemcpy(net.te_proj_w + st.te_off * td, ws->data.data(), (size_t)D * td * 4,
+                             cudaMemcpyHostToDevice));
+      ZV_TRY((int)cudaMemcpy(net.te_proj_b + st.te_off, bs->data.data(), (size_t)D * 4, cudaMemcpyHostToDevice));
+      for (int j = 0; j < nl[i]; ++j) {
+        const std::string f = ep + ".layers." + std::to_string(j) + ".feed_forward1.in_proj.weight";
+        const HostTensor* wf = find(e, f);
+        if (!wf) return 940;
+        const int F1 = (int)wf->shape[0];
+        float* wf_dev = nullptr;
+        ZV_TRY((int)cudaMalloc(&wf_dev, (size_t)F1 * D * 4));
+        cudaMemcpy(wf_dev, wf->data.data(), (size_t)F1 * D * 4, cudaMemcpyHostToDevice);
+        const size_t off = st.layers[j].te_off_ff1;
+        int rc = sgemm_nn(wf_dev, net.te_proj_w + st.te_off * td, net.te_proj_w + off * td, F1, td, D, 0);
+        if (!rc) rc = sgemm_nn(wf_dev, net.te_proj_b + st.te_off, net.te_proj_b + off, F1, 1, D, 0);
+        cudaDeviceSynchronize();
+        cudaFree(wf_dev);
+        ZV_TRY(rc);
+      }
+    }
+  }
+  return 0;
+}
+
+int engine_finalize(Engine& e) {
+  const zv_config& c = e.cfg;
+  ZV_TRY(build_net(e, e.fm, "fm_decoder", 3 * c.feat_dim, c.feat_dim, c.fm_dim, c.fm_feedforward_dim, c.fm_num_heads,
+                   c.fm_num_stacks, c.fm_downsampling_factor, c.fm_num_layers, c.fm_cnn_module_kernel, true,
+                   c.use_guidance_scale_embed != 0));
+  const int one = 1;
+  ZV_TRY(build_net(e, e.text, "text_encoder", c.text_embed_dim, c.feat_dim, c.text_dim, c.text_feedforward_dim,
+                   c.text_num_heads, 1, &one, &c.text_num_layers, &c.text_cnn_module_kernel, false, false));
+  ZV_TRY(upload_named(e, "embed.weight", &e.embed));
+  if (c.dialog) ZV_TRY(upload_named(e, "spk_embed.weight", &e.spk_embed));
+  ZV_TRY((int)cudaDeviceSynchronize());
+  e.finalized = true;
+  // keep only what zv_audio needs; model tensors are now on the device
+  for (auto it = e.raw.begin(); it != e.raw.end();)
+    it = (it->first.rfind("vocoder.", 0) == 0) ? ++it : e.raw.erase(it);
+  return 0;
+}
+
+// ------------------------------------------------------------------ workspace
+int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
+  const size_t rows = (size_t)nb * T;
+  if (rows <= ws.cap_rows && nb <= ws.cap_nb) return 0;
+  cudaDeviceSynchronize();
+  for (void* p : ws.allocs) cudaFree(p);
+  ws.allocs.clear();
+  ws.cap_rows = rows, ws.cap_nb = nb, ws.D = net.D;
+  const size_t D = net.D;
+  const size_t Fmax = (size_t)net.F * 5 / 4;
+  const size_t td = e.cfg.time_embed_dim;
+  auto A = [&](void** p, size_t bytes) { return dev_alloc(e, ws.allocs, p, bytes); };
+  ZV_TRY(A((void**)&ws.X, rows * D * 4));
+  ZV_TRY(A((void**)&ws.Xs, rows * D * 4));
+  ZV_TRY(A((void**)&ws.Y, rows * D * 4));
+  ZV_TRY(A((void**)&ws.vel, rows * net.out_dim * 4));
+  ZV_TRY(A((void**)&ws.xcur, rows * net.out_dim * 4));
+  ZV_TRY(A((void**)&ws.x_in, rows * net.in_pad * 2));
+  ZV_TRY(A((void**)&ws.shadow, rows * D * 2));
+  ZV_TRY(A((void**)&ws.qkp, rows * 288 * 2));
+  ZV_TRY(A((void**)&ws.hidden, rows * Fmax * 2));
+  ZV_TRY(A((void**)&ws.na_v, rows * net.hidden_na * 2));
+  ZV_TRY(A((void**)&ws.na_y, rows * net.hidden_na * 2));
+  ZV_TRY(A((void**)&ws.na_o, rows * net.hidden_na * 2));
+  ZV_TRY(A((void**)&ws.sa_v, rows * 48 * 2));
+  ZV_TRY(A((void**)&ws.sa_o, rows * 48 * 2));
+  ZV_TRY(A((void**)&ws.conv_a, rows * D * 2));
+  ZV_TRY(A((void**)&ws.conv_b, rows * D * 2));
+  for (int i = 0; i < 3; ++i) ZV_TRY(A((void**)&ws.mask[i], rows));
+  ZV_TRY(A((void**)&ws.t_dev, nb * 4));
+  ZV_TRY(A((void**)&ws.g_dev, nb * 4));
+  ZV_TRY(A((void**)&ws.guid_dev, nb * 4));
+  ZV_TRY(A((void**)&ws.te_a, nb * td * 4));
+  ZV_TRY(A((void**)&ws.te_out, (size_t)nb * (net.N_te + 1) * 4));
+  return 0;
+}
+
+static int run_gemm(Engine& e, const Lin& lin, const __nv_bfloat16* A, int lda, int M, EpiParams ep, cudaStream_t s) {
+  GemmPlan p;
+  p.M = M, p.N_pad = lin.N_pad, p.K = lin.K, p.lda = lda, p.ldw = lin.ldw, p.block_n = lin.block_n;
+  ep.mode = lin.mode, ep.M = M, ep.N = lin.N, ep.gate_cols = lin.gate_cols, ep.bias = lin.bias;
+  ZV_K(gemm_launch(A, lin.w, p, ep, e.gemm_impl, s));
+  return 0;
+}
+
+static int get_pos_table(Engine& e, Net& net, Layer& ly, int L, cudaStream_t s, float** out) {
+  auto it = ly.pos_tab.find(L);
+  if (it == ly.pos_tab.end()) {
+    float* E = nullptr;
+    ZV_TRY(dev_alloc(e, e.weight_allocs, (void**)&E, (size_t)net.H * (2 * L - 1) * 4 * sizeof(float)));
+    ZV_K(pos_table(ly.w_pos, net.H, e.cfg.pos_head_dim, e.cfg.pos_dim, L, E, s));
+    it = ly.pos_tab.emplace(L, E).first;
+  }
+  *out = it->second;
+  return 0;
+}
+
+// Zipformer2EncoderLayer.forward in eval mode (zipformer.py:489-642).  X: layer input / output (fp32),
+// ws.Y: working residual stream, ws.shadow: bf16 copy of the current stream (GEMM A operand).
+static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kernel, float* X, int nb, int L,
+                         const uint8_t* mask, const float* te_stack, const float* te_ff1, cudaStream_t s) {
+  const int M = nb * L, D = net.D, hn = net.hidden_na;
+  float* Etab = nullptr;
+  ZV_TRY(get_pos_table(e, net, ly, L, s, &Etab));
+  EpiParams ep;
+  // attention projections from the layer input (before the time embedding is added) -- :526-531
+  ep = EpiParams();
+  ep.L = L, ep.out_bf16 = ws.qkp, ep.ld_bf16 = 288;
+  ZV_TRY(run_gemm(e, ly.attn_in, ws.shadow, D, M, ep, s));
+
+  auto residual = [&](const Lin& lin, const __nv_bfloat16* A, int lda, const float* res, const float* resbias,
+                      const float* orig, const float* bscale) {
+    EpiParams r;
+    r.L = L, r.res = res, r.out_f32 = ws.Y, r.ld_f32 = D, r.out_bf16 = ws.shadow, r.ld_bf16 = D;
+    r.resbias = resbias, r.bias_ld = net.N_te, r.orig = orig, r.bypass_scale = bscale;
+    return run_gemm(e, lin, A, lda, M, r, s);
+  };
+  auto ff = [&](int i, const float* rowbias, const float* res, const float* resbias, const float* orig,
+                const float* bscale) {
+    EpiParams f;
+    f.L = L, f.rowbias = rowbias, f.bias_ld = net.N_te, f.out_bf16 = ws.hidden, f.ld_bf16 = ly.ff_in[i].N;
+    int rc = run_gemm(e, ly.ff_in[i], ws.shadow, D, M, f, s);
+    if (rc) return rc;
+    return residual(ly.ff_out[i], ws.hidden, ly.ff_in[i].N, res, resbias, orig, bscale);
+  };
+  auto self_attn = [&](int i, const float* resbias) {
+    EpiParams v;
+    v.L = L, v.out_bf16 = ws.sa_v, v.ld_bf16 = 48;
+    int rc = run_gemm(e, ly.sa_in[i], ws.shadow, D, M, v, s);
+    if (rc) return rc;
+    AttnParams a;
+    a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.sa_v, a.ldv = 48, a.gate = nullptr, a.ldg = 0;
+    a.out = ws.sa_o, a.ldo = 48, a.nb = nb, a.L = L, a.H = net.H, a.heads = net.H, a.dv = 12;
+    ++g_launch_count;
+    rc = attention(a, s);
+    if (rc) return rc;
+    return residual(ly.sa_out[i], ws.sa_o, 48, ws.Y, resbias, nullptr, nullptr);
+  };
+  auto conv = [&](int i) {
+    EpiParams c;
+    c.L = L, c.mask = mask, c.out_bf16 = ws.conv_a, c.ld_bf16 = D;
+    int rc = run_gemm(e, ly.conv_in[i], ws.shadow, D, M, c, s);
+    if (rc) return rc;
+    ++g_launch_count;
+    rc = dwconv_swooshr(ws.conv_a, ly.dw_w[i], ly.dw_b[i], nb, L, D, kernel, ws.conv_b, s);
+    if (rc) return rc;
+    return residual(ly.conv_out[i], ws.conv_b, D, ws.Y, nullptr, nullptr, nullptr);
+  };
+
+  // src += time_emb; src += FF1(src)  (:532-536): FF1 input bias folded, time_emb added to the stream here
+  ZV_TRY(ff(0, te_ff1, X, te_stack, nullptr, nullptr));
+  // src += NonlinAttention(src, A[0:1])  (:542,558-562)
+  ep = EpiParams();
+  ep.L = L, ep.out_bf16 = ws.na_v, ep.ld_bf16 = hn, ep.out2_bf16 = ws.na_y, ep.ld2_bf16 = hn;
+  ZV_TRY(run_gemm(e, ly.na_in, ws.shadow, D, M, ep, s));
+  {
+    AttnParams a;
+    a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.na_v, a.ldv = hn, a.gate = ws.na_y, a.ldg = hn;
+    a.out = ws.na_o, a.ldo = hn, a.nb = nb, a.L = L, a.H = net.H, a.heads = 1, a.dv = hn;
+    ZV_K(attention(a, s));
+  }
+  ZV_TRY(residual(ly.na_out, ws.na_o, hn, ws.Y, nullptr, nullptr, nullptr));
+  // src += SelfAttn1(src, A); src += time_emb  (:564-579)
+  ZV_TRY(self_attn(0, te_stack));
+  ZV_TRY(conv(0));                                                       // :581-587
+  ZV_TRY(ff(1, nullptr, ws.Y, nullptr, X, ly.bypass_mid_scale));          // :593-598 (FF2 + bypass_mid)
+  ZV_TRY(self_attn(1, te_stack));                                        // :600-616
+  ZV_TRY(conv(1));                                                       // :618-624
+  ZV_TRY(ff(2, nullptr, ws.Y, nullptr, nullptr, nullptr));                // :630-632
+  // src = bypass(src_orig, BiasNorm(src))  (:635-637), in place on X
+  ZV_K(biasnorm_bypass(ws.Y, X, ly.norm_bias, ly.log_scale, ly.bypass_scale, M, D, X, ws.shadow, s));
+  return 0;
+}
+
+int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t* mask_dev, const TimeArgs& ta,
+                float* out, cudaStream_t s) {
+  const int M = nb * T, D = net.D;
+  const int td = e.cfg.time_embed_dim;
+  EpiParams ep;
+  ep.L = T, ep.out_f32 = ws.X, ep.ld_f32 = D, ep.out_bf16 = ws.shadow, ep.ld_bf16 = D;
+  ZV_TRY(run_gemm(e, net.in_proj, ws.x_in, net.in_pad, M, ep, s));
+  if (net.use_time) {
+    if (!ta.t) {
+      e.err = "this network needs a time step";
+      return 950;
+    }
+    ZV_K(time_embed(ta.t, ta.t_stride, ta.g, ta.g_stride, nb, td, net.te_w0, net.te_b0, net.te_w2, net.te_b2,
+                    net.te_wg, ws.te_a, s));
+    ZV_K(small_linear(ws.te_a, net.te_proj_w, net.te_proj_b, nb, net.N_te, td, ws.te_out, s));
+  }
+  for (Stack& st : net.stacks) {
+    const int ds = st.ds;
+    const int L = (T + ds - 1) / ds;
+    float* X = ws.X;
+    const uint8_t* mask = mask_dev;
+    if (ds != 1) {
+      uint8_t* msub = mask_dev ? ws.mask[ds == 2 ? 1 : 2] : nullptr;
+      g_launch_count += msub ? 2 : 1;
+      ZV_TRY(downsample(ws.X, st.ds_w, nb, T, D, ds, ws.Xs, ws.shadow, msub, mask_dev, s));
+      X = ws.Xs, mask = msub;
+    }
+    const float* te_stack = net.use_time ? ws.te_out + st.te_off : nullptr;
+    for (Layer& ly : st.layers) {
+      const float* te_ff1 = net.use_time ? ws.te_out + ly.te_off_ff1 : nullptr;
+      // row pitch of the time-embedding projections is N_te for every layer of this net
+      ZV_TRY(layer_forward(e, net, ws, ly, st.kernel, X, nb, L, mask, te_stack, te_ff1, s));
+    }
+    if (ds != 1) ZV_K(upsample_combine(ws.X, ws.Xs, st.out_comb_scale, nb, T, L, D, ds, ws.shadow, s));
+  }
+  ep = EpiParams();
+  ep.L = T, ep.out_f32 = out, ep.ld_f32 = net.out_dim;
+  ZV_TRY(run_gemm(e, net.out_proj, ws.shadow, D, M, ep, s));
+  return 0;
+}
+
+}  // namespace zv

@@ -1,0 +1,105 @@
+// Engine internals: packed weights, workspace and the per-NFE schedule of kernel launches.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/zipvoice_b200.h"
+#include "zv_gemm.h"
+#include "zv_kernels.h"
+
+namespace zv {
+
+struct HostTensor {
+  std::vector<float> data;
+  std::vector<int64_t> shape;
+  size_t numel() const { return data.size(); }
+};
+
+// One packed Linear: bf16 weight [N_pad][ldw] (rows possibly permuted for fused epilogues) + fp32 bias.
+struct Lin {
+  __nv_bfloat16* w = nullptr;
+  float* bias = nullptr;  // accumulator-column order, length N
+  int N = 0, N_pad = 0, K = 0, ldw = 0, block_n = 0, mode = 0, gate_cols = 0;
+};
+
+struct Layer {
+  Lin attn_in, ff_in[3], ff_out[3], na_in, na_out, sa_in[2], sa_out[2], conv_in[2], conv_out[2];
+  float* w_pos = nullptr;  // [H*dp][pos_dim]
+  float* dw_w[2] = {nullptr, nullptr};
+  float* dw_b[2] = {nullptr, nullptr};
+  float* norm_bias = nullptr;
+  float log_scale = 0.f;
+  float* bypass_scale = nullptr;
+  float* bypass_mid_scale = nullptr;
+  size_t te_off_ff1 = 0;          // column offset of this layer's FF1 row-bias in the te projection
+  std::map<int, float*> pos_tab;  // L -> E[H][2L-1][dp]
+};
+
+struct Stack {
+  int ds = 1, kernel = 0;
+  float ds_w[4] = {1.f, 0.f, 0.f, 0.f};  // softmax(downsample.bias)
+  float* out_comb_scale = nullptr;
+  size_t te_off = 0;  // column offset of te_stack (D columns) in the te projection
+  std::vector<Layer> layers;
+};
+
+struct Net {
+  std::string prefix;
+  int in_dim = 0, in_pad = 0, out_dim = 0, D = 0, F = 0, H = 0, hidden_na = 0;
+  bool use_time = false, use_guidance = false;
+  Lin in_proj, out_proj;
+  float *te_w0 = nullptr, *te_b0 = nullptr, *te_w2 = nullptr, *te_b2 = nullptr, *te_wg = nullptr;
+  float* te_proj_w = nullptr;  // [N_te][time_dim] folded (stack time_emb, FF1 in_proj . time_emb)
+  float* te_proj_b = nullptr;  // [N_te]
+  int N_te = 0;
+  std::vector<Stack> stacks;
+};
+
+struct Workspace {
+  size_t cap_rows = 0;  // nb * T capacity
+  int cap_nb = 0;
+  int D = 0;
+  float *X = nullptr, *Xs = nullptr, *Y = nullptr, *vel = nullptr, *xcur = nullptr;
+  __nv_bfloat16 *x_in = nullptr, *shadow = nullptr, *qkp = nullptr, *hidden = nullptr, *na_v = nullptr,
+                *na_y = nullptr, *na_o = nullptr, *sa_v = nullptr, *sa_o = nullptr, *conv_a = nullptr,
+                *conv_b = nullptr;
+  uint8_t* mask[3] = {nullptr, nullptr, nullptr};  // per distinct downsampling rate (1, 2, 4)
+  float *t_dev = nullptr, *g_dev = nullptr, *te_a = nullptr, *te_out = nullptr, *guid_dev = nullptr;
+  std::vector<void*> allocs;
+};
+
+struct Engine {
+  zv_config cfg;
+  std::map<std::string, HostTensor> raw;
+  bool finalized = false;
+  Net fm, text;
+  float* embed = nullptr;      // [vocab][text_embed_dim]
+  float* spk_embed = nullptr;  // [2][feat_dim]
+  Workspace ws_fm, ws_text;
+  std::vector<void*> weight_allocs;
+  std::string err;
+  int gemm_impl = 0;
+  // audio front-end / vocoder state lives in zv_audio.cu
+  void* audio = nullptr;
+};
+
+extern long long g_launch_count;
+
+int engine_finalize(Engine& e);
+// One TTSZipformer forward on nb sequences of T frames.  ws.x_in holds the bf16 input rows
+// [nb*T][in_pad]; the result (fp32 [nb*T][out_dim]) is written to `out`.
+struct TimeArgs {
+  const float* t = nullptr;  // device; value of sequence b is t[b * t_stride]
+  int t_stride = 0;
+  const float* g = nullptr;  // device guidance scale for the distilled model (embedded), or null
+  int g_stride = 0;
+};
+int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t* mask_dev, const TimeArgs& ta,
+                float* out, cudaStream_t s);
+int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T);
+
+}  // namespace zv

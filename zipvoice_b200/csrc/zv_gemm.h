@@ -1,0 +1,56 @@
+// GEMM interface: C[m][n] = epilogue( sum_k A[m][k] * W[n][k] ), A and W bf16 (K contiguous),
+// fp32 accumulation in TMEM (tcgen05.mma), fused epilogues for the Zipformer layer.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace zv {
+
+enum EpiMode : int {
+  EPI_BIAS_BF16 = 0,  // out_bf16 = acc + bias (+ rowbias[b])
+  EPI_SWOOSHL_BF16 = 1,  // out_bf16 = SwooshL(acc + bias + rowbias[b])            (FF in_proj)
+  EPI_GLU_BF16 = 2,      // cols come in groups of 32 = [16 x | 16 s]; out = x*sigmoid(s), masked frames -> 0
+  EPI_NONLIN_BF16 = 3,   // cols < gate_cols: groups of 32 = [16 s | 16 x] -> out = x*tanh(s);
+                         // cols >= gate_cols: out2 = acc + bias                     (NonlinAttention in_proj)
+  EPI_RESIDUAL = 4,      // v = res + acc + bias (+ resbias[b]); optional bypass vs orig; writes fp32 + bf16
+  EPI_F32 = 5,           // out_f32 = acc + bias (+ rowbias[b])
+};
+
+struct EpiParams {
+  int mode = 0;
+  int M = 0;          // valid rows
+  int N = 0;          // valid accumulator columns
+  int L = 1;          // rows per batch element (b = m / L)
+  int gate_cols = 0;  // EPI_NONLIN_BF16: first accumulator column of the plain (y) part
+  const float* bias = nullptr;     // [N]   accumulator-column order
+  const float* rowbias = nullptr;  // [B][bias_ld] optional, added before the activation
+  int bias_ld = 0;                 // row pitch of rowbias / resbias (per batch element)
+  __nv_bfloat16* out_bf16 = nullptr;
+  int ld_bf16 = 0;
+  __nv_bfloat16* out2_bf16 = nullptr;
+  int ld2_bf16 = 0;
+  float* out_f32 = nullptr;
+  int ld_f32 = 0;
+  const float* res = nullptr;  // EPI_RESIDUAL input (may alias out_f32), same ld as out_f32
+  const float* resbias = nullptr;  // [B][bias_ld] optional (time embedding folded into the residual)
+  const float* orig = nullptr;     // optional bypass: v = orig + (v - orig) * bypass_scale[n]
+  const float* bypass_scale = nullptr;
+  const uint8_t* mask = nullptr;   // [B][L] 1 = padded frame (EPI_GLU_BF16)
+};
+
+struct GemmPlan {
+  int M, N_pad, K;      // N_pad = rows of the packed weight (multiple of block_n)
+  int lda;              // A row pitch in elements (multiple of 8)
+  int ldw;              // W row pitch in elements (multiple of 8, >= K)
+  int block_n;          // multiple of 32, <= 256
+};
+
+// Launch on `stream`.  impl: 0 = tcgen05/TMA kernel, 1 = SIMT checker kernel (tests / debugging only).
+// Returns cudaError_t-like code (0 = ok).
+int gemm_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const GemmPlan& plan, const EpiParams& ep,
+                int impl, cudaStream_t stream);
+
+int gemm_pick_block_n(int n_valid, int mode, int gate_cols);
+
+}  // namespace zv

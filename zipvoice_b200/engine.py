@@ -1,0 +1,159 @@
+"""Host-side owner of one C-ABI handle: model configuration, weights, and thin wrappers that turn
+torch CUDA tensors into raw device pointers + the current CUDA stream.
+
+PyTorch is used here only for device memory, streams and (elsewhere) torch.distributed.
+"""
+import ctypes as C
+from typing import Dict, Optional, Sequence, Union
+
+import torch
+
+from . import _lib
+
+
+class ZvError(RuntimeError):
+    pass
+
+
+def make_config(model_cfg: dict, vocab_size: int, pad_id: int = 0, distill: bool = False, dialog: bool = False,
+                spk_a_id: int = 360, spk_b_id: int = 361) -> _lib.ZvConfig:
+    """model_cfg: the "model" section of model.json (= kwargs of ZipVoice.__init__, zipvoice.py:38-60)."""
+    c = _lib.ZvConfig()
+    ds = list(model_cfg["fm_decoder_downsampling_factor"])
+    if len(ds) > _lib.ZV_MAX_STACKS:
+        raise ValueError("too many encoder stacks")
+    c.feat_dim = model_cfg["feat_dim"]
+    c.fm_num_stacks = len(ds)
+    for i, (d, n, k) in enumerate(zip(ds, model_cfg["fm_decoder_num_layers"],
+                                      model_cfg["fm_decoder_cnn_module_kernel"])):
+        c.fm_downsampling_factor[i], c.fm_num_layers[i], c.fm_cnn_module_kernel[i] = d, n, k
+    c.fm_feedforward_dim = model_cfg["fm_decoder_feedforward_dim"]
+    c.fm_num_heads = model_cfg["fm_decoder_num_heads"]
+    c.fm_dim = model_cfg["fm_decoder_dim"]
+    c.text_num_layers = model_cfg["text_encoder_num_layers"]
+    c.text_feedforward_dim = model_cfg["text_encoder_feedforward_dim"]
+    c.text_cnn_module_kernel = model_cfg["text_encoder_cnn_module_kernel"]
+    c.text_num_heads = model_cfg["text_encoder_num_heads"]
+    c.text_dim = model_cfg["text_encoder_dim"]
+    for k in ("query_head_dim", "value_head_dim", "pos_head_dim", "pos_dim", "time_embed_dim", "text_embed_dim"):
+        setattr(c, k, model_cfg[k])
+    c.vocab_size, c.pad_id = vocab_size, pad_id
+    c.use_guidance_scale_embed, c.dialog = int(distill), int(dialog)
+    c.spk_a_id, c.spk_b_id = spk_a_id, spk_b_id
+    return c
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+class Engine:
+    """One handle per process / GPU.  `state_dict` uses the reference's tensor names."""
+
+    def __init__(self, model_cfg: dict, state_dict: Dict[str, torch.Tensor], vocab_size: int, pad_id: int = 0,
+                 distill: bool = False, dialog: bool = False, spk_a_id: int = 360, spk_b_id: int = 361,
+                 device: Union[str, torch.device] = "cuda:0"):
+        if not torch.cuda.is_available():
+            raise ZvError("zipvoice_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.lib = _lib.load()
+        self.device = torch.device(device)
+        self.model_cfg, self.distill, self.dialog = dict(model_cfg), distill, dialog
+        self.pad_id, self.feat_dim = pad_id, model_cfg["feat_dim"]
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            cfg = make_config(model_cfg, vocab_size, pad_id, distill, dialog, spk_a_id, spk_b_id)
+            self._check(self.lib.zv_create(C.byref(cfg), C.byref(self._h)))
+            for name, t in state_dict.items():
+                t = t.detach().to(dtype=torch.float32).contiguous()
+                shape = (C.c_int64 * max(t.dim(), 1))(*t.shape)
+                self._check(self.lib.zv_set_weight(self._h, name.encode(), _ptr(t), shape, t.dim(),
+                                                   int(t.is_cuda)))
+            self._check(self.lib.zv_finalize_weights(self._h))
+
+    def _check(self, rc: int):
+        if rc != 0:
+            msg = self.lib.zv_last_error(self._h)
+            raise ZvError(f"zipvoice_b200 error {rc}: {msg.decode() if msg else ''}")
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self.lib.zv_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_option(self, key: str, value: int):
+        self._check(self.lib.zv_set_option(self._h, key.encode(), int(value)))
+
+    # ------------------------------------------------------------------ helpers
+    def _prep(self, t: torch.Tensor, dtype=torch.float32) -> torch.Tensor:
+        return t.to(device=self.device, dtype=dtype).contiguous()
+
+    def _guidance(self, guidance_scale, B: int):
+        if torch.is_tensor(guidance_scale):
+            g = guidance_scale.detach().float().reshape(-1).cpu().tolist()
+        else:
+            g = [float(guidance_scale)]
+        assert len(g) in (1, B), "guidance_scale must be a float or a tensor of shape (batch, 1, 1)"
+        return (C.c_float * len(g))(*g), len(g)
+
+    # ------------------------------------------------------------------ hot path
+    def velocity(self, t: float, x, text_condition, speech_condition, padding_mask=None, guidance_scale=0.0,
+                 distill: Optional[bool] = None) -> torch.Tensor:
+        """DiffusionModel.forward / DistillDiffusionModel.forward (solver.py:40-110,127-165)."""
+        distill = self.distill if distill is None else distill
+        x, tc, sc = self._prep(x), self._prep(text_condition), self._prep(speech_condition)
+        B, T, F = x.shape
+        m = None if padding_mask is None else self._prep(padding_mask, torch.uint8)
+        g, glen = self._guidance(guidance_scale, B)
+        out = torch.empty_like(x)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.zv_velocity(self._h, int(distill), float(t), _ptr(x), _ptr(tc), _ptr(sc), _ptr(m), B,
+                                             T, g, glen, _ptr(out), _stream(self.device)))
+        return out
+
+    def sample(self, x, text_condition, speech_condition, padding_mask, num_step=10, guidance_scale=0.0,
+               t_start=0.0, t_end=1.0, t_shift=1.0, distill: Optional[bool] = None) -> torch.Tensor:
+        """EulerSolver.sample (solver.py:182-240); the input x is not modified."""
+        distill = self.distill if distill is None else distill
+        x, tc, sc = self._prep(x), self._prep(text_condition), self._prep(speech_condition)
+        B, T, F = x.shape
+        m = None if padding_mask is None else self._prep(padding_mask, torch.uint8)
+        g, glen = self._guidance(guidance_scale, B)
+        out = torch.empty_like(x)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.zv_sample(self._h, int(distill), _ptr(x), _ptr(tc), _ptr(sc), _ptr(m), B, T,
+                                           int(num_step), g, glen, float(t_start), float(t_end), float(t_shift),
+                                           _ptr(out), _stream(self.device)))
+        return out
+
+    def text_embed(self, tokens_padded: torch.Tensor, tokens_lens: torch.Tensor) -> torch.Tensor:
+        tp, tl = self._prep(tokens_padded, torch.int64), self._prep(tokens_lens, torch.int64)
+        B, S = tp.shape
+        out = torch.empty(B, S, self.feat_dim, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.zv_text_embed(self._h, _ptr(tp), _ptr(tl), B, S, _ptr(out), _stream(self.device)))
+        return out
+
+    def text_condition(self, embed: torch.Tensor, tokens_lens: torch.Tensor, features_lens: torch.Tensor,
+                       num_frames: int):
+        emb = self._prep(embed)
+        tl, fl = self._prep(tokens_lens, torch.int64), self._prep(features_lens, torch.int64)
+        B, S, F = emb.shape
+        out = torch.empty(B, num_frames, F, device=self.device, dtype=torch.float32)
+        mask = torch.empty(B, num_frames, device=self.device, dtype=torch.uint8)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.zv_text_condition(self._h, _ptr(emb), _ptr(tl), _ptr(fl), B, S, num_frames,
+                                                   _ptr(out), _ptr(mask), _stream(self.device)))
+        return out, mask.bool()
+
+    def launch_count(self) -> int:
+        return int(self.lib.zv_launch_count())
