@@ -96,6 +96,14 @@ int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp
                        const uint8_t* mask, const float* V_f32, int ldv, const float* gate_f32, float* out_f32,
                        void* stream);
 int zv_debug_pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E_out, void* stream);
+/* Per-kernel-class device timing: when enabled every launch is bracketed by CUDA events on its stream.
+ * zv_prof_read synchronises the device, fills ms / work / launches (arrays of zv_prof_num_classes()) and
+ * resets the records.  work = algorithmic FLOPs for tensor-bound classes, algorithmic bytes otherwise. */
+int zv_prof_enable(void* handle, int on);
+int zv_prof_num_classes(void);
+const char* zv_prof_class_name(int cls);
+int zv_prof_class_is_tensor(int cls);
+int zv_prof_read(void* handle, double* ms, double* work, long long* launches);
 /* Launch counters: kernels launched by this library since the last reset. */
 long long zv_launch_count(void);
 void zv_launch_count_reset(void);

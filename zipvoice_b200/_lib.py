@@ -46,6 +46,11 @@ _SIGS = {
     "zv_debug_gemm": (_I, [_I, _I, _I, _I, _I, _I, _I] + [_P] * 12),
     "zv_debug_attention": (_I, [_I, _I, _I, _I, _I, _P, _I, _P, _P, _P, _I, _P, _P, _P]),
     "zv_debug_pos_table": (_I, [_P, _I, _I, _I, _I, _P, _P]),
+    "zv_prof_enable": (_I, [_P, _I]),
+    "zv_prof_num_classes": (_I, []),
+    "zv_prof_class_name": (C.c_char_p, [_I]),
+    "zv_prof_class_is_tensor": (_I, [_I]),
+    "zv_prof_read": (_I, [_P, C.POINTER(_D), C.POINTER(_D), C.POINTER(_LL)]),
     "zv_launch_count": (_LL, []),
     "zv_launch_count_reset": (None, []),
 }

@@ -11,6 +11,15 @@ using namespace zv;
 static thread_local std::string g_err;
 static const char* kNullHandle = "null handle";
 
+#define API_K(cls, work, s, expr)                 \
+  do {                                             \
+    ++g_launch_count;                              \
+    if (e->prof.on) e->prof.begin(cls, work, s);   \
+    expr;                                          \
+    if (e->prof.on) e->prof.end(s);                \
+    API_TRY((int)cudaGetLastError());              \
+  } while (0)
+
 #define API_TRY(expr)                                                                     \
   do {                                                                                    \
     int _rc = (expr);                                                                     \
@@ -90,6 +99,7 @@ void zv_destroy(void* handle) {
   Engine* e = (Engine*)handle;
   if (!e) return;
   cudaDeviceSynchronize();
+  e->prof.release();
   for (void* p : e->weight_allocs) cudaFree(p);
   for (void* p : e->ws_fm.allocs) cudaFree(p);
   for (void* p : e->ws_text.allocs) cudaFree(p);
@@ -151,6 +161,23 @@ int zv_time_steps(double t_start, double t_end, int num_step, double t_shift, fl
   return 0;
 }
 
+int zv_prof_enable(void* handle, int on) {
+  Engine* e = (Engine*)handle;
+  if (!e) return 960;
+  cudaDeviceSynchronize();
+  e->prof.recs.clear(), e->prof.used = 0;
+  e->prof.on = on != 0;
+  return 0;
+}
+int zv_prof_num_classes(void) { return KC_COUNT; }
+const char* zv_prof_class_name(int c) { return kclass_name(c); }
+int zv_prof_class_is_tensor(int c) { return kclass_is_tensor(c) ? 1 : 0; }
+int zv_prof_read(void* handle, double* ms, double* work, long long* launches) {
+  Engine* e = (Engine*)handle;
+  if (!e) return 960;
+  return e->prof.read(ms, work, launches);
+}
+
 long long zv_launch_count(void) { return g_launch_count; }
 void zv_launch_count_reset(void) { g_launch_count = 0; }
 
@@ -172,16 +199,17 @@ static int velocity_step(Engine* e, int variant, float t_host, const float* t_de
   const bool cfg = (variant == 0) && !all_zero_g;
   const int nb = cfg ? 2 * B : B;
   const bool hi = t_host > 0.5f;  // solver.py:90 decided on the host from the precomputed time table
-  ++g_launch_count;
-  API_TRY(pack_input(x, text, speech, mask, B, T, F, cfg ? 1 : 0, hi ? 1 : 0, ws.x_in, net.in_pad,
-                     mask ? ws.mask[0] : nullptr, s));
+  // bytes: x read once, text / speech once, bf16 rows written
+  API_K(KC_PACK, (double)B * T * F * 12.0 + (double)nb * T * net.in_pad * 2.0, s,
+        API_TRY(pack_input(x, text, speech, mask, B, T, F, cfg ? 1 : 0, hi ? 1 : 0, ws.x_in, net.in_pad,
+                           mask ? ws.mask[0] : nullptr, s)));
   TimeArgs ta;
   ta.t = t_dev, ta.t_stride = 0;
   if (variant == 1) ta.g = ws.guid_dev, ta.g_stride = guidance_len == 1 ? 0 : 1;
   API_TRY(net_forward(*e, net, ws, nb, T, mask ? ws.mask[0] : nullptr, ta, ws.vel, s));
-  ++g_launch_count;
-  API_TRY(cfg_euler_update(x_update, ws.vel, ws.guid_dev, guidance_len, hi ? 1.0f : 2.0f, B, T, F, cfg ? 1 : 0, dt,
-                           v_out, s));
+  API_K(KC_CFG_EULER, (double)B * T * F * 4.0 * (cfg ? 4 : 3), s,
+        API_TRY(cfg_euler_update(x_update, ws.vel, ws.guid_dev, guidance_len, hi ? 1.0f : 2.0f, B, T, F, cfg ? 1 : 0,
+                                 dt, v_out, s)));
   return 0;
 }
 
@@ -262,17 +290,15 @@ extern "C" int zv_text_embed(void* handle, const int64_t* tokens_padded, const i
   Workspace& ws = e->ws_text;
   API_TRY(ws_reserve(*e, net, ws, B, S));
   const size_t total = (size_t)B * S * net.in_pad;
-  ++g_launch_count;
-  embed_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(tokens_padded, tokens_lens, e->embed, S,
-                                                               e->cfg.text_embed_dim, net.in_pad, e->cfg.vocab_size,
-                                                               ws.x_in, ws.mask[0], total);
-  API_TRY((int)cudaGetLastError());
+  API_K(KC_TEXT, (double)total * 6.0, s,
+        (embed_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(tokens_padded, tokens_lens, e->embed, S,
+                                                                      e->cfg.text_embed_dim, net.in_pad,
+                                                                      e->cfg.vocab_size, ws.x_in, ws.mask[0], total)));
   API_TRY(net_forward(*e, net, ws, B, S, ws.mask[0], TimeArgs(), embed_out, s));
   if (e->cfg.dialog) {
-    ++g_launch_count;
-    spk_add_kernel<<<B, 128, 0, s>>>(tokens_padded, B, S, e->cfg.feat_dim, e->cfg.pad_id, e->cfg.spk_a_id,
-                                     e->cfg.spk_b_id, e->spk_embed, embed_out);
-    API_TRY((int)cudaGetLastError());
+    API_K(KC_TEXT, (double)B * S * e->cfg.feat_dim * 8.0, s,
+          (spk_add_kernel<<<B, 128, 0, s>>>(tokens_padded, B, S, e->cfg.feat_dim, e->cfg.pad_id, e->cfg.spk_a_id,
+                                            e->cfg.spk_b_id, e->spk_embed, embed_out)));
   }
   return 0;
 }
@@ -284,10 +310,10 @@ extern "C" int zv_text_condition(void* handle, const float* embed, const int64_t
   if (!e) return 960;
   e->err.clear();
   const size_t total = (size_t)B * T * e->cfg.feat_dim;
-  ++g_launch_count;
-  text_condition_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      embed, tokens_lens, features_lens, S, T, e->cfg.feat_dim, out, mask_out, total);
-  API_TRY((int)cudaGetLastError());
+  cudaStream_t s = (cudaStream_t)stream;
+  API_K(KC_TEXT, (double)total * 8.0, s,
+        (text_condition_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(embed, tokens_lens, features_lens, S, T,
+                                                                               e->cfg.feat_dim, out, mask_out, total)));
   return 0;
 }
 

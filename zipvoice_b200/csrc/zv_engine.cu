@@ -20,11 +20,53 @@ long long g_launch_count = 0;
       return _rc;                                                                     \
     }                                                                                 \
   } while (0)
-#define ZV_K(expr)      \
-  do {                  \
-    ++g_launch_count;   \
-    ZV_TRY(expr);       \
+// One kernel launch of class `cls` doing `work` algorithmic FLOPs / bytes.
+#define ZV_K(cls, work, s, expr)              \
+  do {                                        \
+    ++g_launch_count;                         \
+    if (e.prof.on) e.prof.begin(cls, work, s); \
+    int _krc = (expr);                        \
+    if (e.prof.on) e.prof.end(s);             \
+    ZV_TRY(_krc);                             \
   } while (0)
+
+static const char* kNames[KC_COUNT] = {"gemm_bias", "gemm_swooshl", "gemm_glu", "gemm_nonlin", "gemm_residual",
+                                       "gemm_f32", "attn_self", "attn_nonlin", "dwconv_swooshr", "biasnorm_bypass",
+                                       "resample", "pack_input", "cfg_euler", "time_embed", "text_glue", "fbank",
+                                       "vocoder_elem"};
+const char* kclass_name(int c) { return c >= 0 && c < KC_COUNT ? kNames[c] : "?"; }
+bool kclass_is_tensor(int c) { return c <= KC_ATTN_NONLIN; }
+
+cudaEvent_t Prof::get() {
+  if (used == pool.size()) {
+    cudaEvent_t ev;
+    cudaEventCreate(&ev);
+    pool.push_back(ev);
+  }
+  return pool[used++];
+}
+void Prof::begin(int cls, double work, cudaStream_t s) {
+  Rec r{cls, work, get(), get()};
+  cudaEventRecord(r.a, s);
+  recs.push_back(r);
+}
+void Prof::end(cudaStream_t s) { cudaEventRecord(recs.back().b, s); }
+int Prof::read(double* ms, double* work, long long* launches) {
+  int rc = (int)cudaDeviceSynchronize();
+  for (int i = 0; i < KC_COUNT; ++i) ms[i] = 0.0, work[i] = 0.0, launches[i] = 0;
+  for (const Rec& r : recs) {
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) ms[r.cls] += t;
+    work[r.cls] += r.work, launches[r.cls] += 1;
+  }
+  recs.clear();
+  used = 0;
+  return rc;
+}
+void Prof::release() {
+  for (cudaEvent_t ev : pool) cudaEventDestroy(ev);
+  pool.clear(), recs.clear(), used = 0;
+}
 
 static int dev_alloc(Engine& e, std::vector<void*>& pool, void** p, size_t bytes) {
   if (bytes == 0) bytes = 16;
@@ -89,7 +131,7 @@ static int pack_linear(Engine& e, const std::string& name, int mode, Lin* lin, i
   const HostTensor* w = find(e, name + ".weight");
   if (!w) return 940;
   const int N = (int)w->shape[0], K = (int)w->shape[1];
-  lin->N = N, lin->K = k_pad_to ? k_pad_to : K, lin->mode = mode;
+  lin->N = N, lin->K = k_pad_to ? k_pad_to : K, lin->K_valid = K, lin->mode = mode;
   lin->gate_cols = mode == EPI_NONLIN_BF16 ? 2 * (N / 3) : 0;
   if ((mode == EPI_GLU_BF16 && (N / 2) % 16) || (mode == EPI_NONLIN_BF16 && (N / 3) % 16)) {
     e.err = "fused epilogue needs channel counts that are multiples of 16: " + name;
@@ -297,7 +339,23 @@ static int run_gemm(Engine& e, const Lin& lin, const __nv_bfloat16* A, int lda, 
   GemmPlan p;
   p.M = M, p.N_pad = lin.N_pad, p.K = lin.K, p.lda = lda, p.ldw = lin.ldw, p.block_n = lin.block_n;
   ep.mode = lin.mode, ep.M = M, ep.N = lin.N, ep.gate_cols = lin.gate_cols, ep.bias = lin.bias;
-  ZV_K(gemm_launch(A, lin.w, p, ep, e.gemm_impl, s));
+  ZV_K(KC_GEMM_BIAS + lin.mode, 2.0 * M * lin.N * (double)lin.K_valid, s,
+       gemm_launch(A, lin.w, p, ep, e.gemm_impl, s));
+  return 0;
+}
+
+// Algorithmic MACs per (query, key) pair and layer: the scores of the H heads are needed once
+// (H * (dq + dp) = 144), each consumer adds its A.V product.  The three passes recompute the
+// scores; only `score_heads` of them are counted as algorithmic work for this launch.
+static int run_attn(Engine& e, int cls, const AttnParams& a, int score_heads, cudaStream_t s) {
+  const double macs = (double)a.nb * a.L * a.L * (score_heads * (32.0 + 4.0) + (double)a.heads * a.dv);
+  ZV_K(cls, 2.0 * macs, s, attention(a, s));
+  return 0;
+}
+// algorithmic bytes: bf16 in + bf16 out
+static int run_dwconv(Engine& e, const __nv_bfloat16* in, const float* w, const float* b, int nb, int L, int C, int k,
+                      __nv_bfloat16* out, cudaStream_t s) {
+  ZV_K(KC_DWCONV, 4.0 * nb * L * C, s, dwconv_swooshr(in, w, b, nb, L, C, k, out, s));
   return 0;
 }
 
@@ -306,7 +364,8 @@ static int get_pos_table(Engine& e, Net& net, Layer& ly, int L, cudaStream_t s, 
   if (it == ly.pos_tab.end()) {
     float* E = nullptr;
     ZV_TRY(dev_alloc(e, e.weight_allocs, (void**)&E, (size_t)net.H * (2 * L - 1) * 4 * sizeof(float)));
-    ZV_K(pos_table(ly.w_pos, net.H, e.cfg.pos_head_dim, e.cfg.pos_dim, L, E, s));
+    ZV_K(KC_TIME_EMBED, (double)net.H * (2 * L - 1) * 16, s,
+         pos_table(ly.w_pos, net.H, e.cfg.pos_head_dim, e.cfg.pos_dim, L, E, s));
     it = ly.pos_tab.emplace(L, E).first;
   }
   *out = it->second;
@@ -349,8 +408,7 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
     AttnParams a;
     a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.sa_v, a.ldv = 48, a.gate = nullptr, a.ldg = 0;
     a.out = ws.sa_o, a.ldo = 48, a.nb = nb, a.L = L, a.H = net.H, a.heads = net.H, a.dv = 12;
-    ++g_launch_count;
-    rc = attention(a, s);
+    rc = run_attn(e, KC_ATTN_SELF, a, i == 0 ? net.H - 1 : 0, s);
     if (rc) return rc;
     return residual(ly.sa_out[i], ws.sa_o, 48, ws.Y, resbias, nullptr, nullptr);
   };
@@ -359,8 +417,7 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
     c.L = L, c.mask = mask, c.out_bf16 = ws.conv_a, c.ld_bf16 = D;
     int rc = run_gemm(e, ly.conv_in[i], ws.shadow, D, M, c, s);
     if (rc) return rc;
-    ++g_launch_count;
-    rc = dwconv_swooshr(ws.conv_a, ly.dw_w[i], ly.dw_b[i], nb, L, D, kernel, ws.conv_b, s);
+    rc = run_dwconv(e, ws.conv_a, ly.dw_w[i], ly.dw_b[i], nb, L, D, kernel, ws.conv_b, s);
     if (rc) return rc;
     return residual(ly.conv_out[i], ws.conv_b, D, ws.Y, nullptr, nullptr, nullptr);
   };
@@ -375,7 +432,7 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
     AttnParams a;
     a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.na_v, a.ldv = hn, a.gate = ws.na_y, a.ldg = hn;
     a.out = ws.na_o, a.ldo = hn, a.nb = nb, a.L = L, a.H = net.H, a.heads = 1, a.dv = hn;
-    ZV_K(attention(a, s));
+    ZV_TRY(run_attn(e, KC_ATTN_NONLIN, a, 1, s));
   }
   ZV_TRY(residual(ly.na_out, ws.na_o, hn, ws.Y, nullptr, nullptr, nullptr));
   // src += SelfAttn1(src, A); src += time_emb  (:564-579)
@@ -386,7 +443,8 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   ZV_TRY(conv(1));                                                       // :618-624
   ZV_TRY(ff(2, nullptr, ws.Y, nullptr, nullptr, nullptr));                // :630-632
   // src = bypass(src_orig, BiasNorm(src))  (:635-637), in place on X
-  ZV_K(biasnorm_bypass(ws.Y, X, ly.norm_bias, ly.log_scale, ly.bypass_scale, M, D, X, ws.shadow, s));
+  ZV_K(KC_BIASNORM, (double)M * D * 14, s,
+       biasnorm_bypass(ws.Y, X, ly.norm_bias, ly.log_scale, ly.bypass_scale, M, D, X, ws.shadow, s));
   return 0;
 }
 
@@ -402,9 +460,11 @@ int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t
       e.err = "this network needs a time step";
       return 950;
     }
-    ZV_K(time_embed(ta.t, ta.t_stride, ta.g, ta.g_stride, nb, td, net.te_w0, net.te_b0, net.te_w2, net.te_b2,
+    ZV_K(KC_TIME_EMBED, 4.0 * (4 * td * td + td), s,
+         time_embed(ta.t, ta.t_stride, ta.g, ta.g_stride, nb, td, net.te_w0, net.te_b0, net.te_w2, net.te_b2,
                     net.te_wg, ws.te_a, s));
-    ZV_K(small_linear(ws.te_a, net.te_proj_w, net.te_proj_b, nb, net.N_te, td, ws.te_out, s));
+    ZV_K(KC_TIME_EMBED, 4.0 * ((double)net.N_te * td + (double)nb * (net.N_te + td)), s,
+         small_linear(ws.te_a, net.te_proj_w, net.te_proj_b, nb, net.N_te, td, ws.te_out, s));
   }
   for (Stack& st : net.stacks) {
     const int ds = st.ds;
@@ -413,8 +473,9 @@ int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t
     const uint8_t* mask = mask_dev;
     if (ds != 1) {
       uint8_t* msub = mask_dev ? ws.mask[ds == 2 ? 1 : 2] : nullptr;
-      g_launch_count += msub ? 2 : 1;
-      ZV_TRY(downsample(ws.X, st.ds_w, nb, T, D, ds, ws.Xs, ws.shadow, msub, mask_dev, s));
+      g_launch_count += msub ? 1 : 0;  // mask subsampling rides in the same launcher
+      ZV_K(KC_RESAMPLE, (double)nb * D * (4.0 * T + 6.0 * L), s,
+           downsample(ws.X, st.ds_w, nb, T, D, ds, ws.Xs, ws.shadow, msub, mask_dev, s));
       X = ws.Xs, mask = msub;
     }
     const float* te_stack = net.use_time ? ws.te_out + st.te_off : nullptr;
@@ -423,7 +484,9 @@ int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t
       // row pitch of the time-embedding projections is N_te for every layer of this net
       ZV_TRY(layer_forward(e, net, ws, ly, st.kernel, X, nb, L, mask, te_stack, te_ff1, s));
     }
-    if (ds != 1) ZV_K(upsample_combine(ws.X, ws.Xs, st.out_comb_scale, nb, T, L, D, ds, ws.shadow, s));
+    if (ds != 1)
+      ZV_K(KC_RESAMPLE, (double)nb * D * (10.0 * T + 4.0 * L), s,
+           upsample_combine(ws.X, ws.Xs, st.out_comb_scale, nb, T, L, D, ds, ws.shadow, s));
   }
   ep = EpiParams();
   ep.L = T, ep.out_f32 = out, ep.ld_f32 = net.out_dim;

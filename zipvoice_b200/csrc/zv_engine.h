@@ -23,7 +23,7 @@ struct HostTensor {
 struct Lin {
   __nv_bfloat16* w = nullptr;
   float* bias = nullptr;  // accumulator-column order, length N
-  int N = 0, N_pad = 0, K = 0, ldw = 0, block_n = 0, mode = 0, gate_cols = 0;
+  int N = 0, N_pad = 0, K = 0, K_valid = 0, ldw = 0, block_n = 0, mode = 0, gate_cols = 0;
 };
 
 struct Layer {
@@ -72,8 +72,32 @@ struct Workspace {
   std::vector<void*> allocs;
 };
 
+// Per-kernel-class device timing (CUDA events on the launching stream), enabled by zv_prof_enable.
+// work = algorithmic FLOPs (tensor-bound classes) or algorithmic bytes (HBM-bound classes) of a launch.
+enum KClass : int {
+  KC_GEMM_BIAS = 0, KC_GEMM_SWOOSHL, KC_GEMM_GLU, KC_GEMM_NONLIN, KC_GEMM_RESIDUAL, KC_GEMM_F32,
+  KC_ATTN_SELF, KC_ATTN_NONLIN, KC_DWCONV, KC_BIASNORM, KC_RESAMPLE, KC_PACK, KC_CFG_EULER, KC_TIME_EMBED,
+  KC_TEXT, KC_FBANK, KC_VOCODER_ELEM, KC_COUNT
+};
+const char* kclass_name(int c);
+bool kclass_is_tensor(int c);
+struct Prof {
+  bool on = false;
+  struct Rec { int cls; double work; cudaEvent_t a, b; };
+  std::vector<Rec> recs;
+  std::vector<cudaEvent_t> pool;
+  size_t used = 0;
+  cudaEvent_t get();
+  void begin(int cls, double work, cudaStream_t s);
+  void end(cudaStream_t s);
+  // synchronises, accumulates elapsed time per class and resets the record list
+  int read(double* ms, double* work, long long* launches);
+  void release();
+};
+
 struct Engine {
   zv_config cfg;
+  Prof prof;
   std::map<std::string, HostTensor> raw;
   bool finalized = false;
   Net fm, text;

@@ -155,5 +155,19 @@ class Engine:
                                                    _ptr(out), _ptr(mask), _stream(self.device)))
         return out, mask.bool()
 
+    def prof_enable(self, on: bool = True):
+        self._check(self.lib.zv_prof_enable(self._h, int(on)))
+
+    def prof_read(self):
+        """-> list of dicts {name, tensor, ms, work, launches} per kernel class (device is synchronised)."""
+        n = self.lib.zv_prof_num_classes()
+        ms, work, cnt = (C.c_double * n)(), (C.c_double * n)(), (C.c_longlong * n)()
+        self._check(self.lib.zv_prof_read(self._h, ms, work, cnt))
+        return [dict(name=self.lib.zv_prof_class_name(i).decode(), tensor=bool(self.lib.zv_prof_class_is_tensor(i)),
+                     ms=ms[i], work=work[i], launches=int(cnt[i])) for i in range(n) if cnt[i]]
+
+    def launch_count_reset(self):
+        self.lib.zv_launch_count_reset()
+
     def launch_count(self) -> int:
         return int(self.lib.zv_launch_count())
