@@ -31,7 +31,7 @@ long long g_launch_count = 0;
   } while (0)
 
 static const char* kNames[KC_COUNT] = {"gemm_bias", "gemm_swooshl", "gemm_glu", "gemm_nonlin", "gemm_residual",
-                                       "gemm_f32", "attn_self", "attn_nonlin", "dwconv_swooshr", "biasnorm_bypass",
+                                       "gemm_f32", "gemm_gelu", "attn_self", "attn_nonlin", "dwconv_swooshr", "biasnorm_bypass",
                                        "resample", "pack_input", "cfg_euler", "time_embed", "text_glue", "fbank",
                                        "vocoder_elem"};
 const char* kclass_name(int c) { return c >= 0 && c < KC_COUNT ? kNames[c] : "?"; }
@@ -68,7 +68,7 @@ void Prof::release() {
   pool.clear(), recs.clear(), used = 0;
 }
 
-static int dev_alloc(Engine& e, std::vector<void*>& pool, void** p, size_t bytes) {
+int dev_alloc(Engine& e, std::vector<void*>& pool, void** p, size_t bytes) {
   if (bytes == 0) bytes = 16;
   cudaError_t rc = cudaMalloc(p, bytes);
   if (rc != cudaSuccess) {
@@ -127,14 +127,12 @@ static inline uint16_t f2bf(float f) {
   return (uint16_t)(u >> 16);
 }
 
-static int pack_linear(Engine& e, const std::string& name, int mode, Lin* lin, int k_pad_to = 0) {
-  const HostTensor* w = find(e, name + ".weight");
-  if (!w) return 940;
-  const int N = (int)w->shape[0], K = (int)w->shape[1];
+int pack_linear_host(Engine& e, const float* w, const float* bias_in, int N, int K, int mode, Lin* lin, int k_pad_to,
+                     const float* row_scale) {
   lin->N = N, lin->K = k_pad_to ? k_pad_to : K, lin->K_valid = K, lin->mode = mode;
   lin->gate_cols = mode == EPI_NONLIN_BF16 ? 2 * (N / 3) : 0;
   if ((mode == EPI_GLU_BF16 && (N / 2) % 16) || (mode == EPI_NONLIN_BF16 && (N / 3) % 16)) {
-    e.err = "fused epilogue needs channel counts that are multiples of 16: " + name;
+    e.err = "fused epilogue needs channel counts that are multiples of 16";
     return 941;
   }
   lin->block_n = gemm_pick_block_n(N, mode, lin->gate_cols);
@@ -143,18 +141,28 @@ static int pack_linear(Engine& e, const std::string& name, int mode, Lin* lin, i
   const std::vector<int> perm = row_perm(mode, N);
   std::vector<uint16_t> wb((size_t)lin->N_pad * lin->ldw, 0);
   for (int n = 0; n < N; ++n) {
-    const float* src = w->data.data() + (size_t)perm[n] * K;
+    const float* src = w + (size_t)perm[n] * K;
+    const float sc = row_scale ? row_scale[perm[n]] : 1.0f;
     uint16_t* dst = wb.data() + (size_t)n * lin->ldw;
-    for (int k = 0; k < K; ++k) dst[k] = f2bf(src[k]);
+    for (int k = 0; k < K; ++k) dst[k] = f2bf(src[k] * sc);
   }
   ZV_TRY(dev_alloc(e, e.weight_allocs, (void**)&lin->w, wb.size() * 2));
   ZV_TRY((int)cudaMemcpy(lin->w, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
-  std::vector<float> bias(N, 0.f);
-  auto it = e.raw.find(name + ".bias");
-  if (it != e.raw.end())
-    for (int n = 0; n < N; ++n) bias[n] = it->second.data[perm[n]];
+  std::vector<float> bias(lin->N_pad, 0.f);
+  if (bias_in)
+    for (int n = 0; n < N; ++n) bias[n] = bias_in[perm[n]] * (row_scale ? row_scale[perm[n]] : 1.0f);
   ZV_TRY(upload_f32(e, bias, &lin->bias));
   return 0;
+}
+
+static int pack_linear(Engine& e, const std::string& name, int mode, Lin* lin, int k_pad_to = 0) {
+  const HostTensor* w = find(e, name + ".weight");
+  if (!w) return 940;
+  auto it = e.raw.find(name + ".bias");
+  int rc = pack_linear_host(e, w->data.data(), it != e.raw.end() ? it->second.data.data() : nullptr, (int)w->shape[0],
+                            (int)w->shape[1], mode, lin, k_pad_to, nullptr);
+  if (rc && e.err.find(name) == std::string::npos) e.err += ": " + name;
+  return rc;
 }
 
 static int build_layer(Engine& e, Net& net, const std::string& p, int kernel, Layer* L) {
@@ -335,7 +343,7 @@ int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
   return 0;
 }
 
-static int run_gemm(Engine& e, const Lin& lin, const __nv_bfloat16* A, int lda, int M, EpiParams ep, cudaStream_t s) {
+int run_gemm(Engine& e, const Lin& lin, const __nv_bfloat16* A, int lda, int M, EpiParams ep, cudaStream_t s) {
   GemmPlan p;
   p.M = M, p.N_pad = lin.N_pad, p.K = lin.K, p.lda = lda, p.ldw = lin.ldw, p.block_n = lin.block_n;
   ep.mode = lin.mode, ep.M = M, ep.N = lin.N, ep.gate_cols = lin.gate_cols, ep.bias = lin.bias;

@@ -75,7 +75,7 @@ struct Workspace {
 // Per-kernel-class device timing (CUDA events on the launching stream), enabled by zv_prof_enable.
 // work = algorithmic FLOPs (tensor-bound classes) or algorithmic bytes (HBM-bound classes) of a launch.
 enum KClass : int {
-  KC_GEMM_BIAS = 0, KC_GEMM_SWOOSHL, KC_GEMM_GLU, KC_GEMM_NONLIN, KC_GEMM_RESIDUAL, KC_GEMM_F32,
+  KC_GEMM_BIAS = 0, KC_GEMM_SWOOSHL, KC_GEMM_GLU, KC_GEMM_NONLIN, KC_GEMM_RESIDUAL, KC_GEMM_F32, KC_GEMM_GELU,
   KC_ATTN_SELF, KC_ATTN_NONLIN, KC_DWCONV, KC_BIASNORM, KC_RESAMPLE, KC_PACK, KC_CFG_EULER, KC_TIME_EMBED,
   KC_TEXT, KC_FBANK, KC_VOCODER_ELEM, KC_COUNT
 };
@@ -125,5 +125,11 @@ struct TimeArgs {
 int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t* mask_dev, const TimeArgs& ta,
                 float* out, cudaStream_t s);
 int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T);
+// Shared with the vocoder (zv_audio.cu): pack one Linear from host fp32 (rows optionally permuted for the
+// fused epilogue of `mode`), and launch it.  row_scale (optional, [N]) multiplies weight rows and bias.
+int pack_linear_host(Engine& e, const float* w, const float* bias, int N, int K, int mode, Lin* lin, int k_pad_to,
+                     const float* row_scale);
+int run_gemm(Engine& e, const Lin& lin, const __nv_bfloat16* A, int lda, int M, EpiParams ep, cudaStream_t s);
+int dev_alloc(Engine& e, std::vector<void*>& pool, void** p, size_t bytes);
 
 }  // namespace zv

@@ -2,10 +2,18 @@
 //   warp 0      : TMA producer (one lane) -- A tile 128x64, W tile block_n x 64, SWIZZLE_128B
 //   warp 1      : MMA issuer (one lane)   -- tcgen05.mma kind::f16, M=128, N=block_n, K=16 x4 per stage
 //   warp 2      : TMEM allocator (512 columns = 2 accumulator stages of <=256 fp32 columns)
-//   warps 4..7  : epilogue: tcgen05.ld 32 lanes x 32 columns -> registers -> fused math -> global
+//   warps 4..11 : epilogue, two column groups x four TMEM lane quarters.  A group walks the 32-column
+//                 chunks of the accumulator tile (chunk c -> group c % 2): tcgen05.ld 32 lanes x 32 columns
+//                 -> registers -> fused math (MUFU ex2/lg2/tanh/rcp) -> swizzled shared-memory staging ->
+//                 one elected thread issues a TMA store (rows / columns outside the tensor are clipped by
+//                 the tensor map).  EPI_RESIDUAL also TMA-loads the fp32 residual chunk one chunk ahead and
+//                 updates it in place in shared memory.
 // Persistent: grid = min(#tiles, #SMs); tile t -> (m_blk = t / n_tiles, n_blk = t % n_tiles).
 #include <cuda.h>
 #include <stdio.h>
+#include <string.h>
+
+#include <unordered_map>
 
 #include "zv_common.cuh"
 #include "zv_gemm.h"
@@ -16,7 +24,6 @@ static constexpr int BM = 128;
 static constexpr int BK = 64;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
 static constexpr int ACC_STAGE_COLS = 256;
-static constexpr int GEMM_THREADS = 256;
 
 // One row, 32 consecutive accumulator columns starting at n0 (n0 % 32 == 0).
 template <int MODE>
@@ -33,11 +40,15 @@ ZV_DEVINL void epi_apply(const EpiParams& ep, int m, int b, int n0, const float 
     }
     v[i] = x;
   }
-  if (MODE == EPI_BIAS_BF16 || MODE == EPI_SWOOSHL_BF16) {
+  if (MODE == EPI_BIAS_BF16 || MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GELU_BF16) {
     __nv_bfloat16* o = ep.out_bf16 + (size_t)m * ep.ld_bf16 + n0;
     if (MODE == EPI_SWOOSHL_BF16) {
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] = swoosh_l(v[i]);
+    }
+    if (MODE == EPI_GELU_BF16) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
     }
     if (nvalid == 32) {
 #pragma unroll
@@ -162,33 +173,96 @@ ZV_DEVINL void epi_apply(const EpiParams& ep, int m, int b, int n0, const float 
   }
 }
 
+static constexpr int NCG = 2;                  // epilogue column groups
+static constexpr int EPI_WARPS = 4 * NCG;
+static constexpr int STG_BF16_BYTES = BM * 64;   // 128 rows x 32 bf16
+static constexpr int STG_F32_BYTES = BM * 128;   // 128 rows x 32 fp32
+
+struct GemmMaps {
+  CUtensorMap A, W;
+  CUtensorMap O0;  // bf16 output (box 32 cols, SWIZZLE_64B; GLU / gated NONLIN: box 16 cols, SWIZZLE_32B)
+  CUtensorMap O1;  // EPI_NONLIN plain part: bf16 (box 32, SWIZZLE_64B); EPI_RESIDUAL: fp32 out (box 32, SWIZZLE_128B)
+  CUtensorMap R;   // EPI_RESIDUAL: fp32 residual input (box 32, SWIZZLE_128B)
+};
+
 struct GemmSmemTail {
   uint64_t full[8];
   uint64_t empty[8];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
+  uint64_t rbar[NCG][2];
   uint32_t tmem_base;
 };
 
+// bytes of epilogue staging per column group
+__host__ __device__ constexpr int stg_group_bytes(int mode) {
+  return mode == EPI_RESIDUAL ? 2 * STG_F32_BYTES + STG_BF16_BYTES : (mode == EPI_F32 ? 0 : 2 * STG_BF16_BYTES);
+}
+
+// 32 fp32 values of one row -> 32 bf16 in a 64-byte staging row (SWIZZLE_64B pattern of the TMA store)
+ZV_DEVINL void stage_row_bf16x32(uint8_t* stg, int r, const float (&v)[32]) {
+  const int x = (r >> 1) & 3;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint4 p = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                         pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+    *reinterpret_cast<uint4*>(stg + r * 64 + ((j ^ x) << 4)) = p;
+  }
+}
+// 16 fp32 values -> 16 bf16 in a 32-byte staging row (SWIZZLE_32B)
+ZV_DEVINL void stage_row_bf16x16(uint8_t* stg, int r, const float (&v)[16]) {
+  const int x = (r >> 2) & 1;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    uint4 p = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                         pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+    *reinterpret_cast<uint4*>(stg + r * 32 + ((j ^ x) << 4)) = p;
+  }
+}
+
+// acc + bias (+ per-batch row bias) for one 32-column chunk; vector loads when the chunk is full
+ZV_DEVINL void add_bias32(float (&v)[32], const float* __restrict__ bias, const float* __restrict__ rowb, int n0,
+                          int N) {
+  if (n0 + 32 <= N) {
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + n0 + i));
+      v[i] += bb.x, v[i + 1] += bb.y, v[i + 2] += bb.z, v[i + 3] += bb.w;
+    }
+    if (rowb) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        const float4 bb = __ldg(reinterpret_cast<const float4*>(rowb + n0 + i));
+        v[i] += bb.x, v[i + 1] += bb.y, v[i + 2] += bb.z, v[i + 3] += bb.w;
+      }
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (n0 + i < N) v[i] += __ldg(bias + n0 + i) + (rowb ? __ldg(rowb + n0 + i) : 0.f);
+  }
+}
+
 template <int MODE>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, int m_tiles,
-               int n_tiles, int k_blocks, int block_n, int stages, EpiParams ep) {
+__global__ void __launch_bounds__(128 + 32 * EPI_WARPS, 1)
+gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, int k_blocks, int block_n, int stages,
+               EpiParams ep) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // carve: [stages x A 16 KB][stages x W block_n*128 B][tail]
+  // carve: [stages x A 16 KB][stages x W block_n*128 B][NCG x epilogue staging][tail]
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int w_stage_bytes = block_n * BK * 2;
   uint8_t* sA = smem;
   uint8_t* sW = smem + stages * A_STAGE_BYTES;
-  GemmSmemTail* tail = reinterpret_cast<GemmSmemTail*>(sW + stages * w_stage_bytes);
+  uint8_t* sStg = sW + stages * w_stage_bytes;
+  GemmSmemTail* tail = reinterpret_cast<GemmSmemTail*>(sStg + NCG * stg_group_bytes(MODE));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_tiles = m_tiles * n_tiles;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&maps.A);
+    tma_prefetch_desc(&maps.W);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < stages; ++i) {
@@ -197,8 +271,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tail->tmem_full[i], 1);
-      mbar_init(&tail->tmem_empty[i], 128);
+      mbar_init(&tail->tmem_empty[i], EPI_WARPS);
     }
+    for (int g = 0; g < NCG; ++g) mbar_init(&tail->rbar[g][0], 1), mbar_init(&tail->rbar[g][1], 1);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(&tail->tmem_base, 512);
@@ -217,8 +292,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&tail->empty[stage], phase ^ 1);
           mbar_arrive_expect_tx(&tail->full[stage], tx);
-          tma_load_2d(sA + stage * A_STAGE_BYTES, &tmA, &tail->full[stage], kb * BK, m_blk * BM);
-          tma_load_2d(sW + stage * w_stage_bytes, &tmW, &tail->full[stage], kb * BK, n_blk * block_n);
+          tma_load_2d(sA + stage * A_STAGE_BYTES, &maps.A, &tail->full[stage], kb * BK, m_blk * BM);
+          tma_load_2d(sW + stage * w_stage_bytes, &maps.W, &tail->full[stage], kb * BK, n_blk * block_n);
           if (++stage == stages) stage = 0, phase ^= 1;
         }
       }
@@ -252,30 +327,149 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     __syncwarp();
   } else if (warp >= 4) {
-    const int q = warp - 4;  // TMEM lane quarter == warp % 4
+    const int q = warp & 3;            // TMEM lane quarter == warp % 4
+    const int cg = (warp - 4) >> 2;    // column group
+    const int r = q * 32 + lane;       // row within the tile
+    const bool leader = (q == 0 && lane == 0);
+    const int bar_id = 1 + cg;
+    uint8_t* stg = sStg + cg * stg_group_bytes(MODE);
+    const int nchunks = block_n >> 5;
+    uint32_t nq = 0;  // chunks processed by this group (selects the staging buffer / residual barrier phase)
+
+    // EPI_RESIDUAL: the leader prefetches the first residual chunk of this group
+    if (MODE == EPI_RESIDUAL && leader && blockIdx.x < total_tiles && cg < nchunks) {
+      const int m_blk = blockIdx.x / n_tiles, n_blk = blockIdx.x % n_tiles;
+      mbar_arrive_expect_tx(&tail->rbar[cg][0], STG_F32_BYTES);
+      tma_load_2d(stg, &maps.R, &tail->rbar[cg][0], n_blk * block_n + cg * 32, m_blk * BM);
+    }
     int it = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
       const int m_blk = t / n_tiles, n_blk = t % n_tiles;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
+      const int m = m_blk * BM + r;
+      const int mm = min(m, ep.M - 1);
+      const int b = mm / ep.L;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * ACC_STAGE_COLS;
+      const float* rowb = (MODE != EPI_RESIDUAL && ep.rowbias) ? ep.rowbias + (size_t)b * ep.bias_ld : nullptr;
       mbar_wait(&tail->tmem_full[as], aphase);
       tc_fence_after();
-      const int m = m_blk * BM + q * 32 + lane;
-      const int b = m / ep.L;
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * ACC_STAGE_COLS;
-      for (int c = 0; c < block_n; c += 32) {
-        uint32_t r0[16], r1[16];
-        tmem_ld16(taddr + c, r0);
-        tmem_ld16(taddr + c + 16, r1);
-        tmem_ld_wait();
-        float acc[32];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) acc[i] = __uint_as_float(r0[i]), acc[16 + i] = __uint_as_float(r1[i]);
-        epi_apply<MODE>(ep, m, b, n_blk * block_n + c, acc);
+      if (cg >= nchunks) {  // this group owns no chunk of the tile: release the accumulator right away
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tail->tmem_empty[as]);
       }
-      tc_fence_before();
-      mbar_arrive(&tail->tmem_empty[as]);
+      for (int c = cg; c < nchunks; c += NCG, ++nq) {
+        const int n0 = n_blk * block_n + c * 32;
+        uint32_t raw[32];
+        tmem_ld32(taddr + c * 32, raw);
+        tmem_ld_wait();
+        if (c + NCG >= nchunks) {  // last accumulator read of this tile by this warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tail->tmem_empty[as]);
+        }
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
+
+        if (MODE == EPI_F32) {
+          epi_apply<EPI_F32>(ep, m, b, n0, v);
+          continue;
+        }
+        if (MODE == EPI_RESIDUAL) {
+          const int sb = nq & 1;
+          float* fb = reinterpret_cast<float*>(stg + sb * STG_F32_BYTES);
+          uint8_t* shadow = stg + 2 * STG_F32_BYTES;
+          if (leader) {
+            // the previous chunk's stores must have finished reading buffer sb^1 and the shadow buffer
+            tma_store_wait_read<0>();
+            // prefetch the residual of the next chunk of this group (possibly in the next tile)
+            int c2 = c + NCG, t2 = t;
+            if (c2 >= nchunks) c2 = cg, t2 = t + gridDim.x;
+            if (t2 < total_tiles) {
+              const int mb2 = t2 / n_tiles, nb2 = t2 % n_tiles;
+              mbar_arrive_expect_tx(&tail->rbar[cg][sb ^ 1], STG_F32_BYTES);
+              tma_load_2d(stg + (sb ^ 1) * STG_F32_BYTES, &maps.R, &tail->rbar[cg][sb ^ 1], nb2 * block_n + c2 * 32,
+                          mb2 * BM);
+            }
+          }
+          add_bias32(v, ep.bias, ep.resbias ? ep.resbias + (size_t)b * ep.bias_ld : nullptr, n0, ep.N);
+          mbar_wait(&tail->rbar[cg][sb], (nq >> 1) & 1);
+          const int x = r & 7;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 rr = *reinterpret_cast<const float4*>(fb + r * 32 + ((j ^ x) << 2));
+            v[4 * j] += rr.x, v[4 * j + 1] += rr.y, v[4 * j + 2] += rr.z, v[4 * j + 3] += rr.w;
+          }
+          if (ep.orig) {
+            const float* og = ep.orig + (size_t)mm * ep.ld_f32 + n0;
+            if (n0 + 32 <= ep.N) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 4) {
+                const float4 oo = *reinterpret_cast<const float4*>(og + i);
+                const float4 bs = __ldg(reinterpret_cast<const float4*>(ep.bypass_scale + n0 + i));
+                v[i] = oo.x + (v[i] - oo.x) * bs.x, v[i + 1] = oo.y + (v[i + 1] - oo.y) * bs.y;
+                v[i + 2] = oo.z + (v[i + 2] - oo.z) * bs.z, v[i + 3] = oo.w + (v[i + 3] - oo.w) * bs.w;
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (n0 + i < ep.N) v[i] = og[i] + (v[i] - og[i]) * ep.bypass_scale[n0 + i];
+            }
+          }
+          __syncwarp();
+          named_bar_sync(bar_id, 128);  // shadow buffer free (leader waited), everyone has read its row
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(fb + r * 32 + ((j ^ x) << 2)) =
+                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          if (ep.out_bf16) stage_row_bf16x32(shadow, r, v);
+          fence_proxy_async_smem();
+          named_bar_sync(bar_id, 128);
+          if (leader) {
+            tma_store_2d(&maps.O1, fb, n0, m_blk * BM);
+            if (ep.out_bf16) tma_store_2d(&maps.O0, shadow, n0, m_blk * BM);
+            tma_store_commit();
+          }
+          continue;
+        }
+        // ---- bf16 outputs
+        add_bias32(v, ep.bias, rowb, n0, ep.N);
+        uint8_t* sbuf = stg + (nq & 1) * STG_BF16_BYTES;
+        const bool gated = (MODE == EPI_GLU_BF16) || (MODE == EPI_NONLIN_BF16 && n0 < ep.gate_cols);
+        float o16[16];
+        if (MODE == EPI_SWOOSHL_BF16) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = swoosh_l_fast(v[i]);
+        } else if (MODE == EPI_GELU_BF16) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+        } else if (MODE == EPI_GLU_BF16) {
+          const bool masked = ep.mask && ep.mask[mm];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) o16[i] = masked ? 0.0f : v[i] * sigmoid_fast(v[16 + i]);
+        } else if (MODE == EPI_NONLIN_BF16) {
+          if (gated) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) o16[i] = v[16 + i] * tanh_approx(v[i]);
+          }
+        }
+        if (leader) tma_store_wait_read<1>();  // the store that last used this staging buffer has read it
+        __syncwarp();
+        named_bar_sync(bar_id, 128);
+        if (gated) stage_row_bf16x16(sbuf, r, o16);
+        else stage_row_bf16x32(sbuf, r, v);
+        fence_proxy_async_smem();
+        named_bar_sync(bar_id, 128);
+        if (leader) {
+          if (MODE == EPI_NONLIN_BF16 && !gated) tma_store_2d(&maps.O1, sbuf, n0 - ep.gate_cols, m_blk * BM);
+          else tma_store_2d(&maps.O0, sbuf, gated ? (n0 >> 1) : n0, m_blk * BM);
+          tma_store_commit();
+        }
+      }
     }
+    if (leader) tma_store_wait_all<0>();
   }
   tc_fence_before();
   __syncthreads();
@@ -319,19 +513,55 @@ static PFN_encodeTiled get_encode_fn() {
   return fn;
 }
 
-// bf16 row-major [rows][cols] with row pitch ld (elements); box = [box_rows][64], SWIZZLE_128B.
-static int make_tmap_bf16(CUtensorMap* tm, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
-                          uint32_t box_rows) {
+// Row-major [rows][cols] tensor with row pitch ld (elements) -> tiled map with box [box_rows][box_cols].
+// Maps are cached by their full description: the workspace pointers are stable, so after the first
+// NFE no driver call is made on the launch path.
+struct TmapKey {
+  const void* ptr;
+  uint64_t rows, cols, ld;
+  uint32_t box_rows, box_cols;
+  int dtype, swizzle;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows &&
+           box_cols == o.box_cols && dtype == o.dtype && swizzle == o.swizzle;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    uint64_t h = reinterpret_cast<uint64_t>(k.ptr) * 0x9E3779B97F4A7C15ull;
+    h ^= (k.rows + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2));
+    h ^= (k.cols * 31 + k.ld * 131 + k.box_rows * 7 + k.box_cols * 3 + k.dtype * 1009 + k.swizzle * 9176 +
+          (h << 6) + (h >> 2));
+    return (size_t)h;
+  }
+};
+static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
+
+static int make_tmap(CUtensorMap* tm, const void* ptr, int dtype /*0 bf16, 1 fp32*/, uint64_t rows, uint64_t cols,
+                     uint64_t ld, uint32_t box_rows, uint32_t box_cols, int swizzle /*32, 64, 128*/) {
+  const TmapKey key{ptr, rows, cols, ld, box_rows, box_cols, dtype, swizzle};
+  auto it = g_tmap_cache.find(key);
+  if (it != g_tmap_cache.end()) {
+    *tm = it->second;
+    return 0;
+  }
   PFN_encodeTiled enc = get_encode_fn();
   if (!enc) return 901;
+  const uint64_t esz = dtype == 0 ? 2 : 4;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld * esz) & 15)) return 906;  // TMA alignment rules
   cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {ld * 2};
-  cuuint32_t box[2] = {64, box_rows};
+  cuuint64_t strides[1] = {ld * esz};
+  cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : 902;
+  const CUtensorMapSwizzle sw = swizzle == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                               : (swizzle == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+  CUresult r = enc(tm, dtype == 0 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                   const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return 902;
+  if (g_tmap_cache.size() > 4096) g_tmap_cache.clear();
+  g_tmap_cache.emplace(key, *tm);
+  return 0;
 }
 
 int gemm_pick_block_n(int n_valid, int mode, int gate_cols) {
@@ -367,17 +597,34 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
   }
-  CUtensorMap tmA, tmW;
-  int rc = make_tmap_bf16(&tmA, A, (uint64_t)p.M, (uint64_t)p.K, (uint64_t)p.lda, BM);
+  GemmMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  int rc = make_tmap(&maps.A, A, 0, (uint64_t)p.M, (uint64_t)p.K, (uint64_t)p.lda, BM, 64, 128);
   if (rc) return rc;
-  rc = make_tmap_bf16(&tmW, W, (uint64_t)p.N_pad, (uint64_t)p.K, (uint64_t)p.ldw, (uint32_t)p.block_n);
+  rc = make_tmap(&maps.W, W, 0, (uint64_t)p.N_pad, (uint64_t)p.K, (uint64_t)p.ldw, (uint32_t)p.block_n, 64, 128);
+  if (rc) return rc;
+  const uint64_t Mu = (uint64_t)ep.M;
+  if (MODE == EPI_BIAS_BF16 || MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GELU_BF16) {
+    rc = make_tmap(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, BM, 32, 64);
+  } else if (MODE == EPI_GLU_BF16) {
+    rc = make_tmap(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N / 2, (uint64_t)ep.ld_bf16, BM, 16, 32);
+  } else if (MODE == EPI_NONLIN_BF16) {
+    rc = make_tmap(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.gate_cols / 2, (uint64_t)ep.ld_bf16, BM, 16, 32);
+    if (!rc && ep.N > ep.gate_cols)
+      rc = make_tmap(&maps.O1, ep.out2_bf16, 0, Mu, (uint64_t)(ep.N - ep.gate_cols), (uint64_t)ep.ld2_bf16, BM, 32, 64);
+  } else if (MODE == EPI_RESIDUAL) {
+    rc = make_tmap(&maps.O1, ep.out_f32, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, BM, 32, 128);
+    if (!rc) rc = make_tmap(&maps.R, ep.res, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, BM, 32, 128);
+    if (!rc && ep.out_bf16)
+      rc = make_tmap(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, BM, 32, 64);
+  }
   if (rc) return rc;
   const int w_stage = p.block_n * BK * 2;
-  const int budget = 227 * 1024 - 1024 - (int)sizeof(GemmSmemTail);
-  int stages = budget / (A_STAGE_BYTES + w_stage);
+  const int fixed = 1024 + (int)sizeof(GemmSmemTail) + NCG * stg_group_bytes(MODE);
+  int stages = (227 * 1024 - fixed) / (A_STAGE_BYTES + w_stage);
   if (stages > 8) stages = 8;
   if (stages < 2) return 903;
-  const int smem = stages * (A_STAGE_BYTES + w_stage) + (int)sizeof(GemmSmemTail) + 1024;
+  const int smem = stages * (A_STAGE_BYTES + w_stage) + fixed;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(gemm_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -387,8 +634,8 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
   const int n_tiles = p.N_pad / p.block_n;
   const int k_blocks = (p.K + BK - 1) / BK;
   const int grid = min(m_tiles * n_tiles, g_num_sms);
-  gemm_tc_kernel<MODE><<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmW, m_tiles, n_tiles, k_blocks, p.block_n, stages,
-                                                             ep);
+  gemm_tc_kernel<MODE><<<grid, 128 + 32 * EPI_WARPS, smem, stream>>>(maps, m_tiles, n_tiles, k_blocks, p.block_n,
+                                                                      stages, ep);
   return (int)cudaGetLastError();
 }
 
@@ -403,6 +650,7 @@ int gemm_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const GemmPlan& 
     case EPI_NONLIN_BF16: return launch_mode<EPI_NONLIN_BF16>(A, W, plan, ep, impl, stream);
     case EPI_RESIDUAL: return launch_mode<EPI_RESIDUAL>(A, W, plan, ep, impl, stream);
     case EPI_F32: return launch_mode<EPI_F32>(A, W, plan, ep, impl, stream);
+    case EPI_GELU_BF16: return launch_mode<EPI_GELU_BF16>(A, W, plan, ep, impl, stream);
   }
   return 905;
 }

@@ -15,6 +15,7 @@ enum EpiMode : int {
                          // cols >= gate_cols: out2 = acc + bias                     (NonlinAttention in_proj)
   EPI_RESIDUAL = 4,      // v = res + acc + bias (+ resbias[b]); optional bypass vs orig; writes fp32 + bf16
   EPI_F32 = 5,           // out_f32 = acc + bias (+ rowbias[b])
+  EPI_GELU_BF16 = 6,     // out_bf16 = GELU_erf(acc + bias)                          (Vocos ConvNeXt pwconv1)
 };
 
 struct EpiParams {
