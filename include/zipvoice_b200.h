@@ -84,8 +84,10 @@ int zv_text_condition(void* handle, const float* embed, const int64_t* tokens_le
 int zv_fbank(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out, void* stream);
 
 /* Vocos.decode (third-party `vocos`; call site bin/infer_zipvoice.py:378): mel (B,100,T) -> wav (B, 256*(T-1)).
- * Weights are set through zv_set_weight with the "vocoder." prefix. */
-int zv_vocos_decode(void* handle, const float* mel, int B, int T, float* wav_out, void* stream);
+ * Weights are set through zv_set_weight with the "vocoder." prefix (vocos checkpoint names: backbone.*,
+ * head.out.*).  lens (B) int64 valid frames per row, or NULL for full rows: frames >= lens[b] are treated
+ * as absent (zero-padded convolutions, as if each utterance were decoded alone) and their samples are 0. */
+int zv_vocos_decode(void* handle, const float* mel, const int64_t* lens, int B, int T, float* wav_out, void* stream);
 
 /* Test / bench hooks (not part of the reference-facing surface). */
 int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int gate_cols, const float* A_f32,

@@ -100,6 +100,7 @@ void zv_destroy(void* handle) {
   if (!e) return;
   cudaDeviceSynchronize();
   e->prof.release();
+  audio_destroy(*e);
   for (void* p : e->weight_allocs) cudaFree(p);
   for (void* p : e->ws_fm.allocs) cudaFree(p);
   for (void* p : e->ws_text.allocs) cudaFree(p);

@@ -49,10 +49,11 @@ struct AttnSmem {
   bf16 v[2][BKV][DV + 8];
   float4 e[2][EWIN];
   uint8_t m[2][BKV];
+  int mflag[2];  // != 0 if the key tile holds padded / out-of-range keys (slow masking path)
 };
 
 template <int DV>
-__global__ void __launch_bounds__(256, 1) attn_kernel(AttnParams p, int chunks, int dv_valid) {
+__global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParams p, int chunks, int dv_valid) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   AttnSmem<DV>& sm = *reinterpret_cast<AttnSmem<DV>*>(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -107,9 +108,13 @@ __global__ void __launch_bounds__(256, 1) attn_kernel(AttnParams p, int chunks, 
       const bool ok = rr >= 0 && rr < R;
       cp_async16(&sm.e[buf][tid], E + (ok ? rr : 0), ok);
     }
-    if (tid < BKV) {
-      const int j = j0 + tid;
-      sm.m[buf][tid] = (j < L) ? (mask ? mask[j] : 0) : 2;  // 2 = beyond the sequence
+    if (tid < 32) {  // warp 0: two keys per lane
+      const int ja = j0 + tid, jb = j0 + tid + 32;
+      const uint8_t ka = (ja < L) ? (mask ? mask[ja] : 0) : 2;  // 2 = beyond the sequence
+      const uint8_t kb = (jb < L) ? (mask ? mask[jb] : 0) : 2;
+      sm.m[buf][tid] = ka, sm.m[buf][tid + 32] = kb;
+      const unsigned any = __ballot_sync(0xffffffffu, (ka | kb) != 0);
+      if (tid == 0) sm.mflag[buf] = any != 0;
     }
   };
   load_tile(0, 0);
@@ -154,21 +159,39 @@ __global__ void __launch_bounds__(256, 1) attn_kernel(AttnParams p, int chunks, 
       mma_bf16(s[nt], qa[0], kb[0], kb[1]);
       mma_bf16(s[nt], qa[1], kb[2], kb[3]);
     }
-    // ---- position term, masks, running max
+    // ---- position term, masks, running max.  Rows rl0 and rl1 = rl0 + 8 see the same relative offset
+    // at columns 8 apart, so the table entry loaded for row rl0 in n-tile nt serves row rl1 in nt + 1.
     float mx0 = -INFINITY, mx1 = -INFINITY;
+    {
+      const float4* ew = &sm.e[buf][2 * qd - rl0 + (BQ - 1)];
+      float4 ep0 = ew[-8], ep1 = ew[-7];
+      if (sm.mflag[buf] == 0) {
 #pragma unroll
-    for (int nt = 0; nt < 8; ++nt) {
+        for (int nt = 0; nt < 8; ++nt) {
+          const float4 ec0 = ew[nt * 8], ec1 = ew[nt * 8 + 1];
+          const float a0 = s[nt][0] + pq0[0] * ec0.x + pq0[1] * ec0.y + pq0[2] * ec0.z + pq0[3] * ec0.w;
+          const float a1 = s[nt][1] + pq0[0] * ec1.x + pq0[1] * ec1.y + pq0[2] * ec1.z + pq0[3] * ec1.w;
+          const float b0 = s[nt][2] + pq1[0] * ep0.x + pq1[1] * ep0.y + pq1[2] * ep0.z + pq1[3] * ep0.w;
+          const float b1 = s[nt][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
+          s[nt][0] = a0, s[nt][1] = a1, s[nt][2] = b0, s[nt][3] = b1;
+          mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
+          ep0 = ec0, ep1 = ec1;
+        }
+      } else {
 #pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int jl = nt * 8 + 2 * qd + e;
-        const uint8_t mk = sm.m[buf][jl];
-        const float4 ea = sm.e[buf][jl - rl0 + (BQ - 1)];
-        const float4 eb = sm.e[buf][jl - rl1 + (BQ - 1)];
-        float sa = s[nt][e] + pq0[0] * ea.x + pq0[1] * ea.y + pq0[2] * ea.z + pq0[3] * ea.w;
-        float sb = s[nt][2 + e] + pq1[0] * eb.x + pq1[1] * eb.y + pq1[2] * eb.z + pq1[3] * eb.w;
-        if (mk) sa = sb = (mk == 1 ? -1000.0f : -INFINITY);
-        s[nt][e] = sa, s[nt][2 + e] = sb;
-        mx0 = fmaxf(mx0, sa), mx1 = fmaxf(mx1, sb);
+        for (int nt = 0; nt < 8; ++nt) {
+          const float4 ec0 = ew[nt * 8], ec1 = ew[nt * 8 + 1];
+          float a0 = s[nt][0] + pq0[0] * ec0.x + pq0[1] * ec0.y + pq0[2] * ec0.z + pq0[3] * ec0.w;
+          float a1 = s[nt][1] + pq0[0] * ec1.x + pq0[1] * ec1.y + pq0[2] * ec1.z + pq0[3] * ec1.w;
+          float b0 = s[nt][2] + pq1[0] * ep0.x + pq1[1] * ep0.y + pq1[2] * ep0.z + pq1[3] * ep0.w;
+          float b1 = s[nt][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
+          const uint8_t k0 = sm.m[buf][nt * 8 + 2 * qd], k1 = sm.m[buf][nt * 8 + 2 * qd + 1];
+          if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
+          if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
+          s[nt][0] = a0, s[nt][1] = a1, s[nt][2] = b0, s[nt][3] = b1;
+          mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
+          ep0 = ec0, ep1 = ec1;
+        }
       }
     }
     mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
@@ -176,22 +199,26 @@ __global__ void __launch_bounds__(256, 1) attn_kernel(AttnParams p, int chunks, 
     mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
     mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
     const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
-    const float sc0 = exp2f((m0 - mn0) * LOG2E), sc1 = exp2f((m1 - mn1) * LOG2E);
-    m0 = mn0, m1 = mn1;
+    const bool grow = (mn0 != m0) || (mn1 != m1);
     const float ms0 = mn0 * LOG2E, ms1 = mn1 * LOG2E;
     float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        const float pa = exp2f(s[nt][e] * LOG2E - ms0), pb = exp2f(s[nt][2 + e] * LOG2E - ms1);
+        const float pa = ex2_approx(fmaf(s[nt][e], LOG2E, -ms0)), pb = ex2_approx(fmaf(s[nt][2 + e], LOG2E, -ms1));
         s[nt][e] = pa, s[nt][2 + e] = pb;
         rs0 += pa, rs1 += pb;
       }
     }
-    l0 = l0 * sc0 + rs0, l1 = l1 * sc1 + rs1;
+    if (__any_sync(0xffffffffu, grow)) {  // warp-uniform: rescale only when some row's running max moved
+      const float sc0 = ex2_approx((m0 - mn0) * LOG2E), sc1 = ex2_approx((m1 - mn1) * LOG2E);
+      l0 *= sc0, l1 *= sc1;
 #pragma unroll
-    for (int n = 0; n < DV / 8; ++n) o[n][0] *= sc0, o[n][1] *= sc0, o[n][2] *= sc1, o[n][3] *= sc1;
+      for (int n = 0; n < DV / 8; ++n) o[n][0] *= sc0, o[n][1] *= sc0, o[n][2] *= sc1, o[n][3] *= sc1;
+      m0 = mn0, m1 = mn1;
+    }
+    l0 += rs0, l1 += rs1;
     // ---- O += P V
 #pragma unroll
     for (int kk = 0; kk < BKV / 16; ++kk) {
@@ -254,6 +281,7 @@ static int launch_attn(const AttnParams& p, int chunks, int dv_valid, cudaStream
 
 int attention(const AttnParams& p, cudaStream_t s) {
   if (p.dv == 12) return launch_attn<16>(p, 1, 12, s);
+  if (p.dv % 192 == 0) return launch_attn<192>(p, p.dv / 192, 192, s);
   if (p.dv % 128 == 0) return launch_attn<128>(p, p.dv / 128, 128, s);
   if (p.dv % 48 == 0) return launch_attn<48>(p, p.dv / 48, 48, s);
   return 930;

@@ -1,20 +1,598 @@
-// VocosFbank mel front-end and Vocos vocoder head.
+// VocosFbank mel front-end (zipvoice/utils/feature.py:36-120) and the Vocos vocoder head
+// (third-party `vocos`, call site zipvoice/bin/infer_zipvoice.py:249-260,378) as CUDA kernels.
+//   mel      : frame (reflect pad 512) x periodic Hann -> real FFT-1024 (packed 512-point radix-8 Stockham
+//              in shared memory, zv_fft.cuh) -> |.| -> sparse HTK mel filterbank (<= 2 filters per bin)
+//              -> log(max(., 1e-7)).  One launch; 5.56 algorithmic bytes per input sample.
+//   vocoder  : embed Conv1d(100->512, k7) as an implicit-im2col tcgen05 GEMM (the TMA tensor map of
+//              the A operand has a 104-element row pitch and 728 columns, so consecutive "rows" are
+//              overlapping 7-frame windows of the zero-padded channel-last mel), LayerNorm kernels,
+//              fused depthwise-conv7 + LayerNorm, pwconv GEMMs with GELU / residual epilogues
+//              (layer scale gamma folded into pwconv2), head GEMM, and the iSTFT: spectrum ->
+//              inverse real FFT-1024 -> Hann -> overlap-add / window-envelope normalisation.
+// Activations of sequence b live at rows [b * Tp, b * Tp + T) with Tp = T + 6 (the 6 slack rows per
+// sequence come from the implicit im2col; every kernel treats frames >= len_b as zero input).
+#include <math.h>
+
 #include "zv_common.cuh"
 #include "zv_engine.h"
+#include "zv_fft.cuh"
+
+namespace zv {
+
+static constexpr int N_FFT = 1024, HOP = 256, N_BINS = 513, N_MELS = 100;
+static constexpr int VC_DIM = 512, VC_INTER = 1536, VC_LAYERS = 8, VC_MELP = 104, VC_K = 7;
+
+struct Audio {
+  // constant tables
+  float2* tw512 = nullptr;    // exp(-2 pi i k / 512)
+  float2* tw1024 = nullptr;   // exp(-2 pi i k / 1024)
+  int* fb_start = nullptr;    // first FFT bin of mel filter m
+  int* fb_count = nullptr;
+  int* fb_off = nullptr;      // offset of its weights in fb_w
+  float* fb_w = nullptr;
+  // vocoder weights
+  bool has_vocoder = false;
+  Lin embed, pw1[VC_LAYERS], pw2[VC_LAYERS], head;
+  float *norm_w = nullptr, *norm_b = nullptr, *fnorm_w = nullptr, *fnorm_b = nullptr;
+  float *dw_w[VC_LAYERS], *dw_b[VC_LAYERS], *ln_w[VC_LAYERS], *ln_b[VC_LAYERS];
+  // vocoder workspace
+  size_t cap_rows = 0;
+  int cap_B = 0;
+  __nv_bfloat16 *melp = nullptr, *h = nullptr, *g = nullptr;
+  float *x = nullptr, *emb = nullptr, *spec = nullptr, *frames = nullptr;
+  int* lens_dev = nullptr;
+  std::vector<void*> ws_allocs;
+};
+
+static int audio_tables(Engine& e, Audio& a) {
+  if (a.tw512) return 0;
+  std::vector<float2> t512(512), t1024(1024);
+  for (int i = 0; i < 512; ++i) t512[i] = make_float2((float)cos(-2.0 * M_PI * i / 512), (float)sin(-2.0 * M_PI * i / 512));
+  for (int i = 0; i < 1024; ++i)
+    t1024[i] = make_float2((float)cos(-2.0 * M_PI * i / 1024), (float)sin(-2.0 * M_PI * i / 1024));
+  // torchaudio.functional.melscale_fbanks(513, 0, 12000, 100, 24000, norm=None, mel_scale="htk") in double
+  const double f_max = 12000.0;
+  auto hz2mel = [](double f) { return 2595.0 * log10(1.0 + f / 700.0); };
+  std::vector<double> fpts(N_MELS + 2);
+  const double mmin = hz2mel(0.0), mmax = hz2mel(f_max);
+  for (int i = 0; i < N_MELS + 2; ++i) {
+    const double m = mmin + (mmax - mmin) * i / (N_MELS + 1);
+    fpts[i] = 700.0 * (pow(10.0, m / 2595.0) - 1.0);
+  }
+  std::vector<int> start(N_MELS), count(N_MELS), off(N_MELS);
+  std::vector<float> w;
+  for (int m = 0; m < N_MELS; ++m) {
+    int first = -1, last = -2;
+    std::vector<float> row(N_BINS, 0.f);
+    for (int k = 0; k < N_BINS; ++k) {
+      const double f = f_max * k / (N_BINS - 1);
+      const double down = (f - fpts[m]) / (fpts[m + 1] - fpts[m]);
+      const double up = (fpts[m + 2] - f) / (fpts[m + 2] - fpts[m + 1]);
+      const double v = fmin(down, up);
+      if (v > 0.0) {
+        row[k] = (float)v;
+        if (first < 0) first = k;
+        last = k;
+      }
+    }
+    start[m] = first < 0 ? 0 : first, count[m] = first < 0 ? 0 : last - first + 1, off[m] = (int)w.size();
+    for (int k = 0; k < count[m]; ++k) w.push_back(row[start[m] + k]);
+  }
+  auto up = [&](const void* src, size_t bytes, void** dst) {
+    int rc = dev_alloc(e, e.weight_allocs, dst, bytes);
+    if (rc) return rc;
+    return (int)cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice);
+  };
+  int rc = up(t512.data(), 512 * sizeof(float2), (void**)&a.tw512);
+  if (!rc) rc = up(t1024.data(), 1024 * sizeof(float2), (void**)&a.tw1024);
+  if (!rc) rc = up(start.data(), N_MELS * 4, (void**)&a.fb_start);
+  if (!rc) rc = up(count.data(), N_MELS * 4, (void**)&a.fb_count);
+  if (!rc) rc = up(off.data(), N_MELS * 4, (void**)&a.fb_off);
+  if (!rc) rc = up(w.data(), w.size() * 4, (void**)&a.fb_w);
+  return rc;
+}
+
+// ------------------------------------------------------------------ mel front-end
+// CTA = 256 threads = 4 frame groups of 64 threads; each group transforms one frame per iteration.
+struct FftSmem {
+  float2 tw512[512];
+  float2 tw1024[1024];
+  float2 buf[4][512];
+  float mag[4][520];
+};
+
+__global__ void __launch_bounds__(256) fbank_kernel(const float* __restrict__ wav, const int64_t* __restrict__ lens,
+                                                    int N, int T, const float2* __restrict__ tw512g,
+                                                    const float2* __restrict__ tw1024g,
+                                                    const int* __restrict__ fb_start, const int* __restrict__ fb_count,
+                                                    const int* __restrict__ fb_off, const float* __restrict__ fb_w,
+                                                    int frames_per_cta, float* __restrict__ mel) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  FftSmem& sm = *reinterpret_cast<FftSmem*>(smem_raw);
+  const int tid = threadIdx.x, g = tid >> 6, j = tid & 63;
+  const int b = blockIdx.y;
+  for (int i = tid; i < 512; i += 256) sm.tw512[i] = tw512g[i];
+  for (int i = tid; i < 1024; i += 256) sm.tw1024[i] = tw1024g[i];
+  __syncthreads();
+  const long long len = lens ? lens[b] : (long long)N;
+  const int Tb = (int)((len + HOP / 2) / HOP);  // lhotse compute_num_frames (round half up)
+  const int n_spec = (int)(len / HOP) + 1;      // frames torchaudio computes (center=True)
+  const float* x = wav + (size_t)b * N;
+  const int t_begin = blockIdx.x * frames_per_cta;
+  for (int it = 0; it < frames_per_cta; it += 4) {
+    const int t = t_begin + it + g;
+    // frames beyond torchaudio's count replicate the last one (feature.py:105-110)
+    const int ts = min(t, n_spec - 1);
+    const bool live = t < T && t < Tb;
+    float2 v[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int n = j + 64 * r;
+      float2 z = make_float2(0.f, 0.f);
+      if (live) {
+        long long s0 = (long long)ts * HOP - N_FFT / 2 + 2 * n, s1 = s0 + 1;
+        s0 = s0 < 0 ? -s0 : (s0 >= len ? 2 * (len - 1) - s0 : s0);
+        s1 = s1 < 0 ? -s1 : (s1 >= len ? 2 * (len - 1) - s1 : s1);
+        s0 = max(0ll, min(s0, len - 1)), s1 = max(0ll, min(s1, len - 1));
+        const float w0 = 0.5f - 0.5f * sm.tw1024[2 * n].x, w1 = 0.5f - 0.5f * sm.tw1024[2 * n + 1].x;
+        z = make_float2(x[s0] * w0, x[s1] * w1);
+      }
+      v[r] = z;
+    }
+    fft512_block<false>(v, j, sm.buf[g], sm.tw512);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int k = j + 64 * r;
+      const float2 X = rfft_unpack(sm.buf[g], k, sm.tw1024[k]);
+      sm.mag[g][k] = sqrtf(X.x * X.x + X.y * X.y);
+    }
+    if (j == 0) {
+      const float2 X = rfft_unpack(sm.buf[g], 512, make_float2(-1.f, 0.f));
+      sm.mag[g][512] = sqrtf(X.x * X.x + X.y * X.y);
+    }
+    __syncthreads();
+    for (int m = j; m < N_MELS; m += 64) {
+      const int st = fb_start[m], cnt = fb_count[m];
+      const float* w = fb_w + fb_off[m];
+      float acc = 0.f;
+      for (int k = 0; k < cnt; ++k) acc = fmaf(sm.mag[g][st + k], __ldg(w + k), acc);
+      if (t < T) mel[((size_t)b * T + t) * N_MELS + m] = live ? logf(fmaxf(acc, 1e-7f)) : 0.f;
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ vocoder kernels
+// mel (B, 100, T) fp32 channel-major -> zero-padded channel-last bf16 rows [(B * Tp + 6)][104]:
+// row b*Tp + 3 + t holds frame t; frames >= len_b and the 3 + 3 border rows are zero (Conv1d padding).
+__global__ void vc_pack_mel_kernel(const float* __restrict__ mel, const int* __restrict__ lens, int B, int T, int Tp,
+                                   __nv_bfloat16* __restrict__ out, size_t total) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= total) return;
+  const int c = (int)(gid % VC_MELP);
+  const size_t row = gid / VC_MELP;
+  const int b = (int)(row / Tp), tp = (int)(row % Tp);
+  const int t = tp - 3;
+  float v = 0.f;
+  if (b < B && c < N_MELS && t >= 0 && t < T && t < lens[b]) v = mel[((size_t)b * N_MELS + c) * T + t];
+  out[gid] = __float2bfloat16(v);
+}
+
+// LayerNorm over 512 channels, one warp per row (two-pass statistics in registers, eps 1e-6).
+__global__ void vc_layernorm_kernel(const float* __restrict__ in, const float* __restrict__ w,
+                                    const float* __restrict__ bias, int rows, float* __restrict__ out_f32,
+                                    __nv_bfloat16* __restrict__ out_bf16) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const float* x = in + (size_t)row * VC_DIM;
+  float4 v[4];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[i] = *reinterpret_cast<const float4*>(x + (i * 32 + lane) * 4);
+    s += v[i].x + v[i].y + v[i].z + v[i].w;
+  }
+  const float mean = warp_sum(s) * (1.0f / VC_DIM);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+    q += a * a + b * b + c * c + d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(q) * (1.0f / VC_DIM) + 1e-6f);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int col = (i * 32 + lane) * 4;
+    const float4 ww = *reinterpret_cast<const float4*>(w + col), bb = *reinterpret_cast<const float4*>(bias + col);
+    float4 r;
+    r.x = (v[i].x - mean) * rstd * ww.x + bb.x, r.y = (v[i].y - mean) * rstd * ww.y + bb.y;
+    r.z = (v[i].z - mean) * rstd * ww.z + bb.z, r.w = (v[i].w - mean) * rstd * ww.w + bb.w;
+    if (out_f32) *reinterpret_cast<float4*>(out_f32 + (size_t)row * VC_DIM + col) = r;
+    if (out_bf16)
+      *reinterpret_cast<uint2*>(out_bf16 + (size_t)row * VC_DIM + col) =
+          make_uint2(pack_bf16x2(r.x, r.y), pack_bf16x2(r.z, r.w));
+  }
+}
+
+// ConvNeXt block head: depthwise Conv1d(k=7, pad 3) over time + LayerNorm -> bf16 (GEMM A operand).
+// CTA = 32 frames of one sequence, all 512 channels; the (32 + 6) x 512 fp32 input tile and the taps
+// are staged in shared memory; one warp produces 4 frames, a lane owns 4 x 4 channels of a frame.
+static constexpr int DWT = 32;
+struct DwSmem {
+  float x[DWT + 6][VC_DIM];
+  float w[VC_K][VC_DIM];
+};
+__global__ void __launch_bounds__(256) vc_dwconv_ln_kernel(const float* __restrict__ in, const int* __restrict__ lens,
+                                                           int T, int Tp, const float* __restrict__ dw_w,
+                                                           const float* __restrict__ dw_b,
+                                                           const float* __restrict__ ln_w,
+                                                           const float* __restrict__ ln_b,
+                                                           __nv_bfloat16* __restrict__ out) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  DwSmem& sm = *reinterpret_cast<DwSmem*>(smem_raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.y, t0 = blockIdx.x * DWT;
+  const int len = min(lens[b], T);
+  const float* src = in + (size_t)b * Tp * VC_DIM;
+  for (int idx = tid; idx < (DWT + 6) * (VC_DIM / 4); idx += 256) {
+    const int r = idx / (VC_DIM / 4), c4 = idx % (VC_DIM / 4);
+    const int t = t0 - 3 + r;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (t >= 0 && t < len) v = *reinterpret_cast<const float4*>(src + (size_t)t * VC_DIM + c4 * 4);
+    *reinterpret_cast<float4*>(&sm.x[r][c4 * 4]) = v;
+  }
+  for (int idx = tid; idx < VC_K * VC_DIM; idx += 256) {
+    const int c = idx / VC_K, k = idx % VC_K;  // weight (512, 1, 7): channel-major
+    sm.w[k][c] = dw_w[idx];
+  }
+  __syncthreads();
+  for (int f = warp * 4; f < warp * 4 + 4; ++f) {
+    const int t = t0 + f;
+    if (t >= T) break;
+    float4 acc[4];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int col = (i * 32 + lane) * 4;
+      float4 a = *reinterpret_cast<const float4*>(dw_b + col);
+#pragma unroll
+      for (int k = 0; k < VC_K; ++k) {
+        const float4 xv = *reinterpret_cast<const float4*>(&sm.x[f + k][col]);
+        const float4 wv = *reinterpret_cast<const float4*>(&sm.w[k][col]);
+        a.x = fmaf(xv.x, wv.x, a.x), a.y = fmaf(xv.y, wv.y, a.y), a.z = fmaf(xv.z, wv.z, a.z), a.w = fmaf(xv.w, wv.w, a.w);
+      }
+      acc[i] = a;
+      s += a.x + a.y + a.z + a.w;
+    }
+    const float mean = warp_sum(s) * (1.0f / VC_DIM);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float a = acc[i].x - mean, bb = acc[i].y - mean, c = acc[i].z - mean, d = acc[i].w - mean;
+      q += a * a + bb * bb + c * c + d * d;
+    }
+    const float rstd = rsqrtf(warp_sum(q) * (1.0f / VC_DIM) + 1e-6f);
+    __nv_bfloat16* o = out + ((size_t)b * Tp + t) * VC_DIM;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int col = (i * 32 + lane) * 4;
+      const float4 ww = *reinterpret_cast<const float4*>(ln_w + col), bb = *reinterpret_cast<const float4*>(ln_b + col);
+      const float r0 = (acc[i].x - mean) * rstd * ww.x + bb.x, r1 = (acc[i].y - mean) * rstd * ww.y + bb.y;
+      const float r2 = (acc[i].z - mean) * rstd * ww.z + bb.z, r3 = (acc[i].w - mean) * rstd * ww.w + bb.w;
+      *reinterpret_cast<uint2*>(o + col) = make_uint2(pack_bf16x2(r0, r1), pack_bf16x2(r2, r3));
+    }
+  }
+}
+
+// ISTFTHead, per frame: spec row = [513 log-magnitudes | 513 phases] (ld = ldspec) ->
+// S = min(exp(m), 100) (cos p + i sin p) -> inverse real FFT-1024 -> x Hann -> frames[row][1024].
+__global__ void __launch_bounds__(256) vc_istft_frames_kernel(const float* __restrict__ spec, int ldspec,
+                                                              const int* __restrict__ lens, int T, int Tp,
+                                                              const float2* __restrict__ tw512g,
+                                                              const float2* __restrict__ tw1024g,
+                                                              int frames_per_cta, float* __restrict__ frames) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  FftSmem& sm = *reinterpret_cast<FftSmem*>(smem_raw);
+  const int tid = threadIdx.x, g = tid >> 6, j = tid & 63;
+  const int b = blockIdx.y;
+  for (int i = tid; i < 512; i += 256) sm.tw512[i] = tw512g[i];
+  for (int i = tid; i < 1024; i += 256) sm.tw1024[i] = tw1024g[i];
+  __syncthreads();
+  const int len = min(lens[b], T);
+  const int t_begin = blockIdx.x * frames_per_cta;
+  for (int it = 0; it < frames_per_cta; it += 4) {
+    const int t = t_begin + it + g;
+    const bool live = t < len;
+    const float* row = spec + ((size_t)b * Tp + min(t, T - 1)) * ldspec;
+    __shared__ float2 nyq[4];  // bin 512 (bins 0..511 go to buf)
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int k = j + 64 * r;
+      float2 s = make_float2(0.f, 0.f);
+      if (live) {
+        const float mag = fminf(expf(row[k]), 100.0f);
+        float sn, cs;
+        sincosf(row[N_BINS + k], &sn, &cs);
+        s = make_float2(mag * cs, mag * sn);
+      }
+      sm.buf[g][k] = s;
+    }
+    if (j == 0) {
+      float2 s = make_float2(0.f, 0.f);
+      if (live) {
+        const float mag = fminf(expf(row[512]), 100.0f);
+        float sn, cs;
+        sincosf(row[N_BINS + 512], &sn, &cs);
+        s = make_float2(mag * cs, mag * sn);
+      }
+      nyq[g] = s;
+    }
+    __syncthreads();
+    float2 v[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int k = j + 64 * r;
+      float2 xk = sm.buf[g][k];
+      float2 xn = k == 0 ? nyq[g] : sm.buf[g][512 - k];
+      if (k == 0) xk.y = 0.f, xn.y = 0.f;  // irfft ignores the imaginary parts of DC and Nyquist
+      v[r] = irfft_pack(xk, xn, sm.tw1024[k]);
+    }
+    __syncthreads();  // all reads of buf done before the transform overwrites it
+    fft512_block<true>(v, j, sm.buf[g], sm.tw512);
+    if (t < T) {
+      float* o = frames + ((size_t)b * Tp + t) * N_FFT;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const int n = j + 64 * r;
+        const float2 z = sm.buf[g][n];
+        const float w0 = 0.5f - 0.5f * sm.tw1024[2 * n].x, w1 = 0.5f - 0.5f * sm.tw1024[2 * n + 1].x;
+        *reinterpret_cast<float2*>(o + 2 * n) =
+            make_float2(z.x * (1.0f / N_FFT) * w0, z.y * (1.0f / N_FFT) * w1);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// Overlap-add with window-envelope normalisation (torch.istft, center=True): output sample n of
+// sequence b sits at padded coordinate c = n + 512 and sums frames t with 0 <= c - 256 t < 1024.
+__global__ void vc_ola_kernel(const float* __restrict__ frames, const int* __restrict__ lens, int T, int Tp,
+                              const float2* __restrict__ tw1024g, int n_out, float* __restrict__ wav) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (n >= n_out) return;
+  const int len = min(lens[b], T);
+  float out = 0.f;
+  if (n < HOP * (len - 1)) {
+    const int c = n + N_FFT / 2;
+    const int t_hi = min(len - 1, c / HOP);
+    float acc = 0.f, env = 0.f;
+    for (int t = t_hi; t >= 0 && c - HOP * t < N_FFT; --t) {
+      const int i = c - HOP * t;
+      const float w = 0.5f - 0.5f * __ldg(&tw1024g[i]).x;
+      acc += frames[((size_t)b * Tp + t) * N_FFT + i];
+      env += w * w;
+    }
+    out = acc / env;
+  }
+  wav[(size_t)b * n_out + n] = out;
+}
+
+__global__ void vc_lens_kernel(const int64_t* __restrict__ lens, int B, int T, int* __restrict__ out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < B) out[b] = lens ? (int)max(0ll, min((long long)lens[b], (long long)T)) : T;
+}
+
+#define AU_TRY(expr)                                                                   \
+  do {                                                                                 \
+    int _rc = (expr);                                                                  \
+    if (_rc) {                                                                         \
+      if (e.err.empty()) {                                                             \
+        char _b[512];                                                                  \
+        snprintf(_b, sizeof(_b), "%s failed with %d at %s:%d", #expr, _rc, __FILE__, __LINE__); \
+        e.err = _b;                                                                    \
+      }                                                                                \
+      return _rc;                                                                      \
+    }                                                                                  \
+  } while (0)
+#define AU_K(cls, work, s, ...)                  \
+  do {                                           \
+    ++g_launch_count;                            \
+    if (e.prof.on) e.prof.begin(cls, work, s);   \
+    __VA_ARGS__;                                 \
+    if (e.prof.on) e.prof.end(s);                \
+    AU_TRY((int)cudaGetLastError());             \
+  } while (0)
+
+static Audio& audio_of(Engine& e) {
+  if (!e.audio) e.audio = new Audio();
+  return *static_cast<Audio*>(e.audio);
+}
+
+void audio_destroy(Engine& e) {
+  if (!e.audio) return;
+  Audio* a = static_cast<Audio*>(e.audio);
+  for (void* p : a->ws_allocs) cudaFree(p);
+  delete a;
+  e.audio = nullptr;
+}
+
+static const HostTensor* vfind(Engine& e, const std::string& name) {
+  auto it = e.raw.find("vocoder." + name);
+  if (it == e.raw.end()) {
+    e.err = "missing vocoder weight: vocoder." + name;
+    return nullptr;
+  }
+  return &it->second;
+}
+static int vupload(Engine& e, const std::string& name, size_t numel, float** out) {
+  const HostTensor* t = vfind(e, name);
+  if (!t) return 940;
+  if (t->numel() != numel) {
+    e.err = "unexpected shape for vocoder." + name;
+    return 944;
+  }
+  AU_TRY(dev_alloc(e, e.weight_allocs, (void**)out, numel * 4));
+  AU_TRY((int)cudaMemcpy(*out, t->data.data(), numel * 4, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+static int vocoder_build(Engine& e, Audio& a) {
+  if (a.has_vocoder) return 0;
+  const HostTensor* ew = vfind(e, "backbone.embed.weight");
+  const HostTensor* eb = vfind(e, "backbone.embed.bias");
+  if (!ew || !eb) return 940;
+  if (ew->shape.size() != 3 || ew->shape[0] != VC_DIM || ew->shape[1] != N_MELS || ew->shape[2] != VC_K) {
+    e.err = "vocoder.backbone.embed.weight must be (512, 100, 7)";
+    return 944;
+  }
+  {  // (out, in, k) -> [out][k * 104 + in]: the implicit-im2col column order
+    std::vector<float> w((size_t)VC_DIM * VC_K * VC_MELP, 0.f);
+    for (int n = 0; n < VC_DIM; ++n)
+      for (int c = 0; c < N_MELS; ++c)
+        for (int k = 0; k < VC_K; ++k)
+          w[(size_t)n * VC_K * VC_MELP + k * VC_MELP + c] = ew->data[((size_t)n * N_MELS + c) * VC_K + k];
+    AU_TRY(pack_linear_host(e, w.data(), eb->data.data(), VC_DIM, VC_K * VC_MELP, EPI_F32, &a.embed, 0, nullptr));
+  }
+  AU_TRY(vupload(e, "backbone.norm.weight", VC_DIM, &a.norm_w));
+  AU_TRY(vupload(e, "backbone.norm.bias", VC_DIM, &a.norm_b));
+  AU_TRY(vupload(e, "backbone.final_layer_norm.weight", VC_DIM, &a.fnorm_w));
+  AU_TRY(vupload(e, "backbone.final_layer_norm.bias", VC_DIM, &a.fnorm_b));
+  for (int i = 0; i < VC_LAYERS; ++i) {
+    const std::string p = "backbone.convnext." + std::to_string(i);
+    AU_TRY(vupload(e, p + ".dwconv.weight", (size_t)VC_DIM * VC_K, &a.dw_w[i]));
+    AU_TRY(vupload(e, p + ".dwconv.bias", VC_DIM, &a.dw_b[i]));
+    AU_TRY(vupload(e, p + ".norm.weight", VC_DIM, &a.ln_w[i]));
+    AU_TRY(vupload(e, p + ".norm.bias", VC_DIM, &a.ln_b[i]));
+    const HostTensor *w1 = vfind(e, p + ".pwconv1.weight"), *b1 = vfind(e, p + ".pwconv1.bias");
+    const HostTensor *w2 = vfind(e, p + ".pwconv2.weight"), *b2 = vfind(e, p + ".pwconv2.bias");
+    const HostTensor* gm = vfind(e, p + ".gamma");
+    if (!w1 || !b1 || !w2 || !b2 || !gm) return 940;
+    AU_TRY(pack_linear_host(e, w1->data.data(), b1->data.data(), VC_INTER, VC_DIM, EPI_GELU_BF16, &a.pw1[i], 0, nullptr));
+    // gamma * (W2 g + b2): the layer scale is folded into the rows of pwconv2
+    AU_TRY(pack_linear_host(e, w2->data.data(), b2->data.data(), VC_DIM, VC_INTER, EPI_RESIDUAL, &a.pw2[i], 0,
+                            gm->data.data()));
+  }
+  const HostTensor *hw = vfind(e, "head.out.weight"), *hb = vfind(e, "head.out.bias");
+  if (!hw || !hb) return 940;
+  AU_TRY(pack_linear_host(e, hw->data.data(), hb->data.data(), N_FFT + 2, VC_DIM, EPI_F32, &a.head, 0, nullptr));
+  a.has_vocoder = true;
+  return 0;
+}
+
+static int vocoder_reserve(Engine& e, Audio& a, int B, int T) {
+  const int Tp = T + 6;
+  const size_t rows = (size_t)B * Tp;
+  if (rows <= a.cap_rows && B <= a.cap_B) return 0;
+  cudaDeviceSynchronize();
+  for (void* p : a.ws_allocs) cudaFree(p);
+  a.ws_allocs.clear();
+  a.cap_rows = rows, a.cap_B = B;
+  auto A = [&](void** p, size_t bytes) {
+    int rc = dev_alloc(e, a.ws_allocs, p, bytes);
+    if (!rc) rc = (int)cudaMemset(*p, 0, bytes);
+    return rc;
+  };
+  AU_TRY(A((void**)&a.melp, (rows + 8) * VC_MELP * 2));
+  AU_TRY(A((void**)&a.x, rows * VC_DIM * 4));
+  AU_TRY(A((void**)&a.emb, rows * VC_DIM * 4));
+  AU_TRY(A((void**)&a.h, rows * VC_DIM * 2));
+  AU_TRY(A((void**)&a.g, rows * VC_INTER * 2));
+  AU_TRY(A((void**)&a.spec, rows * 1028 * 4));
+  AU_TRY(A((void**)&a.frames, rows * N_FFT * 4));
+  AU_TRY(A((void**)&a.lens_dev, (size_t)B * 4));
+  return 0;
+}
+
+}  // namespace zv
 
 using namespace zv;
 
 extern "C" int zv_fbank(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out,
                         void* stream) {
-  Engine* e = (Engine*)handle;
-  if (!e) return 960;
-  e->err = "zv_fbank: kernel not built yet in this revision";
-  return 990;
+  Engine* ep = (Engine*)handle;
+  if (!ep) return 960;
+  Engine& e = *ep;
+  e.err.clear();
+  if (B <= 0 || N <= N_FFT / 2) {
+    e.err = "zv_fbank: need B > 0 and more than 512 samples (reflect padding)";
+    return 964;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  Audio& a = audio_of(e);
+  AU_TRY(audio_tables(e, a));
+  const int T = (N + HOP / 2) / HOP;
+  const int fpc = 16;
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(fbank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FftSmem));
+    attr = true;
+  }
+  dim3 grid((T + fpc - 1) / fpc, B);
+  // algorithmic bytes: 4 B per input sample + 400 B per output frame
+  AU_K(KC_FBANK, (double)B * N * 4.0 + (double)B * T * N_MELS * 4.0, s,
+       (fbank_kernel<<<grid, 256, sizeof(FftSmem), s>>>(wav, lens, N, T, a.tw512, a.tw1024, a.fb_start, a.fb_count,
+                                                        a.fb_off, a.fb_w, fpc, mel_out)));
+  return 0;
 }
 
-extern "C" int zv_vocos_decode(void* handle, const float* mel, int B, int T, float* wav_out, void* stream) {
-  Engine* e = (Engine*)handle;
-  if (!e) return 960;
-  e->err = "zv_vocos_decode: kernel not built yet in this revision";
-  return 990;
+extern "C" int zv_vocos_decode(void* handle, const float* mel, const int64_t* lens, int B, int T, float* wav_out,
+                               void* stream) {
+  Engine* ep = (Engine*)handle;
+  if (!ep) return 960;
+  Engine& e = *ep;
+  e.err.clear();
+  if (B <= 0 || T < 2) {
+    e.err = "zv_vocos_decode: need B > 0 and T >= 2 frames";
+    return 964;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  Audio& a = audio_of(e);
+  AU_TRY(audio_tables(e, a));
+  AU_TRY(vocoder_build(e, a));
+  AU_TRY(vocoder_reserve(e, a, B, T));
+  const int Tp = T + 6, M = B * Tp;
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(vc_dwconv_ln_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DwSmem));
+    cudaFuncSetAttribute(vc_istft_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FftSmem));
+    attr = true;
+  }
+  AU_K(KC_VOCODER_ELEM, B * 12.0, s, (vc_lens_kernel<<<(B + 127) / 128, 128, 0, s>>>(lens, B, T, a.lens_dev)));
+  const size_t tot = (size_t)(M + 6) * VC_MELP;
+  AU_K(KC_VOCODER_ELEM, (double)B * T * N_MELS * 4.0 + tot * 2.0, s,
+       (vc_pack_mel_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(mel, a.lens_dev, B, T, Tp, a.melp, tot)));
+  EpiParams p0;
+  p0.L = Tp, p0.out_f32 = a.emb, p0.ld_f32 = VC_DIM;
+  AU_TRY(run_gemm(e, a.embed, a.melp, VC_MELP, M, p0, s));
+  AU_K(KC_VOCODER_ELEM, (double)M * VC_DIM * 8.0, s,
+       (vc_layernorm_kernel<<<(M + 7) / 8, 256, 0, s>>>(a.emb, a.norm_w, a.norm_b, M, a.x, nullptr)));
+  dim3 dgrid((T + DWT - 1) / DWT, B);
+  for (int i = 0; i < VC_LAYERS; ++i) {
+    AU_K(KC_VOCODER_ELEM, (double)B * T * VC_DIM * 6.0, s,
+         (vc_dwconv_ln_kernel<<<dgrid, 256, sizeof(DwSmem), s>>>(a.x, a.lens_dev, T, Tp, a.dw_w[i], a.dw_b[i],
+                                                                 a.ln_w[i], a.ln_b[i], a.h)));
+    EpiParams p1;
+    p1.L = Tp, p1.out_bf16 = a.g, p1.ld_bf16 = VC_INTER;
+    AU_TRY(run_gemm(e, a.pw1[i], a.h, VC_DIM, M, p1, s));
+    EpiParams p2;
+    p2.L = Tp, p2.res = a.x, p2.out_f32 = a.x, p2.ld_f32 = VC_DIM;
+    AU_TRY(run_gemm(e, a.pw2[i], a.g, VC_INTER, M, p2, s));
+  }
+  AU_K(KC_VOCODER_ELEM, (double)M * VC_DIM * 6.0, s,
+       (vc_layernorm_kernel<<<(M + 7) / 8, 256, 0, s>>>(a.x, a.fnorm_w, a.fnorm_b, M, nullptr, a.h)));
+  EpiParams ph;
+  ph.L = Tp, ph.out_f32 = a.spec, ph.ld_f32 = 1028;
+  AU_TRY(run_gemm(e, a.head, a.h, VC_DIM, M, ph, s));
+  const int fpc = 16;
+  dim3 igrid((T + fpc - 1) / fpc, B);
+  AU_K(KC_VOCODER_ELEM, (double)B * T * (1026.0 + 1024.0) * 4.0, s,
+       (vc_istft_frames_kernel<<<igrid, 256, sizeof(FftSmem), s>>>(a.spec, 1028, a.lens_dev, T, Tp, a.tw512,
+                                                                   a.tw1024, fpc, a.frames)));
+  const int n_out = HOP * (T - 1);
+  dim3 ogrid((n_out + 255) / 256, B);
+  AU_K(KC_VOCODER_ELEM, (double)B * T * N_FFT * 4.0 + (double)B * n_out * 4.0, s,
+       (vc_ola_kernel<<<ogrid, 256, 0, s>>>(a.frames, a.lens_dev, T, Tp, a.tw1024, n_out, wav_out)));
+  return 0;
 }

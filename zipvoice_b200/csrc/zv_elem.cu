@@ -105,11 +105,17 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in
   const int t0 = blockIdx.x * TT;
   const bool active = c < C;
   const bf16* src = in + (size_t)b * L * C;
-  for (int r = threadIdx.y; r < ROWS; r += blockDim.y) {
-    const int t = t0 - PAD + r;
-    uint32_t v = 0;
-    if (active && t >= 0 && t < L) v = *reinterpret_cast<const uint32_t*>(src + (size_t)t * C + c);
-    tile[r][cp] = v;
+  {  // stage the tile with 16-byte loads: a row of 256 channels = 32 chunks of 8 channels
+    const int tid = threadIdx.y * 128 + threadIdx.x;
+#pragma unroll 4
+    for (int idx = tid; idx < ROWS * 32; idx += 256) {
+      const int r = idx >> 5, c16 = idx & 31;
+      const int t = t0 - PAD + r;
+      const int ch = blockIdx.y * 256 + c16 * 8;
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (ch < C && t >= 0 && t < L) v = __ldg(reinterpret_cast<const uint4*>(src + (size_t)t * C + ch));
+      *reinterpret_cast<uint4*>(&tile[r][c16 * 4]) = v;
+    }
   }
   __syncthreads();
   if (!active) return;
@@ -135,7 +141,7 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in
     for (int o = 0; o < 4; ++o) {
       const int t = t0 + tt + o;
       if (t < L)
-        *reinterpret_cast<uint32_t*>(dst + (size_t)t * C + c) = pack_bf16x2(swoosh_r(a0[o]), swoosh_r(a1[o]));
+        *reinterpret_cast<uint32_t*>(dst + (size_t)t * C + c) = pack_bf16x2(swoosh_r_fast(a0[o]), swoosh_r_fast(a1[o]));
     }
   }
 }

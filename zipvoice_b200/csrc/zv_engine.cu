@@ -290,6 +290,15 @@ static int build_net(Engine& e, Net& net, const std::string& prefix, int in_dim,
 
 int engine_finalize(Engine& e) {
   const zv_config& c = e.cfg;
+  if (e.raw.find("fm_decoder.in_proj.weight") == e.raw.end()) {
+    // audio-only handle (mel front-end / vocoder): no acoustic model to pack
+    bool any_model = false;
+    for (auto& kv : e.raw) any_model = any_model || kv.first.rfind("vocoder.", 0) != 0;
+    if (!any_model) {
+      e.finalized = false;
+      return 0;
+    }
+  }
   ZV_TRY(build_net(e, e.fm, "fm_decoder", 3 * c.feat_dim, c.feat_dim, c.fm_dim, c.fm_feedforward_dim, c.fm_num_heads,
                    c.fm_num_stacks, c.fm_downsampling_factor, c.fm_num_layers, c.fm_cnn_module_kernel, true,
                    c.use_guidance_scale_embed != 0));

@@ -125,6 +125,7 @@ struct TimeArgs {
 int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t* mask_dev, const TimeArgs& ta,
                 float* out, cudaStream_t s);
 int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T);
+void audio_destroy(Engine& e);
 // Shared with the vocoder (zv_audio.cu): pack one Linear from host fp32 (rows optionally permuted for the
 // fused epilogue of `mode`), and launch it.  row_scale (optional, [N]) multiplies weight rows and bias.
 int pack_linear_host(Engine& e, const float* w, const float* bias, int N, int K, int mode, Lin* lin, int k_pad_to,
