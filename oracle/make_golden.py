@@ -84,6 +84,16 @@ def main():
     vb = mb.solver.model(t=torch.tensor(0.7), x=xb, text_condition=tb, speech_condition=sb, padding_mask=mkb,
                          guidance_scale=1.5)
     np.savez(os.path.join(OUT, "velocity_base_cfg.npz"), v=vb.numpy())
+    # 7. VocosFbank: the unmodified reference class (lhotse replaced by oracle/shims) on seeded audio
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "shims"))
+    sys.path.insert(0, REF)
+    from zipvoice.utils.feature import VocosFbank
+    fb = VocosFbank()
+    fbank = {}
+    for name, n in (("a", 72000), ("b", 24000 + 77), ("c", 30000 + 200)):
+        wav = synth.make_audio(1, n, seed=7 + n)
+        fbank["mel_" + name] = fb.extract(wav, 24000).numpy()
+    np.savez(os.path.join(OUT, "fbank.npz"), **fbank)
     print("golden written to", OUT)
 
 

@@ -77,3 +77,14 @@ def test_velocity_base_cfg():
     x, t, s, mk = case_inputs(2, 50, 15, seed=11)
     v = O.cfg_velocity(sd, synth.BASE_MODEL_CFG, torch.tensor(0.7), x, t, s, mk, guidance_scale=1.5)
     assert valid_rel_l2(v, _g("velocity_base_cfg.npz")["v"], mk) < TOL
+
+
+def test_fbank_oracle_vs_reference_golden():
+    """oracle/fbank_oracle.py against VocosFbank.extract of the unmodified reference (lhotse shimmed)."""
+    from oracle import fbank_oracle as FO
+    g = _g("fbank.npz")
+    for name, n in (("a", 72000), ("b", 24000 + 77), ("c", 30000 + 200)):
+        wav = synth.make_audio(1, n, seed=7 + n)
+        mel = FO.vocos_fbank(wav[0])
+        assert mel.shape == g["mel_" + name].shape == (FO.num_frames(n), 100)
+        assert float((mel - g["mel_" + name]).abs().max()) < 1e-4

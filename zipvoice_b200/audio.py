@@ -1,0 +1,82 @@
+"""Drop-in objects for the two audio seams of ``generate_sentence(model, vocoder, tokenizer,
+feature_extractor, ...)`` (zipvoice/bin/infer_zipvoice.py:276-294):
+
+* ``VocosFbankB200.extract(samples, sampling_rate)``  mirrors ``VocosFbank.extract``
+  (zipvoice/utils/feature.py:63-116);
+* ``VocosB200.decode(mel)``  mirrors ``vocos.Vocos.decode`` (call site infer_zipvoice.py:378).
+
+Both run entirely in the CUDA library; there is no CPU path.
+"""
+from typing import Dict, Optional, Union
+
+import numpy as np
+import torch
+
+from . import synth
+from .engine import Engine
+
+
+def audio_engine(vocoder_state_dict: Optional[Dict[str, torch.Tensor]] = None, device="cuda:0") -> Engine:
+    """A handle that only carries the mel front-end and (optionally) the vocoder weights."""
+    sd = {}
+    if vocoder_state_dict is not None:
+        sd = {("vocoder." + k): v for k, v in vocoder_state_dict.items()
+              if k.startswith(("backbone.", "head.out."))}
+    return Engine(synth.BASE_MODEL_CFG, sd, synth.VOCAB_SIZE, synth.PAD_ID, device=device)
+
+
+class VocosFbankB200:
+    """num_channels 1 (mono; stereo input is averaged) or 2 (per-channel mels concatenated)."""
+
+    sampling_rate, n_mels, n_fft, hop_length = 24000, 100, 1024, 256
+
+    def __init__(self, engine: Optional[Engine] = None, num_channels: int = 1, device="cuda:0"):
+        assert num_channels in (1, 2)
+        self.num_channels = num_channels
+        self.engine = engine if engine is not None else audio_engine(device=device)
+
+    @property
+    def frame_shift(self) -> float:
+        return self.hop_length / self.sampling_rate
+
+    def feature_dim(self, sampling_rate: int) -> int:
+        return self.n_mels
+
+    def extract(self, samples: Union[np.ndarray, torch.Tensor], sampling_rate: int):
+        assert sampling_rate == self.sampling_rate, (
+            f"Mismatched sampling rate: extractor expects {self.sampling_rate}, got {sampling_rate}")
+        is_numpy = not isinstance(samples, torch.Tensor)
+        if is_numpy:
+            samples = torch.from_numpy(samples)
+        if samples.dim() == 1:
+            samples = samples.unsqueeze(0)
+        else:
+            assert samples.ndim == 2, samples.shape
+        if self.num_channels == 1:
+            if samples.shape[0] == 2:
+                samples = samples.mean(dim=0, keepdims=True)
+        else:
+            assert samples.shape[0] == 2, samples.shape
+        mel = self.engine.fbank(samples.float())                 # (C, T, 100)
+        mel = mel.permute(1, 0, 2).reshape(mel.shape[1], -1)     # (T, 100 * C)
+        return mel.cpu().numpy() if is_numpy else mel
+
+    def extract_batch(self, samples: torch.Tensor, lens: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """(B, N) padded mono batch with valid lengths -> (B, T, 100); frames past an utterance are 0."""
+        return self.engine.fbank(samples, lens)
+
+
+class VocosB200:
+    def __init__(self, state_dict: Dict[str, torch.Tensor], engine: Optional[Engine] = None, device="cuda:0"):
+        self.engine = engine if engine is not None else audio_engine(state_dict, device=device)
+
+    def eval(self):
+        return self
+
+    def to(self, device):
+        return self
+
+    @torch.inference_mode()
+    def decode(self, features_input: torch.Tensor, lens: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """mel (B, 100, T) -> (B, 256 (T - 1))"""
+        return self.engine.vocos_decode(features_input, lens)

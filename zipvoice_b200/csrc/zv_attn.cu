@@ -42,6 +42,13 @@ ZV_DEVINL void mma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+ZV_DEVINL void mma_f16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
 template <int DV>
 struct AttnSmem {
   bf16 q[BQ][QP];
@@ -126,10 +133,10 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
   float pq0[4], pq1[4];
   {
     const int ia = min(i0 + rl0, L - 1), ib = min(i0 + rl1, L - 1);
-    const bf16* pa = qkp + (size_t)ia * p.ldq + 2 * H * DQ + head * 4;
-    const bf16* pb = qkp + (size_t)ib * p.ldq + 2 * H * DQ + head * 4;
+    const __half* pa = reinterpret_cast<const __half*>(qkp + (size_t)ia * p.ldq + 2 * H * DQ + head * 4);
+    const __half* pb = reinterpret_cast<const __half*>(qkp + (size_t)ib * p.ldq + 2 * H * DQ + head * 4);
 #pragma unroll
-    for (int c = 0; c < 4; ++c) pq0[c] = __bfloat162float(pa[c]), pq1[c] = __bfloat162float(pb[c]);
+    for (int c = 0; c < 4; ++c) pq0[c] = __half2float(pa[c]), pq1[c] = __half2float(pb[c]);
   }
   float o[DV / 8][4];
 #pragma unroll
@@ -156,8 +163,8 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
       s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
       uint32_t kb[4];
       ldsm_x4(kb, &sm.k[buf][nt * 8 + (lane & 7)][(lane >> 3) * 8]);
-      mma_bf16(s[nt], qa[0], kb[0], kb[1]);
-      mma_bf16(s[nt], qa[1], kb[2], kb[3]);
+      mma_f16(s[nt], qa[0], kb[0], kb[1]);  // q, k, p are IEEE fp16 (attention in_proj epilogue)
+      mma_f16(s[nt], qa[1], kb[2], kb[3]);
     }
     // ---- position term, masks, running max.  Rows rl0 and rl1 = rl0 + 8 see the same relative offset
     // at columns 8 apart, so the table entry loaded for row rl0 in n-tile nt serves row rl1 in nt + 1.

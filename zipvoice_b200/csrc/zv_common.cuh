@@ -3,6 +3,7 @@
 // small math used by several kernels.
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -33,6 +34,10 @@ ZV_DEVINL float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.7071067
 
 ZV_DEVINL uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+ZV_DEVINL uint32_t pack_f16x2(float lo, float hi) {
+  __half2 v = __floats2half2_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
 ZV_DEVINL float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }

@@ -1,5 +1,6 @@
 // Test hooks: run a single GEMM / attention / position-table kernel on fp32 inputs supplied by the
 // caller (converted to the bf16 operand layout here).  Used by tests/ only.
+#include <cuda_fp16.h>
 #include <vector>
 
 #include "zv_common.cuh"
@@ -18,6 +19,10 @@ __global__ void cvt_pad_kernel(const float* __restrict__ in, int rows, int cols,
 __global__ void cvt_back_kernel(const __nv_bfloat16* __restrict__ in, size_t n, float* out) {
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid < n) out[gid] = __bfloat162float(in[gid]);
+}
+__global__ void cvt_f16_kernel(const float* __restrict__ in, size_t n, __half* out) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid < n) out[gid] = __float2half_rn(in[gid]);
 }
 static void cvt_pad(const float* in, int rows, int cols, int ld_in, __nv_bfloat16* out, int ld_out, cudaStream_t s) {
   const size_t n = (size_t)rows * ld_out;
@@ -79,7 +84,7 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
   cudaMalloc(&q, rows * ldq * 2);
   cudaMalloc(&v, rows * ldv * 2);
   cudaMalloc(&o, rows * ldv * 2);
-  cvt_pad(qkp_f32, (int)rows, ldq, ldq, q, ldq, s);
+  cvt_f16_kernel<<<(unsigned)((rows * ldq + 255) / 256), 256, 0, s>>>(qkp_f32, rows * ldq, reinterpret_cast<__half*>(q));
   cvt_pad(V_f32, (int)rows, ldv, ldv, v, ldv, s);
   if (gate_f32) {
     cudaMalloc(&g, rows * ldv * 2);

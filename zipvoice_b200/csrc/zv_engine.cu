@@ -399,7 +399,7 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   EpiParams ep;
   // attention projections from the layer input (before the time embedding is added) -- :526-531
   ep = EpiParams();
-  ep.L = L, ep.out_bf16 = ws.qkp, ep.ld_bf16 = 288;
+  ep.L = L, ep.out_bf16 = ws.qkp, ep.ld_bf16 = 288, ep.out_f16 = 1;  // q | k | p kept in fp16
   ZV_TRY(run_gemm(e, ly.attn_in, ws.shadow, D, M, ep, s));
 
   auto residual = [&](const Lin& lin, const __nv_bfloat16* A, int lda, const float* res, const float* resbias,

@@ -50,7 +50,12 @@ ZV_DEVINL void epi_apply(const EpiParams& ep, int m, int b, int n0, const float 
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
     }
-    if (nvalid == 32) {
+    if (MODE == EPI_BIAS_BF16 && ep.out_f16) {
+      __half* oh = reinterpret_cast<__half*>(o);
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i < nvalid) oh[i] = __float2half_rn(v[i]);
+    } else if (nvalid == 32) {
 #pragma unroll
       for (int i = 0; i < 32; i += 8) {
         uint4 p = make_uint4(pack_bf16x2(v[i], v[i + 1]), pack_bf16x2(v[i + 2], v[i + 3]),
@@ -206,6 +211,15 @@ ZV_DEVINL void stage_row_bf16x32(uint8_t* stg, int r, const float (&v)[32]) {
   for (int j = 0; j < 4; ++j) {
     uint4 p = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
                          pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+    *reinterpret_cast<uint4*>(stg + r * 64 + ((j ^ x) << 4)) = p;
+  }
+}
+ZV_DEVINL void stage_row_f16x32(uint8_t* stg, int r, const float (&v)[32]) {
+  const int x = (r >> 1) & 3;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint4 p = make_uint4(pack_f16x2(v[8 * j], v[8 * j + 1]), pack_f16x2(v[8 * j + 2], v[8 * j + 3]),
+                         pack_f16x2(v[8 * j + 4], v[8 * j + 5]), pack_f16x2(v[8 * j + 6], v[8 * j + 7]));
     *reinterpret_cast<uint4*>(stg + r * 64 + ((j ^ x) << 4)) = p;
   }
 }
@@ -459,6 +473,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         __syncwarp();
         named_bar_sync(bar_id, 128);
         if (gated) stage_row_bf16x16(sbuf, r, o16);
+        else if (MODE == EPI_BIAS_BF16 && ep.out_f16) stage_row_f16x32(sbuf, r, v);
         else stage_row_bf16x32(sbuf, r, v);
         fence_proxy_async_smem();
         named_bar_sync(bar_id, 128);

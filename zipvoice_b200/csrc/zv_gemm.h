@@ -29,6 +29,7 @@ struct EpiParams {
   int bias_ld = 0;                 // row pitch of rowbias / resbias (per batch element)
   __nv_bfloat16* out_bf16 = nullptr;
   int ld_bf16 = 0;
+  int out_f16 = 0;    // EPI_BIAS_BF16 only: store IEEE fp16 instead of bf16 (attention q / k / p: 11-bit mantissa)
   __nv_bfloat16* out2_bf16 = nullptr;
   int ld2_bf16 = 0;
   float* out_f32 = nullptr;

@@ -49,7 +49,7 @@ int sgemm_nn(const float* A, const float* B, float* C, int M, int N, int K, cuda
 int pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E, cudaStream_t s);
 
 struct AttnParams {
-  const __nv_bfloat16* qkp;  // [nb][L][ldq]: q at h*dq, k at H*dq + h*dq, p at 2*H*dq + h*dp
+  const __nv_bfloat16* qkp;  // IEEE fp16 bit patterns (not bf16) [nb][L][ldq]: q at h*dq, k at H*dq + h*dq, p at 2*H*dq + h*dp
   int ldq;
   const float* E;            // [H][2L-1][4]
   const uint8_t* mask;       // [nb][L] 1 = padded key (may be null)

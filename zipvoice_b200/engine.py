@@ -155,6 +155,29 @@ class Engine:
                                                    _ptr(out), _ptr(mask), _stream(self.device)))
         return out, mask.bool()
 
+    # ------------------------------------------------------------------ audio front-end / vocoder
+    def fbank(self, wav: torch.Tensor, lens: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """VocosFbank log-mel (feature.py:56-116): wav (B, N) fp32 24 kHz mono -> (B, (N + 128) // 256, 100)."""
+        w = self._prep(wav)
+        B, N = w.shape
+        ln = None if lens is None else self._prep(lens, torch.int64)
+        T = (N + 128) // 256
+        out = torch.empty(B, T, 100, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.zv_fbank(self._h, _ptr(w), _ptr(ln), B, N, _ptr(out), _stream(self.device)))
+        return out
+
+    def vocos_decode(self, mel: torch.Tensor, lens: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Vocos.decode: mel (B, 100, T) -> waveform (B, 256 (T - 1)); needs "vocoder.*" weights."""
+        m = self._prep(mel)
+        B, C, T = m.shape
+        assert C == 100
+        ln = None if lens is None else self._prep(lens, torch.int64)
+        out = torch.empty(B, 256 * (T - 1), device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.zv_vocos_decode(self._h, _ptr(m), _ptr(ln), B, T, _ptr(out), _stream(self.device)))
+        return out
+
     def prof_enable(self, on: bool = True):
         self._check(self.lib.zv_prof_enable(self._h, int(on)))
 
