@@ -31,8 +31,9 @@ def test_fbank_reference_golden():
     from zipvoice_b200 import synth
     fb, _, _ = audio()
     g = np.load(os.path.join(GOLDEN, "fbank.npz"))
-    for name, n in (("a", 72000), ("b", 24000 + 77), ("c", 30000 + 200)):
-        wav = synth.make_audio(1, n, seed=7 + n)
+    for name in ("a", "b", "c"):
+        wav = torch.from_numpy(g["wav_" + name])
+        n = wav.shape[1]
         mel = fb.extract(wav, 24000).cpu()
         want = torch.from_numpy(g["mel_" + name])
         assert mel.shape == want.shape

@@ -14,6 +14,9 @@ from tests.conftest import GOLDEN
 pytestmark = pytest.mark.gpu
 
 TOL_NFE = 5e-3
+# the 4x-amplified "stress" weights at T = 300 with CFG (two network passes combined as 2 c - u): measured
+# 5.4e-3 (bf16 operand rounding; fp16 q/k/p moved it by 2 %), init-like weights stay below TOL_NFE
+TOL_NFE_STRESS_CFG = 7e-3
 TOL_MEL = 1e-2
 
 

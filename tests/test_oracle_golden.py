@@ -83,8 +83,9 @@ def test_fbank_oracle_vs_reference_golden():
     """oracle/fbank_oracle.py against VocosFbank.extract of the unmodified reference (lhotse shimmed)."""
     from oracle import fbank_oracle as FO
     g = _g("fbank.npz")
-    for name, n in (("a", 72000), ("b", 24000 + 77), ("c", 30000 + 200)):
-        wav = synth.make_audio(1, n, seed=7 + n)
+    for name in ("a", "b", "c"):
+        wav = g["wav_" + name]
+        n = wav.shape[1]
         mel = FO.vocos_fbank(wav[0])
         assert mel.shape == g["mel_" + name].shape == (FO.num_frames(n), 100)
         assert float((mel - g["mel_" + name]).abs().max()) < 1e-4
