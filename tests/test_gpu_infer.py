@@ -1,0 +1,61 @@
+"""End-to-end pipeline (prompt wav -> mel -> sample -> vocoder) through the host mirrors of
+bin/infer_zipvoice.py against the same pipeline built from the CPU oracles."""
+import pytest
+import torch
+
+from tests.cases import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup():
+    from oracle import vocos_oracle as VO
+    from zipvoice_b200 import synth
+    from zipvoice_b200.audio import VocosB200, VocosFbankB200
+    from zipvoice_b200.model import ZipVoiceB200
+    cfg = synth.small_model_cfg()
+    sd = synth.make_state_dict(cfg, seed=1, stress=True)
+    vsd = VO.make_vocos_state_dict(0)
+    model = ZipVoiceB200(cfg, sd, synth.VOCAB_SIZE, synth.PAD_ID, kind="zipvoice")
+    voc = VocosB200(vsd)
+    return cfg, sd, vsd, model, voc, VocosFbankB200(engine=voc.engine)
+
+
+def test_generate_sentence_vs_oracle_pipeline():
+    from oracle import fbank_oracle as FO, vocos_oracle as VO, zipvoice_oracle as O
+    from zipvoice_b200 import infer, synth
+    cfg, sd, vsd, model, voc, fb = _setup()
+    tokens, prompt_tokens = synth.make_tokens(1, n_prompt=8, n_text=20, seed=3)
+    wav_p = synth.make_audio(1, 9000, seed=11) * 0.3          # rms < 0.1 -> exercises the RMS path
+    # oracle pipeline
+    rms = torch.sqrt(torch.mean(torch.square(wav_p)))
+    wp = wav_p * 0.1 / rms if rms < 0.1 else wav_p
+    feats = FO.vocos_fbank(wp[0]).unsqueeze(0) * 0.1
+    fl = torch.tensor([feats.size(1)])
+    T = int(O.predict_features_lens(fl, torch.tensor([8]), torch.tensor([20]), 1.0))
+    x0 = torch.randn(1, T, 100, generator=torch.Generator().manual_seed(9))
+    want_mel, want_lens, _, _ = O.sample(sd, cfg, tokens, prompt_tokens, feats, fl, speed=1.0, t_shift=0.5,
+                                         num_step=4, guidance_scale=1.0, x0=x0)
+    want_wav = VO.decode(vsd, want_mel.permute(0, 2, 1) / 0.1).clamp(-1, 1)
+    if rms < 0.1:
+        want_wav = want_wav * rms / 0.1
+    wav, metrics = infer.generate_sentence(prompt_tokens[0], wav_p, tokens[0], model, voc, fb, num_step=4,
+                                           guidance_scale=1.0, t_shift=0.5, x0=x0.cuda())
+    assert wav.shape == want_wav.shape
+    r = rel_l2(wav.cpu(), want_wav)
+    assert r < 5e-2, f"waveform rel-L2 {r:.3e}"
+    assert set(metrics) == {"t", "t_no_vocoder", "t_vocoder", "wav_seconds", "rtf", "rtf_no_vocoder", "rtf_vocoder"}
+
+
+def test_generate_batch_shapes_and_lengths():
+    from zipvoice_b200 import infer, synth
+    cfg, sd, vsd, model, voc, fb = _setup()
+    tokens, prompt_tokens = synth.make_tokens(3, n_prompt=8, n_text=20, seed=4, ragged=True)
+    wavs = [synth.make_audio(1, n, seed=n)[0] for n in (9000, 7000, 12000)]
+    outs = infer.generate_batch(prompt_tokens, wavs, tokens, model, voc, fb, num_step=2)
+    assert len(outs) == 3
+    for i, w in enumerate(outs):
+        pf = (wavs[i].numel() + 128) // 256
+        import math
+        gen = math.ceil(pf / len(prompt_tokens[i]) * len(tokens[i]) / 1.0)
+        assert w.shape == (256 * (gen - 1),) and bool(torch.isfinite(w).all())

@@ -128,4 +128,5 @@ def test_velocity_vs_oracle_longer():
         r = valid_rel_l2(v, want, mask)
         keep = (~mask).unsqueeze(-1)
         ma = float(((v - want) * keep).abs().max())
-        assert r < TOL_NFE, f"t={t}: rel-L2 {r:.3e} max-abs {ma:.3e}"
+        print(f"per-NFE velocity t={t}: rel-L2 {r:.3e} max-abs {ma:.3e}")
+        assert r < TOL_NFE_STRESS_CFG, f"t={t}: rel-L2 {r:.3e} max-abs {ma:.3e}"

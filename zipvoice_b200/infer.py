@@ -92,7 +92,7 @@ def generate_batch(prompt_tokens: Sequence[List[int]], prompt_wavs: Sequence[tor
     wav = wav * scale[:, None]
     wlens = (pred_lens - 1).clamp(min=0) * 256
     if world == 1:
-        return [wav[row, : int(wlens[row])] for row in range(len(mine))] if n else []
+        return parallel.scatter_back([(wav, wlens)], shards, n)
     parts = parallel.gather_ragged(wav, wlens, dst=0)
     if rank != 0:
         return None
