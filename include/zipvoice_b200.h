@@ -45,7 +45,8 @@ int zv_set_weight(void* handle, const char* name, const float* data, const int64
  * time-embedding projections).  Fails if a tensor of the architecture is missing. */
 int zv_finalize_weights(void* handle);
 
-/* options: "gemm_impl" 0 = tcgen05 kernel (default), 1 = SIMT checker kernel (tests only). */
+/* options: "gemm_impl" 0 = tcgen05 kernel (default), 1 = SIMT checker kernel (tests only);
+ * "attn_impl" 0 = NonlinAttention on the tcgen05 kernel (default), 1 = mma.sync flash kernel (process-wide). */
 int zv_set_option(void* handle, const char* key, int value);
 
 /* get_time_steps (models/modules/solver.py:256-281), fp32 arithmetic identical to torch
@@ -97,6 +98,7 @@ int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int gate_cols,
 int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp_f32, int ldq, const float* E,
                        const uint8_t* mask, const float* V_f32, int ldv, const float* gate_f32, float* out_f32,
                        void* stream);
+int zv_debug_set_attn_impl(int impl);
 int zv_debug_pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E_out, void* stream);
 /* Per-kernel-class device timing: when enabled every launch is bracketed by CUDA events on its stream.
  * zv_prof_read synchronises the device, fills ms / work / launches (arrays of zv_prof_num_classes()) and

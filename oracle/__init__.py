@@ -7,10 +7,13 @@ Nothing under ``oracle/`` is part of the shipped product.  Only ``tests/``,
 Parity status: PINNED for the model path (text encoder, fm_decoder, CFG wrapper,
 Euler solver, text-condition helpers, dialog speaker embedding) and for the
 VocosFbank mel front-end: ``oracle/make_golden.py`` imports the unmodified
-reference from /root/reference in the build container, feeds it the weights of
-``oracle.weights.make_state_dict`` and stores its outputs under ``tests/golden``;
+reference from /root/reference in the build container (``lhotse`` / ``librosa`` replaced
+by the stand-ins in ``oracle/shims``), feeds it the weights of
+``zipvoice_b200.synth.make_state_dict`` and stores its outputs under ``tests/golden``;
 ``tests/test_oracle_golden.py`` checks this restatement against those files.
-Parity UNPINNED for the Vocos vocoder (third-party ``vocos`` package, not vendored
+Parity UNPINNED for (i) the Vocos vocoder (third-party ``vocos`` package, not vendored
 in the reference, no weights, no tests): ``oracle/vocos_oracle.py`` restates the
-published architecture and is its own oracle.
+published architecture and is its own oracle; (ii) the one-frame boundary of lhotse's
+``compute_num_frames`` (source absent, restated as round-half-up in ``fbank_oracle``).
+The reference is Python: there is no compiled ``oracle/_ref``.
 """

@@ -152,9 +152,11 @@ def ref_attention(qkp, E, mask, V, gate, H, heads, dv):
 
 
 @pytest.mark.parametrize("L", [1, 37, 64, 130, 611])
-@pytest.mark.parametrize("kind", ["self", "nonlin384", "nonlin144"])
+@pytest.mark.parametrize("kind", ["self", "nonlin384", "nonlin144", "nonlin384_mma", "nonlin144_mma"])
 def test_attention(L, kind):
     H, nb = 4, 3
+    _lib().zv_debug_set_attn_impl(1 if kind.endswith("_mma") else 0)
+    kind = kind.replace("_mma", "")
     g = torch.Generator(device="cuda").manual_seed(L)
     rn = lambda *s: torch.randn(*s, device="cuda", generator=g)
     qkp = (rn(nb, L, 288) * 0.7).bfloat16().float()
@@ -168,6 +170,7 @@ def test_attention(L, kind):
     out = torch.zeros(nb, L, ldv, device="cuda")
     rc = _lib().zv_debug_attention(nb, L, H, heads, dv, _p(qkp), 288, _p(E), _p(mask), _p(V), ldv, _p(gate), _p(out),
                                    None)
+    _lib().zv_debug_set_attn_impl(0)
     assert rc == 0
     want = ref_attention(qkp, E, mask, V, gate, H, heads, dv)
     r = rel(out, want)

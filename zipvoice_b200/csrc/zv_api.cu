@@ -7,6 +7,9 @@
 #include "zv_engine.h"
 
 using namespace zv;
+namespace zv {
+extern int g_attn_impl;
+}
 
 static thread_local std::string g_err;
 static const char* kNullHandle = "null handle";
@@ -136,6 +139,7 @@ int zv_set_option(void* handle, const char* key, int value) {
   Engine* e = (Engine*)handle;
   if (!e) return 960;
   if (!strcmp(key, "gemm_impl")) e->gemm_impl = value;
+  else if (!strcmp(key, "attn_impl")) zv::g_attn_impl = value;  // process-wide
   else {
     e->err = std::string("unknown option ") + key;
     return 962;

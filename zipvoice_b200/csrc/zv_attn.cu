@@ -286,7 +286,14 @@ static int launch_attn(const AttnParams& p, int chunks, int dv_valid, cudaStream
   return (int)cudaGetLastError();
 }
 
+int attention_na_tc(const AttnParams& p, cudaStream_t s);
+int g_attn_impl = 0;  // 0: NonlinAttention on the tcgen05 kernel (zv_attn_tc.cu); 1: mma.sync flash kernel everywhere
+
 int attention(const AttnParams& p, cudaStream_t s) {
+  if (p.heads == 1 && g_attn_impl == 0) {
+    const int rc = attention_na_tc(p, s);
+    if (rc >= 0) return rc;
+  }
   if (p.dv == 12) return launch_attn<16>(p, 1, 12, s);
   if (p.dv % 192 == 0) return launch_attn<192>(p, p.dv / 192, 192, s);
   if (p.dv % 128 == 0) return launch_attn<128>(p, p.dv / 128, 128, s);

@@ -1,0 +1,338 @@
+// NonlinAttention value product on tcgen05 (zipformer.py:1499-1544 with the head-0 weights of
+// RelPositionMultiheadAttentionWeights, :542,1529-1536):  O = softmax(q k^T + p.E) X * y,  X up to 384 wide.
+//
+// CTA = 128 queries of one sequence.  The scores are cheap (dq = 32) but every one needs the
+// relative-position term and an exponential on the CUDA cores, while A.X is a 128 x 384 x L product:
+//   sweep 1: S tiles (mma.sync fp16 + position term) -> exact row maxima, nothing stored;
+//   sweep 2: S again, P = exp(S - max) as bf16 into a SWIZZLE_128B K-major shared-memory tile, and ONE
+//            thread issues tcgen05.mma  O[128 x 384] += P[128 x 64] X[64 x 384]  with X tiles TMA-loaded as
+//            MN-major operands (the row-major [key][channel] layout is used as is); O stays in TMEM for the
+//            whole key loop -- no online-softmax rescaling -- and is normalised by the row sums at the end.
+// 16 compute warps (8 row groups x 2 key halves of each 64-key tile) + 1 producer warp (TMA + MMA issue).
+#include <cuda.h>
+
+#include "zv_common.cuh"
+#include "zv_gemm.h"
+#include "zv_kernels.h"
+
+namespace zv {
+
+namespace natc {
+
+static constexpr int BQ = 128, BKV = 64, DQ = 32, QP = DQ + 8, EWIN = 192;
+static constexpr int VSTAGES = 3, NVBOX = 6;  // up to 6 boxes of 64 channels = 384
+static constexpr int COMPUTE_THREADS = 512, THREADS = COMPUTE_THREADS + 32;
+
+struct Smem {
+  bf16 v[VSTAGES][NVBOX][BKV][64];  // MN-major SWIZZLE_128B boxes: [key][64 channels] = 8 KB each
+  bf16 p[2][BQ][BKV];               // K-major SWIZZLE_128B: [query][64 keys]
+  __half q[BQ][QP];
+  __half k[2][BKV][QP];
+  float4 e[2][EWIN];
+  float red[2][BQ];                 // cross-warp (key half) reductions of max / sum
+  uint8_t m[2][BKV];
+  int mflag[2];
+  uint64_t vfull[VSTAGES], vfree[VSTAGES], pfull[2], pfree[2], obar;
+  uint32_t tmem_base;
+};
+
+ZV_DEVINL void cp_async16(void* dst, const void* src, bool valid) {
+  const int sz = valid ? 16 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
+}
+ZV_DEVINL void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+ZV_DEVINL void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+ZV_DEVINL void ldsm_x4(uint32_t (&r)[4], const void* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(smem_u32(p)));
+}
+ZV_DEVINL void mma_f16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// MN-major SWIZZLE_128B operand: 64 MN-elements (128 B) per K row, 8 K rows per 1024-byte swizzle atom
+// (SBO), 64-element MN blocks LBO bytes apart  (cute mma_traits_sm100.hpp, UmmaDescriptor Major-MN, B128).
+ZV_DEVINL uint64_t make_sdesc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+// kind::f16 instruction descriptor, A = bf16 K-major, B = bf16 MN-major (bit 16), D = fp32
+ZV_DEVINL uint32_t make_idesc_bf16_bmn(uint32_t M, uint32_t N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+
+// Scores of this warp's 16 rows x 32 keys of the staged tile: s[nt4][0..1] row g, [2..3] row g + 8.
+// Returns the two row maxima through mx0 / mx1.
+ZV_DEVINL void score_tile(const Smem& sm, int buf, int kh, int lane, int rl0, const uint32_t (&qa)[2][4],
+                          const float (&pq0)[4], const float (&pq1)[4], float (&s)[4][4], float& mx0, float& mx1) {
+  const int qd = lane & 3;
+#pragma unroll
+  for (int n4 = 0; n4 < 4; ++n4) {
+    const int nt = kh * 4 + n4;
+    s[n4][0] = s[n4][1] = s[n4][2] = s[n4][3] = 0.f;
+    uint32_t kb[4];
+    ldsm_x4(kb, &sm.k[buf][nt * 8 + (lane & 7)][(lane >> 3) * 8]);
+    mma_f16(s[n4], qa[0], kb[0], kb[1]);
+    mma_f16(s[n4], qa[1], kb[2], kb[3]);
+  }
+  const float4* ew = &sm.e[buf][kh * 32 + 2 * qd - rl0 + (BQ - 1)];
+  float4 ep0 = ew[-8], ep1 = ew[-7];
+  const bool masked = sm.mflag[buf] != 0;
+  mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+  for (int n4 = 0; n4 < 4; ++n4) {
+    const float4 ec0 = ew[n4 * 8], ec1 = ew[n4 * 8 + 1];
+    float a0 = s[n4][0] + pq0[0] * ec0.x + pq0[1] * ec0.y + pq0[2] * ec0.z + pq0[3] * ec0.w;
+    float a1 = s[n4][1] + pq0[0] * ec1.x + pq0[1] * ec1.y + pq0[2] * ec1.z + pq0[3] * ec1.w;
+    float b0 = s[n4][2] + pq1[0] * ep0.x + pq1[1] * ep0.y + pq1[2] * ep0.z + pq1[3] * ep0.w;
+    float b1 = s[n4][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
+    if (masked) {
+      const uint8_t k0 = sm.m[buf][kh * 32 + n4 * 8 + 2 * qd], k1 = sm.m[buf][kh * 32 + n4 * 8 + 2 * qd + 1];
+      if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
+      if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
+    }
+    s[n4][0] = a0, s[n4][1] = a1, s[n4][2] = b0, s[n4][3] = b1;
+    mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
+    ep0 = ec0, ep1 = ec1;
+  }
+}
+
+}  // namespace natc
+
+using namespace natc;
+
+__global__ void __launch_bounds__(natc::THREADS, 1)
+attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvbox, int n_mma0, int n_mma1) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.y;
+  const int i0 = blockIdx.x * BQ;
+  const int L = p.L, H = p.H, R = 2 * L - 1;
+  const int n_tiles = (L + BKV - 1) / BKV;
+  const __half* qkp = reinterpret_cast<const __half*>(p.qkp) + (size_t)b * L * p.ldq;  // head 0
+  const float4* E = reinterpret_cast<const float4*>(p.E);
+  const uint8_t* mask = p.mask ? p.mask + (size_t)b * L : nullptr;
+  const uint32_t v_stage_bytes = (uint32_t)nvbox * BKV * 64 * 2;
+
+  if (tid == 0) {
+    for (int i = 0; i < VSTAGES; ++i) mbar_init(&sm.vfull[i], 1), mbar_init(&sm.vfree[i], 1);
+    for (int i = 0; i < 2; ++i) mbar_init(&sm.pfull[i], COMPUTE_THREADS), mbar_init(&sm.pfree[i], 1);
+    mbar_init(&sm.obar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 16) tmem_alloc(&sm.tmem_base, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sm.tmem_base;
+
+  if (warp == 16) {
+    // ---------------- producer: X tiles by TMA, P.X by tcgen05.mma
+    if (lane == 0) {
+      tma_prefetch_desc(&tmV);
+      auto load_v = [&](int kt) {
+        const int st = kt % VSTAGES;
+        mbar_arrive_expect_tx(&sm.vfull[st], v_stage_bytes);
+        for (int c = 0; c < nvbox; ++c)
+          tma_load_2d(&sm.v[st][c][0][0], &tmV, &sm.vfull[st], c * 64, b * L + kt * BKV);
+      };
+      for (int kt = 0; kt < min(2, n_tiles); ++kt) load_v(kt);
+      const uint32_t id0 = make_idesc_bf16_bmn(BQ, n_mma0), id1 = make_idesc_bf16_bmn(BQ, max(n_mma1, 16));
+      for (int kt = 0; kt < n_tiles; ++kt) {
+        if (kt + 2 < n_tiles) {
+          if (kt >= 1) mbar_wait(&sm.vfree[(kt + 2) % VSTAGES], ((kt - 1) / VSTAGES) & 1);  // tile kt-1 consumed
+          load_v(kt + 2);
+        }
+        const int st = kt % VSTAGES, pb = kt & 1;
+        mbar_wait(&sm.vfull[st], (kt / VSTAGES) & 1);
+        mbar_wait(&sm.pfull[pb], (kt >> 1) & 1);
+        tc_fence_after();
+        const uint64_t da = make_sdesc_sw128(smem_u32(&sm.p[pb][0][0]));
+        const uint32_t vaddr = smem_u32(&sm.v[st][0][0][0]);
+#pragma unroll
+        for (int k = 0; k < BKV / 16; ++k) {
+          const uint64_t db0 = make_sdesc_mn_sw128(vaddr + k * 2048, BKV * 128, 1024);
+          umma_bf16(tmem_base, da + 2 * k, db0, id0, (kt | k) != 0 ? 1u : 0u);
+          if (n_mma1 > 0) {
+            const uint64_t db1 = make_sdesc_mn_sw128(vaddr + (n_mma0 / 64) * (BKV * 128) + k * 2048, BKV * 128, 1024);
+            umma_bf16(tmem_base + n_mma0, da + 2 * k, db1, id1, (kt | k) != 0 ? 1u : 0u);
+          }
+        }
+        umma_commit(&sm.vfree[st]);
+        umma_commit(&sm.pfree[pb]);
+        if (kt == n_tiles - 1) umma_commit(&sm.obar);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---------------- compute warps
+    const int rg = warp & 7, kh = warp >> 3;
+    const int g = lane >> 2, qd = lane & 3;
+    const int rl0 = rg * 16 + g, rl1 = rl0 + 8;
+    auto cbar = [] { named_bar_sync(1, COMPUTE_THREADS); };
+    // Q tile (once)
+    for (int c = tid; c < BQ * (DQ / 8); c += COMPUTE_THREADS) {
+      const int r = c / (DQ / 8), cc = c % (DQ / 8);
+      const int i = i0 + r;
+      cp_async16(&sm.q[r][cc * 8], qkp + (size_t)min(i, L - 1) * p.ldq + cc * 8, i < L);
+    }
+    auto load_tile = [&](int kt, int buf) {
+      const int j0 = kt * BKV;
+      if (tid < 256) {  // K: 64 rows x 4 chunks of 16 B
+        const int r = tid >> 2, cc = tid & 3;
+        const int j = j0 + r;
+        cp_async16(&sm.k[buf][r][cc * 8], qkp + (size_t)min(j, L - 1) * p.ldq + H * DQ + cc * 8, j < L);
+      } else if (tid < 256 + EWIN) {
+        const int w = tid - 256;
+        const int rr = (j0 - i0 - (BQ - 1)) + (L - 1) + w;
+        const bool ok = rr >= 0 && rr < R;
+        cp_async16(&sm.e[buf][w], E + (ok ? rr : 0), ok);
+      } else if (tid >= 480) {  // warp 15: two keys per lane
+        const int ja = j0 + lane, jb = j0 + lane + 32;
+        const uint8_t ka = (ja < L) ? (mask ? mask[ja] : 0) : 2;
+        const uint8_t kb = (jb < L) ? (mask ? mask[jb] : 0) : 2;
+        sm.m[buf][lane] = ka, sm.m[buf][lane + 32] = kb;
+        const unsigned any = __ballot_sync(0xffffffffu, (ka | kb) != 0);
+        if (lane == 0) sm.mflag[buf] = any != 0;
+      }
+    };
+    float pq0[4], pq1[4];
+    {
+      const __half* pa = qkp + (size_t)min(i0 + rl0, L - 1) * p.ldq + 2 * H * DQ;
+      const __half* pb = qkp + (size_t)min(i0 + rl1, L - 1) * p.ldq + 2 * H * DQ;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) pq0[c] = __half2float(pa[c]), pq1[c] = __half2float(pb[c]);
+    }
+    uint32_t qa[2][4];
+    float s[4][4];
+    const float LOG2E = 1.4426950408889634f;
+    float m0 = -INFINITY, m1 = -INFINITY;
+    // ---- sweep 1: exact row maxima
+    load_tile(0, 0);
+    cp_async_commit();
+    for (int kt = 0; kt < n_tiles; ++kt) {
+      const int buf = kt & 1;
+      if (kt + 1 < n_tiles) load_tile(kt + 1, buf ^ 1);
+      cp_async_commit();
+      cp_async_wait<1>();
+      cbar();
+      if (kt == 0) {
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks) ldsm_x4(qa[ks], &sm.q[rg * 16 + (lane & 15)][ks * 16 + (lane >> 4) * 8]);
+      }
+      float mx0, mx1;
+      score_tile(sm, buf, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+      m0 = fmaxf(m0, mx0), m1 = fmaxf(m1, mx1);
+      cbar();
+    }
+    m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)), m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)), m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+    if (qd == 0) sm.red[kh][rl0] = m0, sm.red[kh][rl1] = m1;
+    cbar();
+    m0 = fmaxf(sm.red[0][rl0], sm.red[1][rl0]), m1 = fmaxf(sm.red[0][rl1], sm.red[1][rl1]);
+    cbar();
+    const float ms0 = m0 * LOG2E, ms1 = m1 * LOG2E;
+    // ---- sweep 2: P = exp(S - max) -> shared memory -> tcgen05.mma
+    float l0 = 0.f, l1 = 0.f;
+    load_tile(0, 0);
+    cp_async_commit();
+    for (int kt = 0; kt < n_tiles; ++kt) {
+      const int buf = kt & 1;
+      if (kt + 1 < n_tiles) load_tile(kt + 1, buf ^ 1);
+      cp_async_commit();
+      cp_async_wait<1>();
+      cbar();
+      float mx0, mx1;
+      score_tile(sm, buf, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+      if (kt >= 2) mbar_wait(&sm.pfree[buf], ((kt >> 1) - 1) & 1);  // the MMAs of tile kt-2 have read p[buf]
+      uint8_t* prow0 = reinterpret_cast<uint8_t*>(&sm.p[buf][rl0][0]);
+      uint8_t* prow1 = reinterpret_cast<uint8_t*>(&sm.p[buf][rl1][0]);
+#pragma unroll
+      for (int n4 = 0; n4 < 4; ++n4) {
+        const float a0 = ex2_approx(fmaf(s[n4][0], LOG2E, -ms0)), a1 = ex2_approx(fmaf(s[n4][1], LOG2E, -ms0));
+        const float b0 = ex2_approx(fmaf(s[n4][2], LOG2E, -ms1)), b1 = ex2_approx(fmaf(s[n4][3], LOG2E, -ms1));
+        l0 += a0 + a1, l1 += b0 + b1;
+        const int chunk = kh * 4 + n4;  // 16-byte chunk = 8 keys
+        *reinterpret_cast<uint32_t*>(prow0 + ((chunk ^ (rl0 & 7)) << 4) + qd * 4) = pack_bf16x2(a0, a1);
+        *reinterpret_cast<uint32_t*>(prow1 + ((chunk ^ (rl1 & 7)) << 4) + qd * 4) = pack_bf16x2(b0, b1);
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(&sm.pfull[buf]);
+      cbar();
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1), l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1), l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    if (qd == 0) sm.red[kh][rl0] = l0, sm.red[kh][rl1] = l1;
+    cbar();
+    // ---- epilogue: O / l * gate -> bf16.  Warp w reads TMEM lane quarter w % 4, column slice w / 4.
+    mbar_wait(&sm.obar, 0);
+    tc_fence_after();
+    const int q4 = warp & 3, cs = warp >> 2;
+    const int row = q4 * 32 + lane;
+    const int i = i0 + row;
+    const float inv = 1.0f / (sm.red[0][row] + sm.red[1][row]);
+    const int ncols = nvbox * 64;
+    for (int c0 = cs * 32; c0 < ncols; c0 += 128) {
+      uint32_t raw[32];
+      tmem_ld32(tmem_base + (static_cast<uint32_t>(q4 * 32) << 16) + c0, raw);
+      tmem_ld_wait();
+      if (i < L && c0 < p.dv) {
+        const size_t grow = (size_t)b * L + i;
+        const bf16* gp = p.gate ? p.gate + grow * p.ldg + c0 : nullptr;
+        bf16* op = p.out + grow * p.ldo + c0;
+#pragma unroll
+        for (int jj = 0; jj < 32; jj += 8) {
+          if (c0 + jj >= p.dv) break;
+          float v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) v[u] = __uint_as_float(raw[jj + u]) * inv;
+          if (gp) {
+            const uint4 gv = *reinterpret_cast<const uint4*>(gp + jj);
+            v[0] *= bf16_lo(gv.x), v[1] *= bf16_hi(gv.x), v[2] *= bf16_lo(gv.y), v[3] *= bf16_hi(gv.y);
+            v[4] *= bf16_lo(gv.z), v[5] *= bf16_hi(gv.z), v[6] *= bf16_lo(gv.w), v[7] *= bf16_hi(gv.w);
+          }
+          *reinterpret_cast<uint4*>(op + jj) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                          pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 16) tmem_dealloc(tmem_base, 512);
+}
+
+// Host launcher; returns -1 if the shape is not supported by this kernel (caller falls back to attn_kernel).
+int attention_na_tc(const AttnParams& p, cudaStream_t s) {
+  if (p.heads != 1 || p.dv % 8 || p.dv > 384 || p.ldv % 8 || p.ldo % 8 || (p.gate && p.ldg % 8)) return -1;
+  const int nvbox = (p.dv + 63) / 64;
+  const int ncols = nvbox * 64;
+  const int n0 = ncols > 256 ? 256 : ncols, n1 = ncols - n0;
+  CUtensorMap tmV;
+  int rc = make_tmap(&tmV, p.V, 0, (uint64_t)p.nb * p.L, (uint64_t)p.dv, (uint64_t)p.ldv, BKV, 64, 128);
+  if (rc) return rc;
+  static bool attr = false;
+  const int smem = (int)sizeof(Smem) + 1024;
+  if (!attr) {
+    cudaFuncSetAttribute(attn_na_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    attr = true;
+  }
+  dim3 grid((p.L + BQ - 1) / BQ, p.nb);
+  attn_na_tc_kernel<<<grid, THREADS, smem, s>>>(tmV, p, nvbox, n0, n1);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace zv

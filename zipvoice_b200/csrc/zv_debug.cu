@@ -104,6 +104,14 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
   return rc;
 }
 
+namespace zv {
+extern int g_attn_impl;
+}
+extern "C" int zv_debug_set_attn_impl(int v) {
+  zv::g_attn_impl = v;
+  return 0;
+}
+
 extern "C" int zv_debug_pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E_out, void* stream) {
   int rc = pos_table(W, H, dp, pos_dim, L, E_out, (cudaStream_t)stream);
   if (!rc) rc = (int)cudaStreamSynchronize((cudaStream_t)stream);

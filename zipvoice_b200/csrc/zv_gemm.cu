@@ -552,7 +552,7 @@ struct TmapKeyHash {
 };
 static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
 
-static int make_tmap(CUtensorMap* tm, const void* ptr, int dtype /*0 bf16, 1 fp32*/, uint64_t rows, uint64_t cols,
+static int make_tmap_impl(CUtensorMap* tm, const void* ptr, int dtype /*0 bf16, 1 fp32*/, uint64_t rows, uint64_t cols,
                      uint64_t ld, uint32_t box_rows, uint32_t box_cols, int swizzle /*32, 64, 128*/) {
   const TmapKey key{ptr, rows, cols, ld, box_rows, box_cols, dtype, swizzle};
   auto it = g_tmap_cache.find(key);
@@ -577,6 +577,11 @@ static int make_tmap(CUtensorMap* tm, const void* ptr, int dtype /*0 bf16, 1 fp3
   if (g_tmap_cache.size() > 4096) g_tmap_cache.clear();
   g_tmap_cache.emplace(key, *tm);
   return 0;
+}
+
+int make_tmap(void* tm, const void* ptr, int dtype, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+              uint32_t box_cols, int swizzle) {
+  return make_tmap_impl(static_cast<CUtensorMap*>(tm), ptr, dtype, rows, cols, ld, box_rows, box_cols, swizzle);
 }
 
 int gemm_pick_block_n(int n_valid, int mode, int gate_cols) {
@@ -614,24 +619,24 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
   }
   GemmMaps maps;
   memset(&maps, 0, sizeof(maps));
-  int rc = make_tmap(&maps.A, A, 0, (uint64_t)p.M, (uint64_t)p.K, (uint64_t)p.lda, BM, 64, 128);
+  int rc = make_tmap_impl(&maps.A, A, 0, (uint64_t)p.M, (uint64_t)p.K, (uint64_t)p.lda, BM, 64, 128);
   if (rc) return rc;
-  rc = make_tmap(&maps.W, W, 0, (uint64_t)p.N_pad, (uint64_t)p.K, (uint64_t)p.ldw, (uint32_t)p.block_n, 64, 128);
+  rc = make_tmap_impl(&maps.W, W, 0, (uint64_t)p.N_pad, (uint64_t)p.K, (uint64_t)p.ldw, (uint32_t)p.block_n, 64, 128);
   if (rc) return rc;
   const uint64_t Mu = (uint64_t)ep.M;
   if (MODE == EPI_BIAS_BF16 || MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GELU_BF16) {
-    rc = make_tmap(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, BM, 32, 64);
+    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, BM, 32, 64);
   } else if (MODE == EPI_GLU_BF16) {
-    rc = make_tmap(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N / 2, (uint64_t)ep.ld_bf16, BM, 16, 32);
+    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N / 2, (uint64_t)ep.ld_bf16, BM, 16, 32);
   } else if (MODE == EPI_NONLIN_BF16) {
-    rc = make_tmap(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.gate_cols / 2, (uint64_t)ep.ld_bf16, BM, 16, 32);
+    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.gate_cols / 2, (uint64_t)ep.ld_bf16, BM, 16, 32);
     if (!rc && ep.N > ep.gate_cols)
-      rc = make_tmap(&maps.O1, ep.out2_bf16, 0, Mu, (uint64_t)(ep.N - ep.gate_cols), (uint64_t)ep.ld2_bf16, BM, 32, 64);
+      rc = make_tmap_impl(&maps.O1, ep.out2_bf16, 0, Mu, (uint64_t)(ep.N - ep.gate_cols), (uint64_t)ep.ld2_bf16, BM, 32, 64);
   } else if (MODE == EPI_RESIDUAL) {
-    rc = make_tmap(&maps.O1, ep.out_f32, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, BM, 32, 128);
-    if (!rc) rc = make_tmap(&maps.R, ep.res, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, BM, 32, 128);
+    rc = make_tmap_impl(&maps.O1, ep.out_f32, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, BM, 32, 128);
+    if (!rc) rc = make_tmap_impl(&maps.R, ep.res, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, BM, 32, 128);
     if (!rc && ep.out_bf16)
-      rc = make_tmap(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, BM, 32, 64);
+      rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, BM, 32, 64);
   }
   if (rc) return rc;
   const int w_stage = p.block_n * BK * 2;
