@@ -52,11 +52,11 @@ ZV_DEVINL void mma_f16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint3
 template <int DV>
 struct AttnSmem {
   bf16 q[BQ][QP];
-  bf16 k[2][BKV][QP];
-  bf16 v[2][BKV][DV + 8];
-  float4 e[2][EWIN];
-  uint8_t m[2][BKV];
-  int mflag[2];  // != 0 if the key tile holds padded / out-of-range keys (slow masking path)
+  bf16 k[3][BKV][QP];
+  bf16 v[3][BKV][DV + 8];
+  float4 e[3][EWIN];
+  // followed by: uint8_t mask[n_tiles * BKV] (0 valid, 1 padded key, 2 beyond the sequence) and
+  // uint8_t flag[n_tiles] (!= 0 if the tile holds masked keys -> slow masking path)
 };
 
 template <int DV>
@@ -75,6 +75,16 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
   const float4* E = reinterpret_cast<const float4*>(p.E) + (size_t)head * R;
   const uint8_t* mask = p.mask ? p.mask + (size_t)b * L : nullptr;
   const int n_tiles = (L + BKV - 1) / BKV;
+  uint8_t* smask = smem_raw + sizeof(AttnSmem<DV>);
+  uint8_t* sflag = smask + n_tiles * BKV;
+  // key-padding mask of the whole sequence and per-tile flags, once
+  for (int j = tid; j < n_tiles * BKV; j += 256) smask[j] = (j < L) ? (mask ? mask[j] : 0) : 2;
+  __syncthreads();
+  for (int t = tid; t < n_tiles; t += 256) {
+    const uint4* mp = reinterpret_cast<const uint4*>(smask + t * BKV);
+    const uint4 a = mp[0], b4 = mp[1], c = mp[2], d = mp[3];
+    sflag[t] = ((a.x | a.y | a.z | a.w | b4.x | b4.y | b4.z | b4.w | c.x | c.y | c.z | c.w | d.x | d.y | d.z | d.w) != 0);
+  }
 
   // zero the value tiles once (columns >= dv_valid are never written by the loads)
   if (dv_valid < DV) {
@@ -115,16 +125,10 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
       const bool ok = rr >= 0 && rr < R;
       cp_async16(&sm.e[buf][tid], E + (ok ? rr : 0), ok);
     }
-    if (tid < 32) {  // warp 0: two keys per lane
-      const int ja = j0 + tid, jb = j0 + tid + 32;
-      const uint8_t ka = (ja < L) ? (mask ? mask[ja] : 0) : 2;  // 2 = beyond the sequence
-      const uint8_t kb = (jb < L) ? (mask ? mask[jb] : 0) : 2;
-      sm.m[buf][tid] = ka, sm.m[buf][tid + 32] = kb;
-      const unsigned any = __ballot_sync(0xffffffffu, (ka | kb) != 0);
-      if (tid == 0) sm.mflag[buf] = any != 0;
-    }
   };
   load_tile(0, 0);
+  cp_async_commit();
+  if (n_tiles > 1) load_tile(1, 1);
   cp_async_commit();
 
   // per-thread rows and position queries
@@ -146,11 +150,14 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
   const float LOG2E = 1.4426950408889634f;
 
   for (int kt = 0; kt < n_tiles; ++kt) {
-    const int buf = kt & 1;
-    if (kt + 1 < n_tiles) load_tile(kt + 1, buf ^ 1);
-    cp_async_commit();
+    // three-stage ring, one barrier per tile: after it every warp has finished tile kt - 1, whose
+    // buffer is the one tile kt + 2 is loaded into
+    const int buf = kt % 3;
     cp_async_wait<1>();
     __syncthreads();
+    if (kt + 2 < n_tiles) load_tile(kt + 2, (kt + 2) % 3);
+    cp_async_commit();
+    const uint8_t* mrow = smask + kt * BKV;
     if (kt == 0) {
 #pragma unroll
       for (int ks = 0; ks < 2; ++ks)
@@ -172,7 +179,7 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
     {
       const float4* ew = &sm.e[buf][2 * qd - rl0 + (BQ - 1)];
       float4 ep0 = ew[-8], ep1 = ew[-7];
-      if (sm.mflag[buf] == 0) {
+      if (sflag[kt] == 0) {
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
           const float4 ec0 = ew[nt * 8], ec1 = ew[nt * 8 + 1];
@@ -192,7 +199,7 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
           float a1 = s[nt][1] + pq0[0] * ec1.x + pq0[1] * ec1.y + pq0[2] * ec1.z + pq0[3] * ec1.w;
           float b0 = s[nt][2] + pq1[0] * ep0.x + pq1[1] * ep0.y + pq1[2] * ep0.z + pq1[3] * ep0.w;
           float b1 = s[nt][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
-          const uint8_t k0 = sm.m[buf][nt * 8 + 2 * qd], k1 = sm.m[buf][nt * 8 + 2 * qd + 1];
+          const uint8_t k0 = mrow[nt * 8 + 2 * qd], k1 = mrow[nt * 8 + 2 * qd + 1];
           if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
           if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
           s[nt][0] = a0, s[nt][1] = a1, s[nt][2] = b0, s[nt][3] = b1;
@@ -242,7 +249,6 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
         mma_bf16(o[2 * n2 + 1], pa, vb[2], vb[3]);
       }
     }
-    __syncthreads();
   }
   // ---- normalise, gate, store
   l0 += __shfl_xor_sync(0xffffffffu, l0, 1), l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
@@ -276,9 +282,11 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
 template <int DV>
 static int launch_attn(const AttnParams& p, int chunks, int dv_valid, cudaStream_t s) {
   static bool attr = false;
-  const int smem = (int)sizeof(AttnSmem<DV>);
+  const int n_tiles = (p.L + BKV - 1) / BKV;
+  const int smem = (int)sizeof(AttnSmem<DV>) + n_tiles * BKV + ((n_tiles + 15) & ~15);
+  if (smem > 227 * 1024) return 931;  // sequence too long for the in-kernel mask copy
   if (!attr) {
-    cudaFuncSetAttribute(attn_kernel<DV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaFuncSetAttribute(attn_kernel<DV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     attr = true;
   }
   dim3 grid((p.L + BQ - 1) / BQ, p.heads * chunks, p.nb);

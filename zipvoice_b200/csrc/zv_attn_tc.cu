@@ -27,13 +27,12 @@ struct Smem {
   bf16 v[VSTAGES][NVBOX][BKV][64];  // MN-major SWIZZLE_128B boxes: [key][64 channels] = 8 KB each
   bf16 p[2][BQ][BKV];               // K-major SWIZZLE_128B: [query][64 keys]
   __half q[BQ][QP];
-  __half k[2][BKV][QP];
-  float4 e[2][EWIN];
+  __half k[3][BKV][QP];
+  float4 e[3][EWIN];
   float red[2][BQ];                 // cross-warp (key half) reductions of max / sum
-  uint8_t m[2][BKV];
-  int mflag[2];
   uint64_t vfull[VSTAGES], vfree[VSTAGES], pfull[2], pfree[2], obar;
   uint32_t tmem_base;
+  // followed by: uint8_t mask[n_tiles * BKV] (0 valid, 1 padded key, 2 beyond the sequence), uint8_t flag[n_tiles]
 };
 
 ZV_DEVINL void cp_async16(void* dst, const void* src, bool valid) {
@@ -75,8 +74,9 @@ ZV_DEVINL uint32_t make_idesc_bf16_bmn(uint32_t M, uint32_t N) {
 
 // Scores of this warp's 16 rows x 32 keys of the staged tile: s[nt4][0..1] row g, [2..3] row g + 8.
 // Returns the two row maxima through mx0 / mx1.
-ZV_DEVINL void score_tile(const Smem& sm, int buf, int kh, int lane, int rl0, const uint32_t (&qa)[2][4],
-                          const float (&pq0)[4], const float (&pq1)[4], float (&s)[4][4], float& mx0, float& mx1) {
+ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, bool masked, int kh, int lane, int rl0,
+                          const uint32_t (&qa)[2][4], const float (&pq0)[4], const float (&pq1)[4], float (&s)[4][4],
+                          float& mx0, float& mx1) {
   const int qd = lane & 3;
 #pragma unroll
   for (int n4 = 0; n4 < 4; ++n4) {
@@ -89,7 +89,6 @@ ZV_DEVINL void score_tile(const Smem& sm, int buf, int kh, int lane, int rl0, co
   }
   const float4* ew = &sm.e[buf][kh * 32 + 2 * qd - rl0 + (BQ - 1)];
   float4 ep0 = ew[-8], ep1 = ew[-7];
-  const bool masked = sm.mflag[buf] != 0;
   mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
   for (int n4 = 0; n4 < 4; ++n4) {
@@ -99,7 +98,7 @@ ZV_DEVINL void score_tile(const Smem& sm, int buf, int kh, int lane, int rl0, co
     float b0 = s[n4][2] + pq1[0] * ep0.x + pq1[1] * ep0.y + pq1[2] * ep0.z + pq1[3] * ep0.w;
     float b1 = s[n4][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
     if (masked) {
-      const uint8_t k0 = sm.m[buf][kh * 32 + n4 * 8 + 2 * qd], k1 = sm.m[buf][kh * 32 + n4 * 8 + 2 * qd + 1];
+      const uint8_t k0 = mrow[kh * 32 + n4 * 8 + 2 * qd], k1 = mrow[kh * 32 + n4 * 8 + 2 * qd + 1];
       if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
       if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
     }
@@ -126,10 +125,12 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
   const float4* E = reinterpret_cast<const float4*>(p.E);
   const uint8_t* mask = p.mask ? p.mask + (size_t)b * L : nullptr;
   const uint32_t v_stage_bytes = (uint32_t)nvbox * BKV * 64 * 2;
+  uint8_t* smask = reinterpret_cast<uint8_t*>(&sm) + sizeof(Smem);
+  uint8_t* sflag = smask + n_tiles * BKV;
 
   if (tid == 0) {
     for (int i = 0; i < VSTAGES; ++i) mbar_init(&sm.vfull[i], 1), mbar_init(&sm.vfree[i], 1);
-    for (int i = 0; i < 2; ++i) mbar_init(&sm.pfull[i], COMPUTE_THREADS), mbar_init(&sm.pfree[i], 1);
+    for (int i = 0; i < 2; ++i) mbar_init(&sm.pfull[i], COMPUTE_THREADS / 32), mbar_init(&sm.pfree[i], 1);
     mbar_init(&sm.obar, 1);
     fence_barrier_init();
   }
@@ -200,15 +201,17 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
         const int rr = (j0 - i0 - (BQ - 1)) + (L - 1) + w;
         const bool ok = rr >= 0 && rr < R;
         cp_async16(&sm.e[buf][w], E + (ok ? rr : 0), ok);
-      } else if (tid >= 480) {  // warp 15: two keys per lane
-        const int ja = j0 + lane, jb = j0 + lane + 32;
-        const uint8_t ka = (ja < L) ? (mask ? mask[ja] : 0) : 2;
-        const uint8_t kb = (jb < L) ? (mask ? mask[jb] : 0) : 2;
-        sm.m[buf][lane] = ka, sm.m[buf][lane + 32] = kb;
-        const unsigned any = __ballot_sync(0xffffffffu, (ka | kb) != 0);
-        if (lane == 0) sm.mflag[buf] = any != 0;
       }
     };
+    // key-padding mask of the whole sequence and per-tile flags, once
+    for (int j = tid; j < n_tiles * BKV; j += COMPUTE_THREADS) smask[j] = (j < L) ? (mask ? mask[j] : 0) : 2;
+    cbar();
+    for (int t = tid; t < n_tiles; t += COMPUTE_THREADS) {
+      const uint4* mp = reinterpret_cast<const uint4*>(smask + t * BKV);
+      const uint4 a = mp[0], b4 = mp[1], c = mp[2], d = mp[3];
+      sflag[t] =
+          ((a.x | a.y | a.z | a.w | b4.x | b4.y | b4.z | b4.w | c.x | c.y | c.z | c.w | d.x | d.y | d.z | d.w) != 0);
+    }
     float pq0[4], pq1[4];
     {
       const __half* pa = qkp + (size_t)min(i0 + rl0, L - 1) * p.ldq + 2 * H * DQ;
@@ -221,22 +224,25 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
     const float LOG2E = 1.4426950408889634f;
     float m0 = -INFINITY, m1 = -INFINITY;
     // ---- sweep 1: exact row maxima
+    // three-stage K / E ring, one barrier per tile (after it every warp has finished tile kt - 1,
+    // whose buffer receives tile kt + 2)
     load_tile(0, 0);
     cp_async_commit();
+    if (n_tiles > 1) load_tile(1, 1);
+    cp_async_commit();
     for (int kt = 0; kt < n_tiles; ++kt) {
-      const int buf = kt & 1;
-      if (kt + 1 < n_tiles) load_tile(kt + 1, buf ^ 1);
-      cp_async_commit();
+      const int buf = kt % 3;
       cp_async_wait<1>();
       cbar();
+      if (kt + 2 < n_tiles) load_tile(kt + 2, (kt + 2) % 3);
+      cp_async_commit();
       if (kt == 0) {
 #pragma unroll
         for (int ks = 0; ks < 2; ++ks) ldsm_x4(qa[ks], &sm.q[rg * 16 + (lane & 15)][ks * 16 + (lane >> 4) * 8]);
       }
       float mx0, mx1;
-      score_tile(sm, buf, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+      score_tile(sm, buf, smask + kt * BKV, sflag[kt] != 0, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
       m0 = fmaxf(m0, mx0), m1 = fmaxf(m1, mx1);
-      cbar();
     }
     m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)), m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
     m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)), m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
@@ -249,17 +255,22 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
     float l0 = 0.f, l1 = 0.f;
     load_tile(0, 0);
     cp_async_commit();
+    if (n_tiles > 1) load_tile(1, 1);
+    cp_async_commit();
     for (int kt = 0; kt < n_tiles; ++kt) {
-      const int buf = kt & 1;
-      if (kt + 1 < n_tiles) load_tile(kt + 1, buf ^ 1);
-      cp_async_commit();
+      const int buf = kt % 3, pb = kt & 1;
       cp_async_wait<1>();
       cbar();
+      if (kt + 2 < n_tiles) load_tile(kt + 2, (kt + 2) % 3);
+      cp_async_commit();
       float mx0, mx1;
-      score_tile(sm, buf, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
-      if (kt >= 2) mbar_wait(&sm.pfree[buf], ((kt >> 1) - 1) & 1);  // the MMAs of tile kt-2 have read p[buf]
-      uint8_t* prow0 = reinterpret_cast<uint8_t*>(&sm.p[buf][rl0][0]);
-      uint8_t* prow1 = reinterpret_cast<uint8_t*>(&sm.p[buf][rl1][0]);
+      score_tile(sm, buf, smask + kt * BKV, sflag[kt] != 0, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+      if (kt >= 2) {  // the MMAs of tile kt-2 have read p[pb]
+        if (lane == 0) mbar_wait(&sm.pfree[pb], ((kt >> 1) - 1) & 1);
+        __syncwarp();
+      }
+      uint8_t* prow0 = reinterpret_cast<uint8_t*>(&sm.p[pb][rl0][0]);
+      uint8_t* prow1 = reinterpret_cast<uint8_t*>(&sm.p[pb][rl1][0]);
 #pragma unroll
       for (int n4 = 0; n4 < 4; ++n4) {
         const float a0 = ex2_approx(fmaf(s[n4][0], LOG2E, -ms0)), a1 = ex2_approx(fmaf(s[n4][1], LOG2E, -ms0));
@@ -270,8 +281,8 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
         *reinterpret_cast<uint32_t*>(prow1 + ((chunk ^ (rl1 & 7)) << 4) + qd * 4) = pack_bf16x2(b0, b1);
       }
       fence_proxy_async_smem();
-      mbar_arrive(&sm.pfull[buf]);
-      cbar();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.pfull[pb]);  // one arrival per warp
     }
     l0 += __shfl_xor_sync(0xffffffffu, l0, 1), l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 1), l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
@@ -325,9 +336,11 @@ int attention_na_tc(const AttnParams& p, cudaStream_t s) {
   int rc = make_tmap(&tmV, p.V, 0, (uint64_t)p.nb * p.L, (uint64_t)p.dv, (uint64_t)p.ldv, BKV, 64, 128);
   if (rc) return rc;
   static bool attr = false;
-  const int smem = (int)sizeof(Smem) + 1024;
+  const int n_tiles = (p.L + BKV - 1) / BKV;
+  const int smem = (int)sizeof(Smem) + 1024 + n_tiles * BKV + ((n_tiles + 15) & ~15);
+  if (smem > 227 * 1024) return -1;  // sequence too long for the in-kernel mask copy: mma.sync kernel instead
   if (!attr) {
-    cudaFuncSetAttribute(attn_na_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaFuncSetAttribute(attn_na_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     attr = true;
   }
   dim3 grid((p.L + BQ - 1) / BQ, p.nb);

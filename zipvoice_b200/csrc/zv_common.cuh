@@ -141,6 +141,43 @@ ZV_DEVINL float tanh_approx(float x) {
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// Packed pairs of fp32 (Blackwell FFMA2 / FADD2 / FMUL2: two fp32 operations per issue slot).
+typedef unsigned long long f32x2;
+ZV_DEVINL f32x2 f2_pack(float a, float b) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+ZV_DEVINL void f2_unpack(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+ZV_DEVINL f32x2 f2_fma(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+ZV_DEVINL f32x2 f2_add(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+ZV_DEVINL f32x2 f2_mul(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// SwooshL on a pair (same formula as swoosh_l_fast)
+ZV_DEVINL void swoosh_l_fast2(float& x0, float& x1) {
+  const float L2E = 1.4426950408889634f;
+  const f32x2 x = f2_pack(x0, x1);
+  float t0, t1;
+  f2_unpack(f2_fma(x, f2_pack(L2E, L2E), f2_pack(-4.0f * L2E, -4.0f * L2E)), t0, t1);
+  const f32x2 s = f2_add(f2_pack(ex2_approx(-fabsf(t0)), ex2_approx(-fabsf(t1))), f2_pack(1.0f, 1.0f));
+  float s0, s1;
+  f2_unpack(s, s0, s1);
+  const f32x2 q = f2_add(f2_pack(fmaxf(t0, 0.f), fmaxf(t1, 0.f)), f2_pack(lg2_approx(s0), lg2_approx(s1)));
+  const f32x2 lin = f2_fma(x, f2_pack(-0.08f, -0.08f), f2_pack(-0.035f, -0.035f));
+  f2_unpack(f2_fma(q, f2_pack(0.6931471805599453f, 0.6931471805599453f), lin), x0, x1);
+}
+
 // softplus(x - off) = ln2 * (max(t, 0) + lg2(1 + 2^-|t|)), t = (x - off) log2(e): no overflow, so the
 // reference's "inf -> x - off" guard (scaling.py:1176-1178) is satisfied by construction.
 ZV_DEVINL float softplus_shift(float x, float off_log2e) {

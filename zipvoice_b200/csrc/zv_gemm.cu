@@ -241,13 +241,15 @@ ZV_DEVINL void add_bias32(float (&v)[32], const float* __restrict__ bias, const 
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
       const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + n0 + i));
-      v[i] += bb.x, v[i + 1] += bb.y, v[i + 2] += bb.z, v[i + 3] += bb.w;
+      f2_unpack(f2_add(f2_pack(v[i], v[i + 1]), f2_pack(bb.x, bb.y)), v[i], v[i + 1]);
+      f2_unpack(f2_add(f2_pack(v[i + 2], v[i + 3]), f2_pack(bb.z, bb.w)), v[i + 2], v[i + 3]);
     }
     if (rowb) {
 #pragma unroll
       for (int i = 0; i < 32; i += 4) {
         const float4 bb = __ldg(reinterpret_cast<const float4*>(rowb + n0 + i));
-        v[i] += bb.x, v[i + 1] += bb.y, v[i + 2] += bb.z, v[i + 3] += bb.w;
+        f2_unpack(f2_add(f2_pack(v[i], v[i + 1]), f2_pack(bb.x, bb.y)), v[i], v[i + 1]);
+        f2_unpack(f2_add(f2_pack(v[i + 2], v[i + 3]), f2_pack(bb.z, bb.w)), v[i + 2], v[i + 3]);
       }
     }
   } else {
@@ -455,7 +457,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         float o16[16];
         if (MODE == EPI_SWOOSHL_BF16) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = swoosh_l_fast(v[i]);
+          for (int i = 0; i < 32; i += 2) swoosh_l_fast2(v[i], v[i + 1]);
         } else if (MODE == EPI_GELU_BF16) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
