@@ -146,6 +146,10 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
       tma_prefetch_desc(&tmV);
       auto load_v = [&](int kt) {
         const int st = kt % VSTAGES;
+        if (p.dbg & 1) {
+          mbar_arrive(&sm.vfull[st]);
+          return;
+        }
         mbar_arrive_expect_tx(&sm.vfull[st], v_stage_bytes);
         for (int c = 0; c < nvbox; ++c)
           tma_load_2d(&sm.v[st][c][0][0], &tmV, &sm.vfull[st], c * 64, b * L + kt * BKV);
@@ -164,7 +168,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
         const uint64_t da = make_sdesc_sw128(smem_u32(&sm.p[pb][0][0]));
         const uint32_t vaddr = smem_u32(&sm.v[st][0][0][0]);
 #pragma unroll
-        for (int k = 0; k < BKV / 16; ++k) {
+        for (int k = 0; k < ((p.dbg & 2) ? 0 : BKV / 16); ++k) {
           const uint64_t db0 = make_sdesc_mn_sw128(vaddr + k * 2048, BKV * 128, 1024);
           umma_bf16(tmem_base, da + 2 * k, db0, id0, (kt | k) != 0 ? 1u : 0u);
           if (n_mma1 > 0) {

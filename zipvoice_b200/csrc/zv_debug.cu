@@ -117,3 +117,41 @@ extern "C" int zv_debug_pos_table(const float* W, int H, int dp, int pos_dim, in
   if (!rc) rc = (int)cudaStreamSynchronize((cudaStream_t)stream);
   return rc;
 }
+
+// Kernel-only timing of the attention kernels on synthetic device data (profiling aid; no parity meaning):
+// runs `iters` launches between two CUDA events and returns the mean milliseconds per launch.
+extern "C" int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv, int use_mask, int dbg, int iters,
+                                        float* ms_out) {
+  const size_t rows = (size_t)nb * L;
+  const int ldq = 288, ldv = heads * dv;
+  __half* q = nullptr;
+  __nv_bfloat16 *v = nullptr, *g = nullptr, *o = nullptr;
+  float* E = nullptr;
+  uint8_t* m = nullptr;
+  cudaMalloc(&q, rows * ldq * 2), cudaMalloc(&v, rows * ldv * 2), cudaMalloc(&g, rows * ldv * 2);
+  cudaMalloc(&o, rows * ldv * 2), cudaMalloc(&E, (size_t)H * (2 * L - 1) * 16), cudaMalloc(&m, rows);
+  cudaMemset(q, 0x2c, rows * ldq * 2);  // fp16 0x2c2c ~ 0.065
+  cudaMemset(v, 0x3c, rows * ldv * 2);  // bf16 0x3c3c ~ 0.0115
+  cudaMemset(g, 0x3f, rows * ldv * 2);
+  cudaMemset(E, 0, (size_t)H * (2 * L - 1) * 16);
+  cudaMemset(m, 0, rows);
+  if (use_mask) cudaMemset(m + rows - L / 4, 1, L / 4);
+  AttnParams a;
+  a.qkp = reinterpret_cast<__nv_bfloat16*>(q), a.ldq = ldq, a.E = E, a.mask = use_mask ? m : nullptr, a.V = v;
+  a.ldv = ldv, a.gate = heads == 1 ? g : nullptr, a.ldg = ldv, a.out = o, a.ldo = ldv, a.nb = nb, a.L = L, a.H = H;
+  a.heads = heads, a.dv = dv, a.dbg = dbg;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0), cudaEventCreate(&e1);
+  int rc = attention(a, 0);
+  cudaDeviceSynchronize();
+  cudaEventRecord(e0, 0);
+  for (int i = 0; i < iters && !rc; ++i) rc = attention(a, 0);
+  cudaEventRecord(e1, 0);
+  if (!rc) rc = (int)cudaDeviceSynchronize();
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  *ms_out = ms / (iters > 0 ? iters : 1);
+  cudaEventDestroy(e0), cudaEventDestroy(e1);
+  cudaFree(q), cudaFree(v), cudaFree(g), cudaFree(o), cudaFree(E), cudaFree(m);
+  return rc;
+}
