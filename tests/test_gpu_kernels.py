@@ -152,7 +152,7 @@ def ref_attention(qkp, E, mask, V, gate, H, heads, dv):
 
 
 @pytest.mark.parametrize("L", [1, 37, 64, 130, 611])
-@pytest.mark.parametrize("kind", ["self", "nonlin384", "nonlin144", "nonlin384_mma", "nonlin144_mma"])
+@pytest.mark.parametrize("kind", ["self", "self_mma", "nonlin384", "nonlin144", "nonlin384_mma", "nonlin144_mma"])
 def test_attention(L, kind):
     H, nb = 4, 3
     _lib().zv_debug_set_attn_impl(1 if kind.endswith("_mma") else 0)

@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libzipvoice_b200.so")
-SOURCES = ["zv_gemm.cu", "zv_attn.cu", "zv_attn_tc.cu", "zv_elem.cu", "zv_time.cu", "zv_engine.cu", "zv_api.cu", "zv_debug.cu",
+SOURCES = ["zv_gemm.cu", "zv_attn.cu", "zv_attn_tc.cu", "zv_attn_sa.cu", "zv_elem.cu", "zv_time.cu", "zv_engine.cu", "zv_api.cu", "zv_debug.cu",
            "zv_audio.cu"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
          "-diag-suppress", "177"]

@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
   const int R = 2 * L - 1;
   const int vcol0 = head * p.dv + chunk * DV;  // first value / output column of this block
   const bf16* qkp = p.qkp + (size_t)b * L * p.ldq;
-  const bf16* V = p.V + (size_t)b * L * p.ldv + vcol0;
+  const bf16* V = p.V + (size_t)b * L * p.ldv + head * (p.vhs ? p.vhs : p.dv) + chunk * DV;
   const float4* E = reinterpret_cast<const float4*>(p.E) + (size_t)head * R;
   const uint8_t* mask = p.mask ? p.mask + (size_t)b * L : nullptr;
   const int n_tiles = (L + BKV - 1) / BKV;
@@ -295,11 +295,17 @@ static int launch_attn(const AttnParams& p, int chunks, int dv_valid, cudaStream
 }
 
 int attention_na_tc(const AttnParams& p, cudaStream_t s);
-int g_attn_impl = 0;  // 0: NonlinAttention on the tcgen05 kernel (zv_attn_tc.cu); 1: mma.sync flash kernel everywhere
+int attention_sa_tma(const AttnParams& p, cudaStream_t s);
+int g_attn_impl = 0;  // 0: TMA-fed SelfAttention (zv_attn_sa.cu) + tcgen05 NonlinAttention (zv_attn_tc.cu);
+                      // 1: the cp.async / mma.sync flash kernel below for everything
 
 int attention(const AttnParams& p, cudaStream_t s) {
   if (p.heads == 1 && g_attn_impl == 0) {
     const int rc = attention_na_tc(p, s);
+    if (rc >= 0) return rc;
+  }
+  if (p.heads == p.H && p.dv == 12 && g_attn_impl == 0) {
+    const int rc = attention_sa_tma(p, s);
     if (rc >= 0) return rc;
   }
   if (p.dv == 12) return launch_attn<16>(p, 1, 12, s);

@@ -1,0 +1,273 @@
+// SelfAttention value product (zipformer.py:1359-1396 on the weights of :1149-1306), dv = 12 per head:
+//   O_h = softmax_j(q_h k_h^T + p_h . E_h[L-1-i+j], key-padded -> -1000) V_h
+// Same flash-style mathematics as attn_kernel<16> (zv_attn.cu) with a Blackwell-style data path: a producer
+// warp feeds a 4-stage shared-memory ring with TMA (K tile: SWIZZLE_64B tensor box of the fp16 q|k|p rows;
+// V tile: 16-column box at column 16 h of the padded value rows; relative-position window: one 1-D bulk copy) and the 8 compute warps
+// (16 query rows each) synchronise only through full / empty mbarriers -- no cp.async address arithmetic in the
+// compute warps and no CTA-wide barrier in the key loop.
+#include <cuda.h>
+
+#include "zv_common.cuh"
+#include "zv_gemm.h"
+#include "zv_kernels.h"
+
+namespace zv {
+namespace sa {
+
+static constexpr int BQ = 128, BKV = 64, DQ = 32, EWIN = 192, STAGES = 4, DVP = 16;
+static constexpr int COMPUTE_THREADS = 256, THREADS = COMPUTE_THREADS + 32;
+
+struct Stage {
+  __half k[BKV][DQ];    // 4 KB, SWIZZLE_64B
+  bf16 v[BKV][DVP];     // 2 KB, no swizzle
+  float4 e[EWIN];       // 3 KB
+};
+struct Smem {
+  __half q[BQ][DQ];     // 8 KB, SWIZZLE_64B (two 64-row boxes)
+  Stage st[STAGES];
+  uint64_t full[STAGES], empty[STAGES], qbar, pad_;
+  // followed by: uint8_t mask[n_tiles * BKV], uint8_t flag[n_tiles]
+};
+
+ZV_DEVINL void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+ZV_DEVINL void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+ZV_DEVINL void mma_f16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+ZV_DEVINL void mma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// 1-D bulk copy global -> shared, completion counted on an mbarrier (bytes multiple of 16, 16-byte aligned)
+ZV_DEVINL void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// byte offset of 16-byte chunk c of row r in a SWIZZLE_64B tile with 64-byte rows
+ZV_DEVINL uint32_t sw64(int r, int c) { return (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4)); }
+
+}  // namespace sa
+
+using namespace sa;
+
+__global__ void __launch_bounds__(sa::THREADS, 2)
+attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__ CUtensorMap tmV, AttnParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.z, head = blockIdx.y, i0 = blockIdx.x * BQ;
+  const int L = p.L, H = p.H, R = 2 * L - 1;
+  const int n_tiles = (L + BKV - 1) / BKV;
+  uint8_t* smask = reinterpret_cast<uint8_t*>(&sm) + sizeof(Smem);
+  uint8_t* sflag = smask + n_tiles * BKV;
+  const uint8_t* mask = p.mask ? p.mask + (size_t)b * L : nullptr;
+
+  if (tid == 0) {
+    for (int i = 0; i < STAGES; ++i) mbar_init(&sm.full[i], 1), mbar_init(&sm.empty[i], COMPUTE_THREADS / 32);
+    mbar_init(&sm.qbar, 1);
+    fence_barrier_init();
+  }
+  // window entries outside the table are never copied: keep them finite
+  for (int i = tid; i < STAGES * EWIN; i += THREADS) sm.st[i / EWIN].e[i % EWIN] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int j = tid; j < n_tiles * BKV; j += THREADS) smask[j] = (j < L) ? (mask ? mask[j] : 0) : 2;
+  fence_proxy_async_smem();
+  __syncthreads();
+  for (int t = tid; t < n_tiles; t += THREADS) {
+    const uint4* mp = reinterpret_cast<const uint4*>(smask + t * BKV);
+    const uint4 a = mp[0], b4 = mp[1], c = mp[2], d = mp[3];
+    sflag[t] =
+        ((a.x | a.y | a.z | a.w | b4.x | b4.y | b4.z | b4.w | c.x | c.y | c.z | c.w | d.x | d.y | d.z | d.w) != 0);
+  }
+  __syncthreads();
+
+  if (warp == COMPUTE_THREADS / 32) {
+    // ---------------- producer
+    if (lane == 0) {
+      tma_prefetch_desc(&tmQK);
+      tma_prefetch_desc(&tmV);
+      if (p.dbg & 8) {
+        mbar_arrive(&sm.qbar);
+      } else {
+        mbar_arrive_expect_tx(&sm.qbar, BQ * DQ * 2);
+        tma_load_2d(&sm.q[0][0], &tmQK, &sm.qbar, head * DQ, b * L + i0);
+        tma_load_2d(&sm.q[64][0], &tmQK, &sm.qbar, head * DQ, b * L + i0 + 64);
+      }
+      const float4* E = reinterpret_cast<const float4*>(p.E) + (size_t)head * R;
+      for (int kt = 0; kt < n_tiles; ++kt) {
+        const int s = kt % STAGES;
+        if (kt >= STAGES) mbar_wait(&sm.empty[s], ((kt / STAGES) - 1) & 1);
+        const int j0 = kt * BKV;
+        const int rr0 = (j0 - i0 - (BQ - 1)) + (L - 1);  // table row of window entry 0
+        const int lo = max(rr0, 0), hi = min(rr0 + EWIN, R);
+        const uint32_t ebytes = (hi > lo && !(p.dbg & 1)) ? (uint32_t)(hi - lo) * 16u : 0u;
+        const uint32_t kbytes = (p.dbg & 4) ? 0u : BKV * DQ * 2, vbytes = (p.dbg & 2) ? 0u : BKV * DVP * 2;
+        mbar_arrive_expect_tx(&sm.full[s], kbytes + vbytes + ebytes);
+        if (kbytes) tma_load_2d(&sm.st[s].k[0][0], &tmQK, &sm.full[s], H * DQ + head * DQ, b * L + j0);
+        if (vbytes) tma_load_2d(&sm.st[s].v[0][0], &tmV, &sm.full[s], head * DVP, b * L + j0);
+        if (ebytes) bulk_load_1d(&sm.st[s].e[lo - rr0], E + lo, ebytes, &sm.full[s]);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---------------- compute warps: 16 query rows each
+    const int g = lane >> 2, qd = lane & 3;
+    const int rl0 = warp * 16 + g, rl1 = rl0 + 8;
+    const __half* qkp = reinterpret_cast<const __half*>(p.qkp) + (size_t)b * L * p.ldq;
+    float pq0[4], pq1[4];
+    {
+      const __half* pa = qkp + (size_t)min(i0 + rl0, L - 1) * p.ldq + 2 * H * DQ + head * 4;
+      const __half* pb = qkp + (size_t)min(i0 + rl1, L - 1) * p.ldq + 2 * H * DQ + head * 4;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) pq0[c] = __half2float(pa[c]), pq1[c] = __half2float(pb[c]);
+    }
+    float o[2][4];
+#pragma unroll
+    for (int n = 0; n < 2; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    const float LOG2E = 1.4426950408889634f;
+    uint32_t qa[2][4];
+    mbar_wait(&sm.qbar, 0);
+    {
+      const uint32_t qbase = smem_u32(&sm.q[0][0]);
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks) ldsm_x4(qa[ks], qbase + sw64(warp * 16 + (lane & 15), ks * 2 + (lane >> 4)));
+    }
+    for (int kt = 0; kt < n_tiles; ++kt) {
+      const int st = kt % STAGES;
+      mbar_wait(&sm.full[st], (kt / STAGES) & 1);
+      const Stage& S = sm.st[st];
+      const uint32_t kbase = smem_u32(&S.k[0][0]), vbase = smem_u32(&S.v[0][0]);
+      const uint8_t* mrow = smask + kt * BKV;
+      // ---- S = Q K^T
+      float s[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        uint32_t kb[4];
+        ldsm_x4(kb, kbase + sw64(nt * 8 + (lane & 7), lane >> 3));
+        mma_f16(s[nt], qa[0], kb[0], kb[1]);
+        mma_f16(s[nt], qa[1], kb[2], kb[3]);
+      }
+      // ---- position term (rows g and g + 8 share table entries 8 columns apart), masks, running max
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+      {
+        const float4* ew = &S.e[2 * qd - rl0 + (BQ - 1)];
+        float4 ep0 = ew[-8], ep1 = ew[-7];
+        const bool masked = sflag[kt] != 0;
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          const float4 ec0 = ew[nt * 8], ec1 = ew[nt * 8 + 1];
+          float a0 = s[nt][0] + pq0[0] * ec0.x + pq0[1] * ec0.y + pq0[2] * ec0.z + pq0[3] * ec0.w;
+          float a1 = s[nt][1] + pq0[0] * ec1.x + pq0[1] * ec1.y + pq0[2] * ec1.z + pq0[3] * ec1.w;
+          float b0 = s[nt][2] + pq1[0] * ep0.x + pq1[1] * ep0.y + pq1[2] * ep0.z + pq1[3] * ep0.w;
+          float b1 = s[nt][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
+          if (masked) {
+            const uint8_t k0 = mrow[nt * 8 + 2 * qd], k1 = mrow[nt * 8 + 2 * qd + 1];
+            if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
+            if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
+          }
+          s[nt][0] = a0, s[nt][1] = a1, s[nt][2] = b0, s[nt][3] = b1;
+          mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
+          ep0 = ec0, ep1 = ec1;
+        }
+      }
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+      const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+      const bool grow = (mn0 != m0) || (mn1 != m1);
+      const float ms0 = mn0 * LOG2E, ms1 = mn1 * LOG2E;
+      float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const float pa = ex2_approx(fmaf(s[nt][e], LOG2E, -ms0)), pb = ex2_approx(fmaf(s[nt][2 + e], LOG2E, -ms1));
+          s[nt][e] = pa, s[nt][2 + e] = pb;
+          rs0 += pa, rs1 += pb;
+        }
+      }
+      if (__any_sync(0xffffffffu, grow)) {
+        const float sc0 = ex2_approx((m0 - mn0) * LOG2E), sc1 = ex2_approx((m1 - mn1) * LOG2E);
+        l0 *= sc0, l1 *= sc1;
+#pragma unroll
+        for (int n = 0; n < 2; ++n) o[n][0] *= sc0, o[n][1] *= sc0, o[n][2] *= sc1, o[n][3] *= sc1;
+        m0 = mn0, m1 = mn1;
+      }
+      l0 += rs0, l1 += rs1;
+      // ---- O += P V
+#pragma unroll
+      for (int kk = 0; kk < BKV / 16; ++kk) {
+        uint32_t pa[4];
+        pa[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
+        pa[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
+        pa[2] = pack_bf16x2(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+        pa[3] = pack_bf16x2(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+        uint32_t vb[4];
+        ldsm_x4_t(vb, vbase + (kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * (DVP * 2) + (lane >> 4) * 16);
+        mma_bf16(o[0], pa, vb[0], vb[1]);
+        mma_bf16(o[1], pa, vb[2], vb[3]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.empty[st]);
+    }
+    // ---- normalise, store (columns >= dv belong to the next head / padding and are dropped)
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1), l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1), l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float inv0 = 1.f / l0, inv1 = 1.f / l1;
+    const int ia = i0 + rl0, ib = i0 + rl1;
+    const int vcol0 = head * p.dv;
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+      const int col = n * 8 + 2 * qd;
+      if (col >= p.dv) continue;
+      if (ia < L)
+        *reinterpret_cast<uint32_t*>(p.out + ((size_t)b * L + ia) * p.ldo + vcol0 + col) =
+            pack_bf16x2(o[n][0] * inv0, o[n][1] * inv0);
+      if (ib < L)
+        *reinterpret_cast<uint32_t*>(p.out + ((size_t)b * L + ib) * p.ldo + vcol0 + col) =
+            pack_bf16x2(o[n][2] * inv1, o[n][3] * inv1);
+    }
+  }
+}
+
+// Host launcher; returns -1 if the shape is not supported (caller falls back to attn_kernel).
+int attention_sa_tma(const AttnParams& p, cudaStream_t s) {
+  // V must be in the padded layout (16 columns per head): the TMA box start has to be 16-byte aligned
+  if (p.dv != 12 || p.vhs != DVP || p.gate || p.heads != p.H || p.ldv % 8 || p.ldq % 8 || (p.ldo & 1)) return -1;
+  const int n_tiles = (p.L + BKV - 1) / BKV;
+  const int smem = (int)sizeof(Smem) + 1024 + n_tiles * BKV + ((n_tiles + 15) & ~15);
+  if (smem > 100 * 1024) return -1;
+  CUtensorMap tmQK, tmV;
+  int rc = make_tmap(&tmQK, p.qkp, 0, (uint64_t)p.nb * p.L, (uint64_t)(2 * p.H * DQ + 4 * p.H), (uint64_t)p.ldq, BKV,
+                     DQ, 64);
+  if (rc) return rc;
+  rc = make_tmap(&tmV, p.V, 0, (uint64_t)p.nb * p.L, (uint64_t)p.heads * DVP, (uint64_t)p.ldv, BKV, DVP, 0);
+  if (rc) return rc;
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(attn_sa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    attr = true;
+  }
+  dim3 grid((p.L + BQ - 1) / BQ, p.heads, p.nb);
+  attn_sa_kernel<<<grid, THREADS, smem, s>>>(tmQK, tmV, p);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace zv

@@ -75,6 +75,15 @@ extern "C" int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int
   return rc;
 }
 
+__global__ void pad_heads_kernel(const float* __restrict__ in, size_t rows, int heads, int dv, int ld_in,
+                                 __nv_bfloat16* __restrict__ out) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= rows * heads * 16) return;
+  const int c = (int)(gid % 16), h = (int)((gid / 16) % heads);
+  const size_t r = gid / (16 * heads);
+  out[gid] = __float2bfloat16(c < dv ? in[r * ld_in + h * dv + c] : 0.f);
+}
+
 extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp_f32, int ldq,
                                   const float* E, const uint8_t* mask, const float* V_f32, int ldv,
                                   const float* gate_f32, float* out_f32, void* stream) {
@@ -85,7 +94,14 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
   cudaMalloc(&v, rows * ldv * 2);
   cudaMalloc(&o, rows * ldv * 2);
   cvt_f16_kernel<<<(unsigned)((rows * ldq + 255) / 256), 256, 0, s>>>(qkp_f32, rows * ldq, reinterpret_cast<__half*>(q));
-  cvt_pad(V_f32, (int)rows, ldv, ldv, v, ldv, s);
+  const bool sa_pad = heads > 1 && dv == 12;  // SelfAttention: 16 columns per head (12 + 4 zeros)
+  if (sa_pad) {
+    cudaFree(v);
+    cudaMalloc(&v, rows * heads * 16 * 2);
+    pad_heads_kernel<<<(unsigned)((rows * heads * 16 + 255) / 256), 256, 0, s>>>(V_f32, rows, heads, dv, ldv, v);
+  } else {
+    cvt_pad(V_f32, (int)rows, ldv, ldv, v, ldv, s);
+  }
   if (gate_f32) {
     cudaMalloc(&g, rows * ldv * 2);
     cvt_pad(gate_f32, (int)rows, ldv, ldv, g, ldv, s);
@@ -94,6 +110,7 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
   AttnParams a;
   a.qkp = q, a.ldq = ldq, a.E = E, a.mask = mask, a.V = v, a.ldv = ldv, a.gate = g, a.ldg = ldv, a.out = o, a.ldo = ldv;
   a.nb = nb, a.L = L, a.H = H, a.heads = heads, a.dv = dv;
+  if (sa_pad) a.ldv = heads * 16, a.vhs = 16;
   int rc = attention(a, s);
   if (!rc) {
     cvt_back(o, rows * ldv, out_f32, s);
@@ -123,7 +140,7 @@ extern "C" int zv_debug_pos_table(const float* W, int H, int dp, int pos_dim, in
 extern "C" int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv, int use_mask, int dbg, int iters,
                                         float* ms_out) {
   const size_t rows = (size_t)nb * L;
-  const int ldq = 288, ldv = heads * dv;
+  const int ldq = 288, ldv = (heads > 1 && dv == 12) ? heads * 16 : heads * dv;
   __half* q = nullptr;
   __nv_bfloat16 *v = nullptr, *g = nullptr, *o = nullptr;
   float* E = nullptr;
@@ -139,7 +156,8 @@ extern "C" int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv,
   AttnParams a;
   a.qkp = reinterpret_cast<__nv_bfloat16*>(q), a.ldq = ldq, a.E = E, a.mask = use_mask ? m : nullptr, a.V = v;
   a.ldv = ldv, a.gate = heads == 1 ? g : nullptr, a.ldg = ldv, a.out = o, a.ldo = ldv, a.nb = nb, a.L = L, a.H = H;
-  a.heads = heads, a.dv = dv, a.dbg = dbg;
+  a.heads = heads, a.dv = dv, a.dbg = dbg, a.vhs = (heads > 1 && dv == 12) ? 16 : 0;
+  if (heads > 1) a.ldo = heads * dv;
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0), cudaEventCreate(&e1);
   int rc = attention(a, 0);

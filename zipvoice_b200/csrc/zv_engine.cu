@@ -177,7 +177,19 @@ static int build_layer(Engine& e, Net& net, const std::string& p, int kernel, La
   ZV_TRY(pack_linear(e, p + ".nonlin_attention.out_proj", EPI_RESIDUAL, &L->na_out));
   for (int i = 0; i < 2; ++i) {
     const std::string a = p + ".self_attn" + std::to_string(i + 1);
-    ZV_TRY(pack_linear(e, a + ".in_proj", EPI_BIAS_BF16, &L->sa_in[i]));
+    {  // value projection padded to 16 columns per head (12 + 4 zero rows): 16-byte aligned TMA boxes per head
+      const HostTensor* w = find(e, a + ".in_proj.weight");
+      const HostTensor* bv = find(e, a + ".in_proj.bias");
+      if (!w || !bv) return 940;
+      const int dv = e.cfg.value_head_dim, K = (int)w->shape[1], Hh = (int)w->shape[0] / dv;
+      std::vector<float> wp((size_t)Hh * 16 * K, 0.f), bp((size_t)Hh * 16, 0.f);
+      for (int h = 0; h < Hh; ++h)
+        for (int c = 0; c < dv; ++c) {
+          memcpy(&wp[((size_t)h * 16 + c) * K], &w->data[((size_t)h * dv + c) * K], (size_t)K * 4);
+          bp[h * 16 + c] = bv->data[h * dv + c];
+        }
+      ZV_TRY(pack_linear_host(e, wp.data(), bp.data(), Hh * 16, K, EPI_BIAS_BF16, &L->sa_in[i], 0, nullptr));
+    }
     ZV_TRY(pack_linear(e, a + ".out_proj", EPI_RESIDUAL, &L->sa_out[i]));
     const std::string c = p + ".conv_module" + std::to_string(i + 1);
     ZV_TRY(pack_linear(e, c + ".in_proj", EPI_GLU_BF16, &L->conv_in[i]));
@@ -339,7 +351,7 @@ int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
   ZV_TRY(A((void**)&ws.na_v, rows * net.hidden_na * 2));
   ZV_TRY(A((void**)&ws.na_y, rows * net.hidden_na * 2));
   ZV_TRY(A((void**)&ws.na_o, rows * net.hidden_na * 2));
-  ZV_TRY(A((void**)&ws.sa_v, rows * 48 * 2));
+  ZV_TRY(A((void**)&ws.sa_v, rows * 64 * 2));
   ZV_TRY(A((void**)&ws.sa_o, rows * 48 * 2));
   ZV_TRY(A((void**)&ws.conv_a, rows * D * 2));
   ZV_TRY(A((void**)&ws.conv_b, rows * D * 2));
@@ -419,11 +431,11 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   };
   auto self_attn = [&](int i, const float* resbias) {
     EpiParams v;
-    v.L = L, v.out_bf16 = ws.sa_v, v.ld_bf16 = 48;
+    v.L = L, v.out_bf16 = ws.sa_v, v.ld_bf16 = 16 * net.H;
     int rc = run_gemm(e, ly.sa_in[i], ws.shadow, D, M, v, s);
     if (rc) return rc;
     AttnParams a;
-    a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.sa_v, a.ldv = 48, a.gate = nullptr, a.ldg = 0;
+    a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.sa_v, a.ldv = 16 * net.H, a.vhs = 16, a.gate = nullptr, a.ldg = 0;
     a.out = ws.sa_o, a.ldo = 48, a.nb = nb, a.L = L, a.H = net.H, a.heads = net.H, a.dv = 12;
     rc = run_attn(e, KC_ATTN_SELF, a, i == 0 ? net.H - 1 : 0, s);
     if (rc) return rc;

@@ -56,7 +56,7 @@ int gemm_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const GemmPlan& 
 int gemm_pick_block_n(int n_valid, int mode, int gate_cols);
 
 // Cached cuTensorMapEncodeTiled for a row-major [rows][cols] tensor with row pitch ld (elements):
-// dtype 0 = 16-bit, 1 = fp32; box [box_rows][box_cols]; swizzle 32 / 64 / 128 bytes.  `tm` is a CUtensorMap*.
+// dtype 0 = 16-bit, 1 = fp32; box [box_rows][box_cols]; swizzle 0 (none) / 32 / 64 / 128 bytes.  `tm` is a CUtensorMap*.
 int make_tmap(void* tm, const void* ptr, int dtype, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
               uint32_t box_cols, int swizzle);
 

@@ -55,6 +55,7 @@ struct AttnParams {
   const uint8_t* mask;       // [nb][L] 1 = padded key (may be null)
   const __nv_bfloat16* V;    // [nb][L][ldv]
   int ldv;
+  int vhs = 0;               // column stride between the heads of V (0 = dv; SelfAttention uses 16: 12 + 4 zeros)
   const __nv_bfloat16* gate; // optional [nb][L][ldg]: out *= gate (NonlinAttention y)
   int ldg;
   __nv_bfloat16* out;        // [nb][L][ldo]
