@@ -12,8 +12,8 @@ generated audio-seconds per second (prompt frames excluded), whole job over all 
   value : inputs resident in HBM, timed with CUDA events around K steps (barrier + sync both sides,
           max over ranks).
   e2e   : the same batch through the public API ``ZipVoiceB200.sample`` (text encoder, text condition,
-          prompt padding, solver, prompt strip) from pinned HOST buffers, H2D and D2H copies inside the
-          timed region; N > 1 adds the NCCL gather of the generated mels to rank 0.
+          prompt padding, solver, prompt strip) + the vocoder, from pinned HOST buffers to HOST waveforms,
+          H2D and D2H copies inside the timed region; N > 1 adds the NCCL gather of the waveforms to rank 0.
   roofline / kernels : one extra instrumented step in which the library brackets every launch of its
           kernels with CUDA events on the launching stream (zv_prof_*).
   cpu_baseline : the CPU oracle (torch fp32 restatement of the reference, oracle/) timed on the host
@@ -189,6 +189,7 @@ def main():
 
     cfg = synth.BASE_MODEL_CFG
     sd = synth.make_state_dict(cfg, seed=0)
+    sd.update({"vocoder." + k: v for k, v in synth.make_vocos_state_dict(0).items()})  # same handle: model + vocoder
     model = ZipVoiceB200(cfg, sd, synth.VOCAB_SIZE, synth.PAD_ID, kind="zipvoice", device=dev)
     eng = model.engine
     B, T = args.batch, PROMPT_FRAMES + TARGET_FRAMES
@@ -243,17 +244,20 @@ def main():
     # ---------------- end to end through the public API from pinned host buffers
     e2e = None
     if not args.no_e2e:
-        out_host = torch.empty(B, TARGET_FRAMES, 100).pin_memory()
-        gathered = [torch.empty(B, TARGET_FRAMES, 100, device=dev) for _ in range(world)] if (world > 1 and rank == 0) else None
+        n_wav = 256 * (TARGET_FRAMES - 1)
+        out_host = torch.empty(B, n_wav).pin_memory()
+        gathered = [torch.empty(B, n_wav, device=dev) for _ in range(world)] if (world > 1 and rank == 0) else None
 
         def step_e2e():
             x1_wo, wo_lens, _, _ = model.sample(tokens, prompt_tokens, pf_host.to(dev, non_blocking=True), pfl,
                                                 features_lens=features_lens, duration="real", num_step=NUM_STEP,
                                                 guidance_scale=GUIDANCE, t_shift=T_SHIFT,
                                                 x0=x0_host.to(dev, non_blocking=True))
+            # bin/infer_zipvoice.py:374-378: undo the feature scale, vocode, clamp
+            wav = eng.vocos_decode(x1_wo.permute(0, 2, 1) / 0.1).clamp(-1, 1)
             if world > 1:
-                dist.gather(x1_wo.contiguous(), gathered, dst=0)
-            out_host.copy_(x1_wo, non_blocking=True)
+                dist.gather(wav, gathered, dst=0)
+            out_host.copy_(wav, non_blocking=True)
             torch.cuda.synchronize()
 
         step_e2e()
@@ -269,7 +273,9 @@ def main():
         e2e = {"value": audio_s / (float(dt.item()) / K), "unit": "audio-s/s",
                "h2d_bytes_per_step": int(pf_host.numel() * 4 + x0_host.numel() * 4 + n_tok * 8 + 3 * B * 8),
                "d2h_bytes_per_step": int(out_host.numel() * 4),
-               "api": "ZipVoiceB200.sample (text encoder + condition + 16-NFE CFG solver + prompt strip)"}
+               "api": "ZipVoiceB200.sample (text encoder + condition + 16-NFE CFG solver + prompt strip) + "
+                      "Vocos decode to 24 kHz waveforms (seeded random vocoder weights); N>1: NCCL gather of the "
+                      "waveforms to rank 0"}
 
     # ---------------- instrumented step: per-kernel-class device time (CUDA events inside the library)
     eng.prof_enable(True)

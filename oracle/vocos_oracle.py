@@ -21,22 +21,9 @@ N_FFT, HOP, DIM, INTER, LAYERS, N_MELS = 1024, 256, 512, 1536, 8, 100
 
 
 def make_vocos_state_dict(seed: int = 0) -> Dict[str, torch.Tensor]:
-    """Seeded random weights with init-like scales (trunc-normal 0.02 in the original; larger here so
-    that every block contributes), layer scale gamma = 1 / num_layers."""
-    g = torch.Generator().manual_seed(1000 + seed)
-    rn = lambda *s, std=1.0: torch.randn(*s, generator=g) * std
-    sd = {"backbone.embed.weight": rn(DIM, N_MELS, 7, std=0.06), "backbone.embed.bias": rn(DIM, std=0.05),
-          "backbone.norm.weight": 1 + rn(DIM, std=0.1), "backbone.norm.bias": rn(DIM, std=0.1),
-          "backbone.final_layer_norm.weight": 1 + rn(DIM, std=0.1), "backbone.final_layer_norm.bias": rn(DIM, std=0.1),
-          "head.out.weight": rn(N_FFT + 2, DIM, std=0.03), "head.out.bias": rn(N_FFT + 2, std=0.3)}
-    for i in range(LAYERS):
-        p = f"backbone.convnext.{i}"
-        sd.update({f"{p}.dwconv.weight": rn(DIM, 1, 7, std=0.3), f"{p}.dwconv.bias": rn(DIM, std=0.1),
-                   f"{p}.norm.weight": 1 + rn(DIM, std=0.1), f"{p}.norm.bias": rn(DIM, std=0.1),
-                   f"{p}.pwconv1.weight": rn(INTER, DIM, std=0.05), f"{p}.pwconv1.bias": rn(INTER, std=0.1),
-                   f"{p}.pwconv2.weight": rn(DIM, INTER, std=0.05), f"{p}.pwconv2.bias": rn(DIM, std=0.1),
-                   f"{p}.gamma": torch.full((DIM,), 1.0 / LAYERS) * (1 + rn(DIM, std=0.2))})
-    return sd
+    """Seeded random vocoder weights (shared with the product-side synthetic generator)."""
+    from zipvoice_b200.synth import make_vocos_state_dict as _mk
+    return _mk(seed)
 
 
 def backbone(sd, mel: torch.Tensor, taps=None) -> torch.Tensor:

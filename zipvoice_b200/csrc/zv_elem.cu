@@ -93,12 +93,14 @@ int f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t s) {
 // is staged in shared memory (bf16x2 per thread-column, conflict-free), taps live in registers,
 // and every thread produces 4 consecutive frames x 2 channels per step so each shared-memory
 // word is read once per 4 outputs.
-template <int K>
+template <int K, int TT, int FG>
 __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in, const float* __restrict__ w,
                                                      const float* __restrict__ bias, int L, int C,
                                                      bf16* __restrict__ out) {
-  constexpr int TT = 64, PAD = K / 2, ROWS = TT + K - 1;
-  __shared__ uint32_t tile[ROWS][128];
+  // TT frames per CTA (the halo of K - 1 frames is re-read: 23 % at TT = 128, K = 31), FG frames per register group
+  constexpr int PAD = K / 2, ROWS = TT + K - 1;
+  extern __shared__ __align__(16) uint32_t tile_raw[];
+  uint32_t(*tile)[128] = reinterpret_cast<uint32_t(*)[128]>(tile_raw);
   const int cp = threadIdx.x;                 // channel pair within chunk
   const int c = blockIdx.y * 256 + cp * 2;    // first channel
   const int b = blockIdx.z;
@@ -107,7 +109,7 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in
   const bf16* src = in + (size_t)b * L * C;
   {  // stage the tile with 16-byte loads: a row of 256 channels = 32 chunks of 8 channels
     const int tid = threadIdx.y * 128 + threadIdx.x;
-#pragma unroll 4
+#pragma unroll 8
     for (int idx = tid; idx < ROWS * 32; idx += 256) {
       const int r = idx >> 5, c16 = idx & 31;
       const int t = t0 - PAD + r;
@@ -124,21 +126,24 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in
   for (int j = 0; j < K; ++j) w0[j] = __ldg(w + (size_t)c * K + j), w1[j] = __ldg(w + (size_t)(c + 1) * K + j);
   const float b0 = __ldg(bias + c), b1 = __ldg(bias + c + 1);
   bf16* dst = out + (size_t)b * L * C;
-  const int per_y = TT / 2;
-  for (int tt = threadIdx.y * per_y; tt < (threadIdx.y + 1) * per_y; tt += 4) {
-    float a0[4] = {b0, b0, b0, b0}, a1[4] = {b1, b1, b1, b1};
+  constexpr int per_y = TT / 2;
+  for (int tt = threadIdx.y * per_y; tt < (threadIdx.y + 1) * per_y; tt += FG) {
+    if (t0 + tt >= L) break;
+    float a0[FG], a1[FG];
 #pragma unroll
-    for (int j = 0; j < K + 3; ++j) {
+    for (int o = 0; o < FG; ++o) a0[o] = b0, a1[o] = b1;
+#pragma unroll
+    for (int j = 0; j < K + FG - 1; ++j) {
       const uint32_t xv = tile[tt + j][cp];
       const float x0 = bf16_lo(xv), x1 = bf16_hi(xv);
 #pragma unroll
-      for (int o = 0; o < 4; ++o) {
+      for (int o = 0; o < FG; ++o) {
         const int tap = j - o;
         if (tap >= 0 && tap < K) a0[o] = fmaf(w0[tap], x0, a0[o]), a1[o] = fmaf(w1[tap], x1, a1[o]);
       }
     }
 #pragma unroll
-    for (int o = 0; o < 4; ++o) {
+    for (int o = 0; o < FG; ++o) {
       const int t = t0 + tt + o;
       if (t < L)
         *reinterpret_cast<uint32_t*>(dst + (size_t)t * C + c) = pack_bf16x2(swoosh_r_fast(a0[o]), swoosh_r_fast(a1[o]));
@@ -146,17 +151,29 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in
   }
 }
 
+template <int K, int TT, int FG>
+static int launch_dwconv(const bf16* in, const float* w, const float* bias, int nb, int L, int C, bf16* out,
+                         cudaStream_t s) {
+  constexpr int smem = (TT + K - 1) * 128 * 4;
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(dwconv_kernel<K, TT, FG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    attr = true;
+  }
+  dim3 grid((L + TT - 1) / TT, (C + 255) / 256, nb), block(128, 2);
+  dwconv_kernel<K, TT, FG><<<grid, block, smem, s>>>(in, w, bias, L, C, out);
+  return (int)cudaGetLastError();
+}
+
 int dwconv_swooshr(const bf16* in, const float* w, const float* bias, int nb, int L, int C, int k, bf16* out,
                    cudaStream_t s) {
-  dim3 grid((L + 63) / 64, (C + 255) / 256, nb), block(128, 2);
   switch (k) {
-    case 7: dwconv_kernel<7><<<grid, block, 0, s>>>(in, w, bias, L, C, out); break;
-    case 9: dwconv_kernel<9><<<grid, block, 0, s>>>(in, w, bias, L, C, out); break;
-    case 15: dwconv_kernel<15><<<grid, block, 0, s>>>(in, w, bias, L, C, out); break;
-    case 31: dwconv_kernel<31><<<grid, block, 0, s>>>(in, w, bias, L, C, out); break;
+    case 7: return launch_dwconv<7, 64, 8>(in, w, bias, nb, L, C, out, s);
+    case 9: return launch_dwconv<9, 64, 8>(in, w, bias, nb, L, C, out, s);
+    case 15: return launch_dwconv<15, 128, 8>(in, w, bias, nb, L, C, out, s);
+    case 31: return launch_dwconv<31, 128, 8>(in, w, bias, nb, L, C, out, s);
     default: return 910;
   }
-  return (int)cudaGetLastError();
 }
 
 // ------------------------------------------------------------------ BiasNorm + bypass (one warp per row)

@@ -196,3 +196,25 @@ def make_audio(batch: int, n_samples: int, seed: int = 7):
     x = x.unfold(1, 5, 1).mean(-1)
     t = torch.arange(n_samples) / 24000.0
     return x + 0.05 * torch.sin(2 * math.pi * 220.0 * t) + 0.03 * torch.sin(2 * math.pi * 1760.0 * t)
+
+
+def make_vocos_state_dict(seed: int = 0) -> Dict[str, torch.Tensor]:
+    """Seeded random weights of the Vocos mel-24khz architecture with the checkpoint's tensor names
+    (``backbone.*``, ``head.out.*``): there is no network for the pretrained vocoder.  Scales are
+    init-like but larger than the original trunc-normal(0.02) so that every block contributes;
+    layer scale gamma ~ 1 / num_layers."""
+    DIM, INTER, LAYERS, N_MELS, N_FFT = 512, 1536, 8, 100, 1024
+    g = torch.Generator().manual_seed(1000 + seed)
+    rn = lambda *s, std=1.0: torch.randn(*s, generator=g) * std
+    sd = {"backbone.embed.weight": rn(DIM, N_MELS, 7, std=0.06), "backbone.embed.bias": rn(DIM, std=0.05),
+          "backbone.norm.weight": 1 + rn(DIM, std=0.1), "backbone.norm.bias": rn(DIM, std=0.1),
+          "backbone.final_layer_norm.weight": 1 + rn(DIM, std=0.1), "backbone.final_layer_norm.bias": rn(DIM, std=0.1),
+          "head.out.weight": rn(N_FFT + 2, DIM, std=0.03), "head.out.bias": rn(N_FFT + 2, std=0.3)}
+    for i in range(LAYERS):
+        p = f"backbone.convnext.{i}"
+        sd.update({f"{p}.dwconv.weight": rn(DIM, 1, 7, std=0.3), f"{p}.dwconv.bias": rn(DIM, std=0.1),
+                   f"{p}.norm.weight": 1 + rn(DIM, std=0.1), f"{p}.norm.bias": rn(DIM, std=0.1),
+                   f"{p}.pwconv1.weight": rn(INTER, DIM, std=0.05), f"{p}.pwconv1.bias": rn(INTER, std=0.1),
+                   f"{p}.pwconv2.weight": rn(DIM, INTER, std=0.05), f"{p}.pwconv2.bias": rn(DIM, std=0.1),
+                   f"{p}.gamma": torch.full((DIM,), 1.0 / LAYERS) * (1 + rn(DIM, std=0.2))})
+    return sd
