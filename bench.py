@@ -260,13 +260,19 @@ def main():
             out_host.copy_(wav, non_blocking=True)
             torch.cuda.synchronize()
 
-        step_e2e()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(K):
+        for _ in range(max(1, min(W, 2))):
             step_e2e()
         barrier()
+        t0 = time.perf_counter()
+        marks = []
+        for _ in range(K):
+            step_e2e()
+            marks.append(time.perf_counter())
+        barrier()
         dt = torch.tensor([time.perf_counter() - t0], device=dev)
+        if rank == 0:
+            print("e2e step wall ms:", [round((b - a) * 1e3, 1) for a, b in zip([t0] + marks[:-1], marks)],
+                  file=sys.stderr)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         n_tok = sum(len(a) + len(b) + 1 for a, b in zip(tokens, prompt_tokens))

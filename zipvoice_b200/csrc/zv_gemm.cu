@@ -178,8 +178,13 @@ ZV_DEVINL void epi_apply(const EpiParams& ep, int m, int b, int n0, const float 
   }
 }
 
-static constexpr int NCG = 2;                  // epilogue column groups
-static constexpr int EPI_WARPS = 4 * NCG;
+// Epilogue column groups (4 warps each, one per TMEM lane quarter).  The modes whose epilogue is
+// transcendental-heavy (SwooshL / GELU / gates) are bound by the epilogue's issue rate when K is
+// short, so they get 4 groups = 4 warps per scheduler; the HBM-bound modes keep 2.
+static constexpr int MAX_NCG = 4;
+__host__ __device__ constexpr int ncg_for(int mode) {
+  return (mode == EPI_SWOOSHL_BF16 || mode == EPI_GELU_BF16 || mode == EPI_GLU_BF16) ? 4 : 2;
+}
 static constexpr int STG_BF16_BYTES = BM * 64;   // 128 rows x 32 bf16
 static constexpr int STG_F32_BYTES = BM * 128;   // 128 rows x 32 fp32
 
@@ -195,7 +200,7 @@ struct GemmSmemTail {
   uint64_t empty[8];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
-  uint64_t rbar[NCG][2];
+  uint64_t rbar[MAX_NCG][2];
   uint32_t tmem_base;
 };
 
@@ -260,9 +265,11 @@ ZV_DEVINL void add_bias32(float (&v)[32], const float* __restrict__ bias, const 
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(128 + 32 * EPI_WARPS, 1)
+__global__ void __launch_bounds__(128 + 128 * ncg_for(MODE), 1)
 gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, int k_blocks, int block_n, int stages,
                EpiParams ep) {
+  constexpr int NCG = ncg_for(MODE);
+  constexpr int EPI_WARPS = 4 * NCG;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages x A 16 KB][stages x W block_n*128 B][NCG x epilogue staging][tail]
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -643,6 +650,7 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
       rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, BM, 32, 64);
   }
   if (rc) return rc;
+  constexpr int NCG = ncg_for(MODE);
   const int w_stage = p.block_n * BK * 2;
   const int fixed = 1024 + (int)sizeof(GemmSmemTail) + NCG * stg_group_bytes(MODE);
   int stages = (227 * 1024 - fixed) / (A_STAGE_BYTES + w_stage);
@@ -658,7 +666,7 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
   const int n_tiles = p.N_pad / p.block_n;
   const int k_blocks = (p.K + BK - 1) / BK;
   const int grid = min(m_tiles * n_tiles, g_num_sms);
-  gemm_tc_kernel<MODE><<<grid, 128 + 32 * EPI_WARPS, smem, stream>>>(maps, m_tiles, n_tiles, k_blocks, p.block_n,
+  gemm_tc_kernel<MODE><<<grid, 128 + 128 * NCG, smem, stream>>>(maps, m_tiles, n_tiles, k_blocks, p.block_n,
                                                                       stages, ep);
   return (int)cudaGetLastError();
 }
