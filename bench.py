@@ -165,6 +165,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=64, help="utterances per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-trace", type=int, default=0, help="diagnostic: N extra e2e steps with per-stage syncs")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--profile-out", default=None, help="write the per-kernel-class table (JSON) here")
     args = ap.parse_args()
@@ -275,6 +276,20 @@ def main():
                   file=sys.stderr)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        if args.e2e_trace and rank == 0:  # diagnostic only: stage times with a sync after each stage
+            for _ in range(args.e2e_trace):
+                w0 = time.perf_counter()
+                x1_wo, _, _, _ = model.sample(tokens, prompt_tokens, pf_host.to(dev, non_blocking=True), pfl,
+                                              features_lens=features_lens, duration="real", num_step=NUM_STEP,
+                                              guidance_scale=GUIDANCE, t_shift=T_SHIFT,
+                                              x0=x0_host.to(dev, non_blocking=True))
+                torch.cuda.synchronize(); w1 = time.perf_counter()
+                wav = eng.vocos_decode(x1_wo.permute(0, 2, 1) / 0.1).clamp(-1, 1)
+                torch.cuda.synchronize(); w2 = time.perf_counter()
+                out_host.copy_(wav, non_blocking=True)
+                torch.cuda.synchronize(); w3 = time.perf_counter()
+                print("e2e trace ms: sample %.1f vocoder %.1f d2h %.1f" % ((w1 - w0) * 1e3, (w2 - w1) * 1e3,
+                                                                           (w3 - w2) * 1e3), file=sys.stderr)
         n_tok = sum(len(a) + len(b) + 1 for a, b in zip(tokens, prompt_tokens))
         e2e = {"value": audio_s / (float(dt.item()) / K), "unit": "audio-s/s",
                "h2d_bytes_per_step": int(pf_host.numel() * 4 + x0_host.numel() * 4 + n_tok * 8 + 3 * B * 8),

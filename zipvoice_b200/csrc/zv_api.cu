@@ -268,8 +268,7 @@ extern "C" int zv_sample(void* handle, int variant, const float* x0, const float
   API_TRY(ws_reserve(*e, e->fm, e->ws_fm, 2 * B, T));
   std::vector<float> ts(num_step + 1);
   zv_time_steps(t_start, t_end, num_step, t_shift, ts.data());
-  float* ts_dev = nullptr;  // time table on the device: no host synchronisation inside the loop
-  API_TRY((int)cudaMallocAsync((void**)&ts_dev, ts.size() * 4, s));
+  float* ts_dev = e->ws_fm.ts_dev;  // time table on the device: no host synchronisation inside the loop
   API_TRY(upload_small(e, ts_dev, ts.data(), (int)ts.size(), s));
   API_TRY(upload_small(e, e->ws_fm.guid_dev, guidance, guidance_len, s));
   const size_t n = (size_t)B * T * e->cfg.feat_dim;
@@ -277,7 +276,6 @@ extern "C" int zv_sample(void* handle, int variant, const float* x0, const float
   for (int i = 0; i < num_step; ++i)
     API_TRY(velocity_step(e, variant, ts[i], ts_dev + i, x1, text, speech, mask, B, T, all_zero, guidance_len, nullptr,
                           x1, ts[i + 1] - ts[i], s));
-  API_TRY((int)cudaFreeAsync(ts_dev, s));
   return 0;
 }
 

@@ -121,32 +121,35 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in
   }
   __syncthreads();
   if (!active) return;
-  float w0[K], w1[K];
+  // taps and accumulators as packed fp32 pairs (channel c, c+1): one FFMA2 per tap and frame
+  f32x2 wp[K];
 #pragma unroll
-  for (int j = 0; j < K; ++j) w0[j] = __ldg(w + (size_t)c * K + j), w1[j] = __ldg(w + (size_t)(c + 1) * K + j);
-  const float b0 = __ldg(bias + c), b1 = __ldg(bias + c + 1);
+  for (int j = 0; j < K; ++j) wp[j] = f2_pack(__ldg(w + (size_t)c * K + j), __ldg(w + (size_t)(c + 1) * K + j));
+  const f32x2 bp = f2_pack(__ldg(bias + c), __ldg(bias + c + 1));
   bf16* dst = out + (size_t)b * L * C;
   constexpr int per_y = TT / 2;
   for (int tt = threadIdx.y * per_y; tt < (threadIdx.y + 1) * per_y; tt += FG) {
     if (t0 + tt >= L) break;
-    float a0[FG], a1[FG];
+    f32x2 acc[FG];
 #pragma unroll
-    for (int o = 0; o < FG; ++o) a0[o] = b0, a1[o] = b1;
+    for (int o = 0; o < FG; ++o) acc[o] = bp;
 #pragma unroll
     for (int j = 0; j < K + FG - 1; ++j) {
       const uint32_t xv = tile[tt + j][cp];
-      const float x0 = bf16_lo(xv), x1 = bf16_hi(xv);
+      const f32x2 xp = f2_pack(bf16_lo(xv), bf16_hi(xv));
 #pragma unroll
       for (int o = 0; o < FG; ++o) {
         const int tap = j - o;
-        if (tap >= 0 && tap < K) a0[o] = fmaf(w0[tap], x0, a0[o]), a1[o] = fmaf(w1[tap], x1, a1[o]);
+        if (tap >= 0 && tap < K) acc[o] = f2_fma(wp[tap], xp, acc[o]);
       }
     }
 #pragma unroll
     for (int o = 0; o < FG; ++o) {
       const int t = t0 + tt + o;
+      float a0, a1;
+      f2_unpack(acc[o], a0, a1);
       if (t < L)
-        *reinterpret_cast<uint32_t*>(dst + (size_t)t * C + c) = pack_bf16x2(swoosh_r_fast(a0[o]), swoosh_r_fast(a1[o]));
+        *reinterpret_cast<uint32_t*>(dst + (size_t)t * C + c) = pack_bf16x2(swoosh_r_fast(a0), swoosh_r_fast(a1));
     }
   }
 }

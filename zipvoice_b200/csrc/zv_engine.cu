@@ -357,6 +357,7 @@ int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
   ZV_TRY(A((void**)&ws.conv_b, rows * D * 2));
   for (int i = 0; i < 3; ++i) ZV_TRY(A((void**)&ws.mask[i], rows));
   ZV_TRY(A((void**)&ws.t_dev, nb * 4));
+  ZV_TRY(A((void**)&ws.ts_dev, 1025 * 4));
   ZV_TRY(A((void**)&ws.g_dev, nb * 4));
   ZV_TRY(A((void**)&ws.guid_dev, nb * 4));
   ZV_TRY(A((void**)&ws.te_a, nb * td * 4));

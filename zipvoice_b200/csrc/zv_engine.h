@@ -68,7 +68,7 @@ struct Workspace {
                 *na_y = nullptr, *na_o = nullptr, *sa_v = nullptr, *sa_o = nullptr, *conv_a = nullptr,
                 *conv_b = nullptr;
   uint8_t* mask[3] = {nullptr, nullptr, nullptr};  // per distinct downsampling rate (1, 2, 4)
-  float *t_dev = nullptr, *g_dev = nullptr, *te_a = nullptr, *te_out = nullptr, *guid_dev = nullptr;
+  float *t_dev = nullptr, *ts_dev = nullptr /* time table of one sample(): 1025 floats */, *g_dev = nullptr, *te_a = nullptr, *te_out = nullptr, *guid_dev = nullptr;
   std::vector<void*> allocs;
 };
 
