@@ -167,6 +167,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-trace", type=int, default=0, help="diagnostic: N extra e2e steps with per-stage syncs")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--gemm-impl", type=int, default=0, help="diagnostic: 0 auto, 2 single-CTA tiles, 3 CTA pairs")
     ap.add_argument("--profile-out", default=None, help="write the per-kernel-class table (JSON) here")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -193,6 +194,8 @@ def main():
     sd.update({"vocoder." + k: v for k, v in synth.make_vocos_state_dict(0).items()})  # same handle: model + vocoder
     model = ZipVoiceB200(cfg, sd, synth.VOCAB_SIZE, synth.PAD_ID, kind="zipvoice", device=dev)
     eng = model.engine
+    if args.gemm_impl:
+        eng.set_option("gemm_impl", args.gemm_impl)
     B, T = args.batch, PROMPT_FRAMES + TARGET_FRAMES
 
     # ---------------- synthetic utterances (different per rank: data-parallel shards)

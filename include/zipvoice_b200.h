@@ -45,7 +45,8 @@ int zv_set_weight(void* handle, const char* name, const float* data, const int64
  * time-embedding projections).  Fails if a tensor of the architecture is missing. */
 int zv_finalize_weights(void* handle);
 
-/* options: "gemm_impl" 0 = tcgen05 kernel (default), 1 = SIMT checker kernel (tests only);
+/* options: "gemm_impl" 0 = tcgen05 kernel, CTA pairs (cta_group::2) for large problems (default), 1 = SIMT checker
+ * kernel (tests only), 2 = tcgen05 single-CTA tiles only, 3 = tcgen05 CTA pairs only;
  * "attn_impl" 0 = NonlinAttention on the tcgen05 kernel (default), 1 = mma.sync flash kernel (process-wide). */
 int zv_set_option(void* handle, const char* key, int value);
 

@@ -87,10 +87,16 @@ CASES = [
     (EPI_RESIDUAL, 333, 512, 48, {}),
     (EPI_RESIDUAL, 129, 192, 640, {}),
     (EPI_RESIDUAL, 20000, 512, 384, {"resbias": True, "L": 1219}),
+    # several persistent rounds per CTA / CTA pair, odd tile counts, ragged last tile
+    (EPI_SWOOSHL, 40100, 1536, 512, {"rowbias": True, "L": 1219}),
+    (EPI_GLU, 38000, 1024, 512, {"mask": True, "L": 1000}),
+    (EPI_NONLIN, 38500, 1152, 512, {"gate_cols": 768}),
+    (EPI_BIAS, 39000, 272, 512, {}),
+    (EPI_RESIDUAL, 38300, 512, 1920, {"orig": True}),
 ]
 
 
-@pytest.mark.parametrize("impl", [1, 0], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("impl", [1, 2, 3, 0], ids=["simt", "tcgen05", "tcgen05_pair", "auto"])
 @pytest.mark.parametrize("case", CASES, ids=lambda c: f"m{c[0]}_{c[1]}x{c[2]}x{c[3]}")
 def test_gemm(case, impl):
     mode, M, N, K, ex = case

@@ -39,7 +39,7 @@ def engine(kind, cfg_name, seed, stress):
     return _engines[key]
 
 
-@pytest.mark.parametrize("gemm_impl", [1, 0], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("gemm_impl", [1, 2, 3], ids=["simt", "tcgen05", "tcgen05_pair"])
 def test_velocity_small_stress(gemm_impl):
     m, cfg, sd = engine("zipvoice", "small", 1, True)
     m.engine.set_option("gemm_impl", gemm_impl)

@@ -7,6 +7,8 @@
 // compute warps and no CTA-wide barrier in the key loop.
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "zv_common.cuh"
 #include "zv_gemm.h"
 #include "zv_kernels.h"
@@ -68,7 +70,8 @@ using namespace sa;
 __global__ void __launch_bounds__(sa::THREADS, 2)
 attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__ CUtensorMap tmV, AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // align inside the shared window (pointer + integer keeps the shared address space: LDS/STS, not generic LD/ST)
+  Smem& sm = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.z, head = blockIdx.y, i0 = blockIdx.x * BQ;
   const int L = p.L, H = p.H, R = 2 * L - 1;
@@ -165,10 +168,12 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       }
       // ---- position term (rows g and g + 8 share table entries 8 columns apart), masks, running max
       float mx0 = -INFINITY, mx1 = -INFINITY;
-      {
+      // two copies of the loop behind ONE warp-uniform branch: with the mask test inside the loop the
+      // compiler predicates ~90 instructions per tile that still take issue slots on mask-free tiles
+      auto pos_term = [&](auto masked_tag) {
+        constexpr bool MASKED = decltype(masked_tag)::value;
         const float4* ew = &S.e[2 * qd - rl0 + (BQ - 1)];
         float4 ep0 = ew[-8], ep1 = ew[-7];
-        const bool masked = sflag[kt] != 0;
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
           const float4 ec0 = ew[nt * 8], ec1 = ew[nt * 8 + 1];
@@ -176,7 +181,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
           float a1 = s[nt][1] + pq0[0] * ec1.x + pq0[1] * ec1.y + pq0[2] * ec1.z + pq0[3] * ec1.w;
           float b0 = s[nt][2] + pq1[0] * ep0.x + pq1[1] * ep0.y + pq1[2] * ep0.z + pq1[3] * ep0.w;
           float b1 = s[nt][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
-          if (masked) {
+          if (MASKED) {
             const uint8_t k0 = mrow[nt * 8 + 2 * qd], k1 = mrow[nt * 8 + 2 * qd + 1];
             if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
             if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
@@ -185,7 +190,9 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
           mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
           ep0 = ec0, ep1 = ec1;
         }
-      }
+      };
+      if (sflag[kt] != 0) pos_term(std::true_type{});
+      else pos_term(std::false_type{});
       mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
       mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
       mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));

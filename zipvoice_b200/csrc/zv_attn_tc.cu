@@ -74,7 +74,10 @@ ZV_DEVINL uint32_t make_idesc_bf16_bmn(uint32_t M, uint32_t N) {
 
 // Scores of this warp's 16 rows x 32 keys of the staged tile: s[nt4][0..1] row g, [2..3] row g + 8.
 // Returns the two row maxima through mx0 / mx1.
-ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, bool masked, int kh, int lane, int rl0,
+// MASKED is a template parameter so that the caller takes ONE warp-uniform branch per tile instead of
+// ~45 predicated mask instructions that occupy issue slots on mask-free tiles.
+template <bool MASKED>
+ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, int kh, int lane, int rl0,
                           const uint32_t (&qa)[2][4], const float (&pq0)[4], const float (&pq1)[4], float (&s)[4][4],
                           float& mx0, float& mx1) {
   const int qd = lane & 3;
@@ -97,7 +100,7 @@ ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, bool mas
     float a1 = s[n4][1] + pq0[0] * ec1.x + pq0[1] * ec1.y + pq0[2] * ec1.z + pq0[3] * ec1.w;
     float b0 = s[n4][2] + pq1[0] * ep0.x + pq1[1] * ep0.y + pq1[2] * ep0.z + pq1[3] * ep0.w;
     float b1 = s[n4][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
-    if (masked) {
+    if (MASKED) {
       const uint8_t k0 = mrow[kh * 32 + n4 * 8 + 2 * qd], k1 = mrow[kh * 32 + n4 * 8 + 2 * qd + 1];
       if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
       if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
@@ -115,7 +118,8 @@ using namespace natc;
 __global__ void __launch_bounds__(natc::THREADS, 1)
 attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvbox, int n_mma0, int n_mma1) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // align inside the shared window (pointer + integer keeps the shared address space: LDS/STS, not generic LD/ST)
+  Smem& sm = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.y;
   const int i0 = blockIdx.x * BQ;
@@ -245,7 +249,8 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
         for (int ks = 0; ks < 2; ++ks) ldsm_x4(qa[ks], &sm.q[rg * 16 + (lane & 15)][ks * 16 + (lane >> 4) * 8]);
       }
       float mx0, mx1;
-      score_tile(sm, buf, smask + kt * BKV, sflag[kt] != 0, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+      if (sflag[kt] != 0) score_tile<true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+      else score_tile<false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
       m0 = fmaxf(m0, mx0), m1 = fmaxf(m1, mx1);
     }
     m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)), m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
@@ -268,7 +273,8 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
       if (kt + 2 < n_tiles) load_tile(kt + 2, (kt + 2) % 3);
       cp_async_commit();
       float mx0, mx1;
-      score_tile(sm, buf, smask + kt * BKV, sflag[kt] != 0, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+      if (sflag[kt] != 0) score_tile<true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+      else score_tile<false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
       if (kt >= 2) {  // the MMAs of tile kt-2 have read p[pb]
         if (lane == 0) mbar_wait(&sm.pfree[pb], ((kt >> 1) - 1) & 1);
         __syncwarp();

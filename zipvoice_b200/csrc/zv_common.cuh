@@ -178,6 +178,26 @@ ZV_DEVINL void swoosh_l_fast2(float& x0, float& x1) {
   f2_unpack(f2_fma(q, f2_pack(0.6931471805599453f, 0.6931471805599453f), lin), x0, x1);
 }
 
+// SwooshL on a pair with ONE MUFU op per element: ln(1 + z), z = 2^-|t| in (0, 1], is a degree-5
+// polynomial z*q(z) on the FMA pipe (max abs error 1.5e-6, far below the bf16 rounding of the result)
+// instead of a second MUFU (lg2).  The GEMM epilogue is MUFU-bound with two per element.
+ZV_DEVINL void swoosh_l_poly2(float& x0, float& x1) {
+  const float L2E = 1.4426950408889634f;
+  const f32x2 x = f2_pack(x0, x1);
+  float t0, t1;
+  f2_unpack(f2_fma(x, f2_pack(L2E, L2E), f2_pack(-4.0f * L2E, -4.0f * L2E)), t0, t1);
+  const f32x2 z = f2_pack(ex2_approx(-fabsf(t0)), ex2_approx(-fabsf(t1)));
+  f32x2 q = f2_fma(z, f2_pack(-0.01834004558622837f, -0.01834004558622837f),
+                   f2_pack(0.08557301759719849f, 0.08557301759719849f));
+  q = f2_fma(q, z, f2_pack(-0.19376389682292938f, -0.19376389682292938f));
+  q = f2_fma(q, z, f2_pack(0.31765028834342957f, 0.31765028834342957f));
+  q = f2_fma(q, z, f2_pack(-0.49787530303001404f, -0.49787530303001404f));
+  q = f2_fma(q, z, f2_pack(0.9999016523361206f, 0.9999016523361206f));
+  const f32x2 lin = f2_fma(x, f2_pack(-0.08f, -0.08f), f2_pack(-0.035f, -0.035f));
+  const f32x2 u = f2_fma(f2_pack(fmaxf(t0, 0.f), fmaxf(t1, 0.f)), f2_pack(0.6931471805599453f, 0.6931471805599453f), lin);
+  f2_unpack(f2_fma(z, q, u), x0, x1);
+}
+
 // softplus(x - off) = ln2 * (max(t, 0) + lg2(1 + 2^-|t|)), t = (x - off) log2(e): no overflow, so the
 // reference's "inf -> x - off" guard (scaling.py:1176-1178) is satisfied by construction.
 ZV_DEVINL float softplus_shift(float x, float off_log2e) {
@@ -221,6 +241,63 @@ ZV_DEVINL void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
 }
+// ------------------------------------------------------------------ CTA pairs (cluster of 2, cta_group::2)
+ZV_DEVINL uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+ZV_DEVINL void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cta address of this CTA -> shared::cluster address of the same offset in CTA `rank`
+ZV_DEVINL uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+// arrive on an mbarrier that lives in another CTA of the cluster (address from mapa_shared)
+ZV_DEVINL void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// 2D tiled load into THIS CTA's shared memory whose completion bytes are signalled on an mbarrier of
+// either CTA of the pair (cluster address): both CTAs of a pair feed the leader's full barrier.
+ZV_DEVINL void tma_load_2d_pair(void* smem_dst, const void* desc, uint32_t bar_cluster_addr, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], "
+      "[%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(desc)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+      : "memory");
+}
+// TMEM allocation for a CTA pair: one warp of EACH CTA executes it with the same shared-memory offset.
+ZV_DEVINL void tmem_alloc_pair(uint32_t* smem_out, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_out)),
+               "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+ZV_DEVINL void tmem_dealloc_pair(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+// D[tmem of both CTAs, 256 rows] (+)= A[128 rows per CTA] * B[N/2 rows per CTA]^T; issued by ONE thread of
+// the leader CTA (rank 0); shared-memory descriptors are offsets valid in both CTAs.
+ZV_DEVINL void umma_bf16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// all previously issued pair MMAs arrive on the mbarrier at this offset in every CTA of `cta_mask`
+ZV_DEVINL void umma_commit_pair(uint64_t* bar, uint16_t cta_mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"(cta_mask)
+      : "memory");
+}
+
 // 32 lanes x 16 consecutive fp32 columns -> 16 registers per thread (thread = TMEM lane).
 ZV_DEVINL void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
   asm volatile(

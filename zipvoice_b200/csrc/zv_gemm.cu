@@ -11,6 +11,7 @@
 // Persistent: grid = min(#tiles, #SMs); tile t -> (m_blk = t / n_tiles, n_blk = t % n_tiles).
 #include <cuda.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <unordered_map>
@@ -200,7 +201,7 @@ struct GemmSmemTail {
   uint64_t empty[8];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
-  uint64_t rbar[MAX_NCG][2];
+  uint64_t rbar[MAX_NCG * 4][2];  // per epilogue warp
   uint32_t tmem_base;
 };
 
@@ -264,7 +265,11 @@ ZV_DEVINL void add_bias32(float (&v)[32], const float* __restrict__ bias, const 
   }
 }
 
-template <int MODE>
+// PAIR: cluster of two CTAs (one TPC) driving `tcgen05.mma.cta_group::2`: the pair owns a 256 x block_n
+// tile, each CTA loads its own 128 rows of A and HALF of the W tile, the leader (cluster rank 0) issues
+// the MMAs for both, accumulators land in each CTA's own TMEM, each CTA runs the epilogue of its rows.
+// Per output element this halves the W bytes pulled from L2, which is what bounds the K = 512 GEMMs.
+template <int MODE, bool PAIR>
 __global__ void __launch_bounds__(128 + 128 * ncg_for(MODE), 1)
 gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, int k_blocks, int block_n, int stages,
                EpiParams ep) {
@@ -272,8 +277,11 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
   constexpr int EPI_WARPS = 4 * NCG;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages x A 16 KB][stages x W block_n*128 B][NCG x epilogue staging][tail]
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int w_stage_bytes = block_n * BK * 2;
+  // align inside the shared window (pointer + integer keeps the shared address space: LDS/STS, not generic LD/ST)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+  const int wn = PAIR ? (block_n >> 1) : block_n;  // W rows this CTA holds per stage
+  const int w_stage_bytes = wn * BK * 2;
   uint8_t* sA = smem;
   uint8_t* sW = smem + stages * A_STAGE_BYTES;
   uint8_t* sStg = sW + stages * w_stage_bytes;
@@ -281,7 +289,11 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int total_tiles = m_tiles * n_tiles;
+  // work units: tiles (single CTA) or pair tiles of 256 rows; unit u -> (u / n_tiles, u % n_tiles)
+  const int unit0 = PAIR ? (blockIdx.x >> 1) : blockIdx.x;
+  const int nunits = PAIR ? (gridDim.x >> 1) : gridDim.x;
+  const int total_tiles = (PAIR ? ((m_tiles + 1) >> 1) : m_tiles) * n_tiles;
+  auto tile_m = [&](int t) { return PAIR ? 2 * (t / n_tiles) + (int)rank : t / n_tiles; };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&maps.A);
@@ -294,14 +306,18 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tail->tmem_full[i], 1);
-      mbar_init(&tail->tmem_empty[i], EPI_WARPS);
+      mbar_init(&tail->tmem_empty[i], PAIR ? 2 * EPI_WARPS : EPI_WARPS);
     }
-    for (int g = 0; g < NCG; ++g) mbar_init(&tail->rbar[g][0], 1), mbar_init(&tail->rbar[g][1], 1);
+    for (int g = 0; g < NCG * 4; ++g) mbar_init(&tail->rbar[g][0], 1), mbar_init(&tail->rbar[g][1], 1);
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(&tail->tmem_base, 512);
+  if (warp == 2) {
+    if (PAIR) tmem_alloc_pair(&tail->tmem_base, 512);
+    else tmem_alloc(&tail->tmem_base, 512);
+  }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = tail->tmem_base;
 
@@ -310,25 +326,33 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t tx = A_STAGE_BYTES + w_stage_bytes;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int m_blk = t / n_tiles, n_blk = t % n_tiles;
+      for (int t = unit0; t < total_tiles; t += nunits) {
+        const int m_blk = tile_m(t), n_blk = t % n_tiles;
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&tail->empty[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&tail->full[stage], tx);
-          tma_load_2d(sA + stage * A_STAGE_BYTES, &maps.A, &tail->full[stage], kb * BK, m_blk * BM);
-          tma_load_2d(sW + stage * w_stage_bytes, &maps.W, &tail->full[stage], kb * BK, n_blk * block_n);
+          if (PAIR) {
+            // both CTAs' bytes complete on the leader's full barrier
+            const uint32_t fb = mapa_shared(smem_u32(&tail->full[stage]), 0);
+            if (rank == 0) mbar_arrive_expect_tx(&tail->full[stage], 2 * tx);
+            tma_load_2d_pair(sA + stage * A_STAGE_BYTES, &maps.A, fb, kb * BK, m_blk * BM);
+            tma_load_2d_pair(sW + stage * w_stage_bytes, &maps.W, fb, kb * BK, n_blk * block_n + (int)rank * wn);
+          } else {
+            mbar_arrive_expect_tx(&tail->full[stage], tx);
+            tma_load_2d(sA + stage * A_STAGE_BYTES, &maps.A, &tail->full[stage], kb * BK, m_blk * BM);
+            tma_load_2d(sW + stage * w_stage_bytes, &maps.W, &tail->full[stage], kb * BK, n_blk * block_n);
+          }
           if (++stage == stages) stage = 0, phase ^= 1;
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(BM, block_n);
+    if (lane == 0 && rank == 0) {
+      const uint32_t idesc = make_idesc_bf16(PAIR ? 2 * BM : BM, block_n);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      for (int t = unit0; t < total_tiles; t += nunits, ++it) {
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&tail->tmem_empty[as], aphase ^ 1);
@@ -340,10 +364,17 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           const uint64_t da = make_sdesc_sw128(smem_u32(sA + stage * A_STAGE_BYTES));
           const uint64_t dw = make_sdesc_sw128(smem_u32(sW + stage * w_stage_bytes));
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            umma_bf16(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit(&tail->empty[stage]);
-          if (kb == k_blocks - 1) umma_commit(&tail->tmem_full[as]);
+          for (int k = 0; k < BK / 16; ++k) {
+            if (PAIR) umma_bf16_pair(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            else umma_bf16(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          if (PAIR) {
+            umma_commit_pair(&tail->empty[stage], 3);
+            if (kb == k_blocks - 1) umma_commit_pair(&tail->tmem_full[as], 3);
+          } else {
+            umma_commit(&tail->empty[stage]);
+            if (kb == k_blocks - 1) umma_commit(&tail->tmem_full[as]);
+          }
           if (++stage == stages) stage = 0, phase ^= 1;
         }
       }
@@ -353,21 +384,27 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     const int q = warp & 3;            // TMEM lane quarter == warp % 4
     const int cg = (warp - 4) >> 2;    // column group
     const int r = q * 32 + lane;       // row within the tile
-    const bool leader = (q == 0 && lane == 0);
-    const int bar_id = 1 + cg;
     uint8_t* stg = sStg + cg * stg_group_bytes(MODE);
     const int nchunks = block_n >> 5;
     uint32_t nq = 0;  // chunks processed by this group (selects the staging buffer / residual barrier phase)
 
     // EPI_RESIDUAL: the leader prefetches the first residual chunk of this group
-    if (MODE == EPI_RESIDUAL && leader && blockIdx.x < total_tiles && cg < nchunks) {
-      const int m_blk = blockIdx.x / n_tiles, n_blk = blockIdx.x % n_tiles;
-      mbar_arrive_expect_tx(&tail->rbar[cg][0], STG_F32_BYTES);
-      tma_load_2d(stg, &maps.R, &tail->rbar[cg][0], n_blk * block_n + cg * 32, m_blk * BM);
+    // tmem_empty lives in the leader CTA of a pair
+    auto release_acc = [&](int as) {
+      if (PAIR) mbar_arrive_cluster(mapa_shared(smem_u32(&tail->tmem_empty[as]), 0));
+      else mbar_arrive(&tail->tmem_empty[as]);
+    };
+    // Every epilogue warp is its own pipeline: it stages, loads and stores only its 32 rows (TMA boxes of
+    // 32 rows), so the only synchronisation inside the epilogue is __syncwarp.
+    uint64_t* rbar = &tail->rbar[cg * 4 + q][0];
+    if (MODE == EPI_RESIDUAL && lane == 0 && unit0 < total_tiles && cg < nchunks) {
+      const int m_blk = tile_m(unit0), n_blk = unit0 % n_tiles;
+      mbar_arrive_expect_tx(&rbar[0], STG_F32_BYTES / 4);
+      tma_load_2d(stg + q * (STG_F32_BYTES / 4), &maps.R, &rbar[0], n_blk * block_n + cg * 32, m_blk * BM + q * 32);
     }
     int it = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-      const int m_blk = t / n_tiles, n_blk = t % n_tiles;
+    for (int t = unit0; t < total_tiles; t += nunits, ++it) {
+      const int m_blk = tile_m(t), n_blk = t % n_tiles;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       const int m = m_blk * BM + r;
@@ -380,7 +417,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       if (cg >= nchunks) {  // this group owns no chunk of the tile: release the accumulator right away
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tail->tmem_empty[as]);
+        if (lane == 0) release_acc(as);
       }
       for (int c = cg; c < nchunks; c += NCG, ++nq) {
         const int n0 = n_blk * block_n + c * 32;
@@ -390,7 +427,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         if (c + NCG >= nchunks) {  // last accumulator read of this tile by this warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&tail->tmem_empty[as]);
+          if (lane == 0) release_acc(as);
         }
         float v[32];
 #pragma unroll
@@ -404,21 +441,21 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           const int sb = nq & 1;
           float* fb = reinterpret_cast<float*>(stg + sb * STG_F32_BYTES);
           uint8_t* shadow = stg + 2 * STG_F32_BYTES;
-          if (leader) {
+          if (lane == 0) {
             // the previous chunk's stores must have finished reading buffer sb^1 and the shadow buffer
             tma_store_wait_read<0>();
             // prefetch the residual of the next chunk of this group (possibly in the next tile)
             int c2 = c + NCG, t2 = t;
-            if (c2 >= nchunks) c2 = cg, t2 = t + gridDim.x;
+            if (c2 >= nchunks) c2 = cg, t2 = t + nunits;
             if (t2 < total_tiles) {
-              const int mb2 = t2 / n_tiles, nb2 = t2 % n_tiles;
-              mbar_arrive_expect_tx(&tail->rbar[cg][sb ^ 1], STG_F32_BYTES);
-              tma_load_2d(stg + (sb ^ 1) * STG_F32_BYTES, &maps.R, &tail->rbar[cg][sb ^ 1], nb2 * block_n + c2 * 32,
-                          mb2 * BM);
+              const int mb2 = tile_m(t2), nb2 = t2 % n_tiles;
+              mbar_arrive_expect_tx(&rbar[sb ^ 1], STG_F32_BYTES / 4);
+              tma_load_2d(stg + (sb ^ 1) * STG_F32_BYTES + q * (STG_F32_BYTES / 4), &maps.R, &rbar[sb ^ 1],
+                          nb2 * block_n + c2 * 32, mb2 * BM + q * 32);
             }
           }
           add_bias32(v, ep.bias, ep.resbias ? ep.resbias + (size_t)b * ep.bias_ld : nullptr, n0, ep.N);
-          mbar_wait(&tail->rbar[cg][sb], (nq >> 1) & 1);
+          mbar_wait(&rbar[sb], (nq >> 1) & 1);
           const int x = r & 7;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -441,18 +478,17 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
                 if (n0 + i < ep.N) v[i] = og[i] + (v[i] - og[i]) * ep.bypass_scale[n0 + i];
             }
           }
-          __syncwarp();
-          named_bar_sync(bar_id, 128);  // shadow buffer free (leader waited), everyone has read its row
+          __syncwarp();  // shadow buffer free (lane 0 waited), every lane has read its row
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             *reinterpret_cast<float4*>(fb + r * 32 + ((j ^ x) << 2)) =
                 make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
           if (ep.out_bf16) stage_row_bf16x32(shadow, r, v);
           fence_proxy_async_smem();
-          named_bar_sync(bar_id, 128);
-          if (leader) {
-            tma_store_2d(&maps.O1, fb, n0, m_blk * BM);
-            if (ep.out_bf16) tma_store_2d(&maps.O0, shadow, n0, m_blk * BM);
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&maps.O1, fb + q * 32 * 32, n0, m_blk * BM + q * 32);
+            if (ep.out_bf16) tma_store_2d(&maps.O0, shadow + q * 32 * 64, n0, m_blk * BM + q * 32);
             tma_store_commit();
           }
           continue;
@@ -478,26 +514,31 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
             for (int i = 0; i < 16; ++i) o16[i] = v[16 + i] * tanh_approx(v[i]);
           }
         }
-        if (leader) tma_store_wait_read<1>();  // the store that last used this staging buffer has read it
+        if (lane == 0) tma_store_wait_read<1>();  // the store that last used this staging buffer has read it
         __syncwarp();
-        named_bar_sync(bar_id, 128);
-        if (gated) stage_row_bf16x16(sbuf, r, o16);
+        // every warp owns bytes [q * 2048, q * 2048 + 2048) of the buffer for both row widths (gated rows use half)
+        if (gated) stage_row_bf16x16(sbuf + q * 2048, lane, o16);
         else if (MODE == EPI_BIAS_BF16 && ep.out_f16) stage_row_f16x32(sbuf, r, v);
         else stage_row_bf16x32(sbuf, r, v);
         fence_proxy_async_smem();
-        named_bar_sync(bar_id, 128);
-        if (leader) {
-          if (MODE == EPI_NONLIN_BF16 && !gated) tma_store_2d(&maps.O1, sbuf, n0 - ep.gate_cols, m_blk * BM);
-          else tma_store_2d(&maps.O0, sbuf, gated ? (n0 >> 1) : n0, m_blk * BM);
+        __syncwarp();
+        if (lane == 0) {
+          const uint8_t* src = sbuf + q * 2048;
+          if (MODE == EPI_NONLIN_BF16 && !gated) tma_store_2d(&maps.O1, src, n0 - ep.gate_cols, m_blk * BM + q * 32);
+          else tma_store_2d(&maps.O0, src, gated ? (n0 >> 1) : n0, m_blk * BM + q * 32);
           tma_store_commit();
         }
       }
     }
-    if (leader) tma_store_wait_all<0>();
+    if (lane == 0) tma_store_wait_all<0>();
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_base, 512);
+  if (PAIR) cluster_sync_all();  // no CTA leaves while its peer may still signal it or be read by the leader's MMAs
+  if (warp == 2) {
+    if (PAIR) tmem_dealloc_pair(tmem_base, 512);
+    else tmem_dealloc(tmem_base, 512);
+  }
 }
 
 // SIMT checker: one thread per (row, 32-column group); same epilogue.  Tests / debugging only.
@@ -612,6 +653,60 @@ int gemm_pick_block_n(int n_valid, int mode, int gate_cols) {
 
 static int g_num_sms = 0;
 
+template <int MODE, bool PAIR>
+static int launch_tc(const GemmMaps& maps, const GemmPlan& p, const EpiParams& ep, cudaStream_t stream) {
+  constexpr int NCG = ncg_for(MODE);
+  constexpr int threads = 128 + 128 * NCG;
+  const int w_stage = (PAIR ? p.block_n / 2 : p.block_n) * BK * 2;
+  const int fixed = 1024 + (int)sizeof(GemmSmemTail) + NCG * stg_group_bytes(MODE);
+  int stages = (227 * 1024 - fixed) / (A_STAGE_BYTES + w_stage);
+  if (stages > 8) stages = 8;
+  if (stages < 2) return 903;
+  const int smem = stages * (A_STAGE_BYTES + w_stage) + fixed;
+  static bool attr_set = false;
+  static int max_clusters = 0;
+  if (!attr_set) {
+    cudaFuncSetAttribute(gemm_tc_kernel<MODE, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (PAIR) {
+      cudaFuncSetAttribute(gemm_tc_kernel<MODE, PAIR>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0);
+      cudaLaunchConfig_t q = {};
+      q.gridDim = dim3(g_num_sms & ~1), q.blockDim = dim3(threads), q.dynamicSmemBytes = 227 * 1024;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = 2, qa[0].val.clusterDim.y = 1, qa[0].val.clusterDim.z = 1;
+      q.attrs = qa, q.numAttrs = 1;
+      if (cudaOccupancyMaxActiveClusters(&max_clusters, gemm_tc_kernel<MODE, PAIR>, &q) != cudaSuccess ||
+          max_clusters < 1) {
+        cudaGetLastError();
+        max_clusters = g_num_sms / 2;
+      }
+      if (getenv("ZV_VERBOSE"))
+        fprintf(stderr, "[zv] gemm mode %d: %d SMs, %d co-resident CTA pairs\n", MODE, g_num_sms, max_clusters);
+    }
+    attr_set = true;
+  }
+  const int m_tiles = (p.M + BM - 1) / BM;
+  const int n_tiles = p.N_pad / p.block_n;
+  const int k_blocks = (p.K + BK - 1) / BK;
+  if (!PAIR) {
+    const int grid = min(m_tiles * n_tiles, g_num_sms);
+    gemm_tc_kernel<MODE, PAIR><<<grid, threads, smem, stream>>>(maps, m_tiles, n_tiles, k_blocks, p.block_n, stages, ep);
+    return (int)cudaGetLastError();
+  }
+  const int units = ((m_tiles + 1) / 2) * n_tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * min(units, min(max_clusters, g_num_sms / 2)));
+  cfg.blockDim = dim3(threads), cfg.dynamicSmemBytes = smem, cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
+  cfg.attrs = at, cfg.numAttrs = 1;
+  return (int)cudaLaunchKernelEx(&cfg, gemm_tc_kernel<MODE, PAIR>, maps, m_tiles, n_tiles, k_blocks, p.block_n, stages,
+                                 ep);
+}
+
+// impl: 0 = tcgen05, CTA pairs when the problem has at least two waves of 128-row tiles; 1 = SIMT checker;
+//       2 = tcgen05 single-CTA tiles only; 3 = tcgen05 CTA pairs only.
 template <int MODE>
 static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const GemmPlan& p, const EpiParams& ep,
                        int impl, cudaStream_t stream) {
@@ -628,47 +723,32 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
   }
+  const int m_tiles_all = (p.M + BM - 1) / BM;
+  const bool pair = impl == 3 || (impl == 0 && (long long)m_tiles_all * (p.N_pad / p.block_n) >= 2LL * g_num_sms);
   GemmMaps maps;
   memset(&maps, 0, sizeof(maps));
   int rc = make_tmap_impl(&maps.A, A, 0, (uint64_t)p.M, (uint64_t)p.K, (uint64_t)p.lda, BM, 64, 128);
   if (rc) return rc;
-  rc = make_tmap_impl(&maps.W, W, 0, (uint64_t)p.N_pad, (uint64_t)p.K, (uint64_t)p.ldw, (uint32_t)p.block_n, 64, 128);
+  rc = make_tmap_impl(&maps.W, W, 0, (uint64_t)p.N_pad, (uint64_t)p.K, (uint64_t)p.ldw,
+                      (uint32_t)(pair ? p.block_n / 2 : p.block_n), 64, 128);
   if (rc) return rc;
   const uint64_t Mu = (uint64_t)ep.M;
   if (MODE == EPI_BIAS_BF16 || MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GELU_BF16) {
-    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, BM, 32, 64);
+    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, 32, 32, 64);
   } else if (MODE == EPI_GLU_BF16) {
-    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N / 2, (uint64_t)ep.ld_bf16, BM, 16, 32);
+    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N / 2, (uint64_t)ep.ld_bf16, 32, 16, 32);
   } else if (MODE == EPI_NONLIN_BF16) {
-    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.gate_cols / 2, (uint64_t)ep.ld_bf16, BM, 16, 32);
+    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.gate_cols / 2, (uint64_t)ep.ld_bf16, 32, 16, 32);
     if (!rc && ep.N > ep.gate_cols)
-      rc = make_tmap_impl(&maps.O1, ep.out2_bf16, 0, Mu, (uint64_t)(ep.N - ep.gate_cols), (uint64_t)ep.ld2_bf16, BM, 32, 64);
+      rc = make_tmap_impl(&maps.O1, ep.out2_bf16, 0, Mu, (uint64_t)(ep.N - ep.gate_cols), (uint64_t)ep.ld2_bf16, 32, 32, 64);
   } else if (MODE == EPI_RESIDUAL) {
-    rc = make_tmap_impl(&maps.O1, ep.out_f32, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, BM, 32, 128);
-    if (!rc) rc = make_tmap_impl(&maps.R, ep.res, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, BM, 32, 128);
+    rc = make_tmap_impl(&maps.O1, ep.out_f32, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, 32, 32, 128);
+    if (!rc) rc = make_tmap_impl(&maps.R, ep.res, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, 32, 32, 128);
     if (!rc && ep.out_bf16)
-      rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, BM, 32, 64);
+      rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, 32, 32, 64);
   }
   if (rc) return rc;
-  constexpr int NCG = ncg_for(MODE);
-  const int w_stage = p.block_n * BK * 2;
-  const int fixed = 1024 + (int)sizeof(GemmSmemTail) + NCG * stg_group_bytes(MODE);
-  int stages = (227 * 1024 - fixed) / (A_STAGE_BYTES + w_stage);
-  if (stages > 8) stages = 8;
-  if (stages < 2) return 903;
-  const int smem = stages * (A_STAGE_BYTES + w_stage) + fixed;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(gemm_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    attr_set = true;
-  }
-  const int m_tiles = (p.M + BM - 1) / BM;
-  const int n_tiles = p.N_pad / p.block_n;
-  const int k_blocks = (p.K + BK - 1) / BK;
-  const int grid = min(m_tiles * n_tiles, g_num_sms);
-  gemm_tc_kernel<MODE><<<grid, 128 + 128 * NCG, smem, stream>>>(maps, m_tiles, n_tiles, k_blocks, p.block_n,
-                                                                      stages, ep);
-  return (int)cudaGetLastError();
+  return pair ? launch_tc<MODE, true>(maps, p, ep, stream) : launch_tc<MODE, false>(maps, p, ep, stream);
 }
 
 int gemm_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const GemmPlan& plan, const EpiParams& ep, int impl,
