@@ -101,6 +101,8 @@ int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp
                        void* stream);
 int zv_debug_set_attn_impl(int impl);
 int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv, int use_mask, int dbg, int iters, float* ms_out);
+int zv_debug_gemm_bench(int mode, int impl, int M, int N, int K, int L, int gate_cols, int block_n, int iters,
+                        float* ms_out);
 int zv_debug_pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E_out, void* stream);
 /* Per-kernel-class device timing: when enabled every launch is bracketed by CUDA events on its stream.
  * zv_prof_read synchronises the device, fills ms / work / launches (arrays of zv_prof_num_classes()) and

@@ -173,3 +173,44 @@ extern "C" int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv,
   cudaFree(q), cudaFree(v), cudaFree(g), cudaFree(o), cudaFree(E), cudaFree(m);
   return rc;
 }
+
+// Kernel-only timing of one GEMM shape on synthetic device data (profiling aid; no parity meaning).
+// block_n <= 0 picks the production tile width.  Returns mean milliseconds per launch.
+extern "C" int zv_debug_gemm_bench(int mode, int impl, int M, int N, int K, int L, int gate_cols, int block_n,
+                                   int iters, float* ms_out) {
+  if (block_n <= 0) block_n = gemm_pick_block_n(N, mode, gate_cols);
+  const int N_pad = (N + block_n - 1) / block_n * block_n;
+  const int ld = (K + 63) / 64 * 64;
+  const int n_out = (mode == EPI_GLU_BF16) ? N / 2 : (mode == EPI_NONLIN_BF16 ? gate_cols / 2 : N);
+  const int n_out2 = mode == EPI_NONLIN_BF16 ? N - gate_cols : 0;
+  const int nb = (M + L - 1) / L;
+  __nv_bfloat16 *A = nullptr, *W = nullptr, *ob = nullptr, *ob2 = nullptr;
+  float *of = nullptr, *bias = nullptr, *rowb = nullptr;
+  cudaMalloc(&A, (size_t)M * ld * 2), cudaMalloc(&W, (size_t)N_pad * ld * 2);
+  cudaMalloc(&ob, (size_t)M * (n_out + 8) * 2), cudaMalloc(&ob2, (size_t)M * (n_out2 + 8) * 2);
+  cudaMalloc(&of, (size_t)M * N * 4), cudaMalloc(&bias, (size_t)N_pad * 4), cudaMalloc(&rowb, (size_t)nb * N_pad * 4);
+  cudaMemset(A, 0x3c, (size_t)M * ld * 2), cudaMemset(W, 0x3c, (size_t)N_pad * ld * 2);
+  cudaMemset(of, 0, (size_t)M * N * 4), cudaMemset(bias, 0, (size_t)N_pad * 4), cudaMemset(rowb, 0, (size_t)nb * N_pad * 4);
+  GemmPlan p;
+  p.M = M, p.N_pad = N_pad, p.K = K, p.lda = ld, p.ldw = ld, p.block_n = block_n;
+  EpiParams ep;
+  ep.mode = mode, ep.M = M, ep.N = N, ep.L = L, ep.gate_cols = gate_cols, ep.bias = bias;
+  ep.rowbias = (mode == EPI_SWOOSHL_BF16) ? rowb : nullptr, ep.resbias = (mode == EPI_RESIDUAL) ? rowb : nullptr;
+  ep.bias_ld = N_pad, ep.out_bf16 = ob, ep.ld_bf16 = (n_out + 7) / 8 * 8, ep.out2_bf16 = ob2, ep.ld2_bf16 = (n_out2 + 7) / 8 * 8;
+  ep.out_f32 = of, ep.ld_f32 = N, ep.res = of;
+  if (mode == EPI_F32) ep.out_bf16 = nullptr;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0), cudaEventCreate(&e1);
+  int rc = gemm_launch(A, W, p, ep, impl, 0);
+  cudaDeviceSynchronize();
+  cudaEventRecord(e0, 0);
+  for (int i = 0; i < iters && !rc; ++i) rc = gemm_launch(A, W, p, ep, impl, 0);
+  cudaEventRecord(e1, 0);
+  if (!rc) rc = (int)cudaDeviceSynchronize();
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  *ms_out = ms / (iters > 0 ? iters : 1);
+  cudaEventDestroy(e0), cudaEventDestroy(e1);
+  cudaFree(A), cudaFree(W), cudaFree(ob), cudaFree(ob2), cudaFree(of), cudaFree(bias), cudaFree(rowb);
+  return rc;
+}

@@ -385,7 +385,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     const int cg = (warp - 4) >> 2;    // column group
     const int r = q * 32 + lane;       // row within the tile
     uint8_t* stg = sStg + cg * stg_group_bytes(MODE);
-    const int nchunks = block_n >> 5;
+    const int nchunks_tile = block_n >> 5;
     uint32_t nq = 0;  // chunks processed by this group (selects the staging buffer / residual barrier phase)
 
     // EPI_RESIDUAL: the leader prefetches the first residual chunk of this group
@@ -397,7 +397,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     // Every epilogue warp is its own pipeline: it stages, loads and stores only its 32 rows (TMA boxes of
     // 32 rows), so the only synchronisation inside the epilogue is __syncwarp.
     uint64_t* rbar = &tail->rbar[cg * 4 + q][0];
-    if (MODE == EPI_RESIDUAL && lane == 0 && unit0 < total_tiles && cg < nchunks) {
+    if (MODE == EPI_RESIDUAL && lane == 0 && unit0 < total_tiles && cg < nchunks_tile) {
       const int m_blk = tile_m(unit0), n_blk = unit0 % n_tiles;
       mbar_arrive_expect_tx(&rbar[0], STG_F32_BYTES / 4);
       tma_load_2d(stg + q * (STG_F32_BYTES / 4), &maps.R, &rbar[0], n_blk * block_n + cg * 32, m_blk * BM + q * 32);
@@ -412,6 +412,10 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       const int b = mm / ep.L;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * ACC_STAGE_COLS;
       const float* rowb = (MODE != EPI_RESIDUAL && ep.rowbias) ? ep.rowbias + (size_t)b * ep.bias_ld : nullptr;
+      // chunks that lie entirely in the padded columns of the last n-tile are skipped (never for EPI_RESIDUAL,
+      // whose prefetch chain assumes full tiles: its N is a multiple of block_n)
+      const int nchunks = (MODE == EPI_RESIDUAL) ? nchunks_tile
+                                                 : min(nchunks_tile, (ep.N - n_blk * block_n + 31) >> 5);
       mbar_wait(&tail->tmem_full[as], aphase);
       tc_fence_after();
       if (cg >= nchunks) {  // this group owns no chunk of the tile: release the accumulator right away
@@ -637,17 +641,18 @@ int make_tmap(void* tm, const void* ptr, int dtype, uint64_t rows, uint64_t cols
 }
 
 int gemm_pick_block_n(int n_valid, int mode, int gate_cols) {
-  // block_n is a multiple of 32 (<= 256); the gated part of EPI_NONLIN_BF16 must end on a tile boundary.
-  // Preference: largest block_n >= 128 with no padding; else largest with <= 12.5 % padding; else least padding.
-  auto ok = [&](int bn) { return !(mode == EPI_NONLIN_BF16 && gate_cols % bn != 0); };
-  auto waste = [&](int bn) { return (n_valid + bn - 1) / bn * bn - n_valid; };
-  for (int bn = 256; bn >= 128; bn -= 32)
-    if (ok(bn) && waste(bn) == 0) return bn;
-  for (int bn = 256; bn >= 32; bn -= 32)
-    if (ok(bn) && waste(bn) * 8 <= n_valid) return bn;
-  int best = 32, best_waste = 1 << 30;
-  for (int bn = 256; bn >= 32; bn -= 32)
-    if (ok(bn) && waste(bn) < best_waste) best = bn, best_waste = waste(bn);
+  // block_n is a multiple of 32 (<= 256: two accumulator stages in 512 TMEM columns); the gated part of
+  // EPI_NONLIN_BF16 must end on a tile boundary.  Measured on B200 (tools/gemm_bench.py, K = 512) the time of
+  // a 128 x bn tile is ~ (160 + 0.6 bn): the A tile is re-read from L2 for every n-tile, so wide tiles win
+  // even with padded columns (N = 1152 -> 5 x 256 beats 6 x 192, N = 1920 -> 8 x 256 beats 10 x 192).
+  int best = 32;
+  double best_cost = 1e30;
+  for (int bn = 32; bn <= 256; bn += 32) {
+    if (mode == EPI_NONLIN_BF16 && gate_cols % bn != 0) continue;
+    const int tiles = (n_valid + bn - 1) / bn;
+    const double cost = tiles * (160.0 + 0.6 * bn);
+    if (cost <= best_cost) best = bn, best_cost = cost;
+  }
   return best;
 }
 
@@ -661,6 +666,8 @@ static int launch_tc(const GemmMaps& maps, const GemmPlan& p, const EpiParams& e
   const int fixed = 1024 + (int)sizeof(GemmSmemTail) + NCG * stg_group_bytes(MODE);
   int stages = (227 * 1024 - fixed) / (A_STAGE_BYTES + w_stage);
   if (stages > 8) stages = 8;
+  static const int stages_cap = getenv("ZV_GEMM_STAGES") ? atoi(getenv("ZV_GEMM_STAGES")) : 0;  // measurement aid
+  if (stages_cap >= 2 && stages > stages_cap) stages = stages_cap;
   if (stages < 2) return 903;
   const int smem = stages * (A_STAGE_BYTES + w_stage) + fixed;
   static bool attr_set = false;
@@ -705,7 +712,7 @@ static int launch_tc(const GemmMaps& maps, const GemmPlan& p, const EpiParams& e
                                  ep);
 }
 
-// impl: 0 = tcgen05, CTA pairs when the problem has at least two waves of 128-row tiles; 1 = SIMT checker;
+// impl: 0 = tcgen05, CTA pairs (cta_group::2) for the shapes where they measure faster; 1 = SIMT checker;
 //       2 = tcgen05 single-CTA tiles only; 3 = tcgen05 CTA pairs only.
 template <int MODE>
 static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const GemmPlan& p, const EpiParams& ep,
@@ -724,7 +731,12 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
     cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
   }
   const int m_tiles_all = (p.M + BM - 1) / BM;
-  const bool pair = impl == 3 || (impl == 0 && (long long)m_tiles_all * (p.N_pad / p.block_n) >= 2LL * g_num_sms);
+  // CTA pairs (cta_group::2) halve the W bytes each SM pulls from L2.  Measured per shape at M = 156 k
+  // (tools/gemm_bench.py): they win where the epilogue is light relative to the main loop -- residual GEMMs
+  // with K >= 1024 (246 vs 261 us at K = 1536) -- and lose or tie for the SwooshL / GLU / tanh-gate epilogues
+  // and the short-K HBM-bound residual GEMMs, which stay on single-CTA tiles.
+  const bool big = (long long)m_tiles_all * (p.N_pad / p.block_n) >= 2LL * g_num_sms;
+  const bool pair = impl == 3 || (impl == 0 && big && MODE == EPI_RESIDUAL && p.K >= 1024);
   GemmMaps maps;
   memset(&maps, 0, sizeof(maps));
   int rc = make_tmap_impl(&maps.A, A, 0, (uint64_t)p.M, (uint64_t)p.K, (uint64_t)p.lda, BM, 64, 128);
