@@ -96,7 +96,7 @@ int f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t s) {
 template <int K, int TT, int FG>
 __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in, const float* __restrict__ w,
                                                      const float* __restrict__ bias, int L, int C,
-                                                     bf16* __restrict__ out) {
+                                                     bf16* __restrict__ out, int ldo) {
   // TT frames per CTA (the halo of K - 1 frames is re-read: 23 % at TT = 128, K = 31), FG frames per register group
   constexpr int PAD = K / 2, ROWS = TT + K - 1;
   extern __shared__ __align__(16) uint32_t tile_raw[];
@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in
 #pragma unroll
   for (int j = 0; j < K; ++j) wp[j] = f2_pack(__ldg(w + (size_t)c * K + j), __ldg(w + (size_t)(c + 1) * K + j));
   const f32x2 bp = f2_pack(__ldg(bias + c), __ldg(bias + c + 1));
-  bf16* dst = out + (size_t)b * L * C;
+  bf16* dst = out + (size_t)b * L * ldo;
   constexpr int per_y = TT / 2;
   for (int tt = threadIdx.y * per_y; tt < (threadIdx.y + 1) * per_y; tt += FG) {
     if (t0 + tt >= L) break;
@@ -149,13 +149,13 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in
       float a0, a1;
       f2_unpack(acc[o], a0, a1);
       if (t < L)
-        *reinterpret_cast<uint32_t*>(dst + (size_t)t * C + c) = pack_bf16x2(swoosh_r_fast(a0), swoosh_r_fast(a1));
+        *reinterpret_cast<uint32_t*>(dst + (size_t)t * ldo + c) = pack_bf16x2(swoosh_r_fast(a0), swoosh_r_fast(a1));
     }
   }
 }
 
 template <int K, int TT, int FG>
-static int launch_dwconv(const bf16* in, const float* w, const float* bias, int nb, int L, int C, bf16* out,
+static int launch_dwconv(const bf16* in, const float* w, const float* bias, int nb, int L, int C, bf16* out, int ldo,
                          cudaStream_t s) {
   constexpr int smem = (TT + K - 1) * 128 * 4;
   static bool attr = false;
@@ -164,17 +164,18 @@ static int launch_dwconv(const bf16* in, const float* w, const float* bias, int 
     attr = true;
   }
   dim3 grid((L + TT - 1) / TT, (C + 255) / 256, nb), block(128, 2);
-  dwconv_kernel<K, TT, FG><<<grid, block, smem, s>>>(in, w, bias, L, C, out);
+  dwconv_kernel<K, TT, FG><<<grid, block, smem, s>>>(in, w, bias, L, C, out, ldo);
   return (int)cudaGetLastError();
 }
 
-int dwconv_swooshr(const bf16* in, const float* w, const float* bias, int nb, int L, int C, int k, bf16* out,
+int dwconv_swooshr(const bf16* in, const float* w, const float* bias, int nb, int L, int C, int k, bf16* out, int ldo,
                    cudaStream_t s) {
+  if (ldo < C || (ldo & 1)) return 911;
   switch (k) {
-    case 7: return launch_dwconv<7, 64, 8>(in, w, bias, nb, L, C, out, s);
-    case 9: return launch_dwconv<9, 64, 8>(in, w, bias, nb, L, C, out, s);
-    case 15: return launch_dwconv<15, 128, 8>(in, w, bias, nb, L, C, out, s);
-    case 31: return launch_dwconv<31, 128, 8>(in, w, bias, nb, L, C, out, s);
+    case 7: return launch_dwconv<7, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
+    case 9: return launch_dwconv<9, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
+    case 15: return launch_dwconv<15, 128, 8>(in, w, bias, nb, L, C, out, ldo, s);
+    case 31: return launch_dwconv<31, 128, 8>(in, w, bias, nb, L, C, out, ldo, s);
     default: return 910;
   }
 }

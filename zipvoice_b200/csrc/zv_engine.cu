@@ -165,6 +165,49 @@ static int pack_linear(Engine& e, const std::string& name, int mode, Lin* lin, i
   return rc;
 }
 
+// SelfAttention.out_proj is folded into the ConvolutionModule that follows it (zipformer.py:564-587,600-624):
+//   x3 = x2 + Wso o + bso (+ te),   x4 = x3 + Wco conv(GLU(Wci x3 + bci)) + bco
+// becomes, with o = the 48-wide attention output kept next to the conv hidden state,
+//   GLU input = [x2 | o] [Wci | Wci Wso]^T + (bci + Wci bso) (+ Wci te as a per-batch row bias)
+//   x4        = x2 + [h | o] [Wco | Wso]^T + (bco + bso) (+ te)
+// so the stream makes ONE fp32 round trip through HBM for the two modules instead of two.
+static int fold_self_attn_into_conv(Engine& e, const std::string& so, const std::string& c, Lin* conv_in,
+                                    Lin* conv_out) {
+  const HostTensor *wso = find(e, so + ".weight"), *bso = find(e, so + ".bias");
+  const HostTensor *wci = find(e, c + ".in_proj.weight"), *bci = find(e, c + ".in_proj.bias");
+  const HostTensor *wco = find(e, c + ".out_proj.weight"), *bco = find(e, c + ".out_proj.bias");
+  if (!wso || !bso || !wci || !bci || !wco || !bco) return 940;
+  const int D = (int)wso->shape[0], V = (int)wso->shape[1], N2 = (int)wci->shape[0];
+  if ((int)wci->shape[1] != D || (int)wco->shape[0] != D || (int)wco->shape[1] != D || V > 64 || D % 64) {
+    e.err = "unexpected conv / self-attention projection shapes at " + c;
+    return 944;
+  }
+  const int Ke = D + V;
+  std::vector<float> wi((size_t)N2 * Ke), bi(N2), wo((size_t)D * Ke), bo(D);
+  for (int n = 0; n < N2; ++n) {
+    const float* w = &wci->data[(size_t)n * D];
+    float* dst = &wi[(size_t)n * Ke];
+    memcpy(dst, w, (size_t)D * 4);
+    double accb = bci->data[n];
+    for (int d = 0; d < D; ++d) accb += (double)w[d] * bso->data[d];
+    bi[n] = (float)accb;
+    for (int j = 0; j < V; ++j) {
+      double acc = 0.0;
+      for (int d = 0; d < D; ++d) acc += (double)w[d] * wso->data[(size_t)d * V + j];
+      dst[D + j] = (float)acc;
+    }
+  }
+  for (int n = 0; n < D; ++n) {
+    memcpy(&wo[(size_t)n * Ke], &wco->data[(size_t)n * D], (size_t)D * 4);
+    memcpy(&wo[(size_t)n * Ke + D], &wso->data[(size_t)n * V], (size_t)V * 4);
+    bo[n] = bco->data[n] + bso->data[n];
+  }
+  ZV_TRY(pack_linear_host(e, wi.data(), bi.data(), N2, Ke, EPI_GLU_BF16, conv_in, D + 64, nullptr));
+  conv_in->K_valid = D;  // algorithmic FLOPs of the reference in_proj; the folded 48 columns are counted below
+  ZV_TRY(pack_linear_host(e, wo.data(), bo.data(), D, Ke, EPI_RESIDUAL, conv_out, D + 64, nullptr));
+  return 0;
+}
+
 static int build_layer(Engine& e, Net& net, const std::string& p, int kernel, Layer* L) {
   ZV_TRY(pack_linear(e, p + ".self_attn_weights.in_proj", EPI_BIAS_BF16, &L->attn_in));
   ZV_TRY(upload_named(e, p + ".self_attn_weights.linear_pos.weight", &L->w_pos));
@@ -190,10 +233,8 @@ static int build_layer(Engine& e, Net& net, const std::string& p, int kernel, La
         }
       ZV_TRY(pack_linear_host(e, wp.data(), bp.data(), Hh * 16, K, EPI_BIAS_BF16, &L->sa_in[i], 0, nullptr));
     }
-    ZV_TRY(pack_linear(e, a + ".out_proj", EPI_RESIDUAL, &L->sa_out[i]));
     const std::string c = p + ".conv_module" + std::to_string(i + 1);
-    ZV_TRY(pack_linear(e, c + ".in_proj", EPI_GLU_BF16, &L->conv_in[i]));
-    ZV_TRY(pack_linear(e, c + ".out_proj", EPI_RESIDUAL, &L->conv_out[i]));
+    ZV_TRY(fold_self_attn_into_conv(e, a + ".out_proj", c, &L->conv_in[i], &L->conv_out[i]));
     ZV_TRY(upload_named(e, c + ".depthwise_conv.weight", &L->dw_w[i]));
     ZV_TRY(upload_named(e, c + ".depthwise_conv.bias", &L->dw_b[i]));
     const HostTensor* dw = find(e, c + ".depthwise_conv.weight");
@@ -261,7 +302,10 @@ static int build_net(Engine& e, Net& net, const std::string& prefix, int in_dim,
     if (use_time) st.te_off = te_cols, te_cols += D;
     for (int j = 0; j < nl[i]; ++j) {
       ZV_TRY(build_layer(e, net, ep + ".layers." + std::to_string(j), st.kernel, &st.layers[j]));
-      if (use_time) st.layers[j].te_off_ff1 = te_cols, te_cols += st.layers[j].ff_in[0].N;
+      if (use_time) {
+        st.layers[j].te_off_ff1 = te_cols, te_cols += st.layers[j].ff_in[0].N;
+        for (int i2 = 0; i2 < 2; ++i2) st.layers[j].te_off_conv[i2] = te_cols, te_cols += st.layers[j].conv_in[i2].N;
+      }
     }
   }
   net.N_te = (int)te_cols;
@@ -294,6 +338,26 @@ static int build_net(Engine& e, Net& net, const std::string& prefix, int in_dim,
         cudaDeviceSynchronize();
         cudaFree(wf_dev);
         ZV_TRY(rc);
+        // conv in_proj sees x + te as well (the time embedding added after each SelfAttention rides in the
+        // folded GEMMs): row bias = Wci te_stack, rows in accumulator (GLU-permuted) order
+        for (int i2 = 0; i2 < 2; ++i2) {
+          const HostTensor* wc = find(e, ep + ".layers." + std::to_string(j) + ".conv_module" + std::to_string(i2 + 1) +
+                                             ".in_proj.weight");
+          if (!wc) return 940;
+          const int N2 = (int)wc->shape[0];
+          const std::vector<int> perm = row_perm(EPI_GLU_BF16, N2);
+          std::vector<float> wperm((size_t)N2 * D);
+          for (int n = 0; n < N2; ++n) memcpy(&wperm[(size_t)n * D], &wc->data[(size_t)perm[n] * D], (size_t)D * 4);
+          float* wc_dev = nullptr;
+          ZV_TRY((int)cudaMalloc(&wc_dev, (size_t)N2 * D * 4));
+          cudaMemcpy(wc_dev, wperm.data(), (size_t)N2 * D * 4, cudaMemcpyHostToDevice);
+          const size_t offc = st.layers[j].te_off_conv[i2];
+          rc = sgemm_nn(wc_dev, net.te_proj_w + st.te_off * td, net.te_proj_w + offc * td, N2, td, D, 0);
+          if (!rc) rc = sgemm_nn(wc_dev, net.te_proj_b + st.te_off, net.te_proj_b + offc, N2, 1, D, 0);
+          cudaDeviceSynchronize();
+          cudaFree(wc_dev);
+          ZV_TRY(rc);
+        }
       }
     }
   }
@@ -352,9 +416,10 @@ int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
   ZV_TRY(A((void**)&ws.na_y, rows * net.hidden_na * 2));
   ZV_TRY(A((void**)&ws.na_o, rows * net.hidden_na * 2));
   ZV_TRY(A((void**)&ws.sa_v, rows * 64 * 2));
-  ZV_TRY(A((void**)&ws.sa_o, rows * 48 * 2));
   ZV_TRY(A((void**)&ws.conv_a, rows * D * 2));
-  ZV_TRY(A((void**)&ws.conv_b, rows * D * 2));
+  // conv hidden state (D columns) + SelfAttention output (48 of the 64 extra columns; the rest stays zero)
+  ZV_TRY(A((void**)&ws.conv_b, rows * (D + 64) * 2));
+  ZV_TRY((int)cudaMemset(ws.conv_b, 0, rows * (D + 64) * 2));
   for (int i = 0; i < 3; ++i) ZV_TRY(A((void**)&ws.mask[i], rows));
   ZV_TRY(A((void**)&ws.t_dev, nb * 4));
   ZV_TRY(A((void**)&ws.ts_dev, 1025 * 4));
@@ -365,9 +430,11 @@ int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
   return 0;
 }
 
-int run_gemm(Engine& e, const Lin& lin, const __nv_bfloat16* A, int lda, int M, EpiParams ep, cudaStream_t s) {
+int run_gemm(Engine& e, const Lin& lin, const __nv_bfloat16* A, int lda, int M, EpiParams ep, cudaStream_t s,
+             const __nv_bfloat16* A2, int lda2, int k_split) {
   GemmPlan p;
   p.M = M, p.N_pad = lin.N_pad, p.K = lin.K, p.lda = lda, p.ldw = lin.ldw, p.block_n = lin.block_n;
+  p.A2 = A2, p.lda2 = lda2, p.k_split = k_split;
   ep.mode = lin.mode, ep.M = M, ep.N = lin.N, ep.gate_cols = lin.gate_cols, ep.bias = lin.bias;
   ZV_K(KC_GEMM_BIAS + lin.mode, 2.0 * M * lin.N * (double)lin.K_valid, s,
        gemm_launch(A, lin.w, p, ep, e.gemm_impl, s));
@@ -384,8 +451,8 @@ static int run_attn(Engine& e, int cls, const AttnParams& a, int score_heads, cu
 }
 // algorithmic bytes: bf16 in + bf16 out
 static int run_dwconv(Engine& e, const __nv_bfloat16* in, const float* w, const float* b, int nb, int L, int C, int k,
-                      __nv_bfloat16* out, cudaStream_t s) {
-  ZV_K(KC_DWCONV, 4.0 * nb * L * C, s, dwconv_swooshr(in, w, b, nb, L, C, k, out, s));
+                      __nv_bfloat16* out, int ld_out, cudaStream_t s) {
+  ZV_K(KC_DWCONV, 4.0 * nb * L * C, s, dwconv_swooshr(in, w, b, nb, L, C, k, out, ld_out, s));
   return 0;
 }
 
@@ -430,26 +497,26 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
     if (rc) return rc;
     return residual(ly.ff_out[i], ws.hidden, ly.ff_in[i].N, res, resbias, orig, bscale);
   };
-  auto self_attn = [&](int i, const float* resbias) {
+  const int ldc = D + 64;  // conv_b row pitch: [conv hidden (D) | SelfAttention output (48) | zeros (16)]
+  auto self_attn = [&](int i) {
     EpiParams v;
     v.L = L, v.out_bf16 = ws.sa_v, v.ld_bf16 = 16 * net.H;
     int rc = run_gemm(e, ly.sa_in[i], ws.shadow, D, M, v, s);
     if (rc) return rc;
     AttnParams a;
     a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.sa_v, a.ldv = 16 * net.H, a.vhs = 16, a.gate = nullptr, a.ldg = 0;
-    a.out = ws.sa_o, a.ldo = 48, a.nb = nb, a.L = L, a.H = net.H, a.heads = net.H, a.dv = 12;
-    rc = run_attn(e, KC_ATTN_SELF, a, i == 0 ? net.H - 1 : 0, s);
-    if (rc) return rc;
-    return residual(ly.sa_out[i], ws.sa_o, 48, ws.Y, resbias, nullptr, nullptr);
+    a.out = ws.conv_b + D, a.ldo = ldc, a.nb = nb, a.L = L, a.H = net.H, a.heads = net.H, a.dv = 12;
+    return run_attn(e, KC_ATTN_SELF, a, i == 0 ? net.H - 1 : 0, s);  // out_proj: folded into conv(i)
   };
-  auto conv = [&](int i) {
+  // SelfAttention(i).out_proj + time embedding + ConvolutionModule(i) with one pass over the fp32 stream
+  auto conv = [&](int i, const float* te_conv, const float* resbias) {
     EpiParams c;
-    c.L = L, c.mask = mask, c.out_bf16 = ws.conv_a, c.ld_bf16 = D;
-    int rc = run_gemm(e, ly.conv_in[i], ws.shadow, D, M, c, s);
+    c.L = L, c.mask = mask, c.out_bf16 = ws.conv_a, c.ld_bf16 = D, c.rowbias = te_conv, c.bias_ld = net.N_te;
+    int rc = run_gemm(e, ly.conv_in[i], ws.shadow, D, M, c, s, ws.conv_b + D, ldc, D);
     if (rc) return rc;
-    rc = run_dwconv(e, ws.conv_a, ly.dw_w[i], ly.dw_b[i], nb, L, D, kernel, ws.conv_b, s);
+    rc = run_dwconv(e, ws.conv_a, ly.dw_w[i], ly.dw_b[i], nb, L, D, kernel, ws.conv_b, ldc, s);
     if (rc) return rc;
-    return residual(ly.conv_out[i], ws.conv_b, D, ws.Y, nullptr, nullptr, nullptr);
+    return residual(ly.conv_out[i], ws.conv_b, ldc, ws.Y, resbias, nullptr, nullptr);
   };
 
   // src += time_emb; src += FF1(src)  (:532-536): FF1 input bias folded, time_emb added to the stream here
@@ -466,11 +533,13 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   }
   ZV_TRY(residual(ly.na_out, ws.na_o, hn, ws.Y, nullptr, nullptr, nullptr));
   // src += SelfAttn1(src, A); src += time_emb  (:564-579)
-  ZV_TRY(self_attn(0, te_stack));
-  ZV_TRY(conv(0));                                                       // :581-587
+  const float* te_c0 = te_stack ? ws.te_out + ly.te_off_conv[0] : nullptr;
+  const float* te_c1 = te_stack ? ws.te_out + ly.te_off_conv[1] : nullptr;
+  ZV_TRY(self_attn(0));
+  ZV_TRY(conv(0, te_c0, te_stack));                                      // :581-587
   ZV_TRY(ff(1, nullptr, ws.Y, nullptr, X, ly.bypass_mid_scale));          // :593-598 (FF2 + bypass_mid)
-  ZV_TRY(self_attn(1, te_stack));                                        // :600-616
-  ZV_TRY(conv(1));                                                       // :618-624
+  ZV_TRY(self_attn(1));                                                  // :600-616
+  ZV_TRY(conv(1, te_c1, te_stack));                                      // :618-624
   ZV_TRY(ff(2, nullptr, ws.Y, nullptr, nullptr, nullptr));                // :630-632
   // src = bypass(src_orig, BiasNorm(src))  (:635-637), in place on X
   ZV_K(KC_BIASNORM, (double)M * D * 14, s,

@@ -27,7 +27,7 @@ struct Lin {
 };
 
 struct Layer {
-  Lin attn_in, ff_in[3], ff_out[3], na_in, na_out, sa_in[2], sa_out[2], conv_in[2], conv_out[2];
+  Lin attn_in, ff_in[3], ff_out[3], na_in, na_out, sa_in[2], conv_in[2], conv_out[2];  // SelfAttention.out_proj lives inside conv_in / conv_out
   float* w_pos = nullptr;  // [H*dp][pos_dim]
   float* dw_w[2] = {nullptr, nullptr};
   float* dw_b[2] = {nullptr, nullptr};
@@ -36,6 +36,7 @@ struct Layer {
   float* bypass_scale = nullptr;
   float* bypass_mid_scale = nullptr;
   size_t te_off_ff1 = 0;          // column offset of this layer's FF1 row-bias in the te projection
+  size_t te_off_conv[2] = {0, 0}; // ... of the two conv in_proj row-biases (W_in te_stack, accumulator order)
   std::map<int, float*> pos_tab;  // L -> E[H][2L-1][dp]
 };
 
@@ -65,7 +66,7 @@ struct Workspace {
   int D = 0;
   float *X = nullptr, *Xs = nullptr, *Y = nullptr, *vel = nullptr, *xcur = nullptr;
   __nv_bfloat16 *x_in = nullptr, *shadow = nullptr, *qkp = nullptr, *hidden = nullptr, *na_v = nullptr,
-                *na_y = nullptr, *na_o = nullptr, *sa_v = nullptr, *sa_o = nullptr, *conv_a = nullptr,
+                *na_y = nullptr, *na_o = nullptr, *sa_v = nullptr, *conv_a = nullptr,
                 *conv_b = nullptr;
   uint8_t* mask[3] = {nullptr, nullptr, nullptr};  // per distinct downsampling rate (1, 2, 4)
   float *t_dev = nullptr, *ts_dev = nullptr /* time table of one sample(): 1025 floats */, *g_dev = nullptr, *te_a = nullptr, *te_out = nullptr, *guid_dev = nullptr;
@@ -130,7 +131,8 @@ void audio_destroy(Engine& e);
 // fused epilogue of `mode`), and launch it.  row_scale (optional, [N]) multiplies weight rows and bias.
 int pack_linear_host(Engine& e, const float* w, const float* bias, int N, int K, int mode, Lin* lin, int k_pad_to,
                      const float* row_scale);
-int run_gemm(Engine& e, const Lin& lin, const __nv_bfloat16* A, int lda, int M, EpiParams ep, cudaStream_t s);
+int run_gemm(Engine& e, const Lin& lin, const __nv_bfloat16* A, int lda, int M, EpiParams ep, cudaStream_t s,
+             const __nv_bfloat16* A2 = nullptr, int lda2 = 0, int k_split = 0);
 int dev_alloc(Engine& e, std::vector<void*>& pool, void** p, size_t bytes);
 
 }  // namespace zv

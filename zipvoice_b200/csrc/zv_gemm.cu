@@ -191,6 +191,7 @@ static constexpr int STG_F32_BYTES = BM * 128;   // 128 rows x 32 fp32
 
 struct GemmMaps {
   CUtensorMap A, W;
+  CUtensorMap A2;  // optional second A operand for k-blocks >= kb_split
   CUtensorMap O0;  // bf16 output (box 32 cols, SWIZZLE_64B; GLU / gated NONLIN: box 16 cols, SWIZZLE_32B)
   CUtensorMap O1;  // EPI_NONLIN plain part: bf16 (box 32, SWIZZLE_64B); EPI_RESIDUAL: fp32 out (box 32, SWIZZLE_128B)
   CUtensorMap R;   // EPI_RESIDUAL: fp32 residual input (box 32, SWIZZLE_128B)
@@ -271,8 +272,8 @@ ZV_DEVINL void add_bias32(float (&v)[32], const float* __restrict__ bias, const 
 // Per output element this halves the W bytes pulled from L2, which is what bounds the K = 512 GEMMs.
 template <int MODE, bool PAIR>
 __global__ void __launch_bounds__(128 + 128 * ncg_for(MODE), 1)
-gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, int k_blocks, int block_n, int stages,
-               EpiParams ep) {
+gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, int k_blocks, int kb_split,
+               int block_n, int stages, EpiParams ep) {
   constexpr int NCG = ncg_for(MODE);
   constexpr int EPI_WARPS = 4 * NCG;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -330,15 +331,17 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         const int m_blk = tile_m(t), n_blk = t % n_tiles;
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&tail->empty[stage], phase ^ 1);
+          const CUtensorMap* mapA = kb < kb_split ? &maps.A : &maps.A2;
+          const int ka = (kb < kb_split ? kb : kb - kb_split) * BK;
           if (PAIR) {
             // both CTAs' bytes complete on the leader's full barrier
             const uint32_t fb = mapa_shared(smem_u32(&tail->full[stage]), 0);
             if (rank == 0) mbar_arrive_expect_tx(&tail->full[stage], 2 * tx);
-            tma_load_2d_pair(sA + stage * A_STAGE_BYTES, &maps.A, fb, kb * BK, m_blk * BM);
+            tma_load_2d_pair(sA + stage * A_STAGE_BYTES, mapA, fb, ka, m_blk * BM);
             tma_load_2d_pair(sW + stage * w_stage_bytes, &maps.W, fb, kb * BK, n_blk * block_n + (int)rank * wn);
           } else {
             mbar_arrive_expect_tx(&tail->full[stage], tx);
-            tma_load_2d(sA + stage * A_STAGE_BYTES, &maps.A, &tail->full[stage], kb * BK, m_blk * BM);
+            tma_load_2d(sA + stage * A_STAGE_BYTES, mapA, &tail->full[stage], ka, m_blk * BM);
             tma_load_2d(sW + stage * w_stage_bytes, &maps.W, &tail->full[stage], kb * BK, n_blk * block_n);
           }
           if (++stage == stages) stage = 0, phase ^= 1;
@@ -548,7 +551,8 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
 // SIMT checker: one thread per (row, 32-column group); same epilogue.  Tests / debugging only.
 template <int MODE>
 __global__ void gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* __restrict__ W, int lda,
-                                 int ldw, int K, int n_groups, EpiParams ep) {
+                                 int ldw, int K, int n_groups, EpiParams ep, const __nv_bfloat16* __restrict__ A2,
+                                 int lda2, int k_split) {
   const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int m = (int)(gid / n_groups);
   const int n0 = (int)(gid % n_groups) * 32;
@@ -557,7 +561,7 @@ __global__ void gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, const __nv
 #pragma unroll
   for (int i = 0; i < 32; ++i) acc[i] = 0.f;
   for (int k = 0; k < K; ++k) {
-    const float a = __bfloat162float(A[(size_t)m * lda + k]);
+    const float a = __bfloat162float(k < k_split ? A[(size_t)m * lda + k] : A2[(size_t)m * lda2 + (k - k_split)]);
 #pragma unroll
     for (int i = 0; i < 32; ++i) acc[i] += a * __bfloat162float(W[(size_t)(n0 + i) * ldw + k]);
   }
@@ -695,9 +699,11 @@ static int launch_tc(const GemmMaps& maps, const GemmPlan& p, const EpiParams& e
   const int m_tiles = (p.M + BM - 1) / BM;
   const int n_tiles = p.N_pad / p.block_n;
   const int k_blocks = (p.K + BK - 1) / BK;
+  const int kb_split = p.A2 ? p.k_split / BK : k_blocks;
   if (!PAIR) {
     const int grid = min(m_tiles * n_tiles, g_num_sms);
-    gemm_tc_kernel<MODE, PAIR><<<grid, threads, smem, stream>>>(maps, m_tiles, n_tiles, k_blocks, p.block_n, stages, ep);
+    gemm_tc_kernel<MODE, PAIR><<<grid, threads, smem, stream>>>(maps, m_tiles, n_tiles, k_blocks, kb_split, p.block_n,
+                                                                 stages, ep);
     return (int)cudaGetLastError();
   }
   const int units = ((m_tiles + 1) / 2) * n_tiles;
@@ -708,8 +714,8 @@ static int launch_tc(const GemmMaps& maps, const GemmPlan& p, const EpiParams& e
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = 2, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
   cfg.attrs = at, cfg.numAttrs = 1;
-  return (int)cudaLaunchKernelEx(&cfg, gemm_tc_kernel<MODE, PAIR>, maps, m_tiles, n_tiles, k_blocks, p.block_n, stages,
-                                 ep);
+  return (int)cudaLaunchKernelEx(&cfg, gemm_tc_kernel<MODE, PAIR>, maps, m_tiles, n_tiles, k_blocks, kb_split,
+                                 p.block_n, stages, ep);
 }
 
 // impl: 0 = tcgen05, CTA pairs (cta_group::2) for the shapes where they measure faster; 1 = SIMT checker;
@@ -721,8 +727,8 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
     const int n_groups = p.N_pad / 32;
     const long long total = (long long)p.M * n_groups;
     const int threads = 128;
-    gemm_simt_kernel<MODE><<<(unsigned)((total + threads - 1) / threads), threads, 0, stream>>>(A, W, p.lda, p.ldw,
-                                                                                                 p.K, n_groups, ep);
+    gemm_simt_kernel<MODE><<<(unsigned)((total + threads - 1) / threads), threads, 0, stream>>>(
+        A, W, p.lda, p.ldw, p.K, n_groups, ep, p.A2, p.lda2, p.A2 ? p.k_split : p.K);
     return (int)cudaGetLastError();
   }
   if (!g_num_sms) {
@@ -739,7 +745,11 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
   const bool pair = impl == 3 || (impl == 0 && big && MODE == EPI_RESIDUAL && p.K >= 1024);
   GemmMaps maps;
   memset(&maps, 0, sizeof(maps));
-  int rc = make_tmap_impl(&maps.A, A, 0, (uint64_t)p.M, (uint64_t)p.K, (uint64_t)p.lda, BM, 64, 128);
+  const int k_a = p.A2 ? p.k_split : p.K;
+  if (p.A2 && (p.k_split % BK || p.k_split <= 0 || p.k_split >= p.K || p.lda2 % 8)) return 907;
+  int rc = make_tmap_impl(&maps.A, A, 0, (uint64_t)p.M, (uint64_t)k_a, (uint64_t)p.lda, BM, 64, 128);
+  if (!rc && p.A2)
+    rc = make_tmap_impl(&maps.A2, p.A2, 0, (uint64_t)p.M, (uint64_t)(p.K - p.k_split), (uint64_t)p.lda2, BM, 64, 128);
   if (rc) return rc;
   rc = make_tmap_impl(&maps.W, W, 0, (uint64_t)p.N_pad, (uint64_t)p.K, (uint64_t)p.ldw,
                       (uint32_t)(pair ? p.block_n / 2 : p.block_n), 64, 128);

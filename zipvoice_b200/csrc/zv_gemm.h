@@ -46,6 +46,10 @@ struct GemmPlan {
   int lda;              // A row pitch in elements (multiple of 8)
   int ldw;              // W row pitch in elements (multiple of 8, >= K)
   int block_n;          // multiple of 32, <= 256
+  // Optional second A operand: K columns >= k_split (multiple of 64) come from A2 (row pitch lda2), so that
+  // [x | y] @ W^T runs without concatenating x and y in memory.
+  const __nv_bfloat16* A2 = nullptr;
+  int lda2 = 0, k_split = 0;
 };
 
 // Launch on `stream`.  impl: 0 = tcgen05/TMA kernel, 1 = SIMT checker kernel (tests / debugging only).

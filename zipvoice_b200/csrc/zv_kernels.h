@@ -19,7 +19,7 @@ int cfg_euler_update(float* x, const float* v, const float* guidance, int guidan
 
 // Depthwise conv over time ("same" zero padding per sequence) + bias + SwooshR (zipformer.py:1672-1678).
 int dwconv_swooshr(const __nv_bfloat16* in, const float* w, const float* bias, int nb, int L, int C, int k,
-                   __nv_bfloat16* out, cudaStream_t s);
+                   __nv_bfloat16* out, int ld_out, cudaStream_t s);
 
 // out = orig + (BiasNorm(src) - orig) * scale   (scaling.py:345-348, zipformer.py:635-637); fp32 + bf16 shadow.
 int biasnorm_bypass(const float* src, const float* orig, const float* nbias, float log_scale, const float* bscale,
