@@ -141,7 +141,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
     float o[2][4];
 #pragma unroll
     for (int n = 0; n < 2; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
-    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY;  // the row sums live in column dv of O (V carries a ones column)
     const float LOG2E = 1.4426950408889634f;
     uint32_t qa[2][4];
     mbar_wait(&sm.qbar, 0);
@@ -200,24 +200,20 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
       const bool grow = (mn0 != m0) || (mn1 != m1);
       const float ms0 = mn0 * LOG2E, ms1 = mn1 * LOG2E;
-      float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const float pa = ex2_approx(fmaf(s[nt][e], LOG2E, -ms0)), pb = ex2_approx(fmaf(s[nt][2 + e], LOG2E, -ms1));
           s[nt][e] = pa, s[nt][2 + e] = pb;
-          rs0 += pa, rs1 += pb;
         }
       }
       if (__any_sync(0xffffffffu, grow)) {
         const float sc0 = ex2_approx((m0 - mn0) * LOG2E), sc1 = ex2_approx((m1 - mn1) * LOG2E);
-        l0 *= sc0, l1 *= sc1;
 #pragma unroll
         for (int n = 0; n < 2; ++n) o[n][0] *= sc0, o[n][1] *= sc0, o[n][2] *= sc1, o[n][3] *= sc1;
         m0 = mn0, m1 = mn1;
       }
-      l0 += rs0, l1 += rs1;
       // ---- O += P V
 #pragma unroll
       for (int kk = 0; kk < BKV / 16; ++kk) {
@@ -235,8 +231,9 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       if (lane == 0) mbar_arrive(&sm.empty[st]);
     }
     // ---- normalise, store (columns >= dv belong to the next head / padding and are dropped)
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 1), l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 1), l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    // column dv = 12 of O (n-tile 1, columns 4..5 -> the lane with qd == 2) is sum_k P[i][k] * 1
+    const float l0 = __shfl_sync(0xffffffffu, o[1][0], (lane & ~3) | 2);
+    const float l1 = __shfl_sync(0xffffffffu, o[1][2], (lane & ~3) | 2);
     const float inv0 = 1.f / l0, inv1 = 1.f / l1;
     const int ia = i0 + rl0, ib = i0 + rl1;
     const int vcol0 = head * p.dv;
@@ -256,7 +253,8 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
 
 // Host launcher; returns -1 if the shape is not supported (caller falls back to attn_kernel).
 int attention_sa_tma(const AttnParams& p, cudaStream_t s) {
-  // V must be in the padded layout (16 columns per head): the TMA box start has to be 16-byte aligned
+  // V must be in the padded layout (16 columns per head: 12 values, a column of ones, zeros): the TMA box start
+  // has to be 16-byte aligned, and the ones column yields the softmax row sums from the P.V product
   if (p.dv != 12 || p.vhs != DVP || p.gate || p.heads != p.H || p.ldv % 8 || p.ldq % 8 || (p.ldo & 1)) return -1;
   const int n_tiles = (p.L + BKV - 1) / BKV;
   const int smem = (int)sizeof(Smem) + 1024 + n_tiles * BKV + ((n_tiles + 15) & ~15);

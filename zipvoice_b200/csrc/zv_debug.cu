@@ -81,7 +81,7 @@ __global__ void pad_heads_kernel(const float* __restrict__ in, size_t rows, int 
   if (gid >= rows * heads * 16) return;
   const int c = (int)(gid % 16), h = (int)((gid / 16) % heads);
   const size_t r = gid / (16 * heads);
-  out[gid] = __float2bfloat16(c < dv ? in[r * ld_in + h * dv + c] : 0.f);
+  out[gid] = __float2bfloat16(c < dv ? in[r * ld_in + h * dv + c] : (c == dv ? 1.0f : 0.f));  // ones column at dv
 }
 
 extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp_f32, int ldq,
@@ -148,7 +148,7 @@ extern "C" int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv,
   cudaMalloc(&q, rows * ldq * 2), cudaMalloc(&v, rows * ldv * 2), cudaMalloc(&g, rows * ldv * 2);
   cudaMalloc(&o, rows * ldv * 2), cudaMalloc(&E, (size_t)H * (2 * L - 1) * 16), cudaMalloc(&m, rows);
   cudaMemset(q, 0x2c, rows * ldq * 2);  // fp16 0x2c2c ~ 0.065
-  cudaMemset(v, 0x3c, rows * ldv * 2);  // bf16 0x3c3c ~ 0.0115
+  cudaMemset(v, 0x3f, rows * ldv * 2);  // bf16 0x3f3f ~ 0.75 (the SelfAttention row sum comes from a V column)
   cudaMemset(g, 0x3f, rows * ldv * 2);
   cudaMemset(E, 0, (size_t)H * (2 * L - 1) * 16);
   cudaMemset(m, 0, rows);

@@ -231,6 +231,9 @@ static int build_layer(Engine& e, Net& net, const std::string& p, int kernel, La
           memcpy(&wp[((size_t)h * 16 + c) * K], &w->data[((size_t)h * dv + c) * K], (size_t)K * 4);
           bp[h * 16 + c] = bv->data[h * dv + c];
         }
+      // column dv of every head is the constant 1 (zero weights, unit bias): P.V then carries the softmax
+      // row sum in that column and the SelfAttention kernel needs no separate accumulation of it
+      for (int h = 0; h < Hh; ++h) bp[h * 16 + dv] = 1.0f;
       ZV_TRY(pack_linear_host(e, wp.data(), bp.data(), Hh * 16, K, EPI_BIAS_BF16, &L->sa_in[i], 0, nullptr));
     }
     const std::string c = p + ".conv_module" + std::to_string(i + 1);
@@ -472,7 +475,7 @@ static int get_pos_table(Engine& e, Net& net, Layer& ly, int L, cudaStream_t s, 
 // Zipformer2EncoderLayer.forward in eval mode (zipformer.py:489-642).  X: layer input / output (fp32),
 // ws.Y: working residual stream, ws.shadow: bf16 copy of the current stream (GEMM A operand).
 static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kernel, float* X, int nb, int L,
-                         const uint8_t* mask, const float* te_stack, const float* te_ff1, cudaStream_t s) {
+                         const uint8_t* mask, const float* te_stack, const float* te_ff1, int te_ld, cudaStream_t s) {
   const int M = nb * L, D = net.D, hn = net.hidden_na;
   float* Etab = nullptr;
   ZV_TRY(get_pos_table(e, net, ly, L, s, &Etab));
@@ -486,13 +489,13 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
                       const float* orig, const float* bscale) {
     EpiParams r;
     r.L = L, r.res = res, r.out_f32 = ws.Y, r.ld_f32 = D, r.out_bf16 = ws.shadow, r.ld_bf16 = D;
-    r.resbias = resbias, r.bias_ld = net.N_te, r.orig = orig, r.bypass_scale = bscale;
+    r.resbias = resbias, r.bias_ld = te_ld, r.orig = orig, r.bypass_scale = bscale;
     return run_gemm(e, lin, A, lda, M, r, s);
   };
   auto ff = [&](int i, const float* rowbias, const float* res, const float* resbias, const float* orig,
                 const float* bscale) {
     EpiParams f;
-    f.L = L, f.rowbias = rowbias, f.bias_ld = net.N_te, f.out_bf16 = ws.hidden, f.ld_bf16 = ly.ff_in[i].N;
+    f.L = L, f.rowbias = rowbias, f.bias_ld = te_ld, f.out_bf16 = ws.hidden, f.ld_bf16 = ly.ff_in[i].N;
     int rc = run_gemm(e, ly.ff_in[i], ws.shadow, D, M, f, s);
     if (rc) return rc;
     return residual(ly.ff_out[i], ws.hidden, ly.ff_in[i].N, res, resbias, orig, bscale);
@@ -511,7 +514,7 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   // SelfAttention(i).out_proj + time embedding + ConvolutionModule(i) with one pass over the fp32 stream
   auto conv = [&](int i, const float* te_conv, const float* resbias) {
     EpiParams c;
-    c.L = L, c.mask = mask, c.out_bf16 = ws.conv_a, c.ld_bf16 = D, c.rowbias = te_conv, c.bias_ld = net.N_te;
+    c.L = L, c.mask = mask, c.out_bf16 = ws.conv_a, c.ld_bf16 = D, c.rowbias = te_conv, c.bias_ld = te_ld;
     int rc = run_gemm(e, ly.conv_in[i], ws.shadow, D, M, c, s, ws.conv_b + D, ldc, D);
     if (rc) return rc;
     rc = run_dwconv(e, ws.conv_a, ly.dw_w[i], ly.dw_b[i], nb, L, D, kernel, ws.conv_b, ldc, s);
@@ -551,6 +554,11 @@ int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t
                 float* out, cudaStream_t s) {
   const int M = nb * T, D = net.D;
   const int td = e.cfg.time_embed_dim;
+  // One time step (and guidance scale) for the whole batch -- the Euler solver's case -- needs ONE row of
+  // time-embedding projections: the per-batch row biases are then read with pitch 0.
+  const bool te_shared = ta.t_stride == 0 && (!ta.g || ta.g_stride == 0);
+  const int nb_te = te_shared ? 1 : nb;
+  const int te_ld = te_shared ? 0 : net.N_te;
   EpiParams ep;
   ep.L = T, ep.out_f32 = ws.X, ep.ld_f32 = D, ep.out_bf16 = ws.shadow, ep.ld_bf16 = D;
   ZV_TRY(run_gemm(e, net.in_proj, ws.x_in, net.in_pad, M, ep, s));
@@ -560,10 +568,10 @@ int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t
       return 950;
     }
     ZV_K(KC_TIME_EMBED, 4.0 * (4 * td * td + td), s,
-         time_embed(ta.t, ta.t_stride, ta.g, ta.g_stride, nb, td, net.te_w0, net.te_b0, net.te_w2, net.te_b2,
+         time_embed(ta.t, ta.t_stride, ta.g, ta.g_stride, nb_te, td, net.te_w0, net.te_b0, net.te_w2, net.te_b2,
                     net.te_wg, ws.te_a, s));
-    ZV_K(KC_TIME_EMBED, 4.0 * ((double)net.N_te * td + (double)nb * (net.N_te + td)), s,
-         small_linear(ws.te_a, net.te_proj_w, net.te_proj_b, nb, net.N_te, td, ws.te_out, s));
+    ZV_K(KC_TIME_EMBED, 4.0 * ((double)net.N_te * td + (double)nb_te * (net.N_te + td)), s,
+         small_linear(ws.te_a, net.te_proj_w, net.te_proj_b, nb_te, net.N_te, td, ws.te_out, s));
   }
   for (Stack& st : net.stacks) {
     const int ds = st.ds;
@@ -581,7 +589,7 @@ int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t
     for (Layer& ly : st.layers) {
       const float* te_ff1 = net.use_time ? ws.te_out + ly.te_off_ff1 : nullptr;
       // row pitch of the time-embedding projections is N_te for every layer of this net
-      ZV_TRY(layer_forward(e, net, ws, ly, st.kernel, X, nb, L, mask, te_stack, te_ff1, s));
+      ZV_TRY(layer_forward(e, net, ws, ly, st.kernel, X, nb, L, mask, te_stack, te_ff1, te_ld, s));
     }
     if (ds != 1)
       ZV_K(KC_RESAMPLE, (double)nb * D * (10.0 * T + 4.0 * L), s,
