@@ -8,7 +8,10 @@
 //            thread issues tcgen05.mma  O[128 x 384] += P[128 x 64] X[64 x 384]  with X tiles TMA-loaded as
 //            MN-major operands (the row-major [key][channel] layout is used as is); O stays in TMEM for the
 //            whole key loop -- no online-softmax rescaling -- and is normalised by the row sums at the end.
-// 16 compute warps (8 row groups x 2 key halves of each 64-key tile) + 1 producer warp (TMA + MMA issue).
+// 16 compute warps (8 row groups x 2 key halves of each 64-key tile) + an MMA warp (X tiles by TMA,
+// tcgen05.mma issue) + a producer warp that streams the K tiles (SWIZZLE_64B boxes of the fp16 q|k|p rows)
+// and the relative-position windows (1-D bulk copies) of BOTH sweeps through a 4-stage full / empty mbarrier
+// ring: the compute warps never meet at a CTA barrier inside the key loops.
 #include <cuda.h>
 
 #include "zv_common.cuh"
@@ -19,35 +22,38 @@ namespace zv {
 
 namespace natc {
 
-static constexpr int BQ = 128, BKV = 64, DQ = 32, QP = DQ + 8, EWIN = 192;
+static constexpr int BQ = 128, BKV = 64, DQ = 32, EWIN = 192;
 static constexpr int VSTAGES = 3, NVBOX = 6;  // up to 6 boxes of 64 channels = 384
-static constexpr int COMPUTE_THREADS = 512, THREADS = COMPUTE_THREADS + 32;
+static constexpr int KSTAGES = 4;
+static constexpr int COMPUTE_THREADS = 512, THREADS = COMPUTE_THREADS + 64;
+static constexpr int MMA_WARP = COMPUTE_THREADS / 32, LOAD_WARP = MMA_WARP + 1;
 
 struct Smem {
   bf16 v[VSTAGES][NVBOX][BKV][64];  // MN-major SWIZZLE_128B boxes: [key][64 channels] = 8 KB each
   bf16 p[2][BQ][BKV];               // K-major SWIZZLE_128B: [query][64 keys]
-  __half q[BQ][QP];
-  __half k[3][BKV][QP];
-  float4 e[3][EWIN];
+  __half k[KSTAGES][BKV][DQ];       // SWIZZLE_64B boxes, 4 KB each
+  __half q[BQ][DQ];                 // SWIZZLE_64B, two 64-row boxes
+  float4 e[KSTAGES][EWIN];
   float red[2][BQ];                 // cross-warp (key half) reductions of max / sum
   uint64_t vfull[VSTAGES], vfree[VSTAGES], pfull[2], pfree[2], obar;
+  uint64_t kfull[KSTAGES], kempty[KSTAGES], qbar;
   uint32_t tmem_base;
   // followed by: uint8_t mask[n_tiles * BKV] (0 valid, 1 padded key, 2 beyond the sequence), uint8_t flag[n_tiles]
 };
 
-ZV_DEVINL void cp_async16(void* dst, const void* src, bool valid) {
-  const int sz = valid ? 16 : 0;
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
-}
-ZV_DEVINL void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-ZV_DEVINL void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-ZV_DEVINL void ldsm_x4(uint32_t (&r)[4], const void* p) {
+ZV_DEVINL void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
-               : "r"(smem_u32(p)));
+               : "r"(addr));
+}
+// byte offset of 16-byte chunk c of row r in a SWIZZLE_64B tile with 64-byte rows
+ZV_DEVINL uint32_t sw64(int r, int c) { return (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4)); }
+// 1-D bulk copy global -> shared, completion counted on an mbarrier (bytes multiple of 16, 16-byte aligned)
+ZV_DEVINL void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
 }
 ZV_DEVINL void mma_f16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile(
@@ -81,12 +87,13 @@ ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, int kh, 
                           const uint32_t (&qa)[2][4], const float (&pq0)[4], const float (&pq1)[4], float (&s)[4][4],
                           float& mx0, float& mx1) {
   const int qd = lane & 3;
+  const uint32_t kbase = smem_u32(&sm.k[buf][0][0]);
 #pragma unroll
   for (int n4 = 0; n4 < 4; ++n4) {
     const int nt = kh * 4 + n4;
     s[n4][0] = s[n4][1] = s[n4][2] = s[n4][3] = 0.f;
     uint32_t kb[4];
-    ldsm_x4(kb, &sm.k[buf][nt * 8 + (lane & 7)][(lane >> 3) * 8]);
+    ldsm_x4(kb, kbase + sw64(nt * 8 + (lane & 7), lane >> 3));
     mma_f16(s[n4], qa[0], kb[0], kb[1]);
     mma_f16(s[n4], qa[1], kb[2], kb[3]);
   }
@@ -116,7 +123,8 @@ ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, int kh, 
 using namespace natc;
 
 __global__ void __launch_bounds__(natc::THREADS, 1)
-attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvbox, int n_mma0, int n_mma1) {
+attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmQK, AttnParams p,
+                  int nvbox, int n_mma0, int n_mma1) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // align inside the shared window (pointer + integer keeps the shared address space: LDS/STS, not generic LD/ST)
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
@@ -135,16 +143,50 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
   if (tid == 0) {
     for (int i = 0; i < VSTAGES; ++i) mbar_init(&sm.vfull[i], 1), mbar_init(&sm.vfree[i], 1);
     for (int i = 0; i < 2; ++i) mbar_init(&sm.pfull[i], COMPUTE_THREADS / 32), mbar_init(&sm.pfree[i], 1);
+    for (int i = 0; i < KSTAGES; ++i) mbar_init(&sm.kfull[i], 1), mbar_init(&sm.kempty[i], COMPUTE_THREADS / 32);
     mbar_init(&sm.obar, 1);
+    mbar_init(&sm.qbar, 1);
     fence_barrier_init();
   }
-  if (warp == 16) tmem_alloc(&sm.tmem_base, 512);
+  if (warp == MMA_WARP) tmem_alloc(&sm.tmem_base, 512);
+  // window entries outside the table are never copied: keep them finite
+  for (int i = tid; i < KSTAGES * EWIN; i += THREADS) sm.e[i / EWIN][i % EWIN] = make_float4(0.f, 0.f, 0.f, 0.f);
+  // key-padding mask of the whole sequence (0 valid, 1 padded, 2 beyond the sequence) and per-tile flags, once
+  for (int j = tid; j < n_tiles * BKV; j += THREADS) smask[j] = (j < L) ? (mask ? mask[j] : 0) : 2;
+  fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  for (int t = tid; t < n_tiles; t += THREADS) {
+    const uint4* mp = reinterpret_cast<const uint4*>(smask + t * BKV);
+    const uint4 a = mp[0], b4 = mp[1], c = mp[2], d = mp[3];
+    sflag[t] =
+        ((a.x | a.y | a.z | a.w | b4.x | b4.y | b4.z | b4.w | c.x | c.y | c.z | c.w | d.x | d.y | d.z | d.w) != 0);
+  }
+  __syncthreads();
   const uint32_t tmem_base = sm.tmem_base;
 
-  if (warp == 16) {
+  if (warp == LOAD_WARP) {
+    // ---------------- producer: Q once, then K tile + position window of every key tile, twice (two sweeps)
+    if (lane == 0) {
+      tma_prefetch_desc(&tmQK);
+      mbar_arrive_expect_tx(&sm.qbar, BQ * DQ * 2);
+      tma_load_2d(&sm.q[0][0], &tmQK, &sm.qbar, 0, b * L + i0);
+      tma_load_2d(&sm.q[64][0], &tmQK, &sm.qbar, 0, b * L + i0 + 64);
+      for (int g = 0; g < 2 * n_tiles; ++g) {
+        const int kt = g < n_tiles ? g : g - n_tiles, st = g % KSTAGES;
+        if (g >= KSTAGES) mbar_wait(&sm.kempty[st], ((g / KSTAGES) - 1) & 1);
+        const int j0 = kt * BKV;
+        const int rr0 = (j0 - i0 - (BQ - 1)) + (L - 1);  // table row of window entry 0
+        const int lo = max(rr0, 0), hi = min(rr0 + EWIN, R);
+        const uint32_t ebytes = hi > lo ? (uint32_t)(hi - lo) * 16u : 0u;
+        mbar_arrive_expect_tx(&sm.kfull[st], BKV * DQ * 2 + ebytes);
+        tma_load_2d(&sm.k[st][0][0], &tmQK, &sm.kfull[st], H * DQ, b * L + j0);
+        if (ebytes) bulk_load_1d(&sm.e[st][lo - rr0], E + lo, ebytes, &sm.kfull[st]);
+      }
+    }
+    __syncwarp();
+  } else if (warp == MMA_WARP) {
     // ---------------- producer: X tiles by TMA, P.X by tcgen05.mma
     if (lane == 0) {
       tma_prefetch_desc(&tmV);
@@ -192,34 +234,6 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
     const int g = lane >> 2, qd = lane & 3;
     const int rl0 = rg * 16 + g, rl1 = rl0 + 8;
     auto cbar = [] { named_bar_sync(1, COMPUTE_THREADS); };
-    // Q tile (once)
-    for (int c = tid; c < BQ * (DQ / 8); c += COMPUTE_THREADS) {
-      const int r = c / (DQ / 8), cc = c % (DQ / 8);
-      const int i = i0 + r;
-      cp_async16(&sm.q[r][cc * 8], qkp + (size_t)min(i, L - 1) * p.ldq + cc * 8, i < L);
-    }
-    auto load_tile = [&](int kt, int buf) {
-      const int j0 = kt * BKV;
-      if (tid < 256) {  // K: 64 rows x 4 chunks of 16 B
-        const int r = tid >> 2, cc = tid & 3;
-        const int j = j0 + r;
-        cp_async16(&sm.k[buf][r][cc * 8], qkp + (size_t)min(j, L - 1) * p.ldq + H * DQ + cc * 8, j < L);
-      } else if (tid < 256 + EWIN) {
-        const int w = tid - 256;
-        const int rr = (j0 - i0 - (BQ - 1)) + (L - 1) + w;
-        const bool ok = rr >= 0 && rr < R;
-        cp_async16(&sm.e[buf][w], E + (ok ? rr : 0), ok);
-      }
-    };
-    // key-padding mask of the whole sequence and per-tile flags, once
-    for (int j = tid; j < n_tiles * BKV; j += COMPUTE_THREADS) smask[j] = (j < L) ? (mask ? mask[j] : 0) : 2;
-    cbar();
-    for (int t = tid; t < n_tiles; t += COMPUTE_THREADS) {
-      const uint4* mp = reinterpret_cast<const uint4*>(smask + t * BKV);
-      const uint4 a = mp[0], b4 = mp[1], c = mp[2], d = mp[3];
-      sflag[t] =
-          ((a.x | a.y | a.z | a.w | b4.x | b4.y | b4.z | b4.w | c.x | c.y | c.z | c.w | d.x | d.y | d.z | d.w) != 0);
-    }
     float pq0[4], pq1[4];
     {
       const __half* pa = qkp + (size_t)min(i0 + rl0, L - 1) * p.ldq + 2 * H * DQ;
@@ -231,26 +245,26 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
     float s[4][4];
     const float LOG2E = 1.4426950408889634f;
     float m0 = -INFINITY, m1 = -INFINITY;
-    // ---- sweep 1: exact row maxima
-    // three-stage K / E ring, one barrier per tile (after it every warp has finished tile kt - 1,
-    // whose buffer receives tile kt + 2)
-    load_tile(0, 0);
-    cp_async_commit();
-    if (n_tiles > 1) load_tile(1, 1);
-    cp_async_commit();
-    for (int kt = 0; kt < n_tiles; ++kt) {
-      const int buf = kt % 3;
-      cp_async_wait<1>();
-      cbar();
-      if (kt + 2 < n_tiles) load_tile(kt + 2, (kt + 2) % 3);
-      cp_async_commit();
-      if (kt == 0) {
+    mbar_wait(&sm.qbar, 0);
+    {
+      const uint32_t qbase = smem_u32(&sm.q[0][0]);
 #pragma unroll
-        for (int ks = 0; ks < 2; ++ks) ldsm_x4(qa[ks], &sm.q[rg * 16 + (lane & 15)][ks * 16 + (lane >> 4) * 8]);
-      }
+      for (int ks = 0; ks < 2; ++ks) ldsm_x4(qa[ks], qbase + sw64(rg * 16 + (lane & 15), ks * 2 + (lane >> 4)));
+    }
+    // the K / E ring is consumed tile by tile: wait full, read into registers, release
+    int gt = 0;  // running tile counter over both sweeps
+    auto ring_release = [&](int st) {
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.kempty[st]);
+    };
+    // ---- sweep 1: exact row maxima
+    for (int kt = 0; kt < n_tiles; ++kt, ++gt) {
+      const int buf = gt % KSTAGES;
+      mbar_wait(&sm.kfull[buf], (gt / KSTAGES) & 1);
       float mx0, mx1;
       if (sflag[kt] != 0) score_tile<true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
       else score_tile<false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+      ring_release(buf);
       m0 = fmaxf(m0, mx0), m1 = fmaxf(m1, mx1);
     }
     m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)), m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
@@ -262,19 +276,13 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
     const float ms0 = m0 * LOG2E, ms1 = m1 * LOG2E;
     // ---- sweep 2: P = exp(S - max) -> shared memory -> tcgen05.mma
     float l0 = 0.f, l1 = 0.f;
-    load_tile(0, 0);
-    cp_async_commit();
-    if (n_tiles > 1) load_tile(1, 1);
-    cp_async_commit();
-    for (int kt = 0; kt < n_tiles; ++kt) {
-      const int buf = kt % 3, pb = kt & 1;
-      cp_async_wait<1>();
-      cbar();
-      if (kt + 2 < n_tiles) load_tile(kt + 2, (kt + 2) % 3);
-      cp_async_commit();
+    for (int kt = 0; kt < n_tiles; ++kt, ++gt) {
+      const int buf = gt % KSTAGES, pb = kt & 1;
+      mbar_wait(&sm.kfull[buf], (gt / KSTAGES) & 1);
       float mx0, mx1;
       if (sflag[kt] != 0) score_tile<true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
       else score_tile<false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+      ring_release(buf);
       if (kt >= 2) {  // the MMAs of tile kt-2 have read p[pb]
         if (lane == 0) mbar_wait(&sm.pfree[pb], ((kt >> 1) - 1) & 1);
         __syncwarp();
@@ -333,7 +341,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, AttnParams p, int nvb
     tc_fence_before();
   }
   __syncthreads();
-  if (warp == 16) tmem_dealloc(tmem_base, 512);
+  if (warp == MMA_WARP) tmem_dealloc(tmem_base, 512);
 }
 
 // Host launcher; returns -1 if the shape is not supported by this kernel (caller falls back to attn_kernel).
@@ -345,6 +353,10 @@ int attention_na_tc(const AttnParams& p, cudaStream_t s) {
   CUtensorMap tmV;
   int rc = make_tmap(&tmV, p.V, 0, (uint64_t)p.nb * p.L, (uint64_t)p.dv, (uint64_t)p.ldv, BKV, 64, 128);
   if (rc) return rc;
+  if (p.ldq % 8) return -1;
+  CUtensorMap tmQK;  // fp16 q | k | p rows: 64-row x 32-column boxes (q of head 0 at column 0, k at column H * 32)
+  rc = make_tmap(&tmQK, p.qkp, 0, (uint64_t)p.nb * p.L, (uint64_t)(2 * p.H * DQ + 4 * p.H), (uint64_t)p.ldq, BKV, DQ, 64);
+  if (rc) return rc;
   static bool attr = false;
   const int n_tiles = (p.L + BKV - 1) / BKV;
   const int smem = (int)sizeof(Smem) + 1024 + n_tiles * BKV + ((n_tiles + 15) & ~15);
@@ -354,7 +366,7 @@ int attention_na_tc(const AttnParams& p, cudaStream_t s) {
     attr = true;
   }
   dim3 grid((p.L + BQ - 1) / BQ, p.nb);
-  attn_na_tc_kernel<<<grid, THREADS, smem, s>>>(tmV, p, nvbox, n0, n1);
+  attn_na_tc_kernel<<<grid, THREADS, smem, s>>>(tmV, tmQK, p, nvbox, n0, n1);
   return (int)cudaGetLastError();
 }
 
