@@ -307,32 +307,45 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
     if (qd == 0) sm.red[kh][rl0] = l0, sm.red[kh][rl1] = l1;
     cbar();
     // ---- epilogue: O / l * gate -> bf16.  Warp w reads TMEM lane quarter w % 4, column slice w / 4.
-    mbar_wait(&sm.obar, 0);
-    tc_fence_after();
     const int q4 = warp & 3, cs = warp >> 2;
     const int row = q4 * 32 + lane;
     const int i = i0 + row;
-    const float inv = 1.0f / (sm.red[0][row] + sm.red[1][row]);
     const int ncols = nvbox * 64;
-    for (int c0 = cs * 32; c0 < ncols; c0 += 128) {
+    const size_t grow = (size_t)b * L + min(i, L - 1);
+    // the gate values do not depend on O: fetch this thread's slice while the last MMAs drain
+    uint4 gv[3][4];
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+      const int c0 = cs * 32 + it * 128;
+#pragma unroll
+      for (int j4 = 0; j4 < 4; ++j4) {
+        gv[it][j4] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);  // bf16 1.0 pairs
+        if (p.gate && c0 + j4 * 8 < p.dv)
+          gv[it][j4] = __ldg(reinterpret_cast<const uint4*>(p.gate + grow * p.ldg + c0 + j4 * 8));
+      }
+    }
+    mbar_wait(&sm.obar, 0);
+    tc_fence_after();
+    const float inv = 1.0f / (sm.red[0][row] + sm.red[1][row]);
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+      const int c0 = cs * 32 + it * 128;
+      if (c0 >= ncols) break;
       uint32_t raw[32];
       tmem_ld32(tmem_base + (static_cast<uint32_t>(q4 * 32) << 16) + c0, raw);
       tmem_ld_wait();
       if (i < L && c0 < p.dv) {
-        const size_t grow = (size_t)b * L + i;
-        const bf16* gp = p.gate ? p.gate + grow * p.ldg + c0 : nullptr;
         bf16* op = p.out + grow * p.ldo + c0;
 #pragma unroll
-        for (int jj = 0; jj < 32; jj += 8) {
+        for (int j4 = 0; j4 < 4; ++j4) {
+          const int jj = j4 * 8;
           if (c0 + jj >= p.dv) break;
           float v[8];
 #pragma unroll
           for (int u = 0; u < 8; ++u) v[u] = __uint_as_float(raw[jj + u]) * inv;
-          if (gp) {
-            const uint4 gv = *reinterpret_cast<const uint4*>(gp + jj);
-            v[0] *= bf16_lo(gv.x), v[1] *= bf16_hi(gv.x), v[2] *= bf16_lo(gv.y), v[3] *= bf16_hi(gv.y);
-            v[4] *= bf16_lo(gv.z), v[5] *= bf16_hi(gv.z), v[6] *= bf16_lo(gv.w), v[7] *= bf16_hi(gv.w);
-          }
+          const uint4 g4 = gv[it][j4];
+          v[0] *= bf16_lo(g4.x), v[1] *= bf16_hi(g4.x), v[2] *= bf16_lo(g4.y), v[3] *= bf16_hi(g4.y);
+          v[4] *= bf16_lo(g4.z), v[5] *= bf16_hi(g4.z), v[6] *= bf16_lo(g4.w), v[7] *= bf16_hi(g4.w);
           *reinterpret_cast<uint4*>(op + jj) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
                                                           pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
         }
