@@ -208,7 +208,7 @@ struct GemmSmemTail {
 
 // bytes of epilogue staging per column group
 __host__ __device__ constexpr int stg_group_bytes(int mode) {
-  return mode == EPI_RESIDUAL ? 2 * STG_F32_BYTES + STG_BF16_BYTES : (mode == EPI_F32 ? 0 : 2 * STG_BF16_BYTES);
+  return (mode == EPI_RESIDUAL || mode == EPI_F32) ? 2 * STG_F32_BYTES + STG_BF16_BYTES : 2 * STG_BF16_BYTES;
 }
 
 // 32 fp32 values of one row -> 32 bf16 in a 64-byte staging row (SWIZZLE_64B pattern of the TMA store)
@@ -441,7 +441,29 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
 
         if (MODE == EPI_F32) {
-          epi_apply<EPI_F32>(ep, m, b, n0, v);
+          if (ep.f32_direct) {  // output pitch not TMA-addressable: plain stores
+            epi_apply<EPI_F32>(ep, m, b, n0, v);
+            continue;
+          }
+          // fp32 rows (+ optional bf16 shadow) staged per warp and written by TMA, like EPI_RESIDUAL without the load
+          float* fb = reinterpret_cast<float*>(stg + (nq & 1) * STG_F32_BYTES);
+          uint8_t* shadow = stg + 2 * STG_F32_BYTES;
+          add_bias32(v, ep.bias, rowb, n0, ep.N);
+          if (lane == 0) tma_store_wait_read<0>();
+          __syncwarp();
+          const int x = r & 7;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(fb + r * 32 + ((j ^ x) << 2)) =
+                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          if (ep.out_bf16) stage_row_bf16x32(shadow, r, v);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&maps.O1, fb + q * 32 * 32, n0, m_blk * BM + q * 32);
+            if (ep.out_bf16) tma_store_2d(&maps.O0, shadow + q * 32 * 64, n0, m_blk * BM + q * 32);
+            tma_store_commit();
+          }
           continue;
         }
         if (MODE == EPI_RESIDUAL) {
@@ -770,6 +792,20 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
       rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, 32, 32, 64);
   }
   if (rc) return rc;
+  if (MODE == EPI_F32) {
+    EpiParams ep2 = ep;
+    const bool tma_ok = (ep.ld_f32 % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.out_f32) & 15) == 0) &&
+                        (!ep.out_bf16 || (ep.ld_bf16 % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.out_bf16) & 15) == 0));
+    if (tma_ok) {
+      rc = make_tmap_impl(&maps.O1, ep.out_f32, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, 32, 32, 128);
+      if (!rc && ep.out_bf16)
+        rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, 32, 32, 64);
+      if (rc) return rc;
+    } else {
+      ep2.f32_direct = 1;
+    }
+    return pair ? launch_tc<MODE, true>(maps, p, ep2, stream) : launch_tc<MODE, false>(maps, p, ep2, stream);
+  }
   return pair ? launch_tc<MODE, true>(maps, p, ep, stream) : launch_tc<MODE, false>(maps, p, ep, stream);
 }
 

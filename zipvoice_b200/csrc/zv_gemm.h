@@ -39,6 +39,7 @@ struct EpiParams {
   const float* orig = nullptr;     // optional bypass: v = orig + (v - orig) * bypass_scale[n]
   const float* bypass_scale = nullptr;
   const uint8_t* mask = nullptr;   // [B][L] 1 = padded frame (EPI_GLU_BF16)
+  int f32_direct = 0;              // EPI_F32: set by the launcher when the output cannot be a TMA tensor (pitch % 4)
 };
 
 struct GemmPlan {
