@@ -98,6 +98,15 @@ ZV_DEVINL void tma_load_2d(void* smem_dst, const void* desc, uint64_t* bar, int 
       : "memory");
 }
 
+// 3D tiled load: coordinates (c0 innermost, c1, c2); elements outside the tensor (also negative
+// coordinates) are zero-filled and still counted in the transaction bytes.
+ZV_DEVINL void tma_load_3d(void* smem_dst, const void* desc, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(desc)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+
 // 2D tiled store smem -> global (bulk async group); rows / columns outside the tensor are clipped.
 ZV_DEVINL void tma_store_2d(const void* desc, const void* smem_src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(

@@ -1,6 +1,8 @@
 // Bandwidth-bound kernels of the Zipformer layer: coalesced, 128-bit vectorised where the
 // layout allows, shared-memory staged where there is reuse (depthwise conv), warp-shuffle
 // reductions (BiasNorm).  Grids are sized from the data; all launches are asynchronous.
+#include <cuda.h>
+
 #include "zv_common.cuh"
 #include "zv_kernels.h"
 
@@ -89,93 +91,120 @@ int f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t s) {
 }
 
 // ------------------------------------------------------------------ depthwise conv + SwooshR
-// Block = (sequence b, 64-frame tile, 256-channel chunk).  The input tile plus a (K-1)-frame halo
-// is staged in shared memory (bf16x2 per thread-column, conflict-free), taps live in registers,
-// and every thread produces 4 consecutive frames x 2 channels per step so each shared-memory
-// word is read once per 4 outputs.
+// Persistent CTAs (two per SM) walk (sequence, 256-channel chunk, TT-frame tile) units.  The input tile plus its
+// (K-1)-frame halo arrives by ONE 3-D TMA box [1][TT+K-1][256 channels] per unit -- frames before / after the
+// sequence and channels beyond C are zero-filled by the tensor map, which is exactly the conv's "same" padding
+// -- into a double-buffered shared-memory tile, so the load of unit i+1 overlaps the FMAs of unit i.  Taps and
+// accumulators are packed fp32 pairs (channels c, c+1): one FFMA2 per tap and frame; every thread produces
+// FG = 8 consecutive frames x 2 channels per step so each shared-memory word is read once per 8 outputs.
 template <int K, int TT, int FG>
-__global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in, const float* __restrict__ w,
-                                                     const float* __restrict__ bias, int L, int C,
-                                                     bf16* __restrict__ out, int ldo) {
-  // TT frames per CTA (the halo of K - 1 frames is re-read: 23 % at TT = 128, K = 31), FG frames per register group
+__global__ void __launch_bounds__(256, 2)
+dwconv_kernel(const __grid_constant__ CUtensorMap tm_in, const float* __restrict__ w, const float* __restrict__ bias,
+              int nb, int L, int C, bf16* __restrict__ out, int ldo) {
   constexpr int PAD = K / 2, ROWS = TT + K - 1;
-  extern __shared__ __align__(16) uint32_t tile_raw[];
-  uint32_t(*tile)[128] = reinterpret_cast<uint32_t(*)[128]>(tile_raw);
-  const int cp = threadIdx.x;                 // channel pair within chunk
-  const int c = blockIdx.y * 256 + cp * 2;    // first channel
-  const int b = blockIdx.z;
-  const int t0 = blockIdx.x * TT;
-  const bool active = c < C;
-  const bf16* src = in + (size_t)b * L * C;
-  {  // stage the tile with 16-byte loads: a row of 256 channels = 32 chunks of 8 channels
-    const int tid = threadIdx.y * 128 + threadIdx.x;
-#pragma unroll 8
-    for (int idx = tid; idx < ROWS * 32; idx += 256) {
-      const int r = idx >> 5, c16 = idx & 31;
-      const int t = t0 - PAD + r;
-      const int ch = blockIdx.y * 256 + c16 * 8;
-      uint4 v = make_uint4(0u, 0u, 0u, 0u);
-      if (ch < C && t >= 0 && t < L) v = __ldg(reinterpret_cast<const uint4*>(src + (size_t)t * C + ch));
-      *reinterpret_cast<uint4*>(&tile[r][c16 * 4]) = v;
-    }
+  constexpr uint32_t TILE_BYTES = ROWS * 128 * 4;
+  extern __shared__ __align__(128) uint8_t dw_smem[];
+  uint8_t* base = dw_smem + ((128u - (smem_u32(dw_smem) & 127u)) & 127u);
+  uint64_t* full = reinterpret_cast<uint64_t*>(base + 2 * TILE_BYTES);
+  const int tid = threadIdx.y * 128 + threadIdx.x;
+  const int cp = threadIdx.x;  // channel pair within the chunk
+  const int n_t = (L + TT - 1) / TT, n_c = (C + 255) / 256;
+  const int units = nb * n_c * n_t;
+  if (tid == 0) {
+    mbar_init(&full[0], 1), mbar_init(&full[1], 1);
+    fence_barrier_init();
   }
   __syncthreads();
-  if (!active) return;
-  // taps and accumulators as packed fp32 pairs (channel c, c+1): one FFMA2 per tap and frame
+  auto issue = [&](int u, int buf) {  // thread 0 only
+    const int tt = u % n_t, b = (u / n_t) % nb, cb = u / (n_t * nb);  // chunk index slowest: taps reload once
+    mbar_arrive_expect_tx(&full[buf], TILE_BYTES);
+    tma_load_3d(base + buf * TILE_BYTES, &tm_in, &full[buf], cb * 256, tt * TT - PAD, b);
+  };
+  if (tid == 0 && (int)blockIdx.x < units) issue(blockIdx.x, 0);
+  int it = 0, cb_prev = -1;
   f32x2 wp[K];
+  f32x2 bp = f2_pack(0.f, 0.f);
+  for (int u = blockIdx.x; u < units; u += gridDim.x, ++it) {
+    const int buf = it & 1;
+    const int tt0 = (u % n_t) * TT, b = (u / n_t) % nb, cb = u / (n_t * nb);
+    // every thread finished reading buffer buf^1 at the barrier that closed the previous unit
+    if (tid == 0 && u + (int)gridDim.x < units) issue(u + gridDim.x, buf ^ 1);
+    const int c = cb * 256 + cp * 2;
+    const bool active = c < C;
+    if (cb != cb_prev && active) {  // taps of this thread's channel pair
 #pragma unroll
-  for (int j = 0; j < K; ++j) wp[j] = f2_pack(__ldg(w + (size_t)c * K + j), __ldg(w + (size_t)(c + 1) * K + j));
-  const f32x2 bp = f2_pack(__ldg(bias + c), __ldg(bias + c + 1));
-  bf16* dst = out + (size_t)b * L * ldo;
-  constexpr int per_y = TT / 2;
-  for (int tt = threadIdx.y * per_y; tt < (threadIdx.y + 1) * per_y; tt += FG) {
-    if (t0 + tt >= L) break;
-    f32x2 acc[FG];
+      for (int j = 0; j < K; ++j) wp[j] = f2_pack(__ldg(w + (size_t)c * K + j), __ldg(w + (size_t)(c + 1) * K + j));
+      bp = f2_pack(__ldg(bias + c), __ldg(bias + c + 1));
+      cb_prev = cb;
+    }
+    mbar_wait(&full[buf], (it >> 1) & 1);
+    if (active) {
+      const uint32_t(*tile)[128] = reinterpret_cast<const uint32_t(*)[128]>(base + buf * TILE_BYTES);
+      bf16* dst = out + (size_t)b * L * ldo;
+      constexpr int per_y = TT / 2;
+      for (int tt = threadIdx.y * per_y; tt < (threadIdx.y + 1) * per_y; tt += FG) {
+        if (tt0 + tt >= L) break;
+        f32x2 acc[FG];
 #pragma unroll
-    for (int o = 0; o < FG; ++o) acc[o] = bp;
+        for (int o = 0; o < FG; ++o) acc[o] = bp;
 #pragma unroll
-    for (int j = 0; j < K + FG - 1; ++j) {
-      const uint32_t xv = tile[tt + j][cp];
-      const f32x2 xp = f2_pack(bf16_lo(xv), bf16_hi(xv));
+        for (int j = 0; j < K + FG - 1; ++j) {
+          const uint32_t xv = tile[tt + j][cp];
+          const f32x2 xp = f2_pack(bf16_lo(xv), bf16_hi(xv));
 #pragma unroll
-      for (int o = 0; o < FG; ++o) {
-        const int tap = j - o;
-        if (tap >= 0 && tap < K) acc[o] = f2_fma(wp[tap], xp, acc[o]);
+          for (int o = 0; o < FG; ++o) {
+            const int tap = j - o;
+            if (tap >= 0 && tap < K) acc[o] = f2_fma(wp[tap], xp, acc[o]);
+          }
+        }
+#pragma unroll
+        for (int o = 0; o < FG; ++o) {
+          const int t = tt0 + tt + o;
+          float a0, a1;
+          f2_unpack(acc[o], a0, a1);
+          if (t < L)
+            *reinterpret_cast<uint32_t*>(dst + (size_t)t * ldo + c) = pack_bf16x2(swoosh_r_fast(a0), swoosh_r_fast(a1));
+        }
       }
     }
-#pragma unroll
-    for (int o = 0; o < FG; ++o) {
-      const int t = t0 + tt + o;
-      float a0, a1;
-      f2_unpack(acc[o], a0, a1);
-      if (t < L)
-        *reinterpret_cast<uint32_t*>(dst + (size_t)t * ldo + c) = pack_bf16x2(swoosh_r_fast(a0), swoosh_r_fast(a1));
-    }
+    __syncthreads();
   }
 }
+
+int make_tmap3d_16(void* tm, const void* ptr, uint64_t n0, uint64_t n1, uint64_t n2, uint64_t ld1, uint64_t ld2,
+                   uint32_t box0, uint32_t box1);  // zv_gemm.cu
 
 template <int K, int TT, int FG>
 static int launch_dwconv(const bf16* in, const float* w, const float* bias, int nb, int L, int C, bf16* out, int ldo,
                          cudaStream_t s) {
-  constexpr int smem = (TT + K - 1) * 128 * 4;
+  constexpr int smem = 2 * (TT + K - 1) * 128 * 4 + 128 + 64;
   static bool attr = false;
+  static int sms = 0;
   if (!attr) {
     cudaFuncSetAttribute(dwconv_kernel<K, TT, FG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     attr = true;
   }
-  dim3 grid((L + TT - 1) / TT, (C + 255) / 256, nb), block(128, 2);
-  dwconv_kernel<K, TT, FG><<<grid, block, smem, s>>>(in, w, bias, L, C, out, ldo);
+  CUtensorMap tm;
+  int rc = make_tmap3d_16(&tm, in, (uint64_t)C, (uint64_t)L, (uint64_t)nb, (uint64_t)C, (uint64_t)L * C, 256,
+                          TT + K - 1);
+  if (rc) return rc;
+  const int units = nb * ((C + 255) / 256) * ((L + TT - 1) / TT);
+  const int grid = units < 2 * sms ? units : 2 * sms;
+  dwconv_kernel<K, TT, FG><<<grid, dim3(128, 2), smem, s>>>(tm, w, bias, nb, L, C, out, ldo);
   return (int)cudaGetLastError();
 }
 
 int dwconv_swooshr(const bf16* in, const float* w, const float* bias, int nb, int L, int C, int k, bf16* out, int ldo,
                    cudaStream_t s) {
-  if (ldo < C || (ldo & 1)) return 911;
+  if (ldo < C || (ldo & 1) || (C & 7)) return 911;
   switch (k) {
     case 7: return launch_dwconv<7, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
     case 9: return launch_dwconv<9, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
-    case 15: return launch_dwconv<15, 128, 8>(in, w, bias, nb, L, C, out, ldo, s);
-    case 31: return launch_dwconv<31, 128, 8>(in, w, bias, nb, L, C, out, ldo, s);
+    case 15: return launch_dwconv<15, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
+    case 31: return launch_dwconv<31, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
     default: return 910;
   }
 }

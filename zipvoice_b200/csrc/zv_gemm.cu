@@ -666,6 +666,49 @@ int make_tmap(void* tm, const void* ptr, int dtype, uint64_t rows, uint64_t cols
   return make_tmap_impl(static_cast<CUtensorMap*>(tm), ptr, dtype, rows, cols, ld, box_rows, box_cols, swizzle);
 }
 
+struct Tmap3Key {
+  const void* ptr;
+  uint64_t n0, n1, n2, ld1, ld2;
+  uint32_t box0, box1;
+  bool operator==(const Tmap3Key& o) const {
+    return ptr == o.ptr && n0 == o.n0 && n1 == o.n1 && n2 == o.n2 && ld1 == o.ld1 && ld2 == o.ld2 && box0 == o.box0 &&
+           box1 == o.box1;
+  }
+};
+struct Tmap3KeyHash {
+  size_t operator()(const Tmap3Key& k) const {
+    uint64_t h = reinterpret_cast<uint64_t>(k.ptr) * 0x9E3779B97F4A7C15ull;
+    h ^= k.n0 * 31 + k.n1 * 131 + k.n2 * 1009 + k.ld1 * 7 + k.ld2 * 3 + k.box0 * 9176 + k.box1 * 77 + (h << 6) + (h >> 2);
+    return (size_t)h;
+  }
+};
+static std::unordered_map<Tmap3Key, CUtensorMap, Tmap3KeyHash> g_tmap3_cache;
+
+int make_tmap3d_16(void* tm, const void* ptr, uint64_t n0, uint64_t n1, uint64_t n2, uint64_t ld1, uint64_t ld2,
+                   uint32_t box0, uint32_t box1) {
+  const Tmap3Key key{ptr, n0, n1, n2, ld1, ld2, box0, box1};
+  auto it = g_tmap3_cache.find(key);
+  if (it != g_tmap3_cache.end()) {
+    *static_cast<CUtensorMap*>(tm) = it->second;
+    return 0;
+  }
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) return 901;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld1 * 2) & 15) || ((ld2 * 2) & 15) || box0 > 256 || box1 > 256)
+    return 906;
+  cuuint64_t dims[3] = {n0, n1, n2};
+  cuuint64_t strides[2] = {ld1 * 2, ld2 * 2};
+  cuuint32_t box[3] = {box0, box1, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(static_cast<CUtensorMap*>(tm), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims,
+                   strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return 902;
+  if (g_tmap3_cache.size() > 1024) g_tmap3_cache.clear();
+  g_tmap3_cache.emplace(key, *static_cast<CUtensorMap*>(tm));
+  return 0;
+}
+
 int gemm_pick_block_n(int n_valid, int mode, int gate_cols) {
   // block_n is a multiple of 32 (<= 256: two accumulator stages in 512 TMEM columns); the gated part of
   // EPI_NONLIN_BF16 must end on a tile boundary.  Measured on B200 (tools/gemm_bench.py, K = 512) the time of

@@ -65,4 +65,9 @@ int gemm_pick_block_n(int n_valid, int mode, int gate_cols);
 int make_tmap(void* tm, const void* ptr, int dtype, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
               uint32_t box_cols, int swizzle);
 
+// 16-bit tensor [n2][n1][n0] (n0 contiguous, pitches ld1 / ld2 in elements), box [1][box1][box0], no swizzle,
+// zero fill outside the tensor.  Not cached by the GEMM map cache key: separate small cache.
+int make_tmap3d_16(void* tm, const void* ptr, uint64_t n0, uint64_t n1, uint64_t n2, uint64_t ld1, uint64_t ld2,
+                   uint32_t box0, uint32_t box1);
+
 }  // namespace zv
