@@ -24,7 +24,7 @@ struct Stage {
   bf16 v[BKV][DVP];     // 2 KB, no swizzle
   float4 e[EWIN];       // 3 KB
 };
-struct Smem {
+struct alignas(16) Smem {  // the key mask that follows is read with 16-byte loads
   __half q[BQ][DQ];     // 8 KB, SWIZZLE_64B (two 64-row boxes)
   Stage st[STAGES];
   uint64_t full[STAGES], empty[STAGES], qbar, pad_;

@@ -28,7 +28,7 @@ static constexpr int KSTAGES = 4;
 static constexpr int COMPUTE_THREADS = 512, THREADS = COMPUTE_THREADS + 64;
 static constexpr int MMA_WARP = COMPUTE_THREADS / 32, LOAD_WARP = MMA_WARP + 1;
 
-struct Smem {
+struct alignas(16) Smem {  // the key mask that follows is read with 16-byte loads
   bf16 v[VSTAGES][NVBOX][BKV][64];  // MN-major SWIZZLE_128B boxes: [key][64 channels] = 8 KB each
   bf16 p[2][BQ][BKV];               // K-major SWIZZLE_128B: [query][64 keys]
   __half k[KSTAGES][BKV][DQ];       // SWIZZLE_64B boxes, 4 KB each
