@@ -320,6 +320,34 @@ def main():
                 "peak": pk["tf_sustained"] if top["bound"] == "tensor" else pk["hbm"], "unit": top["unit"],
                 "frac": top["frac"], "traffic": None, "peak_source": pk["source"] + ", sustained figure",
                 "avg_launch_ms": round(top["ms"] / max(1, top["launches"]), 4)}
+    # ncu DRAM traffic of the dominant kernel (one `ncu --set full` capture, committed under profiles/)
+    tpath = os.path.join(ROOT, "profiles", "r1e_traffic.json")
+    knames = {"gemm_residual": ["gemm_tc_kernel<4, 1>", "gemm_tc_kernel<4, 0>"], "gemm_swooshl": ["gemm_tc_kernel<1, 0>"],
+              "attn_self": ["attn_sa_kernel"], "attn_nonlin": ["attn_na_tc_kernel"]}.get(top["name"], [])
+    if os.path.exists(tpath) and knames:
+        tj = json.load(open(tpath))
+        sel = [tj[k] for k in knames if k in tj]
+        n = sum(x["captured_launches"] for x in sel)
+        if n:
+            roofline["traffic"] = round(sum((x["dram_read_bytes_per_launch"] + x["dram_write_bytes_per_launch"]) *
+                                            x["captured_launches"] for x in sel) / n)
+            roofline["traffic_note"] = (f"bytes per launch, dram__bytes_read.sum + dram__bytes_write.sum, mean of {n} launches "
+                                        "captured in a downsampled stack (profiles/r1e_ncu_full_summary.md, "
+                                        "profiles/r1e_traffic.json); below the algorithmic bytes of those launches because "
+                                        "part of the residual stream is still L2-resident from the producer kernel")
+    if top["name"] == "gemm_residual":
+        # the class is HBM-bound for most of its shapes: the same time against the HBM roofline.  Algorithmic bytes
+        # per residual GEMM = A operand (M x K bf16) + fp32 stream read + write + bf16 shadow (10 B per element)
+        cfgm = synth.BASE_MODEL_CFG
+        D, Fd = cfgm["fm_decoder_dim"], cfgm["fm_decoder_feedforward_dim"]
+        ks = [Fd * 3 // 4, Fd, Fd * 5 // 4, 3 * D // 4, D + 64, D + 64]
+        by = 0.0
+        for ds, nl in zip(cfgm["fm_decoder_downsampling_factor"], cfgm["fm_decoder_num_layers"]):
+            rows = 2 * B * ((T + ds - 1) // ds)
+            by += nl * sum(rows * (k * 2.0 + D * 10.0) for k in ks)
+        by *= NUM_STEP
+        roofline["hbm_view"] = {"algorithmic_bytes_per_step": by, "achieved": round(by / (top["ms"] * 1e-3) / 1e9, 1),
+                                "peak": pk["hbm"], "unit": "GB/s", "frac": round(by / (top["ms"] * 1e-3) / 1e9 / pk["hbm"], 4)}
     flops_step = sum(r["work"] for r in table if r["tensor"])
     whole = {"algorithmic_tflop_per_nfe": round(flops_step / NUM_STEP / 1e12, 3),
              "tensor_frac_whole_step": round(flops_step / (ms_step * 1e-3) / 1e12 / pk["tf_sustained"], 4)}

@@ -31,6 +31,10 @@ typedef struct zv_config {
   int use_guidance_scale_embed; /* 1 for ZipVoiceDistill (zipvoice_distill.py:52-67) */
   int dialog;                   /* 1 for ZipVoiceDialog: spk_embed rows added (zipvoice_dialog.py:127-159) */
   int spk_a_id, spk_b_id;
+  int stereo;                   /* 1 for ZipVoiceDialogStereo (zipvoice_dialog.py:218-256): the fm_decoder is a
+                                 * TTSZipformerTwoStream (zipformer_two_stream.py:219-264) used through its first
+                                 * stream: x and speech_condition are 2*feat_dim wide (two channels), the text
+                                 * condition stays feat_dim wide; in_proj.0 (5*feat_dim -> D), out_proj.0 (D -> 2*feat_dim) */
 } zv_config;
 
 /* Replaces ZipVoice.__init__ (zipvoice.py:38-133): builds the fm_decoder + text_encoder skeleton. */
@@ -57,7 +61,8 @@ int zv_time_steps(double t_start, double t_end, int num_step, double t_shift, fl
 /* One call of DiffusionModel.forward (variant 0, solver.py:40-110: CFG batch doubling, the t>0.5
  * branch, (1+g) cond - g uncond) or DistillDiffusionModel.forward (variant 1, solver.py:127-165)
  * around ZipVoice.forward_fm_decoder (zipvoice.py:135-185) -> TTSZipformer.forward
- * (zipformer.py:242-293).  x,text,speech,v_out: (B,T,feat_dim) fp32; padding_mask (B,T) uint8,
+ * (zipformer.py:242-293).  x,speech,v_out: (B,T,X) fp32 with X = feat_dim (2*feat_dim when cfg.stereo); text:
+ * (B,T,feat_dim); padding_mask (B,T) uint8,
  * 1 = padded, may be NULL; guidance: HOST floats, guidance_len 1 or B. */
 int zv_velocity(void* handle, int variant, float t, const float* x, const float* text_condition,
                 const float* speech_condition, const uint8_t* padding_mask, int B, int T, const float* guidance,

@@ -17,19 +17,43 @@ OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 
 def _ref_model(kind, cfg, sd):
     sys.path.insert(0, REF)
     from zipvoice.models.zipvoice import ZipVoice
-    from zipvoice.models.zipvoice_dialog import ZipVoiceDialog
+    from zipvoice.models.zipvoice_dialog import ZipVoiceDialog, ZipVoiceDialogStereo
     from zipvoice.models.zipvoice_distill import ZipVoiceDistill
     from zipvoice_b200 import synth
-    cls = {"zipvoice": ZipVoice, "distill": ZipVoiceDistill, "dialog": ZipVoiceDialog}[kind]
+    cls = {"zipvoice": ZipVoice, "distill": ZipVoiceDistill, "dialog": ZipVoiceDialog,
+           "dialog_stereo": ZipVoiceDialogStereo}[kind]
     kw = dict(cfg, vocab_size=synth.VOCAB_SIZE, pad_id=synth.PAD_ID)
-    if kind == "dialog":
+    if kind.startswith("dialog"):
         kw.update(spk_a_id=synth.SPK_A_ID, spk_b_id=synth.SPK_B_ID)
     m = cls(**kw).eval()
     m.load_state_dict(sd, strict=True)
     return m
 
 
-from tests.cases import case_inputs  # noqa: E402  (same seeded inputs as the tests)
+from tests.cases import case_inputs, case_inputs_stereo  # noqa: E402  (same seeded inputs as the tests)
+
+
+@torch.inference_mode()
+def stereo():
+    """ZipVoiceDialogStereo (zipvoice_dialog.py:218-256): velocity, CFG Euler and sample() of the unmodified
+    reference on the seeded two-stream weights.  python -m oracle.make_golden stereo"""
+    from zipvoice_b200 import synth
+    torch.set_num_threads(8)
+    small = synth.small_model_cfg()
+    sd = synth.make_state_dict(small, seed=4, dialog=True, stress=True, stereo=True)
+    m = _ref_model("dialog_stereo", small, sd)
+    x0, text, speech, mask = case_inputs_stereo(2, 41, 13, seed=12)
+    v = m.forward_fm_decoder(torch.tensor(0.3), x0, text, speech, mask)
+    x1 = m.solver.sample(x=x0, text_condition=text, speech_condition=speech, padding_mask=mask,
+                         num_step=4, guidance_scale=1.5, t_shift=0.5)
+    tokens, prompt_tokens = synth.make_tokens(2, n_prompt=30, n_text=50, seed=9, dialog=True, ragged=True)
+    pf, pfl = synth.make_prompt_features(2, 16, feat_dim=200, seed=13, ragged=True)
+    torch.manual_seed(666)
+    out = m.sample(tokens=tokens, prompt_tokens=prompt_tokens, prompt_features=pf, prompt_features_lens=pfl,
+                   speed=1.1, t_shift=0.5, duration="predict", num_step=3, guidance_scale=1.5)
+    np.savez(os.path.join(OUT, "dialog_stereo.npz"), v=v.numpy(), x1_cfg=x1.numpy(), x1_wo=out[0].numpy(),
+             wo_lens=out[1].numpy(), x1_prompt=out[2].numpy())
+    print("stereo golden written")
 
 
 @torch.inference_mode()
@@ -99,4 +123,4 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    stereo() if "stereo" in sys.argv[1:] else main()

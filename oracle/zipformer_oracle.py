@@ -196,7 +196,12 @@ def tts_zipformer(sd: SD, p: str, cfg: dict, x: Tensor, t: Optional[Tensor], pad
                   guidance_scale: Optional[Tensor] = None, taps: Optional[dict] = None) -> Tensor:
     """zipformer.py:242-293 TTSZipformer.forward.  x (B,T,Cin) -> (B,T,Cout).
     cfg: downsampling_factor, num_layers, num_heads, query_head_dim, pos_head_dim, pos_dim, time_embed_dim."""
-    x = linear(sd, p + ".in_proj", x.permute(1, 0, 2))
+    # TTSZipformerTwoStream (zipformer_two_stream.py:240-247): two projection pairs, chosen by the input width
+    pj = ""
+    if p + ".in_proj.weight" not in sd:
+        pj = ".0" if x.size(2) == sd[p + ".in_proj.0.weight"].shape[1] else ".1"
+        assert x.size(2) == sd[p + ".in_proj" + pj + ".weight"].shape[1], x.shape
+    x = linear(sd, p + ".in_proj" + pj, x.permute(1, 0, 2))
     time_emb = None
     if t is not None:
         assert t.dim() == 1, t.shape
@@ -215,4 +220,4 @@ def tts_zipformer(sd: SD, p: str, cfg: dict, x: Tensor, t: Optional[Tensor], pad
             x = downsampled_stack(sd, sp, nl, ds, x, time_emb, padding_mask, H, dq, dp, pos_dim, taps)
         if taps is not None:
             taps[sp] = x
-    return linear(sd, p + ".out_proj", x).permute(1, 0, 2)
+    return linear(sd, p + ".out_proj" + pj, x).permute(1, 0, 2)

@@ -15,6 +15,20 @@ def case_inputs(B, T, prompt, seed, ragged=True):
     return x0, text, speech, mask
 
 
+def case_inputs_stereo(B, T, prompt, seed):
+    """Two-channel dialog model (ZipVoiceDialogStereo): x / speech are 200 wide, the text condition 100."""
+    g = torch.Generator().manual_seed(seed)
+    x0 = torch.randn(B, T, 200, generator=g)
+    text = torch.randn(B, T, 100, generator=g) * 0.5
+    speech = torch.randn(B, T, 200, generator=g) * 0.5 - 0.5
+    speech[:, prompt:] = 0
+    lens = torch.full((B,), T, dtype=torch.int64)
+    if B > 1:
+        lens[1:] = torch.randint(T // 2, T, (B - 1,), generator=g)
+    mask = torch.arange(T)[None] >= lens[:, None]
+    return x0, text, speech, mask
+
+
 def rel_l2(a, b):
     return float((a - b).norm() / b.norm().clamp_min(1e-30))
 

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 import torch
 
-from tests.cases import case_inputs, rel_l2, valid_rel_l2
+from tests.cases import case_inputs, case_inputs_stereo, rel_l2, valid_rel_l2
 from tests.conftest import GOLDEN
 
 pytestmark = pytest.mark.gpu
@@ -33,8 +33,8 @@ def engine(kind, cfg_name, seed, stress):
     key = (kind, cfg_name, seed, stress)
     if key not in _engines:
         cfg = synth.small_model_cfg() if cfg_name == "small" else synth.BASE_MODEL_CFG
-        sd = synth.make_state_dict(cfg, seed=seed, distill=(kind == "distill"), dialog=(kind == "dialog"),
-                                   stress=stress)
+        sd = synth.make_state_dict(cfg, seed=seed, distill=(kind == "distill"), dialog=kind.startswith("dialog"),
+                                   stress=stress, stereo=(kind == "dialog_stereo"))
         _engines[key] = (ZipVoiceB200(cfg, sd, synth.VOCAB_SIZE, synth.PAD_ID, kind=kind), cfg, sd)
     return _engines[key]
 
@@ -95,6 +95,36 @@ def test_sample_end_to_end_golden():
     assert r < TOL_MEL, f"sample() generated part rel-L2 {r:.3e}"
     r = rel_l2(out[2].cpu(), g["x1_prompt"])
     assert r < TOL_MEL, f"sample() prompt part rel-L2 {r:.3e}"
+
+
+def test_dialog_stereo_golden():
+    """ZipVoiceDialogStereo through the first stream of the two-stream decoder (200-wide x / speech)."""
+    from zipvoice_b200 import synth
+    from oracle import zipvoice_oracle as O
+    m, cfg, sd = engine("dialog_stereo", "small", 4, True)
+    g = _g("dialog_stereo.npz")
+    x0, text, speech, mask = case_inputs_stereo(2, 41, 13, seed=12)
+    v = m.forward_fm_decoder(torch.tensor(0.3), x0, text, speech, mask).cpu()
+    r = valid_rel_l2(v, g["v"], mask)
+    assert r < TOL_NFE, f"stereo velocity rel-L2 {r:.3e}"
+    x1 = m.solver.sample(x=x0, text_condition=text, speech_condition=speech, padding_mask=mask, num_step=4,
+                         guidance_scale=1.5, t_shift=0.5).cpu()
+    r = valid_rel_l2(x1, g["x1_cfg"], mask)
+    assert r < TOL_MEL, f"stereo CFG Euler rel-L2 {r:.3e}"
+    tokens, prompt_tokens = synth.make_tokens(2, n_prompt=30, n_text=50, seed=9, dialog=True, ragged=True)
+    pf, pfl = synth.make_prompt_features(2, 16, feat_dim=200, seed=13, ragged=True)
+    ptl = torch.tensor([len(t) for t in prompt_tokens])
+    tl = torch.tensor([len(t) for t in tokens])
+    T = int(O.predict_features_lens(pfl, ptl, tl, 1.1).max())
+    torch.manual_seed(666)
+    x0s = torch.randn(2, T, 200)
+    out = m.sample(tokens, prompt_tokens, pf, pfl, speed=1.1, t_shift=0.5, duration="predict", num_step=3,
+                   guidance_scale=1.5, x0=x0s.cuda())
+    assert torch.equal(out[1].cpu(), g["wo_lens"])
+    r = rel_l2(out[0].cpu(), g["x1_wo"])
+    assert r < TOL_MEL, f"stereo sample() generated part rel-L2 {r:.3e}"
+    with pytest.raises(AssertionError):  # zipformer_two_stream.py:240: the width must match an input stream
+        m.forward_fm_decoder(torch.tensor(0.3), x0[..., :100], text, speech[..., :100], mask)
 
 
 def test_dialog_text_embed_golden():

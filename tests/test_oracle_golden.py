@@ -7,7 +7,7 @@ import torch
 
 from oracle import zipvoice_oracle as O
 from zipvoice_b200 import synth
-from tests.cases import case_inputs, rel_l2, valid_rel_l2
+from tests.cases import case_inputs, case_inputs_stereo, rel_l2, valid_rel_l2
 from tests.conftest import GOLDEN
 
 TOL = 2e-5  # fp32 vs fp32, different summation order only
@@ -70,6 +70,30 @@ def test_dialog_text_embed():
     dt, dp = synth.make_tokens(2, n_prompt=30, n_text=60, seed=8, dialog=True, ragged=True)
     emb, _ = O.forward_text_embed(sd, cfg, [p + t for p, t in zip(dp, dt)], dialog=(synth.SPK_A_ID, synth.SPK_B_ID))
     assert rel_l2(emb, _g("dialog_text_embed.npz")["text_embed"]) < TOL
+
+
+def test_dialog_stereo():
+    """ZipVoiceDialogStereo (two-stream decoder, 200-wide features): velocity, CFG Euler, sample()."""
+    cfg = synth.small_model_cfg()
+    sd = synth.make_state_dict(cfg, seed=4, dialog=True, stress=True, stereo=True)
+    g = _g("dialog_stereo.npz")
+    x0, text, speech, mask = case_inputs_stereo(2, 41, 13, seed=12)
+    v = O.forward_fm_decoder(sd, cfg, torch.tensor(0.3), x0, text, speech, mask)
+    assert valid_rel_l2(v, g["v"], mask) < TOL
+    x1 = O.euler_sample(sd, cfg, x0, text, speech, mask, num_step=4, guidance_scale=1.5, t_shift=0.5)
+    assert valid_rel_l2(x1, g["x1_cfg"], mask) < 10 * TOL
+    tokens, prompt_tokens = synth.make_tokens(2, n_prompt=30, n_text=50, seed=9, dialog=True, ragged=True)
+    pf, pfl = synth.make_prompt_features(2, 16, feat_dim=200, seed=13, ragged=True)
+    ptl = torch.tensor([len(t) for t in prompt_tokens])
+    tl = torch.tensor([len(t) for t in tokens])
+    T = int(O.predict_features_lens(pfl, ptl, tl, 1.1).max())
+    torch.manual_seed(666)
+    x0s = torch.randn(2, T, 200)
+    out = O.sample(sd, cfg, tokens, prompt_tokens, pf, pfl, speed=1.1, t_shift=0.5, duration="predict", num_step=3,
+                   guidance_scale=1.5, dialog=(synth.SPK_A_ID, synth.SPK_B_ID), x0=x0s)
+    assert torch.equal(out[1], g["wo_lens"])
+    assert rel_l2(out[0], g["x1_wo"]) < 10 * TOL
+    assert rel_l2(out[2], g["x1_prompt"]) < 10 * TOL
 
 
 def test_velocity_base_cfg():

@@ -25,6 +25,7 @@ class ZvConfig(C.Structure):
         ("time_embed_dim", C.c_int), ("text_embed_dim", C.c_int),
         ("vocab_size", C.c_int), ("pad_id", C.c_int),
         ("use_guidance_scale_embed", C.c_int), ("dialog", C.c_int), ("spk_a_id", C.c_int), ("spk_b_id", C.c_int),
+        ("stereo", C.c_int),
     ]
 
 

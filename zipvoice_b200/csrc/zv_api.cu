@@ -200,13 +200,13 @@ static int velocity_step(Engine* e, int variant, float t_host, const float* t_de
                          float* v_out, float* x_update, float dt, cudaStream_t s) {
   Net& net = e->fm;
   Workspace& ws = e->ws_fm;
-  const int F = e->cfg.feat_dim;
+  const int Ft = e->cfg.feat_dim, F = e->cfg.stereo ? 2 * Ft : Ft;  // F: width of x / speech / velocity
   const bool cfg = (variant == 0) && !all_zero_g;
   const int nb = cfg ? 2 * B : B;
   const bool hi = t_host > 0.5f;  // solver.py:90 decided on the host from the precomputed time table
   // bytes: x read once, text / speech once, bf16 rows written
-  API_K(KC_PACK, (double)B * T * F * 12.0 + (double)nb * T * net.in_pad * 2.0, s,
-        API_TRY(pack_input(x, text, speech, mask, B, T, F, cfg ? 1 : 0, hi ? 1 : 0, ws.x_in, net.in_pad,
+  API_K(KC_PACK, (double)B * T * (2 * F + Ft) * 4.0 + (double)nb * T * net.in_pad * 2.0, s,
+        API_TRY(pack_input(x, text, speech, mask, B, T, F, Ft, cfg ? 1 : 0, hi ? 1 : 0, ws.x_in, net.in_pad,
                            mask ? ws.mask[0] : nullptr, s)));
   TimeArgs ta;
   ta.t = t_dev, ta.t_stride = 0;
@@ -271,7 +271,7 @@ extern "C" int zv_sample(void* handle, int variant, const float* x0, const float
   float* ts_dev = e->ws_fm.ts_dev;  // time table on the device: no host synchronisation inside the loop
   API_TRY(upload_small(e, ts_dev, ts.data(), (int)ts.size(), s));
   API_TRY(upload_small(e, e->ws_fm.guid_dev, guidance, guidance_len, s));
-  const size_t n = (size_t)B * T * e->cfg.feat_dim;
+  const size_t n = (size_t)B * T * e->cfg.feat_dim * (e->cfg.stereo ? 2 : 1);
   if (x1 != x0) API_TRY((int)cudaMemcpyAsync(x1, x0, n * 4, cudaMemcpyDeviceToDevice, s));
   for (int i = 0; i < num_step; ++i)
     API_TRY(velocity_step(e, variant, ts[i], ts_dev + i, x1, text, speech, mask, B, T, all_zero, guidance_len, nullptr,

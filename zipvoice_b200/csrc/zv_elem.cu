@@ -13,7 +13,7 @@ static inline unsigned blocks_for(size_t n, int threads) { return (unsigned)((n 
 // ------------------------------------------------------------------ input packing (+ CFG doubling)
 __global__ void pack_input_kernel(const float* __restrict__ x, const float* __restrict__ text,
                                   const float* __restrict__ speech, const uint8_t* __restrict__ mask, int B, int T,
-                                  int F, int cfg, int zero_speech_uncond, bf16* __restrict__ out, int ldo,
+                                  int Fx, int Ft, int cfg, int zero_speech_uncond, bf16* __restrict__ out, int ldo,
                                   uint8_t* __restrict__ mask_out) {
   // one thread per (row, pair of output columns)
   const int half = ldo >> 1;
@@ -26,26 +26,27 @@ __global__ void pack_input_kernel(const float* __restrict__ x, const float* __re
   const int bo = (int)(row / T);
   const int b = cfg ? (bo % B) : bo;
   const bool uncond = cfg && bo < B;
-  const size_t src = ((size_t)b * T + t) * F;
+  // row = [x (Fx) | text (Ft) | speech (Fx)]: Fx = Ft for the mono models, Fx = 2 Ft for the two-channel dialog model
+  const size_t rowi = (size_t)b * T + t;
   float v[2];
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     const int cc = c + i;
     float val = 0.f;
-    if (cc < F) val = x[src + cc];
-    else if (cc < 2 * F) val = uncond ? 0.f : text[src + cc - F];
-    else if (cc < 3 * F) val = (uncond && zero_speech_uncond) ? 0.f : speech[src + cc - 2 * F];
+    if (cc < Fx) val = x[rowi * Fx + cc];
+    else if (cc < Fx + Ft) val = uncond ? 0.f : text[rowi * Ft + cc - Fx];
+    else if (cc < 2 * Fx + Ft) val = (uncond && zero_speech_uncond) ? 0.f : speech[rowi * Fx + cc - Fx - Ft];
     v[i] = val;
   }
   *reinterpret_cast<uint32_t*>(out + row * ldo + c) = pack_bf16x2(v[0], v[1]);
   if (c == 0 && mask_out) mask_out[row] = mask ? mask[(size_t)b * T + t] : 0;
 }
 
-int pack_input(const float* x, const float* text, const float* speech, const uint8_t* mask, int B, int T, int F,
-               int cfg, int zero_speech_uncond, bf16* out, int ldo, uint8_t* mask_out, cudaStream_t s) {
+int pack_input(const float* x, const float* text, const float* speech, const uint8_t* mask, int B, int T, int Fx,
+               int Ft, int cfg, int zero_speech_uncond, bf16* out, int ldo, uint8_t* mask_out, cudaStream_t s) {
   const size_t n = (size_t)(cfg ? 2 * B : B) * T * (ldo / 2);
-  pack_input_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, text, speech, mask, B, T, F, cfg, zero_speech_uncond, out,
-                                                       ldo, mask_out);
+  pack_input_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, text, speech, mask, B, T, Fx, Ft, cfg, zero_speech_uncond,
+                                                       out, ldo, mask_out);
   return (int)cudaGetLastError();
 }
 

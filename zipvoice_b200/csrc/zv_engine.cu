@@ -257,7 +257,8 @@ static int build_layer(Engine& e, Net& net, const std::string& p, int kernel, La
 }
 
 static int build_net(Engine& e, Net& net, const std::string& prefix, int in_dim, int out_dim, int D, int F, int H,
-                     int n_stacks, const int* ds, const int* nl, const int* kern, bool use_time, bool use_guidance) {
+                     int n_stacks, const int* ds, const int* nl, const int* kern, bool use_time, bool use_guidance,
+                     bool two_stream = false) {
   const zv_config& c = e.cfg;
   net.prefix = prefix, net.in_dim = in_dim, net.out_dim = out_dim, net.D = D, net.F = F, net.H = H;
   net.hidden_na = 3 * D / 4;
@@ -271,8 +272,11 @@ static int build_net(Engine& e, Net& net, const std::string& prefix, int in_dim,
     e.err = "encoder dim must be a multiple of 64 and <= 512";
     return 943;
   }
-  ZV_TRY(pack_linear(e, prefix + ".in_proj", EPI_F32, &net.in_proj, net.in_pad));
-  ZV_TRY(pack_linear(e, prefix + ".out_proj", EPI_F32, &net.out_proj));
+  // TTSZipformerTwoStream keeps two projection pairs in ModuleLists; inference of the stereo dialog model
+  // goes through the first one (zipformer_two_stream.py:240-263, x.size(2) == in_dim[0])
+  const std::string pj = two_stream ? ".0" : "";
+  ZV_TRY(pack_linear(e, prefix + ".in_proj" + pj, EPI_F32, &net.in_proj, net.in_pad));
+  ZV_TRY(pack_linear(e, prefix + ".out_proj" + pj, EPI_F32, &net.out_proj));
   const int td = c.time_embed_dim;
   if (use_time) {
     ZV_TRY(upload_named(e, prefix + ".time_embed.0.weight", &net.te_w0));
@@ -378,9 +382,10 @@ int engine_finalize(Engine& e) {
       return 0;
     }
   }
-  ZV_TRY(build_net(e, e.fm, "fm_decoder", 3 * c.feat_dim, c.feat_dim, c.fm_dim, c.fm_feedforward_dim, c.fm_num_heads,
+  const int fx = c.stereo ? 2 * c.feat_dim : c.feat_dim;
+  ZV_TRY(build_net(e, e.fm, "fm_decoder", 2 * fx + c.feat_dim, fx, c.fm_dim, c.fm_feedforward_dim, c.fm_num_heads,
                    c.fm_num_stacks, c.fm_downsampling_factor, c.fm_num_layers, c.fm_cnn_module_kernel, true,
-                   c.use_guidance_scale_embed != 0));
+                   c.use_guidance_scale_embed != 0, c.stereo != 0));
   const int one = 1;
   ZV_TRY(build_net(e, e.text, "text_encoder", c.text_embed_dim, c.feat_dim, c.text_dim, c.text_feedforward_dim,
                    c.text_num_heads, 1, &one, &c.text_num_layers, &c.text_cnn_module_kernel, false, false));

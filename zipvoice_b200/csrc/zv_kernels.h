@@ -10,8 +10,8 @@ namespace zv {
 // x,text,speech fp32 [B][T][F] -> bf16 [nb][T][ldo] = [x | text | speech | 0-pad]  (zipvoice.py:163).
 // cfg != 0 doubles the batch (solver.py:83-98): rows [0,B) unconditional (text = 0, speech = 0 when
 // zero_speech_uncond), rows [B,2B) conditional.  Also writes the doubled key-padding mask.
-int pack_input(const float* x, const float* text, const float* speech, const uint8_t* mask, int B, int T, int F,
-               int cfg, int zero_speech_uncond, __nv_bfloat16* out, int ldo, uint8_t* mask_out, cudaStream_t s);
+int pack_input(const float* x, const float* text, const float* speech, const uint8_t* mask, int B, int T, int Fx,
+               int Ft, int cfg, int zero_speech_uncond, __nv_bfloat16* out, int ldo, uint8_t* mask_out, cudaStream_t s);
 
 // x += dt * v  (plain, nb == B)   or   x += dt * ((1+g_b) v[B+b] - g_b v[b])  (cfg; solver.py:100-110,239)
 int cfg_euler_update(float* x, const float* v, const float* guidance, int guidance_len, float g_mult, int B, int T,

@@ -16,7 +16,7 @@ class ZvError(RuntimeError):
 
 
 def make_config(model_cfg: dict, vocab_size: int, pad_id: int = 0, distill: bool = False, dialog: bool = False,
-                spk_a_id: int = 360, spk_b_id: int = 361) -> _lib.ZvConfig:
+                spk_a_id: int = 360, spk_b_id: int = 361, stereo: bool = False) -> _lib.ZvConfig:
     """model_cfg: the "model" section of model.json (= kwargs of ZipVoice.__init__, zipvoice.py:38-60)."""
     c = _lib.ZvConfig()
     ds = list(model_cfg["fm_decoder_downsampling_factor"])
@@ -40,6 +40,7 @@ def make_config(model_cfg: dict, vocab_size: int, pad_id: int = 0, distill: bool
     c.vocab_size, c.pad_id = vocab_size, pad_id
     c.use_guidance_scale_embed, c.dialog = int(distill), int(dialog)
     c.spk_a_id, c.spk_b_id = spk_a_id, spk_b_id
+    c.stereo = int(stereo)
     return c
 
 
@@ -56,16 +57,17 @@ class Engine:
 
     def __init__(self, model_cfg: dict, state_dict: Dict[str, torch.Tensor], vocab_size: int, pad_id: int = 0,
                  distill: bool = False, dialog: bool = False, spk_a_id: int = 360, spk_b_id: int = 361,
-                 device: Union[str, torch.device] = "cuda:0"):
+                 device: Union[str, torch.device] = "cuda:0", stereo: bool = False):
         if not torch.cuda.is_available():
             raise ZvError("zipvoice_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
         self.lib = _lib.load()
         self.device = torch.device(device)
-        self.model_cfg, self.distill, self.dialog = dict(model_cfg), distill, dialog
+        self.model_cfg, self.distill, self.dialog, self.stereo = dict(model_cfg), distill, dialog, stereo
         self.pad_id, self.feat_dim = pad_id, model_cfg["feat_dim"]
+        self.x_dim = model_cfg["feat_dim"] * (2 if stereo else 1)  # width of x / speech_condition / velocity
         self._h = C.c_void_p()
         with torch.cuda.device(self.device):
-            cfg = make_config(model_cfg, vocab_size, pad_id, distill, dialog, spk_a_id, spk_b_id)
+            cfg = make_config(model_cfg, vocab_size, pad_id, distill, dialog, spk_a_id, spk_b_id, stereo)
             self._check(self.lib.zv_create(C.byref(cfg), C.byref(self._h)))
             for name, t in state_dict.items():
                 t = t.detach().to(dtype=torch.float32).contiguous()
@@ -112,6 +114,9 @@ class Engine:
         distill = self.distill if distill is None else distill
         x, tc, sc = self._prep(x), self._prep(text_condition), self._prep(speech_condition)
         B, T, F = x.shape
+        # zipformer.py:268 / zipformer_two_stream.py:240: the concatenated width must be the in_proj's
+        assert F == self.x_dim and sc.shape == x.shape and tuple(tc.shape) == (B, T, self.feat_dim), \
+            f"x/speech (B,T,{self.x_dim}) and text (B,T,{self.feat_dim}) expected, got {tuple(x.shape)} {tuple(sc.shape)} {tuple(tc.shape)}"
         m = None if padding_mask is None else self._prep(padding_mask, torch.uint8)
         g, glen = self._guidance(guidance_scale, B)
         out = torch.empty_like(x)
@@ -126,6 +131,9 @@ class Engine:
         distill = self.distill if distill is None else distill
         x, tc, sc = self._prep(x), self._prep(text_condition), self._prep(speech_condition)
         B, T, F = x.shape
+        # zipformer.py:268 / zipformer_two_stream.py:240: the concatenated width must be the in_proj's
+        assert F == self.x_dim and sc.shape == x.shape and tuple(tc.shape) == (B, T, self.feat_dim), \
+            f"x/speech (B,T,{self.x_dim}) and text (B,T,{self.feat_dim}) expected, got {tuple(x.shape)} {tuple(sc.shape)} {tuple(tc.shape)}"
         m = None if padding_mask is None else self._prep(padding_mask, torch.uint8)
         g, glen = self._guidance(guidance_scale, B)
         out = torch.empty_like(x)

@@ -21,13 +21,16 @@ def pad_labels(y: List[List[int]], pad_id: int, device) -> torch.Tensor:
 
 
 class ZipVoiceB200:
-    """kind: "zipvoice" | "distill" | "dialog" (ZipVoice / ZipVoiceDistill / ZipVoiceDialog)."""
+    """kind: "zipvoice" | "distill" | "dialog" | "dialog_stereo"
+    (ZipVoice / ZipVoiceDistill / ZipVoiceDialog / ZipVoiceDialogStereo, zipvoice_dialog.py:218-256: two-channel
+    features of width 2 * feat_dim through the first stream of TTSZipformerTwoStream)."""
 
     def __init__(self, model_cfg: dict, state_dict, vocab_size: int, pad_id: int = 0, kind: str = "zipvoice",
                  spk_a_id: int = 360, spk_b_id: int = 361, device="cuda:0"):
-        assert kind in ("zipvoice", "distill", "dialog")
+        assert kind in ("zipvoice", "distill", "dialog", "dialog_stereo")
         self.engine = Engine(model_cfg, state_dict, vocab_size, pad_id, distill=(kind == "distill"),
-                             dialog=(kind == "dialog"), spk_a_id=spk_a_id, spk_b_id=spk_b_id, device=device)
+                             dialog=kind.startswith("dialog"), spk_a_id=spk_a_id, spk_b_id=spk_b_id, device=device,
+                             stereo=(kind == "dialog_stereo"))
         self.kind, self.pad_id, self.feat_dim = kind, pad_id, model_cfg["feat_dim"]
         self.device = self.engine.device
         self.solver = (B200DistillEulerSolver if kind == "distill" else B200EulerSolver)(self.engine)
@@ -129,10 +132,10 @@ def install(ref_model, model_cfg: dict, device="cuda:0") -> Engine:
     """Patch a reference ``ZipVoice`` / ``ZipVoiceDistill`` / ``ZipVoiceDialog`` nn.Module in place:
     weights are read from its state_dict and ``model.solver`` is replaced (zipvoice.py:133)."""
     name = type(ref_model).__name__
-    distill, dialog = "Distill" in name, "Dialog" in name
+    distill, dialog, stereo = "Distill" in name, "Dialog" in name, "Stereo" in name
     sd = ref_model.state_dict()
     eng = Engine(model_cfg, sd, vocab_size=sd["embed.weight"].shape[0], pad_id=ref_model.pad_id, distill=distill,
                  dialog=dialog, spk_a_id=getattr(ref_model, "spk_a_id", 360),
-                 spk_b_id=getattr(ref_model, "spk_b_id", 361), device=device)
+                 spk_b_id=getattr(ref_model, "spk_b_id", 361), device=device, stereo=stereo)
     ref_model.solver = (B200DistillEulerSolver if distill else B200EulerSolver)(eng)
     return eng

@@ -98,7 +98,7 @@ def _zipformer_shapes(p: str, in_dim, out_dim, D, F, H, dq, dp, dv, pos_dim, ds_
 
 
 def make_state_dict(model_cfg: dict = None, seed: int = 0, distill: bool = False, dialog: bool = False,
-                    stress: bool = False, vocab_size: int = VOCAB_SIZE) -> Dict[str, torch.Tensor]:
+                    stress: bool = False, vocab_size: int = VOCAB_SIZE, stereo: bool = False) -> Dict[str, torch.Tensor]:
     """fp32 CPU state dict with the reference's names.  ``stress`` scales up the attention and
     position projections, out-projections, bypass scales and BiasNorm biases so that every branch
     of the layer contributes visibly to the output."""
@@ -145,6 +145,17 @@ def make_state_dict(model_cfg: dict = None, seed: int = 0, distill: bool = False
             sd[name] = torch.randn(shape, generator=g) if stress else torch.zeros(shape)
         else:
             raise AssertionError(kind)
+    if stereo:
+        # ZipVoiceDialogStereo: TTSZipformerTwoStream keeps two projection pairs in ModuleLists
+        # (zipformer_two_stream.py:139-150): index 0 = two channels (5F -> D, D -> 2F), index 1 = mono
+        F_, D_ = c["feat_dim"], c["fm_decoder_dim"]
+        for k in ("weight", "bias"):
+            sd[f"fm_decoder.in_proj.1.{k}"] = sd.pop(f"fm_decoder.in_proj.{k}")
+            sd[f"fm_decoder.out_proj.1.{k}"] = sd.pop(f"fm_decoder.out_proj.{k}")
+        for name, shape in (("fm_decoder.in_proj.0", (D_, 5 * F_)), ("fm_decoder.out_proj.0", (2 * F_, D_))):
+            g = _gen(seed, name)
+            sd[name + ".weight"] = _uniform(g, shape, 1.0 / math.sqrt(shape[1]))
+            sd[name + ".bias"] = _uniform(g, (shape[0],), 1.0 / math.sqrt(shape[1]))
     sd["embed.weight"] = torch.randn(vocab_size, c["text_embed_dim"], generator=_gen(seed, "embed.weight"))
     if dialog:
         sd["spk_embed.weight"] = torch.randn(2, c["feat_dim"], generator=_gen(seed, "spk_embed.weight")) * 0.1
