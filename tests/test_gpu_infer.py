@@ -59,3 +59,36 @@ def test_generate_batch_shapes_and_lengths():
         import math
         gen = math.ceil(pf / len(prompt_tokens[i]) * len(tokens[i]) / 1.0)
         assert w.shape == (256 * (gen - 1),) and bool(torch.isfinite(w).all())
+
+
+def test_generate_sentence_stereo_vs_oracle_pipeline():
+    """Two-channel dialog pipeline (bin/infer_zipvoice_dialog.py:350-515) against the CPU oracles."""
+    from oracle import fbank_oracle as FO, vocos_oracle as VO, zipvoice_oracle as O
+    from zipvoice_b200 import infer, synth
+    from zipvoice_b200.audio import VocosB200, VocosFbankB200
+    from zipvoice_b200.model import ZipVoiceB200
+    cfg = synth.small_model_cfg()
+    sd = synth.make_state_dict(cfg, seed=4, dialog=True, stress=True, stereo=True)
+    vsd = VO.make_vocos_state_dict(0)
+    model = ZipVoiceB200(cfg, sd, synth.VOCAB_SIZE, synth.PAD_ID, kind="dialog_stereo")
+    voc = VocosB200(vsd)
+    fb = VocosFbankB200(engine=voc.engine, num_channels=2)
+    tokens, prompt_tokens = synth.make_tokens(1, n_prompt=26, n_text=40, seed=3, dialog=True)
+    wav_p = synth.make_audio(2, 9000, seed=12) * 0.3             # (2, N): left / right, rms < 0.1
+    rms = torch.sqrt(torch.mean(torch.square(wav_p)))
+    wp = wav_p * 0.1 / rms if rms < 0.1 else wav_p
+    feats = torch.cat([FO.vocos_fbank(wp[0]), FO.vocos_fbank(wp[1])], dim=-1).unsqueeze(0) * 0.1   # (1, T, 200)
+    fl = torch.tensor([feats.size(1)])
+    T = int(O.predict_features_lens(fl, torch.tensor([26]), torch.tensor([40]), 1.0))
+    x0 = torch.randn(1, T, 200, generator=torch.Generator().manual_seed(9))
+    want_mel, _, _, _ = O.sample(sd, cfg, tokens, prompt_tokens, feats, fl, speed=1.0, t_shift=0.5, num_step=4,
+                                 guidance_scale=1.5, dialog=(synth.SPK_A_ID, synth.SPK_B_ID), x0=x0)
+    wm = want_mel.permute(0, 2, 1) / 0.1
+    want = torch.cat([VO.decode(vsd, wm[:, :100]), VO.decode(vsd, wm[:, 100:])], dim=0).clamp(-1, 1)
+    if rms < 0.1:
+        want = want * rms / 0.1
+    wav, metrics = infer.generate_sentence_stereo(prompt_tokens[0], wav_p, tokens[0], model, voc, fb, num_step=4,
+                                                  guidance_scale=1.5, t_shift=0.5, x0=x0.cuda())
+    assert wav.shape == want.shape and wav.shape[0] == 2
+    r = rel_l2(wav.cpu(), want)
+    assert r < 5e-2, f"stereo waveform rel-L2 {r:.3e}"

@@ -2,6 +2,7 @@
 
 * ``generate_sentence``  -- same arguments, pre/post scaling and metrics as :276-403, but waveforms /
   token ids are passed in directly (tokenizers and audio file I/O are out of scope);
+* ``generate_sentence_stereo`` -- bin/infer_zipvoice_dialog.py:350-515 for ZipVoiceDialogStereo;
 * ``generate_batch``     -- what the reference lacks: a whole list of utterances as ONE padded batch
   (GPU mel extraction of all prompts, one ``sample()``, one batched vocoder call), optionally sharded
   data-parallel over the ranks of torchrun and gathered to rank 0.
@@ -49,6 +50,45 @@ def generate_sentence(prompt_tokens: List[int], prompt_wav: torch.Tensor, tokens
     t2 = time.perf_counter()
     if prompt_rms < target_rms:
         wav = wav * prompt_rms / target_rms                                     # :399-400
+    sec = wav.shape[-1] / sampling_rate
+    metrics = {"t": t2 - t0, "t_no_vocoder": t1 - t0, "t_vocoder": t2 - t1, "wav_seconds": sec,
+               "rtf": (t2 - t0) / sec, "rtf_no_vocoder": (t1 - t0) / sec, "rtf_vocoder": (t2 - t1) / sec}
+    return wav, metrics
+
+
+@torch.inference_mode()
+def generate_sentence_stereo(prompt_tokens: List[int], prompt_wav: torch.Tensor, tokens: List[int], model, vocoder,
+                             feature_extractor, num_step: int = 16, guidance_scale: float = 1.0, speed: float = 1.0,
+                             t_shift: float = 0.5, target_rms: float = 0.1, feat_scale: float = 0.1,
+                             sampling_rate: int = 24000, x0: Optional[torch.Tensor] = None):
+    """bin/infer_zipvoice_dialog.py:350-515 (generate_sentence_stereo) for a two-channel prompt waveform
+    (2, N) already merged / resampled by the caller: RMS over both channels, VocosFbank(num_channels=2)
+    features (T, 200), ZipVoiceDialogStereo.sample, one vocoder pass per channel (:483-490).
+    -> (wav (2, N') on the device, metrics dict with the reference's keys)."""
+    dev = model.device
+    prompt_wav = prompt_wav.to(dev).float()
+    assert prompt_wav.dim() == 2 and prompt_wav.size(0) == 2, \
+        "Merged prompt wav must be stereo for stereo dialogue generation"            # :425-428
+    prompt_wav, prompt_rms = _rms_normalise(prompt_wav, target_rms)                   # :445-447
+    feats = feature_extractor.extract(prompt_wav, sampling_rate=sampling_rate).to(dev)
+    feats = feats.unsqueeze(0) * feat_scale                                           # :454
+    feats_lens = torch.tensor([feats.size(1)], device=dev)
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    pred, pred_lens, _, _ = model.sample(tokens=[tokens], prompt_tokens=[prompt_tokens], prompt_features=feats,
+                                         prompt_features_lens=feats_lens, speed=speed, t_shift=t_shift,
+                                         duration="predict", num_step=num_step, guidance_scale=guidance_scale,
+                                         **({"x0": x0} if x0 is not None else {}))
+    pred = pred.permute(0, 2, 1) / feat_scale                                         # :479 (B, 2F, T)
+    torch.cuda.synchronize(dev)
+    t1 = time.perf_counter()
+    fd = pred.size(1) // 2
+    # both channels in one batched vocoder call (the reference makes two calls, :484-489)
+    wav = vocoder.decode(torch.cat([pred[:, :fd], pred[:, fd:2 * fd]], dim=0).contiguous()).clamp(-1, 1)
+    torch.cuda.synchronize(dev)
+    t2 = time.perf_counter()
+    if prompt_rms < target_rms:
+        wav = wav * prompt_rms / target_rms                                           # :511-512
     sec = wav.shape[-1] / sampling_rate
     metrics = {"t": t2 - t0, "t_no_vocoder": t1 - t0, "t_vocoder": t2 - t1, "wav_seconds": sec,
                "rtf": (t2 - t0) / sec, "rtf_no_vocoder": (t1 - t0) / sec, "rtf_vocoder": (t2 - t1) / sec}
