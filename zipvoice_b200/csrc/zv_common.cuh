@@ -187,6 +187,19 @@ ZV_DEVINL void swoosh_l_fast2(float& x0, float& x1) {
   f2_unpack(f2_fma(q, f2_pack(0.6931471805599453f, 0.6931471805599453f), lin), x0, x1);
 }
 
+// SwooshR on a packed pair (same formula as swoosh_r_fast); returns the packed result
+ZV_DEVINL f32x2 swoosh_r_fast2(f32x2 x) {
+  const float L2E = 1.4426950408889634f;
+  float t0, t1;
+  f2_unpack(f2_fma(x, f2_pack(L2E, L2E), f2_pack(-L2E, -L2E)), t0, t1);
+  const f32x2 s = f2_add(f2_pack(ex2_approx(-fabsf(t0)), ex2_approx(-fabsf(t1))), f2_pack(1.0f, 1.0f));
+  float s0, s1;
+  f2_unpack(s, s0, s1);
+  const f32x2 q = f2_add(f2_pack(fmaxf(t0, 0.f), fmaxf(t1, 0.f)), f2_pack(lg2_approx(s0), lg2_approx(s1)));
+  const f32x2 lin = f2_fma(x, f2_pack(-0.08f, -0.08f), f2_pack(-0.313261687f, -0.313261687f));
+  return f2_fma(q, f2_pack(0.6931471805599453f, 0.6931471805599453f), lin);
+}
+
 // SwooshL on a pair with ONE MUFU op per element: ln(1 + z), z = 2^-|t| in (0, 1], is a degree-5
 // polynomial z*q(z) on the FMA pipe (max abs error 1.5e-6, far below the bf16 rounding of the result)
 // instead of a second MUFU (lg2).  The GEMM epilogue is MUFU-bound with two per element.

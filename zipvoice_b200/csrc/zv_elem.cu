@@ -158,13 +158,21 @@ dwconv_kernel(const __grid_constant__ CUtensorMap tm_in, const float* __restrict
             if (tap >= 0 && tap < K) acc[o] = f2_fma(wp[tap], xp, acc[o]);
           }
         }
+        bf16* op = dst + (size_t)(tt0 + tt) * ldo + c;
+        if (tt0 + tt + FG <= L) {  // whole group inside the sequence: no per-frame predicate
 #pragma unroll
-        for (int o = 0; o < FG; ++o) {
-          const int t = tt0 + tt + o;
-          float a0, a1;
-          f2_unpack(acc[o], a0, a1);
-          if (t < L)
-            *reinterpret_cast<uint32_t*>(dst + (size_t)t * ldo + c) = pack_bf16x2(swoosh_r_fast(a0), swoosh_r_fast(a1));
+          for (int o = 0; o < FG; ++o, op += ldo) {
+            float a0, a1;
+            f2_unpack(swoosh_r_fast2(acc[o]), a0, a1);
+            *reinterpret_cast<uint32_t*>(op) = pack_bf16x2(a0, a1);
+          }
+        } else {
+#pragma unroll
+          for (int o = 0; o < FG; ++o, op += ldo) {
+            float a0, a1;
+            f2_unpack(swoosh_r_fast2(acc[o]), a0, a1);
+            if (tt0 + tt + o < L) *reinterpret_cast<uint32_t*>(op) = pack_bf16x2(a0, a1);
+          }
         }
       }
     }
@@ -201,11 +209,19 @@ static int launch_dwconv(const bf16* in, const float* w, const float* bias, int 
 int dwconv_swooshr(const bf16* in, const float* w, const float* bias, int nb, int L, int C, int k, bf16* out, int ldo,
                    cudaStream_t s) {
   if (ldo < C || (ldo & 1) || (C & 7)) return 911;
+  static const int fg = [] {  // frames per thread step: 16 halves the shared-memory loads per output (ZV_DWCONV_FG=8|16)
+    const char* e = getenv("ZV_DWCONV_FG");
+    return e ? atoi(e) : 16;
+  }();
   switch (k) {
     case 7: return launch_dwconv<7, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
     case 9: return launch_dwconv<9, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
-    case 15: return launch_dwconv<15, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
-    case 31: return launch_dwconv<31, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
+    case 15:
+      return fg == 16 ? launch_dwconv<15, 64, 16>(in, w, bias, nb, L, C, out, ldo, s)
+                      : launch_dwconv<15, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
+    case 31:
+      return fg == 16 ? launch_dwconv<31, 64, 16>(in, w, bias, nb, L, C, out, ldo, s)
+                      : launch_dwconv<31, 64, 8>(in, w, bias, nb, L, C, out, ldo, s);
     default: return 910;
   }
 }
