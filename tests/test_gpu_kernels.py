@@ -158,11 +158,13 @@ def ref_attention(qkp, E, mask, V, gate, H, heads, dv):
 
 
 @pytest.mark.parametrize("L", [1, 37, 64, 130, 611])
-@pytest.mark.parametrize("kind", ["self", "self_mma", "nonlin384", "nonlin144", "nonlin384_mma", "nonlin144_mma"])
+@pytest.mark.parametrize("kind", ["self", "self_mma", "nonlin384", "nonlin144", "nonlin384_mma", "nonlin144_mma",
+                                  "nonlin384_redo", "nonlin144_redo"])
 def test_attention(L, kind):
     H, nb = 4, 3
-    _lib().zv_debug_set_attn_impl(1 if kind.endswith("_mma") else 0)
-    kind = kind.replace("_mma", "")
+    # _mma: the mma.sync flash kernel; _redo: the tcgen05 NonlinAttention kernel with its exact-maxima repeat forced
+    _lib().zv_debug_set_attn_impl(1 if kind.endswith("_mma") else 2 if kind.endswith("_redo") else 0)
+    kind = kind.replace("_mma", "").replace("_redo", "")
     g = torch.Generator(device="cuda").manual_seed(L)
     rn = lambda *s: torch.randn(*s, device="cuda", generator=g)
     qkp = (rn(nb, L, 288) * 0.7).bfloat16().float()
@@ -181,3 +183,27 @@ def test_attention(L, kind):
     want = ref_attention(qkp, E, mask, V, gate, H, heads, dv)
     r = rel(out, want)
     assert r < 8e-3, f"rel-L2 {r:.3e} max-abs {float((out - want).abs().max()):.3e}"
+
+
+@pytest.mark.parametrize("L", [130, 611])
+def test_nonlin_attention_overflow_repeat(L):
+    """Scores of late keys sit ~130 nats above those of key tile 0 and of the early diagonal tiles: the optimistic
+    value sweep of the tcgen05 NonlinAttention kernel must notice and repeat with exact row maxima."""
+    H, nb, dv = 4, 2, 384
+    g = torch.Generator(device="cuda").manual_seed(L)
+    rn = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    qkp = (rn(nb, L, 288) * 0.05).bfloat16().float()
+    qkp[..., :32] += 2.0                                   # q of head 0
+    qkp[:, L // 2:, H * 32: H * 32 + 32] += 2.0            # k of head 0, second half of the keys: s ~ 128
+    qkp = qkp.bfloat16().float()
+    E = rn(H, 2 * L - 1, 4).contiguous()
+    mask = torch.zeros(nb, L, dtype=torch.uint8, device="cuda")
+    V = rn(nb, L, dv).bfloat16().float()
+    gate = rn(nb, L, dv).bfloat16().float()
+    out = torch.zeros(nb, L, dv, device="cuda")
+    rc = _lib().zv_debug_attention(nb, L, H, 1, dv, _p(qkp), 288, _p(E), _p(mask), _p(V), dv, _p(gate), _p(out), None)
+    assert rc == 0
+    want = ref_attention(qkp, E, mask, V, gate, H, 1, dv)
+    assert torch.isfinite(out).all()
+    r = rel(out, want)
+    assert r < 8e-3, f"rel-L2 {r:.3e}"

@@ -298,13 +298,16 @@ int attention_na_tc(const AttnParams& p, cudaStream_t s);
 int attention_sa_tma(const AttnParams& p, cudaStream_t s);
 int g_attn_impl = 0;  // 0: TMA-fed SelfAttention (zv_attn_sa.cu) + tcgen05 NonlinAttention (zv_attn_tc.cu);
                       // 1: the cp.async / mma.sync flash kernel below for everything
+                      // 2: as 0, with the exact-maxima repeat of the NonlinAttention kernel forced (tests)
 
 int attention(const AttnParams& p, cudaStream_t s) {
-  if (p.heads == 1 && g_attn_impl == 0) {
-    const int rc = attention_na_tc(p, s);
+  if (p.heads == 1 && g_attn_impl != 1) {
+    AttnParams q = p;
+    if (g_attn_impl == 2) q.dbg |= 4;
+    const int rc = attention_na_tc(q, s);
     if (rc >= 0) return rc;
   }
-  if (p.heads == p.H && p.dv == 12 && g_attn_impl == 0) {
+  if (p.heads == p.H && p.dv == 12 && g_attn_impl != 1) {
     const int rc = attention_sa_tma(p, s);
     if (rc >= 0) return rc;
   }

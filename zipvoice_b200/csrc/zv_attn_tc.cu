@@ -3,14 +3,19 @@
 //
 // CTA = 128 queries of one sequence.  The scores are cheap (dq = 32) but every one needs the
 // relative-position term and an exponential on the CUDA cores, while A.X is a 128 x 384 x L product:
-//   sweep 1: S tiles (mma.sync fp16 + position term) -> exact row maxima, nothing stored;
-//   sweep 2: S again, P = exp(S - max) as bf16 into a SWIZZLE_128B K-major shared-memory tile, and ONE
+//   reference maxima: S tiles (mma.sync fp16 + position term) of key tile 0 and of the tile under the
+//            diagonal only -> a per-row reference m (nothing stored).  Softmax is shift invariant and P is bf16
+//            (fp32 exponent range), so ANY finite m works as long as exp(S - m) cannot overflow;
+//   value sweep: S of every tile, P = exp(S - m) as bf16 into a SWIZZLE_128B K-major shared-memory tile, and ONE
 //            thread issues tcgen05.mma  O[128 x 384] += P[128 x 64] X[64 x 384]  with X tiles TMA-loaded as
 //            MN-major operands (the row-major [key][channel] layout is used as is); O stays in TMEM for the
 //            whole key loop -- no online-softmax rescaling -- and is normalised by the row sums at the end.
+//   Every thread checks S - m <= 2^OVF_LOG2 on the way; if any score breaks that bound (66 nats above the
+//   reference: not seen with real weights, covered by a unit test) the CTA repeats the work the exact way:
+//   a full maxima sweep, then the value sweep again with the exact row maxima.
 // 16 compute warps (8 row groups x 2 key halves of each 64-key tile) + an MMA warp (X tiles by TMA,
 // tcgen05.mma issue) + a producer warp that streams the K tiles (SWIZZLE_64B boxes of the fp16 q|k|p rows)
-// and the relative-position windows (1-D bulk copies) of BOTH sweeps through a 4-stage full / empty mbarrier
+// and the relative-position windows (1-D bulk copies) of all sweeps through a 4-stage full / empty mbarrier
 // ring: the compute warps never meet at a CTA barrier inside the key loops.
 #include <cuda.h>
 
@@ -25,6 +30,7 @@ namespace natc {
 static constexpr int BQ = 128, BKV = 64, DQ = 32, EWIN = 192;
 static constexpr int VSTAGES = 3, NVBOX = 6;  // up to 6 boxes of 64 channels = 384
 static constexpr int KSTAGES = 4;
+static constexpr float OVF_LOG2 = 96.0f;  // P <= 2^96: 1219 keys x |x| <= 2^10 still sums far below fp32 max
 static constexpr int COMPUTE_THREADS = 512, THREADS = COMPUTE_THREADS + 64;
 static constexpr int MMA_WARP = COMPUTE_THREADS / 32, LOAD_WARP = MMA_WARP + 1;
 
@@ -38,6 +44,7 @@ struct alignas(16) Smem {  // the key mask that follows is read with 16-byte loa
   uint64_t vfull[VSTAGES], vfree[VSTAGES], pfull[2], pfree[2], obar;
   uint64_t kfull[KSTAGES], kempty[KSTAGES], qbar;
   uint32_t tmem_base;
+  uint32_t redo;  // a score exceeded the reference maximum by more than OVF_LOG2: repeat with exact maxima
   // followed by: uint8_t mask[n_tiles * BKV] (0 valid, 1 padded key, 2 beyond the sequence), uint8_t flag[n_tiles]
 };
 
@@ -133,6 +140,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
   const int i0 = blockIdx.x * BQ;
   const int L = p.L, H = p.H, R = 2 * L - 1;
   const int n_tiles = (L + BKV - 1) / BKV;
+  const int kd = min((i0 + BQ / 2) / BKV, n_tiles - 1);  // key tile under the middle of this CTA's diagonal
   const __half* qkp = reinterpret_cast<const __half*>(p.qkp) + (size_t)b * L * p.ldq;  // head 0
   const float4* E = reinterpret_cast<const float4*>(p.E);
   const uint8_t* mask = p.mask ? p.mask + (size_t)b * L : nullptr;
@@ -146,6 +154,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
     for (int i = 0; i < KSTAGES; ++i) mbar_init(&sm.kfull[i], 1), mbar_init(&sm.kempty[i], COMPUTE_THREADS / 32);
     mbar_init(&sm.obar, 1);
     mbar_init(&sm.qbar, 1);
+    sm.redo = (p.dbg & 4) ? 1u : 0u;
     fence_barrier_init();
   }
   if (warp == MMA_WARP) tmem_alloc(&sm.tmem_base, 512);
@@ -167,49 +176,57 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
   const uint32_t tmem_base = sm.tmem_base;
 
   if (warp == LOAD_WARP) {
-    // ---------------- producer: Q once, then K tile + position window of every key tile, twice (two sweeps)
+    // ---------------- producer: Q once, then K tile + position window of every key tile of every sweep
+    int g = 0;
+    auto load_k = [&](int kt) {
+      const int st = g % KSTAGES;
+      if (g >= KSTAGES) mbar_wait(&sm.kempty[st], ((g / KSTAGES) - 1) & 1);
+      const int j0 = kt * BKV;
+      const int rr0 = (j0 - i0 - (BQ - 1)) + (L - 1);  // table row of window entry 0
+      const int lo = max(rr0, 0), hi = min(rr0 + EWIN, R);
+      const uint32_t ebytes = hi > lo ? (uint32_t)(hi - lo) * 16u : 0u;
+      mbar_arrive_expect_tx(&sm.kfull[st], BKV * DQ * 2 + ebytes);
+      tma_load_2d(&sm.k[st][0][0], &tmQK, &sm.kfull[st], H * DQ, b * L + j0);
+      if (ebytes) bulk_load_1d(&sm.e[st][lo - rr0], E + lo, ebytes, &sm.kfull[st]);
+      ++g;
+    };
     if (lane == 0) {
       tma_prefetch_desc(&tmQK);
       mbar_arrive_expect_tx(&sm.qbar, BQ * DQ * 2);
       tma_load_2d(&sm.q[0][0], &tmQK, &sm.qbar, 0, b * L + i0);
       tma_load_2d(&sm.q[64][0], &tmQK, &sm.qbar, 0, b * L + i0 + 64);
-      for (int g = 0; g < 2 * n_tiles; ++g) {
-        const int kt = g < n_tiles ? g : g - n_tiles, st = g % KSTAGES;
-        if (g >= KSTAGES) mbar_wait(&sm.kempty[st], ((g / KSTAGES) - 1) & 1);
-        const int j0 = kt * BKV;
-        const int rr0 = (j0 - i0 - (BQ - 1)) + (L - 1);  // table row of window entry 0
-        const int lo = max(rr0, 0), hi = min(rr0 + EWIN, R);
-        const uint32_t ebytes = hi > lo ? (uint32_t)(hi - lo) * 16u : 0u;
-        mbar_arrive_expect_tx(&sm.kfull[st], BKV * DQ * 2 + ebytes);
-        tma_load_2d(&sm.k[st][0][0], &tmQK, &sm.kfull[st], H * DQ, b * L + j0);
-        if (ebytes) bulk_load_1d(&sm.e[st][lo - rr0], E + lo, ebytes, &sm.kfull[st]);
-      }
+      load_k(0);
+      if (kd != 0) load_k(kd);
+      for (int kt = 0; kt < n_tiles; ++kt) load_k(kt);
+    }
+    __syncwarp();
+    named_bar_sync(2, THREADS);
+    if (sm.redo != 0 && lane == 0) {
+      for (int kt = 0; kt < 2 * n_tiles; ++kt) load_k(kt < n_tiles ? kt : kt - n_tiles);
     }
     __syncwarp();
   } else if (warp == MMA_WARP) {
-    // ---------------- producer: X tiles by TMA, P.X by tcgen05.mma
-    if (lane == 0) {
-      tma_prefetch_desc(&tmV);
-      auto load_v = [&](int kt) {
-        const int st = kt % VSTAGES;
-        if (p.dbg & 1) {
-          mbar_arrive(&sm.vfull[st]);
-          return;
-        }
-        mbar_arrive_expect_tx(&sm.vfull[st], v_stage_bytes);
-        for (int c = 0; c < nvbox; ++c)
-          tma_load_2d(&sm.v[st][c][0][0], &tmV, &sm.vfull[st], c * 64, b * L + kt * BKV);
-      };
-      for (int kt = 0; kt < min(2, n_tiles); ++kt) load_v(kt);
-      const uint32_t id0 = make_idesc_bf16_bmn(BQ, n_mma0), id1 = make_idesc_bf16_bmn(BQ, max(n_mma1, 16));
+    // ---------------- producer: X tiles by TMA, P.X by tcgen05.mma.  c counts tiles over both value sweeps.
+    auto load_v = [&](int c, int kt) {
+      const int st = c % VSTAGES;
+      if (c >= VSTAGES) mbar_wait(&sm.vfree[st], ((c / VSTAGES) - 1) & 1);  // tile c - VSTAGES consumed
+      if (p.dbg & 1) {
+        mbar_arrive(&sm.vfull[st]);
+        return;
+      }
+      mbar_arrive_expect_tx(&sm.vfull[st], v_stage_bytes);
+      for (int cc = 0; cc < nvbox; ++cc)
+        tma_load_2d(&sm.v[st][cc][0][0], &tmV, &sm.vfull[st], cc * 64, b * L + kt * BKV);
+    };
+    const uint32_t id0 = make_idesc_bf16_bmn(BQ, n_mma0), id1 = make_idesc_bf16_bmn(BQ, max(n_mma1, 16));
+    auto value_sweep = [&](int c0) {
+      for (int kt = 0; kt < min(2, n_tiles); ++kt) load_v(c0 + kt, kt);
       for (int kt = 0; kt < n_tiles; ++kt) {
-        if (kt + 2 < n_tiles) {
-          if (kt >= 1) mbar_wait(&sm.vfree[(kt + 2) % VSTAGES], ((kt - 1) / VSTAGES) & 1);  // tile kt-1 consumed
-          load_v(kt + 2);
-        }
-        const int st = kt % VSTAGES, pb = kt & 1;
-        mbar_wait(&sm.vfull[st], (kt / VSTAGES) & 1);
-        mbar_wait(&sm.pfull[pb], (kt >> 1) & 1);
+        const int c = c0 + kt;
+        if (kt + 2 < n_tiles) load_v(c + 2, kt + 2);
+        const int st = c % VSTAGES, pb = c & 1;
+        mbar_wait(&sm.vfull[st], (c / VSTAGES) & 1);
+        mbar_wait(&sm.pfull[pb], (c >> 1) & 1);
         tc_fence_after();
         const uint64_t da = make_sdesc_sw128(smem_u32(&sm.p[pb][0][0]));
         const uint32_t vaddr = smem_u32(&sm.v[st][0][0][0]);
@@ -226,7 +243,14 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
         umma_commit(&sm.pfree[pb]);
         if (kt == n_tiles - 1) umma_commit(&sm.obar);
       }
+    };
+    if (lane == 0) {
+      tma_prefetch_desc(&tmV);
+      value_sweep(0);
     }
+    __syncwarp();
+    named_bar_sync(2, THREADS);
+    if (sm.redo != 0 && lane == 0) value_sweep(n_tiles);
     __syncwarp();
   } else {
     // ---------------- compute warps
@@ -244,7 +268,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
     uint32_t qa[2][4];
     float s[4][4];
     const float LOG2E = 1.4426950408889634f;
-    float m0 = -INFINITY, m1 = -INFINITY;
+    float m0, m1;
     mbar_wait(&sm.qbar, 0);
     {
       const uint32_t qbase = smem_u32(&sm.q[0][0]);
@@ -257,50 +281,74 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.kempty[st]);
     };
-    // ---- sweep 1: exact row maxima
-    for (int kt = 0; kt < n_tiles; ++kt, ++gt) {
-      const int buf = gt % KSTAGES;
-      mbar_wait(&sm.kfull[buf], (gt / KSTAGES) & 1);
-      float mx0, mx1;
-      if (sflag[kt] != 0) score_tile<true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
-      else score_tile<false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
-      ring_release(buf);
-      m0 = fmaxf(m0, mx0), m1 = fmaxf(m1, mx1);
-    }
-    m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)), m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
-    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)), m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
-    if (qd == 0) sm.red[kh][rl0] = m0, sm.red[kh][rl1] = m1;
-    cbar();
-    m0 = fmaxf(sm.red[0][rl0], sm.red[1][rl0]), m1 = fmaxf(sm.red[0][rl1], sm.red[1][rl1]);
-    cbar();
-    const float ms0 = m0 * LOG2E, ms1 = m1 * LOG2E;
-    // ---- sweep 2: P = exp(S - max) -> shared memory -> tcgen05.mma
+    // maxima of the listed key tiles -> m0 / m1 of this thread's two rows, agreed between the two key halves
+    auto maxima = [&](bool full) {
+      m0 = -INFINITY, m1 = -INFINITY;
+      const int count = full ? n_tiles : (kd != 0 ? 2 : 1);
+      for (int it = 0; it < count; ++it, ++gt) {
+        const int kt = full ? it : (it == 0 ? 0 : kd);
+        const int buf = gt % KSTAGES;
+        mbar_wait(&sm.kfull[buf], (gt / KSTAGES) & 1);
+        float mx0, mx1;
+        if (sflag[kt] != 0) score_tile<true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+        else score_tile<false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+        ring_release(buf);
+        m0 = fmaxf(m0, mx0), m1 = fmaxf(m1, mx1);
+      }
+      m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)), m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+      m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)), m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+      if (qd == 0) sm.red[kh][rl0] = m0, sm.red[kh][rl1] = m1;
+      cbar();
+      m0 = fmaxf(sm.red[0][rl0], sm.red[1][rl0]), m1 = fmaxf(sm.red[0][rl1], sm.red[1][rl1]);
+      cbar();
+    };
+    // P = exp(S - m) of every tile -> shared memory -> tcgen05.mma; c0 = running value-tile counter at entry.
+    // Returns true if some score of this thread exceeded its reference by more than OVF_LOG2.
     float l0 = 0.f, l1 = 0.f;
-    for (int kt = 0; kt < n_tiles; ++kt, ++gt) {
-      const int buf = gt % KSTAGES, pb = kt & 1;
-      mbar_wait(&sm.kfull[buf], (gt / KSTAGES) & 1);
-      float mx0, mx1;
-      if (sflag[kt] != 0) score_tile<true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
-      else score_tile<false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
-      ring_release(buf);
-      if (kt >= 2) {  // the MMAs of tile kt-2 have read p[pb]
-        if (lane == 0) mbar_wait(&sm.pfree[pb], ((kt >> 1) - 1) & 1);
-        __syncwarp();
-      }
-      uint8_t* prow0 = reinterpret_cast<uint8_t*>(&sm.p[pb][rl0][0]);
-      uint8_t* prow1 = reinterpret_cast<uint8_t*>(&sm.p[pb][rl1][0]);
+    auto value_sweep = [&](int c0) -> bool {
+      const float ms0 = m0 * LOG2E, ms1 = m1 * LOG2E;
+      bool ovf = false;
+      l0 = 0.f, l1 = 0.f;
+      for (int kt = 0; kt < n_tiles; ++kt, ++gt) {
+        const int c = c0 + kt;
+        const int buf = gt % KSTAGES, pb = c & 1;
+        mbar_wait(&sm.kfull[buf], (gt / KSTAGES) & 1);
+        float mx0, mx1;
+        if (sflag[kt] != 0) score_tile<true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+        else score_tile<false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+        ring_release(buf);
+        ovf |= (fmaf(mx0, LOG2E, -ms0) > OVF_LOG2) | (fmaf(mx1, LOG2E, -ms1) > OVF_LOG2);
+        if (c >= 2) {  // the MMAs of tile c-2 have read p[pb]
+          if (lane == 0) mbar_wait(&sm.pfree[pb], ((c >> 1) - 1) & 1);
+          __syncwarp();
+        }
+        uint8_t* prow0 = reinterpret_cast<uint8_t*>(&sm.p[pb][rl0][0]);
+        uint8_t* prow1 = reinterpret_cast<uint8_t*>(&sm.p[pb][rl1][0]);
 #pragma unroll
-      for (int n4 = 0; n4 < 4; ++n4) {
-        const float a0 = ex2_approx(fmaf(s[n4][0], LOG2E, -ms0)), a1 = ex2_approx(fmaf(s[n4][1], LOG2E, -ms0));
-        const float b0 = ex2_approx(fmaf(s[n4][2], LOG2E, -ms1)), b1 = ex2_approx(fmaf(s[n4][3], LOG2E, -ms1));
-        l0 += a0 + a1, l1 += b0 + b1;
-        const int chunk = kh * 4 + n4;  // 16-byte chunk = 8 keys
-        *reinterpret_cast<uint32_t*>(prow0 + ((chunk ^ (rl0 & 7)) << 4) + qd * 4) = pack_bf16x2(a0, a1);
-        *reinterpret_cast<uint32_t*>(prow1 + ((chunk ^ (rl1 & 7)) << 4) + qd * 4) = pack_bf16x2(b0, b1);
+        for (int n4 = 0; n4 < 4; ++n4) {
+          const float a0 = ex2_approx(fmaf(s[n4][0], LOG2E, -ms0)), a1 = ex2_approx(fmaf(s[n4][1], LOG2E, -ms0));
+          const float b0 = ex2_approx(fmaf(s[n4][2], LOG2E, -ms1)), b1 = ex2_approx(fmaf(s[n4][3], LOG2E, -ms1));
+          l0 += a0 + a1, l1 += b0 + b1;
+          const int chunk = kh * 4 + n4;  // 16-byte chunk = 8 keys
+          *reinterpret_cast<uint32_t*>(prow0 + ((chunk ^ (rl0 & 7)) << 4) + qd * 4) = pack_bf16x2(a0, a1);
+          *reinterpret_cast<uint32_t*>(prow1 + ((chunk ^ (rl1 & 7)) << 4) + qd * 4) = pack_bf16x2(b0, b1);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.pfull[pb]);  // one arrival per warp
       }
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&sm.pfull[pb]);  // one arrival per warp
+      return ovf;
+    };
+    // ---- reference maxima from key tile 0 (always holds valid keys) and the tile under the diagonal
+    maxima(false);
+    // ---- value sweep against the reference
+    if (value_sweep(0)) sm.redo = 1u;
+    named_bar_sync(2, THREADS);
+    const bool redo = sm.redo != 0;
+    if (redo) {  // exact two-sweep repeat, once the MMAs of the abandoned sweep have drained
+      mbar_wait(&sm.obar, 0);
+      maxima(true);
+      value_sweep(n_tiles);
     }
     l0 += __shfl_xor_sync(0xffffffffu, l0, 1), l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 1), l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
@@ -324,7 +372,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
           gv[it][j4] = __ldg(reinterpret_cast<const uint4*>(p.gate + grow * p.ldg + c0 + j4 * 8));
       }
     }
-    mbar_wait(&sm.obar, 0);
+    mbar_wait(&sm.obar, redo ? 1 : 0);
     tc_fence_after();
     const float inv = 1.0f / (sm.red[0][row] + sm.red[1][row]);
 #pragma unroll

@@ -63,7 +63,8 @@ struct AttnParams {
   int nb, L, H;
   int heads;                 // heads processed: H (SelfAttention) or 1 (NonlinAttention, head 0)
   int dv;                    // value width per head (12 or hidden)
-  int dbg = 0;               // profiling experiments only: bit 0 skip value TMA loads, bit 1 skip the P.X MMAs
+  int dbg = 0;               // profiling experiments only: bit 0 skip value TMA loads, bit 1 skip the P.X MMAs,
+                             // bit 2 force the exact-maxima repeat of the NonlinAttention kernel
 };
 int attention(const AttnParams& p, cudaStream_t s);
 
