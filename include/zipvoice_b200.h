@@ -51,7 +51,12 @@ int zv_finalize_weights(void* handle);
 
 /* options: "gemm_impl" 0 = tcgen05 kernel, CTA pairs (cta_group::2) for large problems (default), 1 = SIMT checker
  * kernel (tests only), 2 = tcgen05 single-CTA tiles only, 3 = tcgen05 CTA pairs only;
- * "attn_impl" 0 = NonlinAttention on the tcgen05 kernel (default), 1 = mma.sync flash kernel (process-wide). */
+ * "attn_impl" 0 = NonlinAttention on the tcgen05 kernel (default), 1 = mma.sync flash kernel, 2 = as 0 with the
+ * exact-maxima repeat of the NonlinAttention kernel forced (tests) (process-wide);
+ * "graph_max_rows" (default 32768; 0 = off): zv_sample calls whose network batch x frames is at or below this
+ * value are launch-bound; from the third call of a (shape, schedule, guidance mode) key on they replay a CUDA
+ * graph of the whole NFE loop captured on an engine-owned stream from engine-owned input copies (results are
+ * bit-identical to the plain loop; the caller's stream waits on the replay). */
 int zv_set_option(void* handle, const char* key, int value);
 
 /* get_time_steps (models/modules/solver.py:256-281), fp32 arithmetic identical to torch

@@ -160,3 +160,34 @@ def test_velocity_vs_oracle_longer():
         ma = float(((v - want) * keep).abs().max())
         print(f"per-NFE velocity t={t}: rel-L2 {r:.3e} max-abs {ma:.3e}")
         assert r < TOL_NFE_STRESS_CFG, f"t={t}: rel-L2 {r:.3e} max-abs {ma:.3e}"
+
+
+@pytest.mark.parametrize("kind,guidance", [("zipvoice", 1.0), ("zipvoice", 0.0), ("distill", 3.0)])
+def test_sample_graph_replay_is_bit_identical(kind, guidance):
+    """zv_sample on launch-bound batches replays a captured CUDA graph from the third call of a key on (first call
+    eager, second capture + launch).  Every call must return exactly what the plain loop returns, also after the
+    inputs change under the same key and after a bigger shape reallocated the workspace."""
+    m, cfg, sd = engine(kind, "small", 1, True)
+    eng = m.engine
+    x0, text, speech, mask = case_inputs(2, 37, 11, seed=10)
+    kw = dict(num_step=4, guidance_scale=guidance, t_shift=0.5)
+    eng.set_option("graph_max_rows", 0)
+    want = eng.sample(x0, text, speech, mask, **kw).clone()
+    xb, tb, sb, mb = case_inputs(2, 37, 11, seed=11)
+    want_b = eng.sample(xb, tb, sb, mb, **kw).clone()
+    eng.set_option("graph_max_rows", 32768)
+    eng.launch_count_reset()
+    for i in range(4):
+        got = eng.sample(x0, text, speech, mask, **kw)
+        assert torch.equal(got, want), f"call {i}"
+    per_call = eng.launch_count() // 4
+    assert per_call > 0 and eng.launch_count() == 4 * per_call  # replays are counted like the eager launches
+    assert torch.equal(eng.sample(xb, tb, sb, mb, **kw), want_b)   # same key, other inputs (staging buffers)
+    x2, t2, s2, m2 = case_inputs(3, 61, 20, seed=12)                # bigger shape: workspace grows, graphs dropped
+    eng.set_option("graph_max_rows", 0)
+    want2 = eng.sample(x2, t2, s2, m2, **kw).clone()
+    eng.set_option("graph_max_rows", 32768)
+    for i in range(3):
+        assert torch.equal(eng.sample(x2, t2, s2, m2, **kw), want2), f"shape 2 call {i}"
+    for i in range(3):
+        assert torch.equal(eng.sample(x0, text, speech, mask, **kw), want), f"shape 1 again, call {i}"

@@ -103,6 +103,12 @@ void zv_destroy(void* handle) {
   if (!e) return;
   cudaDeviceSynchronize();
   e->prof.release();
+  for (auto& g : e->graphs)
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+  for (void* p : e->gallocs) cudaFree(p);
+  if (e->gstream) cudaStreamDestroy(e->gstream);
+  if (e->gev_in) cudaEventDestroy(e->gev_in);
+  if (e->gev_out) cudaEventDestroy(e->gev_out);
   audio_destroy(*e);
   for (void* p : e->weight_allocs) cudaFree(p);
   for (void* p : e->ws_fm.allocs) cudaFree(p);
@@ -140,6 +146,7 @@ int zv_set_option(void* handle, const char* key, int value) {
   if (!e) return 960;
   if (!strcmp(key, "gemm_impl")) e->gemm_impl = value;
   else if (!strcmp(key, "attn_impl")) zv::g_attn_impl = value;  // process-wide
+  else if (!strcmp(key, "graph_max_rows")) e->graph_max_rows = value;
   else {
     e->err = std::string("unknown option ") + key;
     return 962;
@@ -234,6 +241,114 @@ static int check_ready(Engine* e, int variant, int B, int T, const float* guidan
   return 0;
 }
 
+// The NFE loop of zv_sample on x1 in place; the time table and the guidance values are already on the device.
+static int sample_loop(Engine* e, int variant, const std::vector<float>& ts, float* x1, const float* text,
+                       const float* speech, const uint8_t* mask, int B, int T, int num_step, bool all_zero,
+                       int guidance_len, cudaStream_t s) {
+  const float* ts_dev = e->ws_fm.ts_dev;
+  for (int i = 0; i < num_step; ++i)
+    API_TRY(velocity_step(e, variant, ts[i], ts_dev + i, x1, text, speech, mask, B, T, all_zero, guidance_len, nullptr,
+                          x1, ts[i + 1] - ts[i], s));
+  return 0;
+}
+
+// Launch-bound batches (a single utterance is ~350 launches of a few microseconds per NFE): the loop is
+// captured once per (shape, schedule, guidance mode) as a CUDA graph working on engine-owned staging buffers
+// and replayed on later calls.  First call of a key: eager (fills the lazily built position tables, tensor-map
+// cache and function attributes); second call: capture + launch; afterwards: launch.  The graph holds workspace
+// addresses, so every graph is dropped when the workspace or the staging buffers are reallocated.
+static int sample_graphed(Engine* e, int variant, const float* x0, const float* text, const float* speech,
+                          const uint8_t* mask, int B, int T, int num_step, bool all_zero, int guidance_len,
+                          double t_start, double t_end, double t_shift, const std::vector<float>& ts, float* x1,
+                          cudaStream_t s) {
+  const int Ft = e->cfg.feat_dim, F = e->cfg.stereo ? 2 * Ft : Ft;
+  const size_t bt = (size_t)B * T;
+  if (!e->gstream) {
+    API_TRY((int)cudaStreamCreateWithFlags(&e->gstream, cudaStreamNonBlocking));
+    API_TRY((int)cudaEventCreateWithFlags(&e->gev_in, cudaEventDisableTiming));
+    API_TRY((int)cudaEventCreateWithFlags(&e->gev_out, cudaEventDisableTiming));
+  }
+  auto drop_graphs = [&] {
+    for (auto& g : e->graphs)
+      if (g.exec) cudaGraphExecDestroy(g.exec);
+    e->graphs.clear();
+  };
+  if (bt > e->g_cap) {
+    cudaDeviceSynchronize();
+    drop_graphs();
+    for (void* p : e->gallocs) cudaFree(p);
+    e->gallocs.clear();
+    API_TRY(dev_alloc(*e, e->gallocs, (void**)&e->gx, bt * F * 4));
+    API_TRY(dev_alloc(*e, e->gallocs, (void**)&e->gtext, bt * Ft * 4));
+    API_TRY(dev_alloc(*e, e->gallocs, (void**)&e->gspeech, bt * F * 4));
+    API_TRY(dev_alloc(*e, e->gallocs, (void**)&e->gmask, bt));
+    e->g_cap = bt;
+  }
+  if (e->graphs_ws_gen != e->ws_fm.gen) {
+    drop_graphs();
+    e->graphs_ws_gen = e->ws_fm.gen;
+  }
+  cudaStream_t gs = e->gstream;
+  API_TRY((int)cudaEventRecord(e->gev_in, s));
+  API_TRY((int)cudaStreamWaitEvent(gs, e->gev_in, 0));
+  API_TRY((int)cudaMemcpyAsync(e->gx, x0, bt * F * 4, cudaMemcpyDeviceToDevice, gs));
+  API_TRY((int)cudaMemcpyAsync(e->gtext, text, bt * Ft * 4, cudaMemcpyDeviceToDevice, gs));
+  API_TRY((int)cudaMemcpyAsync(e->gspeech, speech, bt * F * 4, cudaMemcpyDeviceToDevice, gs));
+  if (mask) API_TRY((int)cudaMemcpyAsync(e->gmask, mask, bt, cudaMemcpyDeviceToDevice, gs));
+  const uint8_t* gm = mask ? e->gmask : nullptr;
+
+  auto bits = [](double d) {
+    unsigned long long u;
+    memcpy(&u, &d, 8);
+    return u;
+  };
+  const std::vector<unsigned long long> key = {(unsigned long long)variant, (unsigned long long)B, (unsigned long long)T,
+                                               (unsigned long long)num_step, (unsigned long long)all_zero,
+                                               (unsigned long long)guidance_len, bits(t_start), bits(t_end), bits(t_shift),
+                                               (unsigned long long)(mask != nullptr), (unsigned long long)e->gemm_impl,
+                                               (unsigned long long)zv::g_attn_impl};
+  Engine::SampleGraph* g = nullptr;
+  for (auto& c : e->graphs)
+    if (c.key == key) g = &c;
+  int rc = 0;
+  if (!g) {  // first sighting: eager
+    Engine::SampleGraph c;
+    c.key = key;
+    e->graphs.push_back(c);
+    rc = sample_loop(e, variant, ts, e->gx, e->gtext, e->gspeech, gm, B, T, num_step, all_zero, guidance_len, gs);
+  } else if (g->unsupported) {
+    rc = sample_loop(e, variant, ts, e->gx, e->gtext, e->gspeech, gm, B, T, num_step, all_zero, guidance_len, gs);
+  } else {
+    if (!g->exec) {
+      const long long l0 = g_launch_count;
+      cudaGraph_t graph = nullptr;
+      cudaError_t ce = cudaStreamBeginCapture(gs, cudaStreamCaptureModeThreadLocal);
+      if (ce == cudaSuccess) {
+        rc = sample_loop(e, variant, ts, e->gx, e->gtext, e->gspeech, gm, B, T, num_step, all_zero, guidance_len, gs);
+        ce = cudaStreamEndCapture(gs, &graph);
+      }
+      g->launches = g_launch_count - l0;
+      g_launch_count = l0;  // captured, not executed
+      if (rc == 0 && ce == cudaSuccess && graph) ce = cudaGraphInstantiate(&g->exec, graph, 0);
+      if (graph) cudaGraphDestroy(graph);
+      if (rc != 0 || ce != cudaSuccess || !g->exec) {  // not capturable here: remember and run the plain loop
+        cudaGetLastError();
+        g->exec = nullptr, g->unsupported = true;
+        rc = sample_loop(e, variant, ts, e->gx, e->gtext, e->gspeech, gm, B, T, num_step, all_zero, guidance_len, gs);
+      }
+    }
+    if (g->exec) {
+      API_TRY((int)cudaGraphLaunch(g->exec, gs));
+      g_launch_count += g->launches;
+    }
+  }
+  if (rc) return rc;
+  API_TRY((int)cudaMemcpyAsync(x1, e->gx, bt * F * 4, cudaMemcpyDeviceToDevice, gs));
+  API_TRY((int)cudaEventRecord(e->gev_out, gs));
+  API_TRY((int)cudaStreamWaitEvent(s, e->gev_out, 0));
+  return 0;
+}
+
 extern "C" int zv_velocity(void* handle, int variant, float t, const float* x, const float* text,
                            const float* speech, const uint8_t* mask, int B, int T, const float* guidance,
                            int guidance_len, float* v_out, void* stream) {
@@ -272,11 +387,12 @@ extern "C" int zv_sample(void* handle, int variant, const float* x0, const float
   API_TRY(upload_small(e, ts_dev, ts.data(), (int)ts.size(), s));
   API_TRY(upload_small(e, e->ws_fm.guid_dev, guidance, guidance_len, s));
   const size_t n = (size_t)B * T * e->cfg.feat_dim * (e->cfg.stereo ? 2 : 1);
+  const bool cfg2 = (variant == 0) && !all_zero;
+  if (e->graph_max_rows > 0 && !e->prof.on && (size_t)(cfg2 ? 2 : 1) * B * T <= (size_t)e->graph_max_rows)
+    return sample_graphed(e, variant, x0, text, speech, mask, B, T, num_step, all_zero, guidance_len, t_start, t_end,
+                          t_shift, ts, x1, s);
   if (x1 != x0) API_TRY((int)cudaMemcpyAsync(x1, x0, n * 4, cudaMemcpyDeviceToDevice, s));
-  for (int i = 0; i < num_step; ++i)
-    API_TRY(velocity_step(e, variant, ts[i], ts_dev + i, x1, text, speech, mask, B, T, all_zero, guidance_len, nullptr,
-                          x1, ts[i + 1] - ts[i], s));
-  return 0;
+  return sample_loop(e, variant, ts, x1, text, speech, mask, B, T, num_step, all_zero, guidance_len, s);
 }
 
 extern "C" int zv_text_embed(void* handle, const int64_t* tokens_padded, const int64_t* tokens_lens, int B, int S,

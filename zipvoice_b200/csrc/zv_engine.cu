@@ -407,6 +407,7 @@ int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
   for (void* p : ws.allocs) cudaFree(p);
   ws.allocs.clear();
   ws.cap_rows = rows, ws.cap_nb = nb, ws.D = net.D;
+  ++ws.gen;
   const size_t D = net.D;
   const size_t Fmax = (size_t)net.F * 5 / 4;
   const size_t td = e.cfg.time_embed_dim;

@@ -62,6 +62,7 @@ struct Net {
 
 struct Workspace {
   size_t cap_rows = 0;  // nb * T capacity
+  unsigned long long gen = 0;  // bumped whenever the buffers are reallocated (captured graphs hold their addresses)
   int cap_nb = 0;
   int D = 0;
   float *X = nullptr, *Xs = nullptr, *Y = nullptr, *vel = nullptr, *xcur = nullptr;
@@ -108,6 +109,24 @@ struct Engine {
   std::vector<void*> weight_allocs;
   std::string err;
   int gemm_impl = 0;
+  // CUDA-graph replay of whole zv_sample calls for launch-bound batches (zv_api.cu): the NFE loop of a
+  // (shape, schedule, guidance mode) key is captured once on `gstream` from engine-owned staging buffers
+  // and replayed afterwards.  graph_max_rows: nb * T at or below which the graph path is taken (0 = off).
+  struct SampleGraph {
+    std::vector<unsigned long long> key;
+    cudaGraphExec_t exec = nullptr;  // null: key seen once (ran eagerly), capture on the next call
+    long long launches = 0;          // kernels inside the graph (added to the launch counter per replay)
+    bool unsupported = false;        // capture failed once: stay on the eager path
+  };
+  int graph_max_rows = 32768;
+  std::vector<SampleGraph> graphs;
+  unsigned long long graphs_ws_gen = 0;
+  cudaStream_t gstream = nullptr;
+  cudaEvent_t gev_in = nullptr, gev_out = nullptr;
+  std::vector<void*> gallocs;
+  size_t g_cap = 0;  // staging capacity in B * T elements
+  float *gx = nullptr, *gtext = nullptr, *gspeech = nullptr;
+  uint8_t* gmask = nullptr;
   // audio front-end / vocoder state lives in zv_audio.cu
   void* audio = nullptr;
 };
