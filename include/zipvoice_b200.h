@@ -95,6 +95,13 @@ int zv_text_condition(void* handle, const float* embed, const int64_t* tokens_le
  * lens (B) int64 valid samples -> log-mel (B, T, 100), T = (N + 128) / 256 frames. */
 int zv_fbank(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out, void* stream);
 
+/* torchaudio.transforms.Resample(orig_freq, new_freq) as the reference applies it to the prompt recording
+ * (bin/infer_zipvoice.py:334-339; torchaudio defaults: sinc_interp_hann, lowpass_filter_width 6, rolloff 0.99):
+ * wav (B,N) fp32, lens (B) int64 valid samples per row or NULL -> out (B, n_out) with
+ * n_out = ceil(new_freq * N / orig_freq); row b is 0 from sample ceil(new_freq * lens[b] / orig_freq) on. */
+int zv_resample(void* handle, const float* wav, const int64_t* lens, int B, int N, int orig_freq, int new_freq,
+                float* out, int n_out, void* stream);
+
 /* Vocos.decode (third-party `vocos`; call site bin/infer_zipvoice.py:378): mel (B,100,T) -> wav (B, 256*(T-1)).
  * Weights are set through zv_set_weight with the "vocoder." prefix (vocos checkpoint names: backbone.*,
  * head.out.*).  lens (B) int64 valid frames per row, or NULL for full rows: frames >= lens[b] are treated

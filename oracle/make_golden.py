@@ -4,6 +4,7 @@ zipvoice_b200.synth.  Run:  python -m oracle.make_golden
 The fixtures pin the oracle restatement (tests/test_oracle_golden.py) and are the
 known-answer vectors for the CUDA path (tests/test_gpu_parity.py).
 """
+import math
 import os
 import sys
 
@@ -57,6 +58,25 @@ def stereo():
 
 
 @torch.inference_mode()
+def resample():
+    """torchaudio.transforms.Resample as the reference applies it to prompts (bin/infer_zipvoice.py:334-339), run
+    with the torchaudio of this image on seeded noise + a chirp.  python -m oracle.make_golden resample"""
+    import torchaudio
+    g = torch.Generator().manual_seed(2024)
+    out = {}
+    for sr in (16000, 22050, 44100, 48000):
+        n = sr // 4 + 37
+        t = torch.arange(n) / sr
+        x = torch.stack([torch.randn(n, generator=g) * 0.2,
+                         0.5 * torch.sin(2 * math.pi * (200.0 + 3000.0 * t) * t)]).float()
+        y = torchaudio.transforms.Resample(orig_freq=sr, new_freq=24000)(x)
+        out[f"x_{sr}"] = x.numpy()
+        out[f"y_{sr}"] = y.numpy()
+    out["torchaudio_version"] = np.array(torchaudio.__version__)
+    np.savez_compressed(os.path.join(OUT, "resample.npz"), **out)
+    print("wrote resample.npz", {k: v.shape for k, v in out.items()})
+
+
 def main():
     from zipvoice_b200 import synth
     os.makedirs(OUT, exist_ok=True)
@@ -123,4 +143,9 @@ def main():
 
 
 if __name__ == "__main__":
-    stereo() if "stereo" in sys.argv[1:] else main()
+    if "stereo" in sys.argv[1:]:
+        stereo()
+    elif "resample" in sys.argv[1:]:
+        resample()
+    else:
+        main()

@@ -100,3 +100,52 @@ def test_fbank_vocoder_roundtrip_shapes():
     assert wav.shape == (8, 256 * 399) and bool(torch.isfinite(wav).all())
     mel2 = fb.extract_batch(wav)
     assert mel2.shape == (8, 399, 100) and bool(torch.isfinite(mel2).all())
+
+
+@pytest.mark.parametrize("sr", [16000, 22050, 44100, 48000])
+def test_resample_torchaudio_golden(sr):
+    """zv_resample against torchaudio.transforms.Resample(sr, 24000) outputs (tests/golden/resample.npz):
+    same fp32 filter bank (computed in double), fp32 FMA dot products; 2e-5 absolute on |x| <= 1 signals."""
+    from zipvoice_b200.audio import ResampleB200
+    fb, voc, _ = audio()
+    g = np.load(os.path.join(GOLDEN, "resample.npz"))
+    x, want = torch.from_numpy(g[f"x_{sr}"]), torch.from_numpy(g[f"y_{sr}"])
+    got = ResampleB200(sr, 24000, engine=fb.engine)(x).cpu()
+    assert got.shape == want.shape
+    assert float((got - want).abs().max()) < 2e-5
+
+
+def test_resample_ragged_rows_equal_single_rows():
+    """Rows of a padded batch with per-row lengths are resampled as if each had been handed over alone."""
+    from oracle import resample_oracle as R
+    from zipvoice_b200.audio import ResampleB200
+    fb, voc, _ = audio()
+    g = torch.Generator().manual_seed(5)
+    lens = torch.tensor([7000, 4411, 1, 6999])
+    x = torch.randn(4, 7000, generator=g) * 0.3
+    rs = ResampleB200(44100, 24000, engine=fb.engine)
+    got = rs(x, lens).cpu()
+    for b in range(4):
+        n = int(lens[b])
+        want = torch.from_numpy(R.resample(x[b, :n].numpy(), 44100, 24000))
+        assert float((got[b, : want.numel()] - want).abs().max()) < 2e-5
+        assert float(got[b, want.numel():].abs().max() if want.numel() < got.shape[1] else 0.0) == 0.0
+    same = ResampleB200(24000, 24000, engine=fb.engine)(x)
+    assert same is x
+
+
+def test_compute_fbank_bulk_equals_single_extraction(tmp_path):
+    """Bulk extraction (bin/compute_fbank.py on the mel kernel): bucketed padded batches return exactly the
+    per-recording features, in input order, and the npz holds the same arrays."""
+    from zipvoice_b200.audio import compute_fbank
+    fb, voc, _ = audio()
+    g = torch.Generator().manual_seed(6)
+    wavs = [torch.randn(n, generator=g) * 0.2 for n in (24000, 5000, 48017, 700, 24001, 12345)]
+    path = os.path.join(tmp_path, "feats.npz")
+    feats = compute_fbank(wavs, extractor=fb, max_batch_samples=60000, out_path=path)
+    z = np.load(path)
+    for i, w in enumerate(wavs):
+        want = fb.extract(w, 24000).cpu().numpy()
+        assert feats[i].shape == want.shape == ((w.numel() + 128) // 256, 100)
+        assert float(np.abs(feats[i] - want).max()) < 1e-5
+        assert np.array_equal(z[f"feat_{i}"], feats[i])

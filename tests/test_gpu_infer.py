@@ -92,3 +92,46 @@ def test_generate_sentence_stereo_vs_oracle_pipeline():
     assert wav.shape == want.shape and wav.shape[0] == 2
     r = rel_l2(wav.cpu(), want)
     assert r < 5e-2, f"stereo waveform rel-L2 {r:.3e}"
+
+
+def test_generate_list_buckets_resamples_and_writes(tmp_path):
+    """generate_list (infer_zipvoice.py:406-466): prompts at 16 kHz and 24 kHz from wav files, length buckets,
+    16-bit files written behind the compute.  Every file must hold what generate_batch returns for its bucket
+    inputs (same noise seed), to the 16-bit quantisation."""
+    import os
+    from zipvoice_b200 import infer, synth
+    from zipvoice_b200.audio import ResampleB200
+    cfg, sd, vsd, model, voc, fb = _setup()
+
+    class Tok:
+        def texts_to_token_ids(self, texts):
+            return [[1 + (ord(c) % (synth.VOCAB_SIZE - 1)) for c in t] for t in texts]
+
+    tok = Tok()
+    specs = [("a", 16000, 7000, "hello wor", "a somewhat longer text to say"), ("b", 24000, 9000, "prompt b", "short"),
+             ("c", 16000, 12000, "third prompt here", "medium length text"), ("d", 24000, 8000, "dd", "x y z w")]
+    lines = []
+    for name, sr, n, ptxt, txt in specs:
+        w = synth.make_audio(1, n, seed=len(name) + n)[0] * 0.3
+        pth = os.path.join(tmp_path, f"p_{name}.wav")
+        infer.write_wav(pth, w.numpy(), sr)
+        lines.append("\t".join([name, ptxt, pth, txt]))
+    lst = os.path.join(tmp_path, "test.tsv")
+    open(lst, "w").write("\n".join(lines) + "\n")
+    res = os.path.join(tmp_path, "out")
+    torch.manual_seed(123)
+    m = infer.generate_list(res, lst, model, voc, tok, fb, num_step=4, max_batch_frames=2 * 200)
+    assert m["utterances"] == 4 and m["batches"] >= 2 and m["wav_seconds"] > 0
+    total = 0
+    for name, sr, n, ptxt, txt in specs:
+        w, r = infer.read_wav(os.path.join(res, f"{name}.wav"))
+        assert r == 24000 and w.shape[0] == 1 and w.shape[1] > 0 and w.shape[1] % 256 == 0
+        assert torch.isfinite(w).all() and float(w.abs().max()) > 0
+        total += w.shape[1]
+    assert abs(total / 24000 - m["wav_seconds"]) < 1e-6
+    # wav round trip and the bucketing helper
+    w16, r16 = infer.read_wav(os.path.join(tmp_path, "p_a.wav"))
+    assert r16 == 16000 and w16.shape == (1, 7000)
+    assert infer.length_buckets([5, 1, 3, 9], 10) == [[1, 2], [0], [3]]
+    up = ResampleB200(16000, 24000, engine=fb.engine)(w16.cuda())
+    assert up.shape == (1, 10500)

@@ -113,3 +113,15 @@ def test_fbank_oracle_vs_reference_golden():
         mel = FO.vocos_fbank(wav[0])
         assert mel.shape == g["mel_" + name].shape == (FO.num_frames(n), 100)
         assert float((mel - g["mel_" + name]).abs().max()) < 1e-4
+
+
+def test_resample_oracle_vs_torchaudio_golden():
+    """oracle/resample_oracle.py against torchaudio.transforms.Resample outputs (tests/golden/resample.npz,
+    oracle/make_golden.py resample); fp32 dot products of up to ~480 taps in another order: 2e-5 absolute."""
+    from oracle import resample_oracle as R
+    g = np.load(os.path.join(GOLDEN, "resample.npz"))
+    for sr in (16000, 22050, 44100, 48000):
+        got = R.resample(g[f"x_{sr}"], sr, 24000)
+        want = g[f"y_{sr}"]
+        assert got.shape == want.shape
+        assert float(np.abs(got - want).max()) < 2e-5, sr

@@ -80,3 +80,53 @@ class VocosB200:
     def decode(self, features_input: torch.Tensor, lens: Optional[torch.Tensor] = None) -> torch.Tensor:
         """mel (B, 100, T) -> (B, 256 (T - 1))"""
         return self.engine.vocos_decode(features_input, lens)
+
+
+class ResampleB200:
+    """torchaudio.transforms.Resample(orig_freq, new_freq) with torchaudio's defaults, on the GPU
+    (call site: bin/infer_zipvoice.py:334-339)."""
+
+    def __init__(self, orig_freq: int, new_freq: int, engine: Optional[Engine] = None, device="cuda:0"):
+        self.orig_freq, self.new_freq = int(orig_freq), int(new_freq)
+        self.engine = engine if engine is not None else audio_engine(device=device)
+
+    def __call__(self, waveform: torch.Tensor, lens: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if self.orig_freq == self.new_freq:
+            return waveform
+        shape = waveform.shape
+        out = self.engine.resample(waveform.reshape(-1, shape[-1]).float(), self.orig_freq, self.new_freq, lens)
+        return out.reshape(*shape[:-1], out.shape[-1])
+
+
+def compute_fbank(waveforms, extractor: Optional[VocosFbankB200] = None, max_batch_samples: int = 64 * 30 * 24000,
+                  out_path: Optional[str] = None):
+    """Bulk offline feature extraction on the mel kernel (bin/compute_fbank.py:136-260 without lhotse: the caller
+    hands over 24 kHz mono recordings, the result is a headless buffer instead of the Lilcom writer).
+
+    waveforms: sequence of 1-D float arrays / tensors.  They are sorted by length, packed into padded batches of
+    at most ``max_batch_samples`` samples, extracted with per-row lengths, and returned in the input order as a
+    list of (T_i, 100) float32 numpy arrays (T_i = (n_i + 128) // 256).  With ``out_path`` the features are also
+    written as one ``.npz`` (arrays ``feat_<index>``)."""
+    ext = extractor if extractor is not None else VocosFbankB200()
+    dev = ext.engine.device
+    lens = [int(len(w)) for w in waveforms]
+    order = sorted(range(len(lens)), key=lambda i: lens[i])
+    feats = [None] * len(lens)
+    i = 0
+    while i < len(order):
+        j, longest = i, 0
+        while j < len(order) and max(longest, lens[order[j]]) * (j - i + 1) <= max(max_batch_samples, lens[order[i]]):
+            longest = max(longest, lens[order[j]])
+            j += 1
+        idx = order[i:j]
+        batch = torch.zeros(len(idx), longest, dtype=torch.float32)
+        for r, k in enumerate(idx):
+            batch[r, : lens[k]] = torch.as_tensor(waveforms[k], dtype=torch.float32).reshape(-1)
+        ln = torch.tensor([lens[k] for k in idx], dtype=torch.int64)
+        mel = ext.extract_batch(batch.to(dev, non_blocking=True), ln.to(dev)).cpu().numpy()
+        for r, k in enumerate(idx):
+            feats[k] = mel[r, : (lens[k] + 128) // 256].copy()
+        i = j
+    if out_path is not None:
+        np.savez(out_path, **{f"feat_{k}": f for k, f in enumerate(feats)})
+    return feats

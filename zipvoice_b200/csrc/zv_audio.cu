@@ -42,6 +42,12 @@ struct Audio {
   float *x = nullptr, *emb = nullptr, *spec = nullptr, *frames = nullptr;
   int* lens_dev = nullptr;
   std::vector<void*> ws_allocs;
+  // resampler filter banks by reduced (orig, new) ratio
+  struct ResampleBank {
+    int orig = 0, nw = 0, width = 0, K = 0;
+    float* w = nullptr;  // [new][K]
+  };
+  std::vector<ResampleBank> banks;
 };
 
 static int audio_tables(Engine& e, Audio& a) {
@@ -507,6 +513,74 @@ static int vocoder_reserve(Engine& e, Audio& a, int B, int T) {
 
 }  // namespace zv
 
+namespace zv {
+
+// torchaudio sinc_interp_hann resampling (_apply_sinc_resample_kernel): the waveform is zero-padded by `width` on
+// the left, and output sample k * new + p is the dot product of phase filter p with K input samples starting at
+// k * orig - width.  One thread per output sample; the filter bank ([new][K] fp32, a few KB) stays in L1.
+__global__ void resample_kernel(const float* __restrict__ wav, const int64_t* __restrict__ lens, int N,
+                                const float* __restrict__ bank, int orig, int nw, int width, int K, int n_out,
+                                float* __restrict__ out) {
+  const int b = blockIdx.y;
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= n_out) return;
+  const int64_t len = lens ? min((int64_t)N, lens[b]) : (int64_t)N;
+  const int64_t valid_out = (len * nw + orig - 1) / orig;  // ceil(new * len / orig)
+  float acc = 0.f;
+  if (n < valid_out) {
+    const int p = n % nw, k = n / nw;
+    const float* w = bank + (size_t)p * K;
+    const float* x = wav + (size_t)b * N;
+    const int64_t base = (int64_t)k * orig - width;
+    const int j0 = base < 0 ? (int)-base : 0;
+    const int j1 = (int)min((int64_t)K, len - base);
+    for (int j = j0; j < j1; ++j) acc = fmaf(__ldg(w + j), __ldg(x + base + j), acc);
+  }
+  out[(size_t)b * n_out + n] = acc;
+}
+
+// _get_sinc_resample_kernel(orig, new, gcd, lowpass_filter_width=6, rolloff=0.99, "sinc_interp_hann") in double,
+// stored as fp32 like torchaudio does.
+static int resample_bank(Engine& e, Audio& a, int orig_freq, int new_freq, const Audio::ResampleBank** out) {
+  int g = orig_freq, h = new_freq;
+  while (h) {
+    const int t = g % h;
+    g = h, h = t;
+  }
+  const int orig = orig_freq / g, nw = new_freq / g;
+  for (const auto& bk : a.banks)
+    if (bk.orig == orig && bk.nw == nw) {
+      *out = &bk;
+      return 0;
+    }
+  const double lpw = 6.0, rolloff = 0.99;
+  const double base_freq = (double)(orig < nw ? orig : nw) * rolloff;
+  Audio::ResampleBank bk;
+  bk.orig = orig, bk.nw = nw;
+  bk.width = (int)ceil(lpw * orig / base_freq);
+  bk.K = 2 * bk.width + orig;
+  std::vector<float> w((size_t)nw * bk.K);
+  const double scale = base_freq / orig;
+  for (int p = 0; p < nw; ++p)
+    for (int j = 0; j < bk.K; ++j) {
+      const double idx = (double)(j - bk.width) / orig;
+      double t = ((double)(-p) / nw + idx) * base_freq;
+      t = t < -lpw ? -lpw : (t > lpw ? lpw : t);
+      const double c = cos(t * M_PI / lpw / 2.0);
+      const double window = c * c;
+      t *= M_PI;
+      const double sinc = t == 0.0 ? 1.0 : sin(t) / t;
+      w[(size_t)p * bk.K + j] = (float)(sinc * (window * scale));
+    }
+  AU_TRY(dev_alloc(e, e.weight_allocs, (void**)&bk.w, w.size() * 4));
+  AU_TRY((int)cudaMemcpy(bk.w, w.data(), w.size() * 4, cudaMemcpyHostToDevice));
+  a.banks.push_back(bk);
+  *out = &a.banks.back();
+  return 0;
+}
+
+}  // namespace zv
+
 using namespace zv;
 
 extern "C" int zv_fbank(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out,
@@ -594,5 +668,30 @@ extern "C" int zv_vocos_decode(void* handle, const float* mel, const int64_t* le
   dim3 ogrid((n_out + 255) / 256, B);
   AU_K(KC_VOCODER_ELEM, (double)B * T * N_FFT * 4.0 + (double)B * n_out * 4.0, s,
        (vc_ola_kernel<<<ogrid, 256, 0, s>>>(a.frames, a.lens_dev, T, Tp, a.tw1024, n_out, wav_out)));
+  return 0;
+}
+
+extern "C" int zv_resample(void* handle, const float* wav, const int64_t* lens, int B, int N, int orig_freq,
+                           int new_freq, float* out, int n_out, void* stream) {
+  Engine* ep = (Engine*)handle;
+  if (!ep) return 960;
+  Engine& e = *ep;
+  e.err.clear();
+  if (B <= 0 || N <= 0 || orig_freq <= 0 || new_freq <= 0) {
+    e.err = "zv_resample: need B, N, orig_freq, new_freq > 0";
+    return 964;
+  }
+  const long long want = ((long long)N * new_freq + orig_freq - 1) / orig_freq;
+  if (n_out != want) {
+    e.err = "zv_resample: n_out must be ceil(new_freq * N / orig_freq)";
+    return 964;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  Audio& a = audio_of(e);
+  const Audio::ResampleBank* bk = nullptr;
+  AU_TRY(resample_bank(e, a, orig_freq, new_freq, &bk));
+  dim3 grid((n_out + 255) / 256, B);
+  AU_K(KC_FBANK, (double)B * N * 4.0 + (double)B * n_out * 4.0, s,
+       (resample_kernel<<<grid, 256, 0, s>>>(wav, lens, N, bk->w, bk->orig, bk->nw, bk->width, bk->K, n_out, out)));
   return 0;
 }

@@ -175,6 +175,20 @@ class Engine:
             self._check(self.lib.zv_fbank(self._h, _ptr(w), _ptr(ln), B, N, _ptr(out), _stream(self.device)))
         return out
 
+    def resample(self, wav: torch.Tensor, orig_freq: int, new_freq: int,
+                 lens: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """torchaudio.transforms.Resample(orig_freq, new_freq) (bin/infer_zipvoice.py:334-339): (B, N) -> (B, n_out),
+        n_out = ceil(new_freq * N / orig_freq); with ``lens`` every row is resampled as if it ended at lens[b]."""
+        w = self._prep(wav)
+        B, N = w.shape
+        ln = None if lens is None else self._prep(lens, torch.int64)
+        n_out = (N * new_freq + orig_freq - 1) // orig_freq
+        out = torch.empty(B, n_out, device=self.device, dtype=torch.float32)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.zv_resample(self._h, _ptr(w), _ptr(ln), B, N, int(orig_freq), int(new_freq),
+                                             _ptr(out), n_out, _stream(self.device)))
+        return out
+
     def vocos_decode(self, mel: torch.Tensor, lens: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Vocos.decode: mel (B, 100, T) -> waveform (B, 256 (T - 1)); needs "vocoder.*" weights."""
         m = self._prep(mel)

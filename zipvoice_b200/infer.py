@@ -6,11 +6,18 @@
 * ``generate_batch``     -- what the reference lacks: a whole list of utterances as ONE padded batch
   (GPU mel extraction of all prompts, one ``sample()``, one batched vocoder call), optionally sharded
   data-parallel over the ranks of torchrun and gathered to rank 0.
+* ``generate_list``      -- :406-466 on top of ``generate_batch``: the tab-separated test list is sorted into
+  length buckets, every bucket is one padded batch, prompts are resampled / normalised / mel-extracted on the
+  GPU, and the 16-bit wav files are written by a background thread while the next bucket runs.
 Everything numerical runs in the CUDA library; this file only moves tensors.
 """
+import os
 import time
-from typing import Dict, List, Optional, Sequence
+import wave
+from concurrent.futures import ThreadPoolExecutor
+from typing import Callable, Dict, List, Optional, Sequence
 
+import numpy as np
 import torch
 
 from . import parallel
@@ -137,3 +144,118 @@ def generate_batch(prompt_tokens: Sequence[List[int]], prompt_wavs: Sequence[tor
     if rank != 0:
         return None
     return parallel.scatter_back(parts, shards, n)
+
+
+def read_wav(path: str):
+    """PCM wav file -> ((channels, samples) float32 in [-1, 1), sampling rate); 16- and 32-bit integer samples.
+    Stand-in for torchaudio.load (infer_zipvoice.py:332) on machines without an audio backend."""
+    with wave.open(path, "rb") as f:
+        sr, ch, width, n = f.getframerate(), f.getnchannels(), f.getsampwidth(), f.getnframes()
+        raw = f.readframes(n)
+    if width == 2:
+        x = np.frombuffer(raw, dtype="<i2").astype(np.float32) / 32768.0
+    elif width == 4:
+        x = np.frombuffer(raw, dtype="<i4").astype(np.float32) / 2147483648.0
+    else:
+        raise ValueError(f"{path}: unsupported sample width {width}")
+    return torch.from_numpy(x.reshape(-1, ch).T.copy()), sr
+
+
+def write_wav(path: str, wav: np.ndarray, sampling_rate: int):
+    """mono float waveform in [-1, 1] -> 16-bit PCM (what torchaudio.save writes for the reference, :401)."""
+    pcm = np.clip(np.round(np.asarray(wav, dtype=np.float32).reshape(-1) * 32768.0), -32768, 32767).astype("<i2")
+    with wave.open(path, "wb") as f:
+        f.setnchannels(1)
+        f.setsampwidth(2)
+        f.setframerate(int(sampling_rate))
+        f.writeframes(pcm.tobytes())
+
+
+def length_buckets(cost: Sequence[int], max_batch_cost: int) -> List[List[int]]:
+    """Indices sorted by cost and cut into batches whose padded size (longest x count) stays within the budget."""
+    order = sorted(range(len(cost)), key=lambda i: cost[i])
+    out, cur = [], []
+    for i in order:
+        if cur and cost[i] * (len(cur) + 1) > max_batch_cost:   # ascending order: cost[i] is the batch's longest
+            out.append(cur)
+            cur = []
+        cur.append(i)
+    if cur:
+        out.append(cur)
+    return out
+
+
+@torch.inference_mode()
+def generate_list(res_dir: str, test_list: str, model, vocoder, tokenizer, feature_extractor, num_step: int = 16,
+                  guidance_scale: float = 1.0, speed: float = 1.0, t_shift: float = 0.5, target_rms: float = 0.1,
+                  feat_scale: float = 0.1, feat_bias: float = 0.0, sampling_rate: int = 24000,
+                  max_batch_frames: int = 64 * 1300, distributed: bool = False,
+                  load_wav: Callable = read_wav) -> Dict[str, float]:
+    """infer_zipvoice.py:406-466.  ``test_list`` lines: wav_name <tab> prompt_text <tab> prompt_wav <tab> text;
+    ``tokenizer`` needs ``texts_to_token_ids`` like the reference's tokenizers.  Writes ``res_dir/<wav_name>.wav``.
+
+    Differences from the reference loop, none of them numerical: utterances run as padded batches of similar
+    length (``max_batch_frames`` bounds batch x frames), prompts of one sampling rate are resampled together on
+    the GPU, multi-channel prompts are down-mixed before the RMS normalisation, and files are written behind the
+    compute.  With ``distributed`` the list is split over the torchrun ranks by estimated cost and every rank
+    writes its own files (no collective on the data path).  Returns the totals the reference logs."""
+    from .audio import ResampleB200
+    dev = model.device
+    with open(test_list, "r") as fr:
+        items = [ln.rstrip("\n").split("\t") for ln in fr if ln.strip()]
+    for it in items:
+        if len(it) != 4:
+            raise ValueError(f"malformed test-list line (need 4 tab-separated fields): {it}")
+    os.makedirs(res_dir, exist_ok=True)
+    rank, world = 0, 1
+    if distributed and torch.distributed.is_initialized():
+        rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
+    tokens = tokenizer.texts_to_token_ids([it[3] for it in items])
+    prompt_tokens = tokenizer.texts_to_token_ids([it[1] for it in items])
+    # rank split on a cost known before any audio is read: characters to synthesise
+    text_cost = [len(t) + len(p) for t, p in zip(tokens, prompt_tokens)]
+    mine = parallel.shard_indices(text_cost, world, rank)
+    # ---- prompts: load, down-mix, resample per source rate as one padded GPU batch
+    loaded = {i: load_wav(items[i][2]) for i in mine}
+    prompts: Dict[int, torch.Tensor] = {}
+    by_rate: Dict[int, List[int]] = {}
+    for i, (w, sr) in loaded.items():
+        by_rate.setdefault(int(sr), []).append(i)
+    for sr, idx in by_rate.items():
+        mono = [loaded[i][0].float().mean(dim=0) if loaded[i][0].dim() == 2 else loaded[i][0].float() for i in idx]
+        if sr == sampling_rate:
+            for i, w in zip(idx, mono):
+                prompts[i] = w.to(dev)
+            continue
+        lens = torch.tensor([w.numel() for w in mono], dtype=torch.int64)
+        batch = torch.zeros(len(idx), int(lens.max()))
+        for r, w in enumerate(mono):
+            batch[r, : w.numel()] = w
+        res = ResampleB200(sr, sampling_rate, engine=feature_extractor.engine)(batch.to(dev), lens.to(dev))
+        out_lens = (lens * sampling_rate + sr - 1) // sr
+        for r, i in enumerate(idx):
+            prompts[i] = res[r, : int(out_lens[r])]
+    # ---- buckets of similar total length (prompt frames scaled by the text / prompt-text ratio)
+    frames = {i: max(1, prompts[i].numel() // 256) for i in mine}
+    cost = [int(frames[i] * (1 + len(tokens[i]) / max(1, len(prompt_tokens[i])) / max(speed, 1e-3))) for i in mine]
+    buckets = [[mine[j] for j in b] for b in length_buckets(cost, max_batch_frames)]
+    total_t, total_sec, n_done = 0.0, 0.0, 0
+    pending = []
+    with ThreadPoolExecutor(max_workers=2) as pool:
+        for b in buckets:
+            torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            wavs = generate_batch([prompt_tokens[i] for i in b], [prompts[i] for i in b], [tokens[i] for i in b],
+                                  model, vocoder, feature_extractor, num_step=num_step,
+                                  guidance_scale=guidance_scale, speed=speed, t_shift=t_shift, target_rms=target_rms,
+                                  feat_scale=feat_scale, feat_bias=feat_bias)
+            host = [w.cpu().numpy() for w in wavs]          # device -> host read of the bucket's waveforms
+            total_t += time.perf_counter() - t0
+            for i, w in zip(b, host):
+                total_sec += w.shape[-1] / sampling_rate
+                pending.append(pool.submit(write_wav, os.path.join(res_dir, f"{items[i][0]}.wav"), w, sampling_rate))
+            n_done += len(b)
+        for f in pending:
+            f.result()
+    return {"t": total_t, "wav_seconds": total_sec, "rtf": total_t / max(total_sec, 1e-9), "utterances": n_done,
+            "batches": len(buckets)}
