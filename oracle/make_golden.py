@@ -58,6 +58,23 @@ def stereo():
 
 
 @torch.inference_mode()
+@torch.inference_mode()
+def intermediate():
+    """ZipVoice.sample_intermediate (zipvoice.py:488-534) of the unmodified reference: per-sample guidance
+    (batch, 1, 1), t in [0.2, 0.7], two Euler steps.  python -m oracle.make_golden intermediate"""
+    from zipvoice_b200 import synth
+    torch.set_num_threads(8)
+    small = synth.small_model_cfg()
+    sd = synth.make_state_dict(small, seed=1, stress=True)
+    m = _ref_model("zipvoice", small, sd)
+    inp = synth.make_intermediate_inputs(seed=31)
+    x, lens = m.sample_intermediate(tokens=inp["tokens"], features=inp["features"], features_lens=inp["features_lens"],
+                                    noise=inp["noise"], speech_condition_mask=inp["speech_condition_mask"],
+                                    t_start=0.2, t_end=0.7, num_step=2, guidance_scale=inp["guidance_scale"])
+    np.savez(os.path.join(OUT, "sample_intermediate.npz"), x=x.numpy(), lens=lens.numpy())
+    print("sample_intermediate golden written", x.shape, lens)
+
+
 def resample():
     """torchaudio.transforms.Resample as the reference applies it to prompts (bin/infer_zipvoice.py:334-339), run
     with the torchaudio of this image on seeded noise + a chirp.  python -m oracle.make_golden resample"""
@@ -147,5 +164,7 @@ if __name__ == "__main__":
         stereo()
     elif "resample" in sys.argv[1:]:
         resample()
+    elif "intermediate" in sys.argv[1:]:
+        intermediate()
     else:
         main()

@@ -189,3 +189,17 @@ def sample(sd, model_cfg, tokens, prompt_tokens, prompt_features, prompt_feature
         x1_wo[i, :wl] = x1[i, pl:pl + wl]
         x1_prompt[i, :pl] = x1[i, :pl]
     return x1_wo, wo_lens, x1_prompt, prompt_features_lens
+
+
+@torch.inference_mode()
+def sample_intermediate(sd, model_cfg, tokens, features, features_lens, noise, speech_condition_mask, t_start: float,
+                        t_end: float, num_step: int = 1, guidance_scale=None, distill=False, pad_id=0):
+    """models/zipvoice.py:488-534 ZipVoice.sample_intermediate (teacher roll-out of the distillation recipe,
+    bin/train_zipvoice_distill.py:439-460): real feature lengths, speech condition = features outside the mask,
+    Euler steps over [t_start, t_end] without time shifting, guidance (batch, 1, 1) per sample."""
+    embed, tokens_lens = forward_text_embed(sd, model_cfg, tokens, pad_id)
+    text_condition, padding_mask = forward_text_condition(embed, tokens_lens, features_lens)
+    speech_condition = torch.where(speech_condition_mask.unsqueeze(-1), torch.zeros(()), features)
+    x = euler_sample(sd, model_cfg, noise, text_condition, speech_condition, padding_mask, num_step=num_step,
+                     guidance_scale=guidance_scale, t_start=t_start, t_end=t_end, distill=distill)
+    return x, (~padding_mask).sum(-1)

@@ -191,3 +191,19 @@ def test_sample_graph_replay_is_bit_identical(kind, guidance):
         assert torch.equal(eng.sample(x2, t2, s2, m2, **kw), want2), f"shape 2 call {i}"
     for i in range(3):
         assert torch.equal(eng.sample(x0, text, speech, mask, **kw), want), f"shape 1 again, call {i}"
+
+
+def test_sample_intermediate_golden():
+    """ZipVoiceB200.sample_intermediate (zipvoice.py:488-534: per-sample guidance tensor (batch, 1, 1), arbitrary
+    t_start / t_end) against the unmodified reference's output on the valid frames."""
+    from zipvoice_b200 import synth
+    m, cfg, sd = engine("zipvoice", "small", 1, True)
+    inp = synth.make_intermediate_inputs(seed=31)
+    g = _g("sample_intermediate.npz")
+    x, lens = m.sample_intermediate(tokens=inp["tokens"], features=inp["features"], features_lens=inp["features_lens"],
+                                    noise=inp["noise"], speech_condition_mask=inp["speech_condition_mask"],
+                                    t_start=0.2, t_end=0.7, num_step=2, guidance_scale=inp["guidance_scale"])
+    assert lens.cpu().tolist() == g["lens"].tolist()
+    mask = torch.arange(x.shape[1])[None, :] >= g["lens"][:, None]
+    r = valid_rel_l2(x.cpu(), g["x"], mask)
+    assert r < TOL_MEL, f"sample_intermediate rel-L2 {r:.3e}"

@@ -125,3 +125,17 @@ def test_resample_oracle_vs_torchaudio_golden():
         want = g[f"y_{sr}"]
         assert got.shape == want.shape
         assert float(np.abs(got - want).max()) < 2e-5, sr
+
+
+def test_sample_intermediate():
+    """oracle sample_intermediate against ZipVoice.sample_intermediate of the unmodified reference
+    (tests/golden/sample_intermediate.npz): per-sample guidance tensor, t in [0.2, 0.7]."""
+    cfg = synth.small_model_cfg()
+    sd = synth.make_state_dict(cfg, seed=1, stress=True)
+    inp = synth.make_intermediate_inputs(seed=31)
+    g = np.load(os.path.join(GOLDEN, "sample_intermediate.npz"))
+    x, lens = O.sample_intermediate(sd, cfg, inp["tokens"], inp["features"], inp["features_lens"], inp["noise"],
+                                    inp["speech_condition_mask"], 0.2, 0.7, num_step=2,
+                                    guidance_scale=inp["guidance_scale"])
+    assert lens.tolist() == g["lens"].tolist()
+    assert rel_l2(x, torch.from_numpy(g["x"])) < 1e-5

@@ -229,3 +229,18 @@ def make_vocos_state_dict(seed: int = 0) -> Dict[str, torch.Tensor]:
                    f"{p}.pwconv2.weight": rn(DIM, INTER, std=0.05), f"{p}.pwconv2.bias": rn(DIM, std=0.1),
                    f"{p}.gamma": torch.full((DIM,), 1.0 / LAYERS) * (1 + rn(DIM, std=0.2))})
     return sd
+
+
+def make_intermediate_inputs(seed: int = 31, B: int = 2, T: int = 43, n_tokens: int = 17):
+    """Seeded inputs of ZipVoice.sample_intermediate (zipvoice.py:488-534): ragged feature lengths, a prompt-like
+    speech-condition mask (True = not conditioned) and a per-sample guidance tensor (batch, 1, 1)."""
+    g = torch.Generator().manual_seed(seed)
+    tokens = [torch.randint(1, VOCAB_SIZE, (n_tokens - 3 * b,), generator=g).tolist() for b in range(B)]
+    features = torch.randn(B, T, 100, generator=g) * 0.5 - 0.5
+    features_lens = torch.tensor([T - 6 * b for b in range(B)], dtype=torch.int64)
+    noise = torch.randn(B, T, 100, generator=g)
+    start = torch.tensor([9 + 4 * b for b in range(B)])
+    speech_condition_mask = torch.arange(T)[None, :] >= start[:, None]
+    guidance_scale = torch.tensor([0.5 + 1.5 * b for b in range(B)]).reshape(B, 1, 1)
+    return {"tokens": tokens, "features": features, "features_lens": features_lens, "noise": noise,
+            "speech_condition_mask": speech_condition_mask, "guidance_scale": guidance_scale}
