@@ -321,10 +321,13 @@ def main():
                 "frac": top["frac"], "traffic": None, "peak_source": pk["source"] + ", sustained figure",
                 "avg_launch_ms": round(top["ms"] / max(1, top["launches"]), 4)}
     # ncu DRAM traffic of the dominant kernel (one `ncu --set full` capture, committed under profiles/)
-    tpath = os.path.join(ROOT, "profiles", "r1e_traffic.json")
+    import glob
+    tfiles = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
+    tpath = tfiles[-1] if tfiles else ""
+    ttag = os.path.basename(tpath)[:-len("_traffic.json")] if tpath else ""
     knames = {"gemm_residual": ["gemm_tc_kernel<4, 1>", "gemm_tc_kernel<4, 0>"], "gemm_swooshl": ["gemm_tc_kernel<1, 0>"],
               "attn_self": ["attn_sa_kernel"], "attn_nonlin": ["attn_na_tc_kernel"]}.get(top["name"], [])
-    if os.path.exists(tpath) and knames:
+    if tpath and knames:
         tj = json.load(open(tpath))
         sel = [tj[k] for k in knames if k in tj]
         n = sum(x["captured_launches"] for x in sel)
@@ -332,8 +335,8 @@ def main():
             roofline["traffic"] = round(sum((x["dram_read_bytes_per_launch"] + x["dram_write_bytes_per_launch"]) *
                                             x["captured_launches"] for x in sel) / n)
             roofline["traffic_note"] = (f"bytes per launch, dram__bytes_read.sum + dram__bytes_write.sum, mean of {n} launches "
-                                        "captured in a downsampled stack (profiles/r1e_ncu_full_summary.md, "
-                                        "profiles/r1e_traffic.json); below the algorithmic bytes of those launches because "
+                                        f"captured in a downsampled stack (profiles/{ttag}_ncu_full_summary.md, "
+                                        f"profiles/{ttag}_traffic.json); below the algorithmic bytes of those launches because "
                                         "part of the residual stream is still L2-resident from the producer kernel")
     if top["name"] == "gemm_residual":
         # The residual GEMMs (N = 512, K = 384 ... 1920) carry the fp32 residual stream through their epilogue and
