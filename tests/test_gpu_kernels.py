@@ -93,6 +93,10 @@ CASES = [
     (EPI_NONLIN, 38500, 1152, 512, {"gate_cols": 768}),
     (EPI_BIAS, 39000, 272, 512, {}),
     (EPI_RESIDUAL, 38300, 512, 1920, {"orig": True}),
+    # partial last wave cut into column slices (TileSched in zv_gemm.cu): 150 tiles -> 2 leftover tiles in 2 slices;
+    # the quarter-rate residual shape of the bench, 610 tiles -> 18 leftover tiles in 4 slices
+    (EPI_SWOOSHL, 3823, 1152, 512, {"rowbias": True, "L": 1000}),
+    (EPI_RESIDUAL, 39040, 512, 576, {"resbias": True, "L": 305}),
 ]
 
 

@@ -150,7 +150,12 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
 #pragma unroll
       for (int ks = 0; ks < 2; ++ks) ldsm_x4(qa[ks], qbase + sw64(warp * 16 + (lane & 15), ks * 2 + (lane >> 4)));
     }
-    for (int kt = 0; kt < n_tiles; ++kt) {
+    // One key tile.  TAIL = the last tile of the sequence: only its first nbv 8-key blocks hold keys (the rest
+    // is beyond L and would contribute exp(-inf) = 0), so their MMAs, position terms and exponentials are skipped
+    // behind warp-uniform tests; every other tile runs the unconditional copy of the body.
+    auto key_tile = [&](const int kt, auto tail_tag) {
+      constexpr bool TAIL = decltype(tail_tag)::value;
+      const int nbv = TAIL ? (L - kt * BKV + 7) >> 3 : 8;
       const int st = kt % STAGES;
       mbar_wait(&sm.full[st], (kt / STAGES) & 1);
       const Stage& S = sm.st[st];
@@ -161,6 +166,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
         s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        if (TAIL && nt >= nbv) continue;
         uint32_t kb[4];
         ldsm_x4(kb, kbase + sw64(nt * 8 + (lane & 7), lane >> 3));
         mma_f16(s[nt], qa[0], kb[0], kb[1]);
@@ -176,6 +182,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
         float4 ep0 = ew[-8], ep1 = ew[-7];
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
+          if (TAIL && nt >= nbv) break;
           const float4 ec0 = ew[nt * 8], ec1 = ew[nt * 8 + 1];
           float a0 = s[nt][0] + pq0[0] * ec0.x + pq0[1] * ec0.y + pq0[2] * ec0.z + pq0[3] * ec0.w;
           float a1 = s[nt][1] + pq0[0] * ec1.x + pq0[1] * ec1.y + pq0[2] * ec1.z + pq0[3] * ec1.w;
@@ -202,6 +209,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       const float ms0 = mn0 * LOG2E, ms1 = mn1 * LOG2E;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
+        if (TAIL && nt >= nbv) break;  // s stays 0 = P of the absent keys
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const float pa = ex2_approx(fmaf(s[nt][e], LOG2E, -ms0)), pb = ex2_approx(fmaf(s[nt][2 + e], LOG2E, -ms1));
@@ -217,6 +225,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       // ---- O += P V
 #pragma unroll
       for (int kk = 0; kk < BKV / 16; ++kk) {
+        if (TAIL && 2 * kk >= nbv) break;
         uint32_t pa[4];
         pa[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
         pa[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
@@ -229,7 +238,9 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.empty[st]);
-    }
+    };
+    for (int kt = 0; kt + 1 < n_tiles; ++kt) key_tile(kt, std::false_type{});
+    key_tile(n_tiles - 1, std::true_type{});
     // ---- normalise, store (columns >= dv belong to the next head / padding and are dropped)
     // column dv = 12 of O (n-tile 1, columns 4..5 -> the lane with qd == 2) is sum_k P[i][k] * 1
     const float l0 = __shfl_sync(0xffffffffu, o[1][0], (lane & ~3) | 2);

@@ -8,7 +8,8 @@
 //                 one elected thread issues a TMA store (rows / columns outside the tensor are clipped by
 //                 the tensor map).  EPI_RESIDUAL also TMA-loads the fp32 residual chunk one chunk ahead and
 //                 updates it in place in shared memory.
-// Persistent: grid = min(#tiles, #SMs); tile t -> (m_blk = t / n_tiles, n_blk = t % n_tiles).
+// Persistent: grid = min(#tiles, #SMs); tile t -> (m_blk = t / n_tiles, n_blk = t % n_tiles); the tiles of a partial
+// last wave are cut into narrower column slices so that every CTA gets one (TileSched).
 #include <cuda.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -191,10 +192,20 @@ static constexpr int STG_F32_BYTES = BM * 128;   // 128 rows x 32 fp32
 
 struct GemmMaps {
   CUtensorMap A, W;
+  CUtensorMap Wt;  // W with a box of block_n / split rows: the narrow units of the last wave (TileSched)
   CUtensorMap A2;  // optional second A operand for k-blocks >= kb_split
   CUtensorMap O0;  // bf16 output (box 32 cols, SWIZZLE_64B; GLU / gated NONLIN: box 16 cols, SWIZZLE_32B)
   CUtensorMap O1;  // EPI_NONLIN plain part: bf16 (box 32, SWIZZLE_64B); EPI_RESIDUAL: fp32 out (box 32, SWIZZLE_128B)
   CUtensorMap R;   // EPI_RESIDUAL: fp32 residual input (box 32, SWIZZLE_128B)
+};
+
+// Work schedule of one launch.  Units [0, main_units) are full tiles (128 x block_n; 256 x block_n for CTA pairs)
+// in the order unit -> (unit / n_tiles, unit % n_tiles).  A tile count that is not a multiple of the CTA count
+// would leave most SMs idle for one whole tile time at the end, so the launcher cuts the remaining tiles of the
+// last wave into `split` column slices each: units >= main_units are 128 x (block_n / split) slices, again one
+// per CTA.  split = 1: no narrow units.
+struct TileSched {
+  int main_units, total_units, split;
 };
 
 struct GemmSmemTail {
@@ -273,7 +284,7 @@ ZV_DEVINL void add_bias32(float (&v)[32], const float* __restrict__ bias, const 
 template <int MODE, bool PAIR>
 __global__ void __launch_bounds__(128 + 128 * ncg_for(MODE), 1)
 gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, int k_blocks, int kb_split,
-               int block_n, int stages, EpiParams ep) {
+               int block_n, int stages, EpiParams ep, TileSched sched) {
   constexpr int NCG = ncg_for(MODE);
   constexpr int EPI_WARPS = 4 * NCG;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -281,8 +292,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
   // align inside the shared window (pointer + integer keeps the shared address space: LDS/STS, not generic LD/ST)
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
-  const int wn = PAIR ? (block_n >> 1) : block_n;  // W rows this CTA holds per stage
-  const int w_stage_bytes = wn * BK * 2;
+  const int w_stage_bytes = (PAIR ? (block_n >> 1) : block_n) * BK * 2;  // W rows this CTA holds per stage
   uint8_t* sA = smem;
   uint8_t* sW = smem + stages * A_STAGE_BYTES;
   uint8_t* sStg = sW + stages * w_stage_bytes;
@@ -293,12 +303,25 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
   // work units: tiles (single CTA) or pair tiles of 256 rows; unit u -> (u / n_tiles, u % n_tiles)
   const int unit0 = PAIR ? (blockIdx.x >> 1) : blockIdx.x;
   const int nunits = PAIR ? (gridDim.x >> 1) : gridDim.x;
-  const int total_tiles = (PAIR ? ((m_tiles + 1) >> 1) : m_tiles) * n_tiles;
-  auto tile_m = [&](int t) { return PAIR ? 2 * (t / n_tiles) + (int)rank : t / n_tiles; };
+  const int total_tiles = sched.total_units;
+  const int bn_tail = block_n / sched.split;
+  // unit -> first row block, first accumulator column and width of the unit
+  auto decode = [&](int t, int& m_blk, int& n0, int& bn) {
+    int tile = t, sub = 0;
+    bn = block_n;
+    if (t >= sched.main_units) {
+      const int u = t - sched.main_units;
+      tile = sched.main_units + u / sched.split, sub = u % sched.split, bn = bn_tail;
+    }
+    const int mu = tile / n_tiles;
+    m_blk = PAIR ? 2 * mu + (int)rank : mu;
+    n0 = (tile - mu * n_tiles) * block_n + sub * bn;
+  };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&maps.A);
     tma_prefetch_desc(&maps.W);
+    if (sched.split > 1) tma_prefetch_desc(&maps.Wt);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < stages; ++i) {
@@ -326,9 +349,12 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      const uint32_t tx = A_STAGE_BYTES + w_stage_bytes;
       for (int t = unit0; t < total_tiles; t += nunits) {
-        const int m_blk = tile_m(t), n_blk = t % n_tiles;
+        int m_blk, n0t, bn;
+        decode(t, m_blk, n0t, bn);
+        const int wn = PAIR ? (bn >> 1) : bn;
+        const uint32_t tx = A_STAGE_BYTES + wn * BK * 2;
+        const CUtensorMap* mapW = bn == block_n ? &maps.W : &maps.Wt;
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&tail->empty[stage], phase ^ 1);
           const CUtensorMap* mapA = kb < kb_split ? &maps.A : &maps.A2;
@@ -338,11 +364,11 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
             const uint32_t fb = mapa_shared(smem_u32(&tail->full[stage]), 0);
             if (rank == 0) mbar_arrive_expect_tx(&tail->full[stage], 2 * tx);
             tma_load_2d_pair(sA + stage * A_STAGE_BYTES, mapA, fb, ka, m_blk * BM);
-            tma_load_2d_pair(sW + stage * w_stage_bytes, &maps.W, fb, kb * BK, n_blk * block_n + (int)rank * wn);
+            tma_load_2d_pair(sW + stage * w_stage_bytes, mapW, fb, kb * BK, n0t + (int)rank * wn);
           } else {
             mbar_arrive_expect_tx(&tail->full[stage], tx);
             tma_load_2d(sA + stage * A_STAGE_BYTES, mapA, &tail->full[stage], ka, m_blk * BM);
-            tma_load_2d(sW + stage * w_stage_bytes, &maps.W, &tail->full[stage], kb * BK, n_blk * block_n);
+            tma_load_2d(sW + stage * w_stage_bytes, mapW, &tail->full[stage], kb * BK, n0t);
           }
           if (++stage == stages) stage = 0, phase ^= 1;
         }
@@ -351,7 +377,8 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     __syncwarp();
   } else if (warp == 1) {
     if (lane == 0 && rank == 0) {
-      const uint32_t idesc = make_idesc_bf16(PAIR ? 2 * BM : BM, block_n);
+      const uint32_t idesc_main = make_idesc_bf16(PAIR ? 2 * BM : BM, block_n);
+      const uint32_t idesc_tail = make_idesc_bf16(PAIR ? 2 * BM : BM, bn_tail);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -361,6 +388,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         mbar_wait(&tail->tmem_empty[as], aphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * ACC_STAGE_COLS;
+        const uint32_t idesc = t < sched.main_units ? idesc_main : idesc_tail;
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&tail->full[stage], phase);
           tc_fence_after();
@@ -388,7 +416,6 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     const int cg = (warp - 4) >> 2;    // column group
     const int r = q * 32 + lane;       // row within the tile
     uint8_t* stg = sStg + cg * stg_group_bytes(MODE);
-    const int nchunks_tile = block_n >> 5;
     uint32_t nq = 0;  // chunks processed by this group (selects the staging buffer / residual barrier phase)
 
     // EPI_RESIDUAL: the leader prefetches the first residual chunk of this group
@@ -400,14 +427,18 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     // Every epilogue warp is its own pipeline: it stages, loads and stores only its 32 rows (TMA boxes of
     // 32 rows), so the only synchronisation inside the epilogue is __syncwarp.
     uint64_t* rbar = &tail->rbar[cg * 4 + q][0];
-    if (MODE == EPI_RESIDUAL && lane == 0 && unit0 < total_tiles && cg < nchunks_tile) {
-      const int m_blk = tile_m(unit0), n_blk = unit0 % n_tiles;
+    // (every unit of an EPI_RESIDUAL launch is at least 32 * NCG columns wide: each group owns a chunk of it)
+    if (MODE == EPI_RESIDUAL && lane == 0 && unit0 < total_tiles) {
+      int m_blk, n0t, bn;
+      decode(unit0, m_blk, n0t, bn);
       mbar_arrive_expect_tx(&rbar[0], STG_F32_BYTES / 4);
-      tma_load_2d(stg + q * (STG_F32_BYTES / 4), &maps.R, &rbar[0], n_blk * block_n + cg * 32, m_blk * BM + q * 32);
+      tma_load_2d(stg + q * (STG_F32_BYTES / 4), &maps.R, &rbar[0], n0t + cg * 32, m_blk * BM + q * 32);
     }
     int it = 0;
     for (int t = unit0; t < total_tiles; t += nunits, ++it) {
-      const int m_blk = tile_m(t), n_blk = t % n_tiles;
+      int m_blk, n0t, bn;
+      decode(t, m_blk, n0t, bn);
+      const int nchunks_tile = bn >> 5;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       const int m = m_blk * BM + r;
@@ -418,7 +449,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       // chunks that lie entirely in the padded columns of the last n-tile are skipped (never for EPI_RESIDUAL,
       // whose prefetch chain assumes full tiles: its N is a multiple of block_n)
       const int nchunks = (MODE == EPI_RESIDUAL) ? nchunks_tile
-                                                 : min(nchunks_tile, (ep.N - n_blk * block_n + 31) >> 5);
+                                                 : min(nchunks_tile, (ep.N - n0t + 31) >> 5);
       mbar_wait(&tail->tmem_full[as], aphase);
       tc_fence_after();
       if (cg >= nchunks) {  // this group owns no chunk of the tile: release the accumulator right away
@@ -427,7 +458,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         if (lane == 0) release_acc(as);
       }
       for (int c = cg; c < nchunks; c += NCG, ++nq) {
-        const int n0 = n_blk * block_n + c * 32;
+        const int n0 = n0t + c * 32;
         uint32_t raw[32];
         tmem_ld32(taddr + c * 32, raw);
         tmem_ld_wait();
@@ -477,10 +508,11 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
             int c2 = c + NCG, t2 = t;
             if (c2 >= nchunks) c2 = cg, t2 = t + nunits;
             if (t2 < total_tiles) {
-              const int mb2 = tile_m(t2), nb2 = t2 % n_tiles;
+              int mb2 = m_blk, n02 = n0t, bn2;
+              if (t2 != t) decode(t2, mb2, n02, bn2);
               mbar_arrive_expect_tx(&rbar[sb ^ 1], STG_F32_BYTES / 4);
               tma_load_2d(stg + (sb ^ 1) * STG_F32_BYTES + q * (STG_F32_BYTES / 4), &maps.R, &rbar[sb ^ 1],
-                          nb2 * block_n + c2 * 32, mb2 * BM + q * 32);
+                          n02 + c2 * 32, mb2 * BM + q * 32);
             }
           }
           add_bias32(v, ep.bias, ep.resbias ? ep.resbias + (size_t)b * ep.bias_ld : nullptr, n0, ep.N);
@@ -728,7 +760,8 @@ int gemm_pick_block_n(int n_valid, int mode, int gate_cols) {
 static int g_num_sms = 0;
 
 template <int MODE, bool PAIR>
-static int launch_tc(const GemmMaps& maps, const GemmPlan& p, const EpiParams& ep, cudaStream_t stream) {
+static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const GemmPlan& p, const EpiParams& ep,
+                     cudaStream_t stream) {
   constexpr int NCG = ncg_for(MODE);
   constexpr int threads = 128 + 128 * NCG;
   const int w_stage = (PAIR ? p.block_n / 2 : p.block_n) * BK * 2;
@@ -765,22 +798,45 @@ static int launch_tc(const GemmMaps& maps, const GemmPlan& p, const EpiParams& e
   const int n_tiles = p.N_pad / p.block_n;
   const int k_blocks = (p.K + BK - 1) / BK;
   const int kb_split = p.A2 ? p.k_split / BK : k_blocks;
+  const int units = (PAIR ? (m_tiles + 1) / 2 : m_tiles) * n_tiles;
+  const int nunits = PAIR ? min(units, min(max_clusters, g_num_sms / 2)) : min(units, g_num_sms);
+  // Last wave: R = units % nunits tiles would keep R CTAs busy for a whole tile time while the others idle.  Cut
+  // them into `split` column slices (one slice per CTA, R * split <= nunits).  A slice keeps every epilogue column
+  // group busy (>= 32 NCG columns), is a legal UMMA N, and ends the gated part of EPI_NONLIN on a slice boundary.
+  TileSched sched = {units, units, 1};
+  GemmMaps maps = maps_in;
+  static const int tail_split = getenv("ZV_GEMM_TAILSPLIT") ? atoi(getenv("ZV_GEMM_TAILSPLIT")) : 1;
+  const int rem = units % nunits;
+  if (tail_split && units > nunits && rem != 0) {
+    int split = 1;
+    for (int sp = 2; sp <= 8; sp *= 2) {
+      const int bn = p.block_n / sp;
+      if (p.block_n % sp || bn % 32 || bn < 32 * NCG || rem * sp > nunits) break;
+      if (MODE == EPI_NONLIN_BF16 && ep.gate_cols % bn != 0) break;
+      split = sp;
+    }
+    if (split > 1) {
+      const int bn = p.block_n / split;
+      const int rc = make_tmap_impl(&maps.Wt, W, 0, (uint64_t)p.N_pad, (uint64_t)p.K, (uint64_t)p.ldw,
+                                    (uint32_t)(PAIR ? bn / 2 : bn), 64, 128);
+      if (rc) return rc;
+      sched.main_units = units - rem, sched.split = split, sched.total_units = units - rem + rem * split;
+    }
+  }
   if (!PAIR) {
-    const int grid = min(m_tiles * n_tiles, g_num_sms);
-    gemm_tc_kernel<MODE, PAIR><<<grid, threads, smem, stream>>>(maps, m_tiles, n_tiles, k_blocks, kb_split, p.block_n,
-                                                                 stages, ep);
+    gemm_tc_kernel<MODE, PAIR><<<nunits, threads, smem, stream>>>(maps, m_tiles, n_tiles, k_blocks, kb_split,
+                                                                   p.block_n, stages, ep, sched);
     return (int)cudaGetLastError();
   }
-  const int units = ((m_tiles + 1) / 2) * n_tiles;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(2 * min(units, min(max_clusters, g_num_sms / 2)));
+  cfg.gridDim = dim3(2 * nunits);
   cfg.blockDim = dim3(threads), cfg.dynamicSmemBytes = smem, cfg.stream = stream;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = 2, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
   cfg.attrs = at, cfg.numAttrs = 1;
   return (int)cudaLaunchKernelEx(&cfg, gemm_tc_kernel<MODE, PAIR>, maps, m_tiles, n_tiles, k_blocks, kb_split,
-                                 p.block_n, stages, ep);
+                                 p.block_n, stages, ep, sched);
 }
 
 // impl: 0 = tcgen05, CTA pairs (cta_group::2) for the shapes where they measure faster; 1 = SIMT checker;
@@ -847,9 +903,9 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
     } else {
       ep2.f32_direct = 1;
     }
-    return pair ? launch_tc<MODE, true>(maps, p, ep2, stream) : launch_tc<MODE, false>(maps, p, ep2, stream);
+    return pair ? launch_tc<MODE, true>(maps, W, p, ep2, stream) : launch_tc<MODE, false>(maps, W, p, ep2, stream);
   }
-  return pair ? launch_tc<MODE, true>(maps, p, ep, stream) : launch_tc<MODE, false>(maps, p, ep, stream);
+  return pair ? launch_tc<MODE, true>(maps, W, p, ep, stream) : launch_tc<MODE, false>(maps, W, p, ep, stream);
 }
 
 int gemm_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const GemmPlan& plan, const EpiParams& ep, int impl,
