@@ -211,3 +211,28 @@ def test_nonlin_attention_overflow_repeat(L):
     assert torch.isfinite(out).all()
     r = rel(out, want)
     assert r < 8e-3, f"rel-L2 {r:.3e}"
+
+
+@pytest.mark.parametrize("L", [130, 611, 1219])
+def test_self_attention_reference_repeat(L):
+    """SelfAttention kernel: interior key tiles are exponentiated against the running reference maximum without
+    waiting for their own maximum.  Scores of the late keys sit ~130 nats above everything before them, far over the
+    2^64 bound: the warp must notice, repeat that tile with the exact online-softmax step and carry on."""
+    H, nb, dv = 4, 2, 12
+    g = torch.Generator(device="cuda").manual_seed(L)
+    rn = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    qkp = (rn(nb, L, 288) * 0.05).bfloat16().float()
+    qkp[..., : H * 32] += 2.0                              # q of every head
+    qkp[:, L // 2:, H * 32: 2 * H * 32] += 2.0             # k of every head, second half of the keys: s ~ 128
+    qkp = qkp.bfloat16().float()
+    E = rn(H, 2 * L - 1, 4).contiguous()
+    mask = torch.zeros(nb, L, dtype=torch.uint8, device="cuda")
+    mask[1, L - 5:] = 1
+    V = rn(nb, L, H * dv).bfloat16().float()
+    out = torch.zeros(nb, L, H * dv, device="cuda")
+    rc = _lib().zv_debug_attention(nb, L, H, H, dv, _p(qkp), 288, _p(E), _p(mask), _p(V), H * dv, None, _p(out), None)
+    assert rc == 0
+    want = ref_attention(qkp, E, mask, V, None, H, H, dv)
+    assert torch.isfinite(out).all()
+    r = rel(out, want)
+    assert r < 8e-3, f"rel-L2 {r:.3e}"

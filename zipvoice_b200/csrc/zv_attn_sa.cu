@@ -18,6 +18,8 @@ namespace sa {
 
 static constexpr int BQ = 128, BKV = 64, DQ = 32, EWIN = 192, STAGES = 4, DVP = 16;
 static constexpr int COMPUTE_THREADS = 256, THREADS = COMPUTE_THREADS + 32;
+// speculative tiles: exponent bound (log2) of P against the running reference (2^64 * 1219 keys << fp32 max)
+static constexpr float SPEC_LOG2 = 64.0f;
 
 struct Stage {
   __half k[BKV][DQ];    // 4 KB, SWIZZLE_64B
@@ -113,7 +115,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       const float4* E = reinterpret_cast<const float4*>(p.E) + (size_t)head * R;
       for (int kt = 0; kt < n_tiles; ++kt) {
         const int s = kt % STAGES;
-        if (kt >= STAGES) mbar_wait(&sm.empty[s], ((kt / STAGES) - 1) & 1);
+        if (kt >= STAGES) mbar_wait_backoff(&sm.empty[s], ((kt / STAGES) - 1) & 1);
         const int j0 = kt * BKV;
         const int rr0 = (j0 - i0 - (BQ - 1)) + (L - 1);  // table row of window entry 0
         const int lo = max(rr0, 0), hi = min(rr0 + EWIN, R);
@@ -150,12 +152,20 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
 #pragma unroll
       for (int ks = 0; ks < 2; ++ks) ldsm_x4(qa[ks], qbase + sw64(warp * 16 + (lane & 15), ks * 2 + (lane >> 4)));
     }
-    // One key tile.  TAIL = the last tile of the sequence: only its first nbv 8-key blocks hold keys (the rest
-    // is beyond L and would contribute exp(-inf) = 0), so their MMAs, position terms and exponentials are skipped
-    // behind warp-uniform tests; every other tile runs the unconditional copy of the body.
-    auto key_tile = [&](const int kt, auto tail_tag) {
-      constexpr bool TAIL = decltype(tail_tag)::value;
-      const int nbv = TAIL ? (L - kt * BKV + 7) >> 3 : 8;
+    // One key tile, as ONE straight-line block per variant so that the scheduler can overlap the tensor, FMA and
+    // MUFU work of a warp:
+    //   SPEC  -- interior tiles: P = exp(S - m) against the running reference m WITHOUT waiting for the tile's own
+    //            maximum (softmax is shift invariant; P is bf16 and the sums fp32, so any shift whose exponent
+    //            stays below 2^SPEC_LOG2 is exact to rounding).  The tile maximum is reduced on the side; if some
+    //            score exceeds its reference by more than SPEC_LOG2 the warp returns false before touching O and
+    //            the caller repeats the tile the exact way.
+    //   exact -- tile 0 (sets the reference), the last tile (only its first nbv 8-key blocks hold keys: the MMAs,
+    //            position terms and exponentials of the absent blocks are skipped) and repeats: classic online
+    //            softmax with the maximum first and O rescaled when it grows.
+    auto key_tile = [&](const int kt, auto spec_tag, auto masked_tag) -> bool {
+      constexpr bool SPEC = decltype(spec_tag)::value;
+      constexpr bool MASKED = decltype(masked_tag)::value;
+      const int nbv = SPEC ? 8 : min(8, (L - kt * BKV + 7) >> 3);
       const int st = kt % STAGES;
       mbar_wait(&sm.full[st], (kt / STAGES) & 1);
       const Stage& S = sm.st[st];
@@ -166,23 +176,23 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
         s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-        if (TAIL && nt >= nbv) continue;
+        if (!SPEC && nt >= nbv) continue;
         uint32_t kb[4];
         ldsm_x4(kb, kbase + sw64(nt * 8 + (lane & 7), lane >> 3));
         mma_f16(s[nt], qa[0], kb[0], kb[1]);
         mma_f16(s[nt], qa[1], kb[2], kb[3]);
       }
-      // ---- position term (rows g and g + 8 share table entries 8 columns apart), masks, running max
+      // ---- position term (rows g and g + 8 share table entries 8 columns apart), masks, tile maximum;
+      //      SPEC: P right away (mx0 / mx1 then hold the largest P of the two rows: the vote below depends on the
+      //      exponentials, which keeps them next to the FMAs in the schedule instead of behind the branch)
       float mx0 = -INFINITY, mx1 = -INFINITY;
-      // two copies of the loop behind ONE warp-uniform branch: with the mask test inside the loop the
-      // compiler predicates ~90 instructions per tile that still take issue slots on mask-free tiles
-      auto pos_term = [&](auto masked_tag) {
-        constexpr bool MASKED = decltype(masked_tag)::value;
+      const float msr0 = m0 * LOG2E, msr1 = m1 * LOG2E;
+      {
         const float4* ew = &S.e[2 * qd - rl0 + (BQ - 1)];
         float4 ep0 = ew[-8], ep1 = ew[-7];
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
-          if (TAIL && nt >= nbv) break;
+          if (!SPEC && nt >= nbv) break;
           const float4 ec0 = ew[nt * 8], ec1 = ew[nt * 8 + 1];
           float a0 = s[nt][0] + pq0[0] * ec0.x + pq0[1] * ec0.y + pq0[2] * ec0.z + pq0[3] * ec0.w;
           float a1 = s[nt][1] + pq0[0] * ec1.x + pq0[1] * ec1.y + pq0[2] * ec1.z + pq0[3] * ec1.w;
@@ -193,30 +203,38 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
             if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
             if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
           }
+          if (SPEC) {
+            a0 = ex2_approx(fmaf(a0, LOG2E, -msr0)), a1 = ex2_approx(fmaf(a1, LOG2E, -msr0));
+            b0 = ex2_approx(fmaf(b0, LOG2E, -msr1)), b1 = ex2_approx(fmaf(b1, LOG2E, -msr1));
+          }
           s[nt][0] = a0, s[nt][1] = a1, s[nt][2] = b0, s[nt][3] = b1;
           mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
           ep0 = ec0, ep1 = ec1;
         }
-      };
-      if (sflag[kt] != 0) pos_term(std::true_type{});
-      else pos_term(std::false_type{});
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-      const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
-      const bool grow = (mn0 != m0) || (mn1 != m1);
+      }
+      float mn0 = m0, mn1 = m1;
+      if (!SPEC) {
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+      }
       const float ms0 = mn0 * LOG2E, ms1 = mn1 * LOG2E;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
-        if (TAIL && nt >= nbv) break;  // s stays 0 = P of the absent keys
+        if (SPEC || nt >= nbv) break;  // s stays 0 = P of the absent keys
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const float pa = ex2_approx(fmaf(s[nt][e], LOG2E, -ms0)), pb = ex2_approx(fmaf(s[nt][2 + e], LOG2E, -ms1));
           s[nt][e] = pa, s[nt][2 + e] = pb;
         }
       }
-      if (__any_sync(0xffffffffu, grow)) {
+      if (SPEC) {
+        // a lane's own maxima suffice: any lane over the bound sends the whole warp to the exact repeat
+        const float bound = 18446744073709551616.0f;  // 2^SPEC_LOG2
+        if (__any_sync(0xffffffffu, !(fmaxf(mx0, mx1) <= bound))) return false;
+      } else if (__any_sync(0xffffffffu, (mn0 != m0) || (mn1 != m1))) {
         const float sc0 = ex2_approx((m0 - mn0) * LOG2E), sc1 = ex2_approx((m1 - mn1) * LOG2E);
 #pragma unroll
         for (int n = 0; n < 2; ++n) o[n][0] *= sc0, o[n][1] *= sc0, o[n][2] *= sc1, o[n][3] *= sc1;
@@ -225,7 +243,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       // ---- O += P V
 #pragma unroll
       for (int kk = 0; kk < BKV / 16; ++kk) {
-        if (TAIL && 2 * kk >= nbv) break;
+        if (!SPEC && 2 * kk >= nbv) break;
         uint32_t pa[4];
         pa[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
         pa[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
@@ -238,9 +256,15 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.empty[st]);
+      return true;
     };
-    for (int kt = 0; kt + 1 < n_tiles; ++kt) key_tile(kt, std::false_type{});
-    key_tile(n_tiles - 1, std::true_type{});
+    const std::true_type yes{};
+    const std::false_type no{};
+    for (int kt = 0; kt < n_tiles; ++kt) {
+      bool done = false;
+      if (kt != 0 && kt != n_tiles - 1 && !(p.dbg & 16)) done = sflag[kt] != 0 ? key_tile(kt, yes, yes) : key_tile(kt, yes, no);
+      if (!done) key_tile(kt, no, yes);
+    }
     // ---- normalise, store (columns >= dv belong to the next head / padding and are dropped)
     // column dv = 12 of O (n-tile 1, columns 4..5 -> the lane with qd == 2) is sum_k P[i][k] * 1
     const float l0 = __shfl_sync(0xffffffffu, o[1][0], (lane & ~3) | 2);

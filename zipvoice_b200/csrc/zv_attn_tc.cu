@@ -180,7 +180,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
     int g = 0;
     auto load_k = [&](int kt) {
       const int st = g % KSTAGES;
-      if (g >= KSTAGES) mbar_wait(&sm.kempty[st], ((g / KSTAGES) - 1) & 1);
+      if (g >= KSTAGES) mbar_wait_backoff(&sm.kempty[st], ((g / KSTAGES) - 1) & 1);
       const int j0 = kt * BKV;
       const int rr0 = (j0 - i0 - (BQ - 1)) + (L - 1);  // table row of window entry 0
       const int lo = max(rr0, 0), hi = min(rr0 + EWIN, R);

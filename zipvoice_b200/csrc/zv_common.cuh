@@ -85,6 +85,11 @@ ZV_DEVINL void mbar_wait(uint64_t* bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
+// For producer warps that run several stages ahead: back off between polls so that the spinning warp does not
+// take issue slots from the compute warps of its scheduler (the wake-up delay is hidden by the ring depth).
+ZV_DEVINL void mbar_wait_backoff(uint64_t* bar, uint32_t parity, unsigned ns = 128) {
+  while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
+}
 
 // ------------------------------------------------------------------ TMA
 ZV_DEVINL void tma_prefetch_desc(const void* desc) {

@@ -760,7 +760,7 @@ int gemm_pick_block_n(int n_valid, int mode, int gate_cols) {
 static int g_num_sms = 0;
 
 template <int MODE, bool PAIR>
-static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const GemmPlan& p, const EpiParams& ep,
+static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const GemmPlan& p, const EpiParams& ep_in,
                      cudaStream_t stream) {
   constexpr int NCG = ncg_for(MODE);
   constexpr int threads = 128 + 128 * NCG;
@@ -805,6 +805,7 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
   // group busy (>= 32 NCG columns), is a legal UMMA N, and ends the gated part of EPI_NONLIN on a slice boundary.
   TileSched sched = {units, units, 1};
   GemmMaps maps = maps_in;
+  const EpiParams& ep = ep_in;
   static const int tail_split = getenv("ZV_GEMM_TAILSPLIT") ? atoi(getenv("ZV_GEMM_TAILSPLIT")) : 1;
   const int rem = units % nunits;
   if (tail_split && units > nunits && rem != 0) {
