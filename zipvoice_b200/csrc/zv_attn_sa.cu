@@ -162,10 +162,12 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
     //   exact -- tile 0 (sets the reference), the last tile (only its first nbv 8-key blocks hold keys: the MMAs,
     //            position terms and exponentials of the absent blocks are skipped) and repeats: classic online
     //            softmax with the maximum first and O rescaled when it grows.
-    auto key_tile = [&](const int kt, auto spec_tag, auto masked_tag) -> bool {
-      constexpr bool SPEC = decltype(spec_tag)::value;
+    // mode_tag: 0 = SPEC, 1 = exact, 2 = exact with the block count of the last tile
+    auto key_tile = [&](const int kt, auto mode_tag, auto masked_tag) -> bool {
+      constexpr bool SPEC = decltype(mode_tag)::value == 0;
+      constexpr bool TAIL = decltype(mode_tag)::value == 2;
       constexpr bool MASKED = decltype(masked_tag)::value;
-      const int nbv = SPEC ? 8 : min(8, (L - kt * BKV + 7) >> 3);
+      const int nbv = TAIL ? min(8, (L - kt * BKV + 7) >> 3) : 8;
       const int st = kt % STAGES;
       mbar_wait(&sm.full[st], (kt / STAGES) & 1);
       const Stage& S = sm.st[st];
@@ -176,7 +178,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
         s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-        if (!SPEC && nt >= nbv) continue;
+        if (TAIL && nt >= nbv) continue;
         uint32_t kb[4];
         ldsm_x4(kb, kbase + sw64(nt * 8 + (lane & 7), lane >> 3));
         mma_f16(s[nt], qa[0], kb[0], kb[1]);
@@ -192,7 +194,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
         float4 ep0 = ew[-8], ep1 = ew[-7];
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
-          if (!SPEC && nt >= nbv) break;
+          if (TAIL && nt >= nbv) break;
           const float4 ec0 = ew[nt * 8], ec1 = ew[nt * 8 + 1];
           float a0 = s[nt][0] + pq0[0] * ec0.x + pq0[1] * ec0.y + pq0[2] * ec0.z + pq0[3] * ec0.w;
           float a1 = s[nt][1] + pq0[0] * ec1.x + pq0[1] * ec1.y + pq0[2] * ec1.z + pq0[3] * ec1.w;
@@ -223,7 +225,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       const float ms0 = mn0 * LOG2E, ms1 = mn1 * LOG2E;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
-        if (SPEC || nt >= nbv) break;  // s stays 0 = P of the absent keys
+        if (SPEC || (TAIL && nt >= nbv)) break;  // s stays 0 = P of the absent keys
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const float pa = ex2_approx(fmaf(s[nt][e], LOG2E, -ms0)), pb = ex2_approx(fmaf(s[nt][2 + e], LOG2E, -ms1));
@@ -243,7 +245,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       // ---- O += P V
 #pragma unroll
       for (int kk = 0; kk < BKV / 16; ++kk) {
-        if (!SPEC && 2 * kk >= nbv) break;
+        if (TAIL && 2 * kk >= nbv) break;
         uint32_t pa[4];
         pa[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
         pa[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
@@ -258,13 +260,23 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       if (lane == 0) mbar_arrive(&sm.empty[st]);
       return true;
     };
-    const std::true_type yes{};
-    const std::false_type no{};
-    for (int kt = 0; kt < n_tiles; ++kt) {
+    const std::true_type masked{};
+    const std::false_type clear{};
+    const std::integral_constant<int, 0> spec{};
+    const std::integral_constant<int, 1> exact{};
+    const std::integral_constant<int, 2> exact_tail{};
+    bool flag = sflag[0] != 0;
+    for (int kt = 0; kt + 1 < n_tiles; ++kt) {
+      const bool mk = flag;
+      flag = sflag[kt + 1] != 0;  // fetched a tile ahead of its use
       bool done = false;
-      if (kt != 0 && kt != n_tiles - 1 && !(p.dbg & 16)) done = sflag[kt] != 0 ? key_tile(kt, yes, yes) : key_tile(kt, yes, no);
-      if (!done) key_tile(kt, no, yes);
+      if (kt != 0 && !(p.dbg & 16)) done = mk ? key_tile(kt, spec, masked) : key_tile(kt, spec, clear);
+      if (!done) {
+        if (mk) key_tile(kt, exact, masked);
+        else key_tile(kt, exact, clear);
+      }
     }
+    key_tile(n_tiles - 1, exact_tail, masked);
     // ---- normalise, store (columns >= dv belong to the next head / padding and are dropped)
     // column dv = 12 of O (n-tile 1, columns 4..5 -> the lane with qd == 2) is sum_k P[i][k] * 1
     const float l0 = __shfl_sync(0xffffffffu, o[1][0], (lane & ~3) | 2);
