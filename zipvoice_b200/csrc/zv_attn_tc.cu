@@ -130,8 +130,8 @@ ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, int kh, 
 using namespace natc;
 
 __global__ void __launch_bounds__(natc::THREADS, 1)
-attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmQK, AttnParams p,
-                  int nvbox, int n_mma0, int n_mma1) {
+attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmQK,
+                  const __grid_constant__ CUtensorMap tmG, AttnParams p, int nvbox, int n_mma0, int n_mma1) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // align inside the shared window (pointer + integer keeps the shared address space: LDS/STS, not generic LD/ST)
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
@@ -207,7 +207,9 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
     __syncwarp();
   } else if (warp == MMA_WARP) {
     // ---------------- producer: X tiles by TMA, P.X by tcgen05.mma.  c counts tiles over both value sweeps.
-    auto load_v = [&](int c, int kt) {
+    // v counts the uses of the X ring (value tiles, then the two halves of the gate tile of every sweep)
+    auto load_v = [&](int v, int kt) {
+      const int c = v;
       const int st = c % VSTAGES;
       if (c >= VSTAGES) mbar_wait(&sm.vfree[st], ((c / VSTAGES) - 1) & 1);  // tile c - VSTAGES consumed
       if (p.dbg & 1) {
@@ -218,14 +220,36 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
       for (int cc = 0; cc < nvbox; ++cc)
         tma_load_2d(&sm.v[st][cc][0][0], &tmV, &sm.vfull[st], cc * 64, b * L + kt * BKV);
     };
+    // The gate tile y[128 queries][<= 384] of the epilogue rides behind the value tiles in the same ring: its two
+    // halves (3 boxes of 128 rows x 64 channels = one 48 KB stage each) are uses n_tiles and n_tiles + 1 of the
+    // sweep, so they arrive while the last two key tiles are still being worked on.
+    auto load_gate = [&](int v, int part) {
+      const int st = v % VSTAGES;
+      if (v >= VSTAGES) mbar_wait(&sm.vfree[st], ((v / VSTAGES) - 1) & 1);
+      const int nbox = min(3, nvbox - 3 * part);
+      if (!p.gate || nbox <= 0) {
+        mbar_arrive(&sm.vfull[st]);
+        return;
+      }
+      mbar_arrive_expect_tx(&sm.vfull[st], (uint32_t)nbox * BQ * 128);
+      for (int cc = 0; cc < nbox; ++cc)
+        tma_load_2d(reinterpret_cast<uint8_t*>(&sm.v[st][0][0][0]) + cc * (BQ * 128), &tmG, &sm.vfull[st],
+                    (3 * part + cc) * 64, b * L + i0);
+    };
     const uint32_t id0 = make_idesc_bf16_bmn(BQ, n_mma0), id1 = make_idesc_bf16_bmn(BQ, max(n_mma1, 16));
-    auto value_sweep = [&](int c0) {
-      for (int kt = 0; kt < min(2, n_tiles); ++kt) load_v(c0 + kt, kt);
+    // c0 / v0: P-buffer and X-ring use counters at entry
+    auto value_sweep = [&](int c0, int v0) {
+      auto issue = [&](int idx) {
+        if (idx < n_tiles) load_v(v0 + idx, idx);
+        else if (idx < n_tiles + 2) load_gate(v0 + idx, idx - n_tiles);
+      };
+      issue(0);
+      issue(1);
       for (int kt = 0; kt < n_tiles; ++kt) {
-        const int c = c0 + kt;
-        if (kt + 2 < n_tiles) load_v(c + 2, kt + 2);
-        const int st = c % VSTAGES, pb = c & 1;
-        mbar_wait(&sm.vfull[st], (c / VSTAGES) & 1);
+        const int c = c0 + kt, v = v0 + kt;
+        issue(kt + 2);
+        const int st = v % VSTAGES, pb = c & 1;
+        mbar_wait(&sm.vfull[st], (v / VSTAGES) & 1);
         mbar_wait(&sm.pfull[pb], (c >> 1) & 1);
         tc_fence_after();
         const uint64_t da = make_sdesc_sw128(smem_u32(&sm.p[pb][0][0]));
@@ -246,11 +270,19 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
     };
     if (lane == 0) {
       tma_prefetch_desc(&tmV);
-      value_sweep(0);
+      if (p.gate) tma_prefetch_desc(&tmG);
+      value_sweep(0, 0);
     }
     __syncwarp();
     named_bar_sync(2, THREADS);
-    if (sm.redo != 0 && lane == 0) value_sweep(n_tiles);
+    if (sm.redo != 0 && lane == 0) {
+      // the gate halves of the abandoned sweep are not consumed by any MMA: retire them by hand
+      for (int v = n_tiles; v < n_tiles + 2; ++v) {
+        mbar_wait(&sm.vfull[v % VSTAGES], (v / VSTAGES) & 1);
+        mbar_arrive(&sm.vfree[v % VSTAGES]);
+      }
+      value_sweep(n_tiles, n_tiles + 2);
+    }
     __syncwarp();
   } else {
     // ---------------- compute warps
@@ -360,17 +392,14 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
     const int i = i0 + row;
     const int ncols = nvbox * 64;
     const size_t grow = (size_t)b * L + min(i, L - 1);
-    // the gate values do not depend on O: fetch this thread's slice while the last MMAs drain
-    uint4 gv[3][4];
+    // the gate tile sits in the two X-ring stages behind the last value tile (SWIZZLE_128B boxes of 128 rows)
+    const int vg = (redo ? n_tiles + 2 : 0) + n_tiles;
+    const uint8_t* gst[2];
 #pragma unroll
-    for (int it = 0; it < 3; ++it) {
-      const int c0 = cs * 32 + it * 128;
-#pragma unroll
-      for (int j4 = 0; j4 < 4; ++j4) {
-        gv[it][j4] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);  // bf16 1.0 pairs
-        if (p.gate && c0 + j4 * 8 < p.dv)
-          gv[it][j4] = __ldg(reinterpret_cast<const uint4*>(p.gate + grow * p.ldg + c0 + j4 * 8));
-      }
+    for (int part = 0; part < 2; ++part) {
+      const int v = vg + part;
+      mbar_wait(&sm.vfull[v % VSTAGES], (v / VSTAGES) & 1);
+      gst[part] = reinterpret_cast<const uint8_t*>(&sm.v[v % VSTAGES][0][0][0]);
     }
     mbar_wait(&sm.obar, redo ? 1 : 0);
     tc_fence_after();
@@ -391,7 +420,12 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
           float v[8];
 #pragma unroll
           for (int u = 0; u < 8; ++u) v[u] = __uint_as_float(raw[jj + u]) * inv;
-          const uint4 g4 = gv[it][j4];
+          uint4 g4 = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);  // bf16 1.0 pairs
+          if (p.gate) {
+            const int col = c0 + jj, box = col >> 6;
+            g4 = *reinterpret_cast<const uint4*>(gst[box >= 3] + (box % 3) * (BQ * 128) + row * 128 +
+                                                 ((((col & 63) >> 3) ^ (row & 7)) << 4));
+          }
           v[0] *= bf16_lo(g4.x), v[1] *= bf16_hi(g4.x), v[2] *= bf16_lo(g4.y), v[3] *= bf16_hi(g4.y);
           v[4] *= bf16_lo(g4.z), v[5] *= bf16_hi(g4.z), v[6] *= bf16_lo(g4.w), v[7] *= bf16_hi(g4.w);
           *reinterpret_cast<uint4*>(op + jj) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
@@ -418,6 +452,11 @@ int attention_na_tc(const AttnParams& p, cudaStream_t s) {
   CUtensorMap tmQK;  // fp16 q | k | p rows: 64-row x 32-column boxes (q of head 0 at column 0, k at column H * 32)
   rc = make_tmap(&tmQK, p.qkp, 0, (uint64_t)p.nb * p.L, (uint64_t)(2 * p.H * DQ + 4 * p.H), (uint64_t)p.ldq, BKV, DQ, 64);
   if (rc) return rc;
+  CUtensorMap tmG = tmV;  // gate rows as 128 x 64 boxes (not read by the kernel without a gate)
+  if (p.gate) {
+    rc = make_tmap(&tmG, p.gate, 0, (uint64_t)p.nb * p.L, (uint64_t)p.dv, (uint64_t)p.ldg, BQ, 64, 128);
+    if (rc) return rc;
+  }
   static bool attr = false;
   const int n_tiles = (p.L + BKV - 1) / BKV;
   const int smem = (int)sizeof(Smem) + 1024 + n_tiles * BKV + ((n_tiles + 15) & ~15);
@@ -427,7 +466,7 @@ int attention_na_tc(const AttnParams& p, cudaStream_t s) {
     attr = true;
   }
   dim3 grid((p.L + BQ - 1) / BQ, p.nb);
-  attn_na_tc_kernel<<<grid, THREADS, smem, s>>>(tmV, tmQK, p, nvbox, n0, n1);
+  attn_na_tc_kernel<<<grid, THREADS, smem, s>>>(tmV, tmQK, tmG, p, nvbox, n0, n1);
   return (int)cudaGetLastError();
 }
 
