@@ -31,6 +31,7 @@ static constexpr int BQ = 128, BKV = 64, DQ = 32, EWIN = 192;
 static constexpr int VSTAGES = 3, NVBOX = 6;  // up to 6 boxes of 64 channels = 384
 static constexpr int KSTAGES = 4;
 static constexpr float OVF_LOG2 = 96.0f;  // P <= 2^96: 1219 keys x |x| <= 2^10 still sums far below fp32 max
+static constexpr float OVF_BOUND = 79228162514264337593543950336.0f;  // 2^96
 static constexpr int COMPUTE_THREADS = 512, THREADS = COMPUTE_THREADS + 64;
 static constexpr int MMA_WARP = COMPUTE_THREADS / 32, LOAD_WARP = MMA_WARP + 1;
 
@@ -89,10 +90,12 @@ ZV_DEVINL uint32_t make_idesc_bf16_bmn(uint32_t M, uint32_t N) {
 // Returns the two row maxima through mx0 / mx1.
 // MASKED is a template parameter so that the caller takes ONE warp-uniform branch per tile instead of
 // ~45 predicated mask instructions that occupy issue slots on mask-free tiles.
-template <bool MASKED>
+// EXP: the value sweep -- s becomes P = exp2(S log2e - ms) right where each score is finished, so that the MUFU
+// work interleaves with the position FMAs of the next block; mx0 / mx1 then hold the largest P of the two rows.
+template <bool MASKED, bool EXP>
 ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, int kh, int lane, int rl0,
                           const uint32_t (&qa)[2][4], const float (&pq0)[4], const float (&pq1)[4], float (&s)[4][4],
-                          float& mx0, float& mx1) {
+                          float& mx0, float& mx1, float ms0 = 0.f, float ms1 = 0.f) {
   const int qd = lane & 3;
   const uint32_t kbase = smem_u32(&sm.k[buf][0][0]);
 #pragma unroll
@@ -118,6 +121,11 @@ ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, int kh, 
       const uint8_t k0 = mrow[kh * 32 + n4 * 8 + 2 * qd], k1 = mrow[kh * 32 + n4 * 8 + 2 * qd + 1];
       if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
       if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
+    }
+    if (EXP) {
+      const float LOG2E = 1.4426950408889634f;
+      a0 = ex2_approx(fmaf(a0, LOG2E, -ms0)), a1 = ex2_approx(fmaf(a1, LOG2E, -ms0));
+      b0 = ex2_approx(fmaf(b0, LOG2E, -ms1)), b1 = ex2_approx(fmaf(b1, LOG2E, -ms1));
     }
     s[n4][0] = a0, s[n4][1] = a1, s[n4][2] = b0, s[n4][3] = b1;
     mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
@@ -322,8 +330,8 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
         const int buf = gt % KSTAGES;
         mbar_wait(&sm.kfull[buf], (gt / KSTAGES) & 1);
         float mx0, mx1;
-        if (sflag[kt] != 0) score_tile<true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
-        else score_tile<false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+        if (sflag[kt] != 0) score_tile<true, false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+        else score_tile<false, false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
         ring_release(buf);
         m0 = fmaxf(m0, mx0), m1 = fmaxf(m1, mx1);
       }
@@ -346,10 +354,12 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
         const int buf = gt % KSTAGES, pb = c & 1;
         mbar_wait(&sm.kfull[buf], (gt / KSTAGES) & 1);
         float mx0, mx1;
-        if (sflag[kt] != 0) score_tile<true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
-        else score_tile<false>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1);
+        if (sflag[kt] != 0)
+          score_tile<true, true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1, ms0, ms1);
+        else
+          score_tile<false, true>(sm, buf, smask + kt * BKV, kh, lane, rl0, qa, pq0, pq1, s, mx0, mx1, ms0, ms1);
         ring_release(buf);
-        ovf |= (fmaf(mx0, LOG2E, -ms0) > OVF_LOG2) | (fmaf(mx1, LOG2E, -ms1) > OVF_LOG2);
+        ovf |= !(fmaxf(mx0, mx1) <= OVF_BOUND);  // largest P of the tile against 2^OVF_LOG2 (also catches NaN)
         if (c >= 2) {  // the MMAs of tile c-2 have read p[pb]
           if (lane == 0) mbar_wait(&sm.pfree[pb], ((c >> 1) - 1) & 1);
           __syncwarp();
@@ -358,8 +368,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
         uint8_t* prow1 = reinterpret_cast<uint8_t*>(&sm.p[pb][rl1][0]);
 #pragma unroll
         for (int n4 = 0; n4 < 4; ++n4) {
-          const float a0 = ex2_approx(fmaf(s[n4][0], LOG2E, -ms0)), a1 = ex2_approx(fmaf(s[n4][1], LOG2E, -ms0));
-          const float b0 = ex2_approx(fmaf(s[n4][2], LOG2E, -ms1)), b1 = ex2_approx(fmaf(s[n4][3], LOG2E, -ms1));
+          const float a0 = s[n4][0], a1 = s[n4][1], b0 = s[n4][2], b1 = s[n4][3];
           l0 += a0 + a1, l1 += b0 + b1;
           const int chunk = kh * 4 + n4;  // 16-byte chunk = 8 keys
           *reinterpret_cast<uint32_t*>(prow0 + ((chunk ^ (rl0 & 7)) << 4) + qd * 4) = pack_bf16x2(a0, a1);
