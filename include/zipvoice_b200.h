@@ -94,6 +94,12 @@ int zv_text_condition(void* handle, const float* embed, const int64_t* tokens_le
 /* VocosFbank.extract / _feature_fn (zipvoice/utils/feature.py:56-116): wav (B,N) fp32 24 kHz mono,
  * lens (B) int64 valid samples -> log-mel (B, T, 100), T = (N + 128) / 256 frames. */
 int zv_fbank(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out, void* stream);
+/* BigVGANFbank.extract (zipvoice/utils/feature.py:133-204 on zipvoice/utils/_bigvgan_mel_feature.py:42-111; the
+ * alternative feature type of conf/zipvoice_base_bigvgan_v2.json, selected at bin/infer_zipvoice.py:585-586): reflect
+ * padding 384, un-centred frames, sqrt(|X|^2 + 1e-9), librosa Slaney mel basis, log(clamp(., 1e-5)).  Same shapes
+ * as zv_fbank. */
+int zv_fbank_bigvgan(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out,
+                     void* stream);
 
 /* torchaudio.transforms.Resample(orig_freq, new_freq) as the reference applies it to the prompt recording
  * (bin/infer_zipvoice.py:334-339; torchaudio defaults: sinc_interp_hann, lowpass_filter_width 6, rolloff 0.99):

@@ -55,3 +55,40 @@ def vocos_fbank(samples: torch.Tensor) -> torch.Tensor:
     elif logmel.shape[0] < t:
         logmel = torch.cat([logmel, logmel[-1:].expand(t - logmel.shape[0], -1)], 0)
     return logmel
+
+
+# ---------------------------------------------------------------- BigVGAN features (alternative vocoder config)
+def bigvgan_mel_basis() -> np.ndarray:
+    """librosa.filters.mel(sr=24000, n_fft=1024, n_mels=100, fmin=0, fmax=None) -> (100, 513), Slaney scale and
+    area normalisation (zipvoice/utils/_bigvgan_mel_feature.py:76-79; restated in oracle/shims/librosa/filters.py)."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "shims"))
+    try:
+        from librosa.filters import mel
+    finally:
+        sys.path.pop(0)
+    return mel(sr=SR, n_fft=N_FFT, n_mels=N_MELS, fmin=0, fmax=None)
+
+
+def bigvgan_fbank(samples: torch.Tensor) -> torch.Tensor:
+    """BigVGANFbank.extract, num_channels=1 (zipvoice/utils/feature.py:133-204 on
+    _bigvgan_mel_feature.py:42-111): reflect padding (1024 - 256) / 2 = 384 per side, frames WITHOUT centering,
+    periodic Hann, sqrt(re^2 + im^2 + 1e-9), Slaney mel basis, log(clamp(., 1e-5)) -> (T, 100) with T forced to
+    lhotse's compute_num_frames (replicating the last frame: the un-centred STFT yields N // 256 frames)."""
+    x = samples.reshape(-1).to(torch.float32)
+    n = x.numel()
+    pad = (N_FFT - HOP) // 2
+    xp = torch.nn.functional.pad(x[None, None], (pad, pad), mode="reflect")[0, 0]
+    frames = xp.unfold(0, N_FFT, HOP)
+    win = torch.hann_window(N_FFT, periodic=True)
+    spec = torch.fft.rfft(frames * win, dim=-1)
+    mag = torch.sqrt(spec.real ** 2 + spec.imag ** 2 + 1e-9)
+    mel = mag @ torch.from_numpy(bigvgan_mel_basis()).T
+    logmel = torch.log(torch.clamp(mel, min=1e-5))
+    t = num_frames(n)
+    if logmel.shape[0] > t:
+        logmel = logmel[:t]
+    elif logmel.shape[0] < t:
+        logmel = torch.cat([logmel, logmel[-1:].expand(t - logmel.shape[0], -1)], 0)
+    return logmel

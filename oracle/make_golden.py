@@ -159,8 +159,31 @@ def main():
     print("golden written to", OUT)
 
 
+def bigvgan():
+    """BigVGANFbank.extract of the unmodified reference (zipvoice/utils/feature.py:133-204) on seeded audio; ``lhotse``
+    and ``librosa`` come from oracle/shims (librosa.filters.mel is a restatement: that function is unpinned)."""
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "shims"))
+    sys.path.insert(0, REF)
+    from zipvoice.utils.feature import BigVGANFbank
+    from zipvoice_b200 import synth
+    fb = BigVGANFbank()
+    out = {}
+    for name, n in (("a", 12345), ("b", 24000 + 77), ("c", 30000 + 200), ("d", 256 * 40 + 128)):
+        wav = synth.make_audio(1, n, seed=7 + n)
+        out["wav_" + name] = wav.numpy()
+        out["mel_" + name] = fb.extract(wav, 24000).numpy()
+    st = synth.make_audio(2, 20000, seed=5)
+    out["wav_stereo"] = st.numpy()
+    out["mel_stereo_mono"] = fb.extract(st, 24000).numpy()            # num_channels=1: channel mean
+    out["mel_stereo_2ch"] = BigVGANFbank(num_channels=2).extract(st, 24000).numpy()
+    np.savez(os.path.join(OUT, "fbank_bigvgan.npz"), **out)
+    print("bigvgan golden written to", OUT)
+
+
 if __name__ == "__main__":
-    if "stereo" in sys.argv[1:]:
+    if "bigvgan" in sys.argv[1:]:
+        bigvgan()
+    elif "stereo" in sys.argv[1:]:
         stereo()
     elif "resample" in sys.argv[1:]:
         resample()

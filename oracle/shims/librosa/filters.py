@@ -1,2 +1,41 @@
-def mel(*a, **k):
-    raise NotImplementedError("librosa is not available; BigVGAN features are out of scope")
+"""TEST INFRASTRUCTURE ONLY -- restatement of ``librosa.filters.mel`` (librosa 0.10, third-party, source absent:
+PARITY UNPINNED for this one function) following its published algorithm: Slaney mel scale (linear below 1 kHz
+with 200/3 Hz per mel, logarithmic above with step ln(6.4)/27), triangular filters between consecutive mel
+points evaluated on the rfft bin frequencies, Slaney area normalisation 2 / (f[m+2] - f[m]); float64 arithmetic,
+result cast to float32.  Used by the reference at zipvoice/utils/_bigvgan_mel_feature.py:76-79."""
+import numpy as np
+
+_F_SP = 200.0 / 3.0
+_MIN_LOG_HZ = 1000.0
+_MIN_LOG_MEL = _MIN_LOG_HZ / _F_SP
+_LOGSTEP = np.log(6.4) / 27.0
+
+
+def hz_to_mel(f):
+    f = np.asarray(f, dtype=np.float64)
+    lin = f / _F_SP
+    log = _MIN_LOG_MEL + np.log(np.maximum(f, 1e-300) / _MIN_LOG_HZ) / _LOGSTEP
+    return np.where(f >= _MIN_LOG_HZ, log, lin)
+
+
+def mel_to_hz(m):
+    m = np.asarray(m, dtype=np.float64)
+    return np.where(m >= _MIN_LOG_MEL, _MIN_LOG_HZ * np.exp(_LOGSTEP * (m - _MIN_LOG_MEL)), _F_SP * m)
+
+
+def mel(*, sr, n_fft, n_mels=128, fmin=0.0, fmax=None, htk=False, norm="slaney", dtype=np.float32):
+    assert not htk and norm == "slaney", "only the defaults the reference uses are restated"
+    if fmax is None:
+        fmax = float(sr) / 2
+    fftfreqs = np.fft.rfftfreq(n=n_fft, d=1.0 / sr)
+    mel_f = mel_to_hz(np.linspace(hz_to_mel(fmin), hz_to_mel(fmax), n_mels + 2))
+    fdiff = np.diff(mel_f)
+    ramps = np.subtract.outer(mel_f, fftfreqs)
+    weights = np.zeros((n_mels, 1 + n_fft // 2), dtype=np.float64)
+    for i in range(n_mels):
+        lower = -ramps[i] / fdiff[i]
+        upper = ramps[i + 2] / fdiff[i + 1]
+        weights[i] = np.maximum(0, np.minimum(lower, upper))
+    enorm = 2.0 / (mel_f[2:n_mels + 2] - mel_f[:n_mels])
+    weights *= enorm[:, np.newaxis]
+    return weights.astype(dtype)

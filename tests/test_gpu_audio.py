@@ -63,6 +63,43 @@ def test_fbank_batch_ragged_and_numpy():
     assert float((m1 - want).abs().max()) < 2e-4
 
 
+def test_bigvgan_fbank_reference_golden_and_ragged_batch():
+    """BigVGANFbank features (feature.py:133-204) on the mel kernel: the golden of the unmodified reference class
+    (tests/golden/fbank_bigvgan.npz; mono, stereo averaged, two-channel), then a ragged padded batch against the
+    oracle.  log floor 1e-5 and the 1e-9 under the square root keep every value O(1): 2e-4 absolute as for VocosFbank."""
+    from oracle import fbank_oracle as FO
+    from zipvoice_b200 import synth
+    from zipvoice_b200.audio import BigVGANFbankB200
+    eng = audio()[0].engine
+    fb = BigVGANFbankB200(engine=eng)
+    g = np.load(os.path.join(GOLDEN, "fbank_bigvgan.npz"))
+    for name in ("a", "b", "c", "d"):
+        wav = torch.from_numpy(g["wav_" + name])
+        mel = fb.extract(wav, 24000).cpu()
+        want = torch.from_numpy(g["mel_" + name])
+        assert mel.shape == want.shape
+        err = float((mel - want).abs().max())
+        assert err < 2e-4, f"{name}: max-abs {err:.3e}"
+    st = torch.from_numpy(g["wav_stereo"])
+    assert float((fb.extract(st, 24000).cpu() - torch.from_numpy(g["mel_stereo_mono"])).abs().max()) < 2e-4
+    fb2 = BigVGANFbankB200(engine=eng, num_channels=2)
+    m2 = fb2.extract(st, 24000).cpu()
+    assert m2.shape == (FO.num_frames(st.shape[1]), 200)
+    assert float((m2 - torch.from_numpy(g["mel_stereo_2ch"])).abs().max()) < 2e-4
+    lens = torch.tensor([48000, 31234, 20000, 47999, 1024 + 128])
+    wav = synth.make_audio(5, 48000, seed=13)
+    wav = wav * (torch.arange(48000)[None] < lens[:, None])
+    mel = fb.extract_batch(wav, lens).cpu()
+    for b in range(5):
+        want = FO.bigvgan_fbank(wav[b, : int(lens[b])])
+        t = want.shape[0]
+        assert float((mel[b, :t] - want).abs().max()) < 2e-4, b
+        if t < mel.shape[1]:
+            assert float(mel[b, t:].abs().max()) == 0.0
+    with pytest.raises(AssertionError):
+        fb.extract(wav[0], 16000)
+
+
 @pytest.mark.parametrize("B,T", [(1, 50), (3, 281), (2, 938)])
 def test_vocos_decode_vs_oracle(B, T):
     from oracle import vocos_oracle as VO

@@ -115,6 +115,26 @@ def test_fbank_oracle_vs_reference_golden():
         assert float((mel - g["mel_" + name]).abs().max()) < 1e-4
 
 
+def test_bigvgan_fbank_oracle_vs_reference_golden():
+    """oracle/fbank_oracle.bigvgan_fbank against BigVGANFbank.extract of the unmodified reference (lhotse shimmed,
+    librosa.filters.mel restated in oracle/shims: the mel basis itself is unpinned, everything around it is pinned)."""
+    from oracle import fbank_oracle as FO
+    g = _g("fbank_bigvgan.npz")
+    for name in ("a", "b", "c", "d"):
+        wav = g["wav_" + name]
+        mel = FO.bigvgan_fbank(wav[0])
+        assert mel.shape == g["mel_" + name].shape == (FO.num_frames(wav.shape[1]), 100)
+        assert float((mel - g["mel_" + name]).abs().max()) < 1e-4
+    st = g["wav_stereo"]
+    assert float((FO.bigvgan_fbank(st.mean(0)) - g["mel_stereo_mono"]).abs().max()) < 1e-4
+    two = torch.cat([FO.bigvgan_fbank(st[0]), FO.bigvgan_fbank(st[1])], dim=1)
+    assert float((two - g["mel_stereo_2ch"]).abs().max()) < 1e-4
+    basis = FO.bigvgan_mel_basis()
+    assert basis.shape == (100, 513) and basis.dtype == np.float32
+    # Slaney area normalisation: every filter integrates to ~1 Hz^-1 x bin width
+    assert np.allclose(basis.sum(1) * (24000 / 1024), 1.0, atol=0.15)
+
+
 def test_resample_oracle_vs_torchaudio_golden():
     """oracle/resample_oracle.py against torchaudio.transforms.Resample outputs (tests/golden/resample.npz,
     oracle/make_golden.py resample); fp32 dot products of up to ~480 taps in another order: 2e-5 absolute."""

@@ -43,6 +43,7 @@ _SIGS = {
     "zv_text_embed": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "zv_text_condition": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P, _P]),
     "zv_fbank": (_I, [_P, _P, _P, _I, _I, _P, _P]),
+    "zv_fbank_bigvgan": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "zv_vocos_decode": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "zv_resample": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P]),
     "zv_debug_gemm": (_I, [_I, _I, _I, _I, _I, _I, _I] + [_P] * 12),

@@ -29,6 +29,7 @@ class VocosFbankB200:
     """num_channels 1 (mono; stereo input is averaged) or 2 (per-channel mels concatenated)."""
 
     sampling_rate, n_mels, n_fft, hop_length = 24000, 100, 1024, 256
+    kind = "vocos"  # which feature kernel of the engine (BigVGANFbankB200 overrides)
 
     def __init__(self, engine: Optional[Engine] = None, num_channels: int = 1, device="cuda:0"):
         assert num_channels in (1, 2)
@@ -57,13 +58,22 @@ class VocosFbankB200:
                 samples = samples.mean(dim=0, keepdims=True)
         else:
             assert samples.shape[0] == 2, samples.shape
-        mel = self.engine.fbank(samples.float())                 # (C, T, 100)
+        mel = self.engine.fbank(samples.float(), kind=self.kind)  # (C, T, 100)
         mel = mel.permute(1, 0, 2).reshape(mel.shape[1], -1)     # (T, 100 * C)
         return mel.cpu().numpy() if is_numpy else mel
 
     def extract_batch(self, samples: torch.Tensor, lens: Optional[torch.Tensor] = None) -> torch.Tensor:
         """(B, N) padded mono batch with valid lengths -> (B, T, 100); frames past an utterance are 0."""
-        return self.engine.fbank(samples, lens)
+        return self.engine.fbank(samples, lens, kind=self.kind)
+
+
+class BigVGANFbankB200(VocosFbankB200):
+    """BigVGANFbank (zipvoice/utils/feature.py:133-204; feature type "bigvgan_v2", bin/infer_zipvoice.py:585-586): same
+    interface and frame count as VocosFbank, features = log(clamp(slaney_mel(sqrt(|STFT|^2 + 1e-9)), 1e-5)) of frames
+    that are NOT centred (reflect padding (n_fft - hop) / 2).  The bigvgan vocoder itself is a third-party network
+    (``bigvgan`` package, absent here) and is not part of this path."""
+
+    kind = "bigvgan"
 
 
 class VocosB200:

@@ -30,6 +30,9 @@ struct Audio {
   int* fb_count = nullptr;
   int* fb_off = nullptr;      // offset of its weights in fb_w
   float* fb_w = nullptr;
+  // the same four arrays for the BigVGAN features: librosa Slaney mel basis with area normalisation
+  int *sl_start = nullptr, *sl_count = nullptr, *sl_off = nullptr;
+  float* sl_w = nullptr;
   // vocoder weights
   bool has_vocoder = false;
   Lin embed, pw1[VC_LAYERS], pw2[VC_LAYERS], head;
@@ -84,6 +87,37 @@ static int audio_tables(Engine& e, Audio& a) {
     start[m] = first < 0 ? 0 : first, count[m] = first < 0 ? 0 : last - first + 1, off[m] = (int)w.size();
     for (int k = 0; k < count[m]; ++k) w.push_back(row[start[m] + k]);
   }
+  // librosa.filters.mel(sr=24000, n_fft=1024, n_mels=100, fmin=0, fmax=None): Slaney scale (200/3 Hz per mel below
+  // 1 kHz, logarithmic above with step ln(6.4)/27), triangles on the rfft bin frequencies, each filter scaled by
+  // 2 / (f[m+2] - f[m]); double arithmetic, fp32 weights (zipvoice/utils/_bigvgan_mel_feature.py:76-79)
+  std::vector<int> sl_start(N_MELS), sl_count(N_MELS), sl_off(N_MELS);
+  std::vector<float> sl_w;
+  {
+    const double f_sp = 200.0 / 3.0, min_log_hz = 1000.0, min_log_mel = min_log_hz / f_sp, logstep = log(6.4) / 27.0;
+    auto hz2sl = [&](double f) { return f >= min_log_hz ? min_log_mel + log(f / min_log_hz) / logstep : f / f_sp; };
+    auto sl2hz = [&](double m) { return m >= min_log_mel ? min_log_hz * exp(logstep * (m - min_log_mel)) : f_sp * m; };
+    std::vector<double> mf(N_MELS + 2);
+    const double lo = hz2sl(0.0), hi = hz2sl(f_max);
+    for (int i = 0; i < N_MELS + 2; ++i) mf[i] = sl2hz(lo + (hi - lo) * i / (N_MELS + 1));
+    for (int m = 0; m < N_MELS; ++m) {
+      int first = -1, last = -2;
+      std::vector<float> row(N_BINS, 0.f);
+      const double enorm = 2.0 / (mf[m + 2] - mf[m]);
+      for (int k = 0; k < N_BINS; ++k) {
+        const double f = 24000.0 * k / N_FFT;
+        const double lower = (f - mf[m]) / (mf[m + 1] - mf[m]);
+        const double upper = (mf[m + 2] - f) / (mf[m + 2] - mf[m + 1]);
+        const double v = fmin(lower, upper);
+        if (v > 0.0) {
+          row[k] = (float)(v * enorm);
+          if (first < 0) first = k;
+          last = k;
+        }
+      }
+      sl_start[m] = first < 0 ? 0 : first, sl_count[m] = first < 0 ? 0 : last - first + 1, sl_off[m] = (int)sl_w.size();
+      for (int k = 0; k < sl_count[m]; ++k) sl_w.push_back(row[sl_start[m] + k]);
+    }
+  }
   auto up = [&](const void* src, size_t bytes, void** dst) {
     int rc = dev_alloc(e, e.weight_allocs, dst, bytes);
     if (rc) return rc;
@@ -95,11 +129,24 @@ static int audio_tables(Engine& e, Audio& a) {
   if (!rc) rc = up(count.data(), N_MELS * 4, (void**)&a.fb_count);
   if (!rc) rc = up(off.data(), N_MELS * 4, (void**)&a.fb_off);
   if (!rc) rc = up(w.data(), w.size() * 4, (void**)&a.fb_w);
+  if (!rc) rc = up(sl_start.data(), N_MELS * 4, (void**)&a.sl_start);
+  if (!rc) rc = up(sl_count.data(), N_MELS * 4, (void**)&a.sl_count);
+  if (!rc) rc = up(sl_off.data(), N_MELS * 4, (void**)&a.sl_off);
+  if (!rc) rc = up(sl_w.data(), sl_w.size() * 4, (void**)&a.sl_w);
   return rc;
 }
 
 // ------------------------------------------------------------------ mel front-end
 // CTA = 256 threads = 4 frame groups of 64 threads; each group transforms one frame per iteration.
+// The two feature types of zipvoice/utils/feature.py share the kernel:
+//   VocosFbank   (:36-120)  frames centred (reflect pad 512), N / 256 + 1 STFT frames, |X|, HTK basis, log clamp 1e-7
+//   BigVGANFbank (:133-204) reflect pad (1024 - 256) / 2 = 384 and no centring, N / 256 frames,
+//                           sqrt(|X|^2 + 1e-9), Slaney basis, log clamp 1e-5
+struct FbankVariant {
+  int pad;           // samples of reflect padding before frame 0
+  int extra_frames;  // STFT frames = len / HOP + extra_frames
+  float mag_eps, log_floor;
+};
 struct FftSmem {
   float2 tw512[512];
   float2 tw1024[1024];
@@ -112,7 +159,7 @@ __global__ void __launch_bounds__(256) fbank_kernel(const float* __restrict__ wa
                                                     const float2* __restrict__ tw1024g,
                                                     const int* __restrict__ fb_start, const int* __restrict__ fb_count,
                                                     const int* __restrict__ fb_off, const float* __restrict__ fb_w,
-                                                    int frames_per_cta, float* __restrict__ mel) {
+                                                    int frames_per_cta, FbankVariant var, float* __restrict__ mel) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   FftSmem& sm = *reinterpret_cast<FftSmem*>(smem_raw);
   const int tid = threadIdx.x, g = tid >> 6, j = tid & 63;
@@ -122,7 +169,7 @@ __global__ void __launch_bounds__(256) fbank_kernel(const float* __restrict__ wa
   __syncthreads();
   const long long len = lens ? lens[b] : (long long)N;
   const int Tb = (int)((len + HOP / 2) / HOP);  // lhotse compute_num_frames (round half up)
-  const int n_spec = (int)(len / HOP) + 1;      // frames torchaudio computes (center=True)
+  const int n_spec = max((int)(len / HOP) + var.extra_frames, 1);  // frames the reference STFT computes
   const float* x = wav + (size_t)b * N;
   const int t_begin = blockIdx.x * frames_per_cta;
   for (int it = 0; it < frames_per_cta; it += 4) {
@@ -136,7 +183,7 @@ __global__ void __launch_bounds__(256) fbank_kernel(const float* __restrict__ wa
       const int n = j + 64 * r;
       float2 z = make_float2(0.f, 0.f);
       if (live) {
-        long long s0 = (long long)ts * HOP - N_FFT / 2 + 2 * n, s1 = s0 + 1;
+        long long s0 = (long long)ts * HOP - var.pad + 2 * n, s1 = s0 + 1;
         s0 = s0 < 0 ? -s0 : (s0 >= len ? 2 * (len - 1) - s0 : s0);
         s1 = s1 < 0 ? -s1 : (s1 >= len ? 2 * (len - 1) - s1 : s1);
         s0 = max(0ll, min(s0, len - 1)), s1 = max(0ll, min(s1, len - 1));
@@ -150,11 +197,11 @@ __global__ void __launch_bounds__(256) fbank_kernel(const float* __restrict__ wa
     for (int r = 0; r < 8; ++r) {
       const int k = j + 64 * r;
       const float2 X = rfft_unpack(sm.buf[g], k, sm.tw1024[k]);
-      sm.mag[g][k] = sqrtf(X.x * X.x + X.y * X.y);
+      sm.mag[g][k] = sqrtf(X.x * X.x + X.y * X.y + var.mag_eps);
     }
     if (j == 0) {
       const float2 X = rfft_unpack(sm.buf[g], 512, make_float2(-1.f, 0.f));
-      sm.mag[g][512] = sqrtf(X.x * X.x + X.y * X.y);
+      sm.mag[g][512] = sqrtf(X.x * X.x + X.y * X.y + var.mag_eps);
     }
     __syncthreads();
     for (int m = j; m < N_MELS; m += 64) {
@@ -162,7 +209,7 @@ __global__ void __launch_bounds__(256) fbank_kernel(const float* __restrict__ wa
       const float* w = fb_w + fb_off[m];
       float acc = 0.f;
       for (int k = 0; k < cnt; ++k) acc = fmaf(sm.mag[g][st + k], __ldg(w + k), acc);
-      if (t < T) mel[((size_t)b * T + t) * N_MELS + m] = live ? logf(fmaxf(acc, 1e-7f)) : 0.f;
+      if (t < T) mel[((size_t)b * T + t) * N_MELS + m] = live ? logf(fmaxf(acc, var.log_floor)) : 0.f;
     }
     __syncthreads();
   }
@@ -583,8 +630,8 @@ static int resample_bank(Engine& e, Audio& a, int orig_freq, int new_freq, const
 
 using namespace zv;
 
-extern "C" int zv_fbank(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out,
-                        void* stream) {
+static int fbank_launch(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out,
+                        void* stream, bool bigvgan) {
   Engine* ep = (Engine*)handle;
   if (!ep) return 960;
   Engine& e = *ep;
@@ -605,10 +652,22 @@ extern "C" int zv_fbank(void* handle, const float* wav, const int64_t* lens, int
   }
   dim3 grid((T + fpc - 1) / fpc, B);
   // algorithmic bytes: 4 B per input sample + 400 B per output frame
+  const FbankVariant var = bigvgan ? FbankVariant{(N_FFT - HOP) / 2, 0, 1e-9f, 1e-5f} : FbankVariant{N_FFT / 2, 1, 0.f, 1e-7f};
   AU_K(KC_FBANK, (double)B * N * 4.0 + (double)B * T * N_MELS * 4.0, s,
-       (fbank_kernel<<<grid, 256, sizeof(FftSmem), s>>>(wav, lens, N, T, a.tw512, a.tw1024, a.fb_start, a.fb_count,
-                                                        a.fb_off, a.fb_w, fpc, mel_out)));
+       (fbank_kernel<<<grid, 256, sizeof(FftSmem), s>>>(
+           wav, lens, N, T, a.tw512, a.tw1024, bigvgan ? a.sl_start : a.fb_start, bigvgan ? a.sl_count : a.fb_count,
+           bigvgan ? a.sl_off : a.fb_off, bigvgan ? a.sl_w : a.fb_w, fpc, var, mel_out)));
   return 0;
+}
+
+extern "C" int zv_fbank(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out,
+                        void* stream) {
+  return fbank_launch(handle, wav, lens, B, N, mel_out, stream, false);
+}
+
+extern "C" int zv_fbank_bigvgan(void* handle, const float* wav, const int64_t* lens, int B, int N, float* mel_out,
+                                void* stream) {
+  return fbank_launch(handle, wav, lens, B, N, mel_out, stream, true);
 }
 
 extern "C" int zv_vocos_decode(void* handle, const float* mel, const int64_t* lens, int B, int T, float* wav_out,

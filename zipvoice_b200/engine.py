@@ -164,15 +164,18 @@ class Engine:
         return out, mask.bool()
 
     # ------------------------------------------------------------------ audio front-end / vocoder
-    def fbank(self, wav: torch.Tensor, lens: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """VocosFbank log-mel (feature.py:56-116): wav (B, N) fp32 24 kHz mono -> (B, (N + 128) // 256, 100)."""
+    def fbank(self, wav: torch.Tensor, lens: Optional[torch.Tensor] = None, kind: str = "vocos") -> torch.Tensor:
+        """VocosFbank log-mel (feature.py:56-116), or with kind="bigvgan" the BigVGANFbank features (feature.py:133-204):
+        wav (B, N) fp32 24 kHz mono -> (B, (N + 128) // 256, 100)."""
+        assert kind in ("vocos", "bigvgan"), kind
         w = self._prep(wav)
         B, N = w.shape
         ln = None if lens is None else self._prep(lens, torch.int64)
         T = (N + 128) // 256
         out = torch.empty(B, T, 100, device=self.device, dtype=torch.float32)
         with torch.cuda.device(self.device):
-            self._check(self.lib.zv_fbank(self._h, _ptr(w), _ptr(ln), B, N, _ptr(out), _stream(self.device)))
+            fn = self.lib.zv_fbank if kind == "vocos" else self.lib.zv_fbank_bigvgan
+            self._check(fn(self._h, _ptr(w), _ptr(ln), B, N, _ptr(out), _stream(self.device)))
         return out
 
     def resample(self, wav: torch.Tensor, orig_freq: int, new_freq: int,
