@@ -11,42 +11,38 @@ namespace zv {
 static inline unsigned blocks_for(size_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
 // ------------------------------------------------------------------ input packing (+ CFG doubling)
+// One CTA per output row (no per-element index division); a thread packs one pair of columns.  Fx and Ft are even
+// (checked by the launcher), so a pair never straddles two segments and is fetched with one 8-byte load.
 __global__ void pack_input_kernel(const float* __restrict__ x, const float* __restrict__ text,
                                   const float* __restrict__ speech, const uint8_t* __restrict__ mask, int B, int T,
                                   int Fx, int Ft, int cfg, int zero_speech_uncond, bf16* __restrict__ out, int ldo,
                                   uint8_t* __restrict__ mask_out) {
-  // one thread per (row, pair of output columns)
-  const int half = ldo >> 1;
-  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int nb = cfg ? 2 * B : B;
-  if (gid >= (size_t)nb * T * half) return;
-  const int c = (int)(gid % half) * 2;
-  const size_t row = gid / half;
-  const int t = (int)(row % T);
-  const int bo = (int)(row / T);
-  const int b = cfg ? (bo % B) : bo;
+  const int row = blockIdx.x;  // bo * T + t
+  const int bo = row / T, t = row - bo * T;
+  const int b = (cfg && bo >= B) ? bo - B : bo;
   const bool uncond = cfg && bo < B;
   // row = [x (Fx) | text (Ft) | speech (Fx)]: Fx = Ft for the mono models, Fx = 2 Ft for the two-channel dialog model
   const size_t rowi = (size_t)b * T + t;
-  float v[2];
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int cc = c + i;
-    float val = 0.f;
-    if (cc < Fx) val = x[rowi * Fx + cc];
-    else if (cc < Fx + Ft) val = uncond ? 0.f : text[rowi * Ft + cc - Fx];
-    else if (cc < 2 * Fx + Ft) val = (uncond && zero_speech_uncond) ? 0.f : speech[rowi * Fx + cc - Fx - Ft];
-    v[i] = val;
+  for (int c = threadIdx.x * 2; c < ldo; c += blockDim.x * 2) {
+    float2 v = make_float2(0.f, 0.f);
+    if (c < Fx) v = *reinterpret_cast<const float2*>(x + rowi * Fx + c);
+    else if (c < Fx + Ft) {
+      if (!uncond) v = *reinterpret_cast<const float2*>(text + rowi * Ft + c - Fx);
+    } else if (c < 2 * Fx + Ft) {
+      if (!(uncond && zero_speech_uncond)) v = *reinterpret_cast<const float2*>(speech + rowi * Fx + c - Fx - Ft);
+    }
+    *reinterpret_cast<uint32_t*>(out + (size_t)row * ldo + c) = pack_bf16x2(v.x, v.y);
   }
-  *reinterpret_cast<uint32_t*>(out + row * ldo + c) = pack_bf16x2(v[0], v[1]);
-  if (c == 0 && mask_out) mask_out[row] = mask ? mask[(size_t)b * T + t] : 0;
+  if (threadIdx.x == 0 && mask_out) mask_out[row] = mask ? mask[rowi] : 0;
 }
 
 int pack_input(const float* x, const float* text, const float* speech, const uint8_t* mask, int B, int T, int Fx,
                int Ft, int cfg, int zero_speech_uncond, bf16* out, int ldo, uint8_t* mask_out, cudaStream_t s) {
-  const size_t n = (size_t)(cfg ? 2 * B : B) * T * (ldo / 2);
-  pack_input_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, text, speech, mask, B, T, Fx, Ft, cfg, zero_speech_uncond,
-                                                       out, ldo, mask_out);
+  if ((Fx & 1) || (Ft & 1) || (ldo & 1)) return 913;
+  const int rows = (cfg ? 2 * B : B) * T;
+  const int threads = ((ldo / 2 + 31) / 32) * 32;
+  pack_input_kernel<<<rows, threads < 256 ? threads : 256, 0, s>>>(x, text, speech, mask, B, T, Fx, Ft, cfg,
+                                                                    zero_speech_uncond, out, ldo, mask_out);
   return (int)cudaGetLastError();
 }
 
