@@ -147,7 +147,6 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
   for (int n = 0; n < DV / 8; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
   uint32_t qa[2][4];
-  const float LOG2E = 1.4426950408889634f;
 
   for (int kt = 0; kt < n_tiles; ++kt) {
     // three-stage ring, one barrier per tile: after it every warp has finished tile kt - 1, whose
@@ -200,8 +199,8 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
           float b0 = s[nt][2] + pq1[0] * ep0.x + pq1[1] * ep0.y + pq1[2] * ep0.z + pq1[3] * ep0.w;
           float b1 = s[nt][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
           const uint8_t k0 = mrow[nt * 8 + 2 * qd], k1 = mrow[nt * 8 + 2 * qd + 1];
-          if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
-          if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
+          if (k0) a0 = b0 = (k0 == 1 ? ATTN_MASKED : -INFINITY);
+          if (k1) a1 = b1 = (k1 == 1 ? ATTN_MASKED : -INFINITY);
           s[nt][0] = a0, s[nt][1] = a1, s[nt][2] = b0, s[nt][3] = b1;
           mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
           ep0 = ec0, ep1 = ec1;
@@ -214,19 +213,19 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
     mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
     const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
     const bool grow = (mn0 != m0) || (mn1 != m1);
-    const float ms0 = mn0 * LOG2E, ms1 = mn1 * LOG2E;
+    const float ms0 = mn0, ms1 = mn1;  // scores are in log2 units
     float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        const float pa = ex2_approx(fmaf(s[nt][e], LOG2E, -ms0)), pb = ex2_approx(fmaf(s[nt][2 + e], LOG2E, -ms1));
+        const float pa = ex2_approx(s[nt][e] - ms0), pb = ex2_approx(s[nt][2 + e] - ms1);
         s[nt][e] = pa, s[nt][2 + e] = pb;
         rs0 += pa, rs1 += pb;
       }
     }
     if (__any_sync(0xffffffffu, grow)) {  // warp-uniform: rescale only when some row's running max moved
-      const float sc0 = ex2_approx((m0 - mn0) * LOG2E), sc1 = ex2_approx((m1 - mn1) * LOG2E);
+      const float sc0 = ex2_approx(m0 - mn0), sc1 = ex2_approx(m1 - mn1);
       l0 *= sc0, l1 *= sc1;
 #pragma unroll
       for (int n = 0; n < DV / 8; ++n) o[n][0] *= sc0, o[n][1] *= sc0, o[n][2] *= sc1, o[n][3] *= sc1;

@@ -144,7 +144,6 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
 #pragma unroll
     for (int n = 0; n < 2; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
     float m0 = -INFINITY, m1 = -INFINITY;  // the row sums live in column dv of O (V carries a ones column)
-    const float LOG2E = 1.4426950408889634f;
     uint32_t qa[2][4];
     mbar_wait(&sm.qbar, 0);
     {
@@ -177,8 +176,13 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       float s[8][4];
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
-        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-        if (TAIL && nt >= nbv) continue;
+        // SPEC: the accumulators start at minus the reference (scores are in log2 units), so the finished score
+        // is the exponent itself
+        s[nt][0] = s[nt][1] = SPEC ? -m0 : 0.f, s[nt][2] = s[nt][3] = SPEC ? -m1 : 0.f;
+        if (TAIL && nt >= nbv) {
+          s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+          continue;
+        }
         uint32_t kb[4];
         ldsm_x4(kb, kbase + sw64(nt * 8 + (lane & 7), lane >> 3));
         mma_f16(s[nt], qa[0], kb[0], kb[1]);
@@ -188,7 +192,6 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       //      SPEC: P right away (mx0 / mx1 then hold the largest P of the two rows: the vote below depends on the
       //      exponentials, which keeps them next to the FMAs in the schedule instead of behind the branch)
       float mx0 = -INFINITY, mx1 = -INFINITY;
-      const float msr0 = m0 * LOG2E, msr1 = m1 * LOG2E;
       {
         const float4* ew = &S.e[2 * qd - rl0 + (BQ - 1)];
         float4 ep0 = ew[-8], ep1 = ew[-7];
@@ -202,13 +205,10 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
           float b1 = s[nt][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
           if (MASKED) {
             const uint8_t k0 = mrow[nt * 8 + 2 * qd], k1 = mrow[nt * 8 + 2 * qd + 1];
-            if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
-            if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
+            if (k0) a0 = (k0 == 1 ? ATTN_MASKED - (SPEC ? m0 : 0.f) : -INFINITY), b0 = (k0 == 1 ? ATTN_MASKED - (SPEC ? m1 : 0.f) : -INFINITY);
+            if (k1) a1 = (k1 == 1 ? ATTN_MASKED - (SPEC ? m0 : 0.f) : -INFINITY), b1 = (k1 == 1 ? ATTN_MASKED - (SPEC ? m1 : 0.f) : -INFINITY);
           }
-          if (SPEC) {
-            a0 = ex2_approx(fmaf(a0, LOG2E, -msr0)), a1 = ex2_approx(fmaf(a1, LOG2E, -msr0));
-            b0 = ex2_approx(fmaf(b0, LOG2E, -msr1)), b1 = ex2_approx(fmaf(b1, LOG2E, -msr1));
-          }
+          if (SPEC) a0 = ex2_approx(a0), a1 = ex2_approx(a1), b0 = ex2_approx(b0), b1 = ex2_approx(b1);
           s[nt][0] = a0, s[nt][1] = a1, s[nt][2] = b0, s[nt][3] = b1;
           mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
           ep0 = ec0, ep1 = ec1;
@@ -222,13 +222,13 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
         mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
         mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
       }
-      const float ms0 = mn0 * LOG2E, ms1 = mn1 * LOG2E;
+      const float ms0 = mn0, ms1 = mn1;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
         if (SPEC || (TAIL && nt >= nbv)) break;  // s stays 0 = P of the absent keys
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-          const float pa = ex2_approx(fmaf(s[nt][e], LOG2E, -ms0)), pb = ex2_approx(fmaf(s[nt][2 + e], LOG2E, -ms1));
+          const float pa = ex2_approx(s[nt][e] - ms0), pb = ex2_approx(s[nt][2 + e] - ms1);
           s[nt][e] = pa, s[nt][2 + e] = pb;
         }
       }
@@ -237,7 +237,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
         const float bound = 18446744073709551616.0f;  // 2^SPEC_LOG2
         if (__any_sync(0xffffffffu, !(fmaxf(mx0, mx1) <= bound))) return false;
       } else if (__any_sync(0xffffffffu, (mn0 != m0) || (mn1 != m1))) {
-        const float sc0 = ex2_approx((m0 - mn0) * LOG2E), sc1 = ex2_approx((m1 - mn1) * LOG2E);
+        const float sc0 = ex2_approx(m0 - mn0), sc1 = ex2_approx(m1 - mn1);
 #pragma unroll
         for (int n = 0; n < 2; ++n) o[n][0] *= sc0, o[n][1] *= sc0, o[n][2] *= sc1, o[n][3] *= sc1;
         m0 = mn0, m1 = mn1;

@@ -90,8 +90,9 @@ ZV_DEVINL uint32_t make_idesc_bf16_bmn(uint32_t M, uint32_t N) {
 // Returns the two row maxima through mx0 / mx1.
 // MASKED is a template parameter so that the caller takes ONE warp-uniform branch per tile instead of
 // ~45 predicated mask instructions that occupy issue slots on mask-free tiles.
-// EXP: the value sweep -- s becomes P = exp2(S log2e - ms) right where each score is finished, so that the MUFU
-// work interleaves with the position FMAs of the next block; mx0 / mx1 then hold the largest P of the two rows.
+// EXP: the value sweep -- the MMA accumulators start at minus the reference (scores are in log2 units), so a
+// finished score is the exponent of P = exp2(S - ms); the exponentials are taken right there and interleave with the
+// position FMAs of the next block; mx0 / mx1 then hold the largest P of the two rows.
 template <bool MASKED, bool EXP>
 ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, int kh, int lane, int rl0,
                           const uint32_t (&qa)[2][4], const float (&pq0)[4], const float (&pq1)[4], float (&s)[4][4],
@@ -101,7 +102,7 @@ ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, int kh, 
 #pragma unroll
   for (int n4 = 0; n4 < 4; ++n4) {
     const int nt = kh * 4 + n4;
-    s[n4][0] = s[n4][1] = s[n4][2] = s[n4][3] = 0.f;
+    s[n4][0] = s[n4][1] = EXP ? -ms0 : 0.f, s[n4][2] = s[n4][3] = EXP ? -ms1 : 0.f;
     uint32_t kb[4];
     ldsm_x4(kb, kbase + sw64(nt * 8 + (lane & 7), lane >> 3));
     mma_f16(s[n4], qa[0], kb[0], kb[1]);
@@ -119,14 +120,10 @@ ZV_DEVINL void score_tile(const Smem& sm, int buf, const uint8_t* mrow, int kh, 
     float b1 = s[n4][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
     if (MASKED) {
       const uint8_t k0 = mrow[kh * 32 + n4 * 8 + 2 * qd], k1 = mrow[kh * 32 + n4 * 8 + 2 * qd + 1];
-      if (k0) a0 = b0 = (k0 == 1 ? -1000.0f : -INFINITY);
-      if (k1) a1 = b1 = (k1 == 1 ? -1000.0f : -INFINITY);
+      if (k0) a0 = (k0 == 1 ? ATTN_MASKED - (EXP ? ms0 : 0.f) : -INFINITY), b0 = (k0 == 1 ? ATTN_MASKED - (EXP ? ms1 : 0.f) : -INFINITY);
+      if (k1) a1 = (k1 == 1 ? ATTN_MASKED - (EXP ? ms0 : 0.f) : -INFINITY), b1 = (k1 == 1 ? ATTN_MASKED - (EXP ? ms1 : 0.f) : -INFINITY);
     }
-    if (EXP) {
-      const float LOG2E = 1.4426950408889634f;
-      a0 = ex2_approx(fmaf(a0, LOG2E, -ms0)), a1 = ex2_approx(fmaf(a1, LOG2E, -ms0));
-      b0 = ex2_approx(fmaf(b0, LOG2E, -ms1)), b1 = ex2_approx(fmaf(b1, LOG2E, -ms1));
-    }
+    if (EXP) a0 = ex2_approx(a0), a1 = ex2_approx(a1), b0 = ex2_approx(b0), b1 = ex2_approx(b1);
     s[n4][0] = a0, s[n4][1] = a1, s[n4][2] = b0, s[n4][3] = b1;
     mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
     ep0 = ec0, ep1 = ec1;
@@ -307,7 +304,6 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
     }
     uint32_t qa[2][4];
     float s[4][4];
-    const float LOG2E = 1.4426950408889634f;
     float m0, m1;
     mbar_wait(&sm.qbar, 0);
     {
@@ -346,7 +342,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
     // Returns true if some score of this thread exceeded its reference by more than OVF_LOG2.
     float l0 = 0.f, l1 = 0.f;
     auto value_sweep = [&](int c0) -> bool {
-      const float ms0 = m0 * LOG2E, ms1 = m1 * LOG2E;
+      const float ms0 = m0, ms1 = m1;  // log2 units
       bool ovf = false;
       l0 = 0.f, l1 = 0.f;
       for (int kt = 0; kt < n_tiles; ++kt, ++gt) {

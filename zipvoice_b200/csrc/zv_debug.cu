@@ -84,6 +84,17 @@ __global__ void pad_heads_kernel(const float* __restrict__ in, size_t rows, int 
   out[gid] = __float2bfloat16(c < dv ? in[r * ld_in + h * dv + c] : (c == dv ? 1.0f : 0.f));  // ones column at dv
 }
 
+// natural-unit test inputs -> the log2-unit contract of the attention kernels (ATTN_LOG2E, zv_kernels.h):
+// q columns [0, nq) of the fp16 q | k | p rows and the whole position table are scaled by log2(e)
+__global__ void cvt_qkp_log2_kernel(const float* __restrict__ in, size_t n, int ldq, int nq, __half* __restrict__ out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = __float2half_rn(in[i] * ((int)(i % ldq) < nq ? ATTN_LOG2E : 1.0f));
+}
+__global__ void scale_f32_kernel(const float* __restrict__ in, size_t n, float sc, float* __restrict__ out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = in[i] * sc;
+}
+
 extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp_f32, int ldq,
                                   const float* E, const uint8_t* mask, const float* V_f32, int ldv,
                                   const float* gate_f32, float* out_f32, void* stream) {
@@ -93,7 +104,12 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
   cudaMalloc(&q, rows * ldq * 2);
   cudaMalloc(&v, rows * ldv * 2);
   cudaMalloc(&o, rows * ldv * 2);
-  cvt_f16_kernel<<<(unsigned)((rows * ldq + 255) / 256), 256, 0, s>>>(qkp_f32, rows * ldq, reinterpret_cast<__half*>(q));
+  cvt_qkp_log2_kernel<<<(unsigned)((rows * ldq + 255) / 256), 256, 0, s>>>(qkp_f32, rows * ldq, ldq, H * 32,
+                                                                          reinterpret_cast<__half*>(q));
+  float* Es = nullptr;
+  const size_t ne = (size_t)H * (2 * L - 1) * 4;
+  cudaMalloc(&Es, ne * 4);
+  scale_f32_kernel<<<(unsigned)((ne + 255) / 256), 256, 0, s>>>(E, ne, ATTN_LOG2E, Es);
   const bool sa_pad = heads > 1 && dv == 12;  // SelfAttention: 16 columns per head (12 + 4 zeros)
   if (sa_pad) {
     cudaFree(v);
@@ -108,7 +124,7 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
   }
   cudaMemsetAsync(o, 0, rows * ldv * 2, s);
   AttnParams a;
-  a.qkp = q, a.ldq = ldq, a.E = E, a.mask = mask, a.V = v, a.ldv = ldv, a.gate = g, a.ldg = ldv, a.out = o, a.ldo = ldv;
+  a.qkp = q, a.ldq = ldq, a.E = Es, a.mask = mask, a.V = v, a.ldv = ldv, a.gate = g, a.ldg = ldv, a.out = o, a.ldo = ldv;
   a.nb = nb, a.L = L, a.H = H, a.heads = heads, a.dv = dv;
   if (sa_pad) a.ldv = heads * 16, a.vhs = 16;
   int rc = attention(a, s);
@@ -116,7 +132,7 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
     cvt_back(o, rows * ldv, out_f32, s);
     rc = (int)cudaStreamSynchronize(s);
   }
-  cudaFree(q), cudaFree(v), cudaFree(o);
+  cudaFree(q), cudaFree(v), cudaFree(o), cudaFree(Es);
   if (g) cudaFree(g);
   return rc;
 }

@@ -209,8 +209,25 @@ static int fold_self_attn_into_conv(Engine& e, const std::string& so, const std:
 }
 
 static int build_layer(Engine& e, Net& net, const std::string& p, int kernel, Layer* L) {
-  ZV_TRY(pack_linear(e, p + ".self_attn_weights.in_proj", EPI_BIAS_BF16, &L->attn_in));
-  ZV_TRY(upload_named(e, p + ".self_attn_weights.linear_pos.weight", &L->w_pos));
+  {
+    // The attention kernels take their scores in log2 units (ATTN_LOG2E, zv_kernels.h): the q rows of the in_proj
+    // (rows [0, H * 32) of [q | k | p], zipformer.py:1220-1233) and linear_pos are scaled by log2(e) once, here.
+    const HostTensor* w = find(e, p + ".self_attn_weights.in_proj.weight");
+    const HostTensor* b = find(e, p + ".self_attn_weights.in_proj.bias");
+    const HostTensor* wp = find(e, p + ".self_attn_weights.linear_pos.weight");
+    if (!w || !b || !wp) return 940;
+    const int N = (int)w->shape[0], K = (int)w->shape[1], nq = net.H * 32;
+    if (N < 2 * nq) {
+      e.err = "unexpected attention in_proj shape at " + p;
+      return 944;
+    }
+    std::vector<float> ws(w->data), bs(b->data), wps(wp->data);
+    for (size_t i = 0; i < (size_t)nq * K; ++i) ws[i] *= ATTN_LOG2E;
+    for (int i = 0; i < nq; ++i) bs[i] *= ATTN_LOG2E;
+    for (float& v : wps) v *= ATTN_LOG2E;
+    ZV_TRY(pack_linear_host(e, ws.data(), bs.data(), N, K, EPI_BIAS_BF16, &L->attn_in, 0, nullptr));
+    ZV_TRY(upload_f32(e, wps, &L->w_pos));
+  }
   for (int i = 0; i < 3; ++i) {
     const std::string f = p + ".feed_forward" + std::to_string(i + 1);
     ZV_TRY(pack_linear(e, f + ".in_proj", EPI_SWOOSHL_BF16, &L->ff_in[i]));

@@ -48,10 +48,15 @@ int sgemm_nn(const float* A, const float* B, float* C, int M, int N, int K, cuda
 // (zipformer.py:983-1056,1215-1219).  W [H*dp][pos_dim].
 int pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E, cudaStream_t s);
 
+// The scores arrive in LOG2 units: the producer scales q (the rows of the attention in_proj that make q) and the
+// relative-position table E by log2(e), so that softmax = exp2(S - max) without a multiply per score and the
+// reference of a speculative tile can be folded into the MMA accumulator initialisation.  Key padding = ATTN_MASKED.
+static constexpr float ATTN_LOG2E = 1.4426950408889634f;
+static constexpr float ATTN_MASKED = -1000.0f * 1.4426950408889634f;  // masked_fill(-1000) of zipformer.py:1286-1289
 struct AttnParams {
   const __nv_bfloat16* qkp;  // IEEE fp16 bit patterns (not bf16) [nb][L][ldq]: q at h*dq, k at H*dq + h*dq, p at 2*H*dq + h*dp
   int ldq;
-  const float* E;            // [H][2L-1][4]
+  const float* E;            // [H][2L-1][4], times log2(e)
   const uint8_t* mask;       // [nb][L] 1 = padded key (may be null)
   const __nv_bfloat16* V;    // [nb][L][ldv]
   int ldv;
