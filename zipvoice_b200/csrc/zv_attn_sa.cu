@@ -17,7 +17,9 @@ namespace zv {
 namespace sa {
 
 static constexpr int BQ = 128, BKV = 64, DQ = 32, EWIN = 192, STAGES = 4, DVP = 16;
-static constexpr int COMPUTE_THREADS = 256, THREADS = COMPUTE_THREADS + 32;
+static constexpr int COMPUTE_THREADS = 256, THREADS = COMPUTE_THREADS + 64;  // + producer warp + MMA warp
+static constexpr int PRODUCER_WARP = COMPUTE_THREADS / 32, MMA_WARP = PRODUCER_WARP + 1;
+static constexpr int S_COLS = 2 * BKV;  // TMEM columns: two S[128 x 64] fp32 accumulators
 // speculative tiles: exponent bound (log2) of P against the running reference (2^64 * 1219 keys << fp32 max)
 static constexpr float SPEC_LOG2 = 64.0f;
 
@@ -30,6 +32,8 @@ struct alignas(16) Smem {  // the key mask that follows is read with 16-byte loa
   __half q[BQ][DQ];     // 8 KB, SWIZZLE_64B (two 64-row boxes)
   Stage st[STAGES];
   uint64_t full[STAGES], empty[STAGES], qbar, pad_;
+  uint64_t sfull[2], sfree[2];  // S accumulator in TMEM: written by the MMAs of a tile / read by all compute warps
+  uint32_t tmem_base, pad2_[3];
   // followed by: uint8_t mask[n_tiles * BKV], uint8_t flag[n_tiles]
 };
 
@@ -43,11 +47,40 @@ ZV_DEVINL void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                : "r"(addr));
 }
-ZV_DEVINL void mma_f16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+// K-major SWIZZLE_64B operand with 64-byte rows (32 fp16): 8-row swizzle atoms 512 B apart (SBO), LBO unused;
+// version 1 (sm_100), layout_type 4 = SWIZZLE_64B (cute/arch/mma_sm100_desc.hpp)
+ZV_DEVINL uint64_t make_sdesc_sw64(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(512 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(4) << 61;
+  return d;
+}
+// kind::f16 instruction descriptor: A, B = IEEE fp16 (format 0) K-major, D = fp32
+ZV_DEVINL uint32_t make_idesc_f16(uint32_t M, uint32_t N) { return (1u << 4) | ((N >> 3) << 17) | ((M >> 4) << 24); }
+// 16 TMEM lanes x 64 fp32 columns in the mma.sync accumulator layout: r[4 nt + {0,1}] = lane g, columns
+// 8 nt + 2 qd + {0,1}; r[4 nt + {2,3}] = lane g + 8 (cute SM100_TMEM_LOAD_16dp256b8x)
+ZV_DEVINL void tmem_ld_16x256b_x8(uint32_t taddr, float (&s)[8][4]) {
+  uint32_t r[32];
   asm volatile(
-      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+      "tcgen05.ld.sync.aligned.16x256b.x8.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < 32; ++i) s[i >> 2][i & 3] = __uint_as_float(r[i]);
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, fp16 inputs (format chosen by the instruction descriptor); ONE thread issues
+ZV_DEVINL void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  umma_bf16(tmem_d, desc_a, desc_b, idesc, accumulate);  // same tcgen05.mma.kind::f16 instruction
 }
 ZV_DEVINL void mma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile(
@@ -85,13 +118,17 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
   if (tid == 0) {
     for (int i = 0; i < STAGES; ++i) mbar_init(&sm.full[i], 1), mbar_init(&sm.empty[i], COMPUTE_THREADS / 32);
     mbar_init(&sm.qbar, 1);
+    for (int i = 0; i < 2; ++i) mbar_init(&sm.sfull[i], 1), mbar_init(&sm.sfree[i], COMPUTE_THREADS / 32);
     fence_barrier_init();
   }
+  if (warp == MMA_WARP) tmem_alloc(&sm.tmem_base, S_COLS);
   // window entries outside the table are never copied: keep them finite
   for (int i = tid; i < STAGES * EWIN; i += THREADS) sm.st[i / EWIN].e[i % EWIN] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int j = tid; j < n_tiles * BKV; j += THREADS) smask[j] = (j < L) ? (mask ? mask[j] : 0) : 2;
   fence_proxy_async_smem();
+  tc_fence_before();
   __syncthreads();
+  tc_fence_after();
   for (int t = tid; t < n_tiles; t += THREADS) {
     const uint4* mp = reinterpret_cast<const uint4*>(smask + t * BKV);
     const uint4 a = mp[0], b4 = mp[1], c = mp[2], d = mp[3];
@@ -100,7 +137,27 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
   }
   __syncthreads();
 
-  if (warp == COMPUTE_THREADS / 32) {
+  const uint32_t tmem_base = sm.tmem_base;
+  if (warp == MMA_WARP) {
+    // ---------------- S = Q K^T of every key tile on tcgen05: fp16 operands straight from the TMA-written
+    // SWIZZLE_64B tiles, fp32 accumulator S[128 x 64] in TMEM, double buffered against the compute warps
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_f16(BQ, BKV);
+      mbar_wait(&sm.qbar, 0);
+      const uint64_t dq = make_sdesc_sw64(smem_u32(&sm.q[0][0]));
+      for (int kt = 0; kt < n_tiles; ++kt) {
+        const int st = kt % STAGES, sb = kt & 1;
+        mbar_wait(&sm.full[st], (kt / STAGES) & 1);
+        if (kt >= 2) mbar_wait(&sm.sfree[sb], ((kt >> 1) - 1) & 1);
+        tc_fence_after();
+        const uint64_t dk = make_sdesc_sw64(smem_u32(&sm.st[st].k[0][0]));
+#pragma unroll
+        for (int k = 0; k < DQ / 16; ++k) umma_f16(tmem_base + sb * BKV, dq + 2 * k, dk + 2 * k, idesc, k);
+        umma_commit(&sm.sfull[sb]);
+      }
+    }
+    __syncwarp();
+  } else if (warp == PRODUCER_WARP) {
     // ---------------- producer
     if (lane == 0) {
       tma_prefetch_desc(&tmQK);
@@ -131,7 +188,9 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
   } else {
     // ---------------- compute warps: 16 query rows each
     const int g = lane >> 2, qd = lane & 3;
-    const int rl0 = warp * 16 + g, rl1 = rl0 + 8;
+    // a warp reads TMEM lanes of its own quarter only (warp % 4): rows 32 (warp % 4) + 16 (warp / 4) + ...
+    const int row0 = 32 * (warp & 3) + 16 * (warp >> 2);
+    const int rl0 = row0 + g, rl1 = rl0 + 8;
     const __half* qkp = reinterpret_cast<const __half*>(p.qkp) + (size_t)b * L * p.ldq;
     float pq0[4], pq1[4];
     {
@@ -144,13 +203,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
 #pragma unroll
     for (int n = 0; n < 2; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
     float m0 = -INFINITY, m1 = -INFINITY;  // the row sums live in column dv of O (V carries a ones column)
-    uint32_t qa[2][4];
-    mbar_wait(&sm.qbar, 0);
-    {
-      const uint32_t qbase = smem_u32(&sm.q[0][0]);
-#pragma unroll
-      for (int ks = 0; ks < 2; ++ks) ldsm_x4(qa[ks], qbase + sw64(warp * 16 + (lane & 15), ks * 2 + (lane >> 4)));
-    }
+    const uint32_t s_taddr = tmem_base + (static_cast<uint32_t>(row0) << 16);
     // One key tile, as ONE straight-line block per variant so that the scheduler can overlap the tensor, FMA and
     // MUFU work of a warp:
     //   SPEC  -- interior tiles: P = exp(S - m) against the running reference m WITHOUT waiting for the tile's own
@@ -170,23 +223,26 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
       const int st = kt % STAGES;
       mbar_wait(&sm.full[st], (kt / STAGES) & 1);
       const Stage& S = sm.st[st];
-      const uint32_t kbase = smem_u32(&S.k[0][0]), vbase = smem_u32(&S.v[0][0]);
+      const uint32_t vbase = smem_u32(&S.v[0][0]);
       const uint8_t* mrow = smask + kt * BKV;
-      // ---- S = Q K^T
+      // ---- S = Q K^T from TMEM (this warp's 16 rows, all 64 keys, mma.sync accumulator layout)
+      const int sb = kt & 1;
       float s[8][4];
+      mbar_wait(&sm.sfull[sb], (kt >> 1) & 1);
+      tc_fence_after();
+      tmem_ld_16x256b_x8(s_taddr + sb * BKV, s);
+      tc_fence_before();
+      // the buffer is handed back once this warp cannot need the raw scores again: a speculative tile may still be
+      // repeated the exact way (the repeat reads S again), so it releases after its vote
+      auto release_s = [&] {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.sfree[sb]);
+      };
+      if (!SPEC) release_s();
+      if (TAIL) {  // blocks beyond the sequence: P = 0
 #pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        // SPEC: the accumulators start at minus the reference (scores are in log2 units), so the finished score
-        // is the exponent itself
-        s[nt][0] = s[nt][1] = SPEC ? -m0 : 0.f, s[nt][2] = s[nt][3] = SPEC ? -m1 : 0.f;
-        if (TAIL && nt >= nbv) {
-          s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-          continue;
-        }
-        uint32_t kb[4];
-        ldsm_x4(kb, kbase + sw64(nt * 8 + (lane & 7), lane >> 3));
-        mma_f16(s[nt], qa[0], kb[0], kb[1]);
-        mma_f16(s[nt], qa[1], kb[2], kb[3]);
+        for (int nt = 0; nt < 8; ++nt)
+          if (nt >= nbv) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
       }
       // ---- position term (rows g and g + 8 share table entries 8 columns apart), masks, tile maximum;
       //      SPEC: P right away (mx0 / mx1 then hold the largest P of the two rows: the vote below depends on the
@@ -205,10 +261,10 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
           float b1 = s[nt][3] + pq1[0] * ep1.x + pq1[1] * ep1.y + pq1[2] * ep1.z + pq1[3] * ep1.w;
           if (MASKED) {
             const uint8_t k0 = mrow[nt * 8 + 2 * qd], k1 = mrow[nt * 8 + 2 * qd + 1];
-            if (k0) a0 = (k0 == 1 ? ATTN_MASKED - (SPEC ? m0 : 0.f) : -INFINITY), b0 = (k0 == 1 ? ATTN_MASKED - (SPEC ? m1 : 0.f) : -INFINITY);
-            if (k1) a1 = (k1 == 1 ? ATTN_MASKED - (SPEC ? m0 : 0.f) : -INFINITY), b1 = (k1 == 1 ? ATTN_MASKED - (SPEC ? m1 : 0.f) : -INFINITY);
+            if (k0) a0 = b0 = (k0 == 1 ? ATTN_MASKED : -INFINITY);
+            if (k1) a1 = b1 = (k1 == 1 ? ATTN_MASKED : -INFINITY);
           }
-          if (SPEC) a0 = ex2_approx(a0), a1 = ex2_approx(a1), b0 = ex2_approx(b0), b1 = ex2_approx(b1);
+          if (SPEC) a0 = ex2_approx(a0 - m0), a1 = ex2_approx(a1 - m0), b0 = ex2_approx(b0 - m1), b1 = ex2_approx(b1 - m1);
           s[nt][0] = a0, s[nt][1] = a1, s[nt][2] = b0, s[nt][3] = b1;
           mx0 = fmaxf(mx0, fmaxf(a0, a1)), mx1 = fmaxf(mx1, fmaxf(b0, b1));
           ep0 = ec0, ep1 = ec1;
@@ -236,6 +292,7 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
         // a lane's own maxima suffice: any lane over the bound sends the whole warp to the exact repeat
         const float bound = 18446744073709551616.0f;  // 2^SPEC_LOG2
         if (__any_sync(0xffffffffu, !(fmaxf(mx0, mx1) <= bound))) return false;
+        release_s();
       } else if (__any_sync(0xffffffffu, (mn0 != m0) || (mn1 != m1))) {
         const float sc0 = ex2_approx(m0 - mn0), sc1 = ex2_approx(m1 - mn1);
 #pragma unroll
@@ -296,6 +353,9 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
             pack_bf16x2(o[n][2] * inv1, o[n][3] * inv1);
     }
   }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == MMA_WARP) tmem_dealloc(tmem_base, S_COLS);
 }
 
 // Host launcher; returns -1 if the shape is not supported (caller falls back to attn_kernel).
