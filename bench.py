@@ -147,14 +147,14 @@ def run_reference(args):
     value = TARGET_FRAMES * FRAME_S / (NUM_STEP * per_nfe)
     sample = ("1 utterance of the batch (B=1 -> CFG batch 2, T=1219), each step = 1 guided fm_decoder NFE of the "
               "torch-fp32 CPU oracle port; audio-s/s = 10 s / (16 NFE x s/NFE)")
-    print(json.dumps({
+    _emit({
         "impl": "reference", "metric": "audio_sec_per_sec", "value": value, "unit": "audio-s/s",
         "n_gpus": args.gpus, "steps": K, "warmup": args.warmup, "ms_per_step": per_nfe * 1e3,
         "ms_per_nfe": per_nfe * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD},
         "cpu_baseline": {"value": value, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def main():
@@ -388,10 +388,43 @@ def main():
         os.makedirs(os.path.dirname(os.path.abspath(args.profile_out)), exist_ok=True)
         json.dump({"ms_per_step": ms_step, "kernels": kernels, "whole_step": whole}, open(args.profile_out, "w"),
                   indent=1)
-    print(json.dumps(line))
+    _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+class _StdoutToStderr:
+    """Everything but the result line goes to stderr: libraries write to file descriptor 1 behind Python's back
+    (NCCL prints its version banner there), and the driver expects exactly one JSON line on stdout."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self._saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def restore(self):
+        sys.stdout.flush()
+        os.dup2(self._saved, 1)
+
+    def __exit__(self, *exc):
+        self.restore()
+        os.close(self._saved)
+        return False
+
+
+_REDIRECT = None
+
+
+def _emit(line: dict) -> None:
+    """Print the result line on the real stdout."""
+    if _REDIRECT is not None:
+        _REDIRECT.restore()
+    print(json.dumps(line), flush=True)
+    if _REDIRECT is not None:
+        os.dup2(2, 1)
+
+
 if __name__ == "__main__":
-    main()
+    with _StdoutToStderr() as _REDIRECT:
+        main()
