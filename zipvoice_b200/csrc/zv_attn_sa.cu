@@ -1,10 +1,15 @@
 // SelfAttention value product (zipformer.py:1359-1396 on the weights of :1149-1306), dv = 12 per head:
-//   O_h = softmax_j(q_h k_h^T + p_h . E_h[L-1-i+j], key-padded -> -1000) V_h
-// Same flash-style mathematics as attn_kernel<16> (zv_attn.cu) with a Blackwell-style data path: a producer
-// warp feeds a 4-stage shared-memory ring with TMA (K tile: SWIZZLE_64B tensor box of the fp16 q|k|p rows;
-// V tile: 16-column box at column 16 h of the padded value rows; relative-position window: one 1-D bulk copy) and the 8 compute warps
-// (16 query rows each) synchronise only through full / empty mbarriers -- no cp.async address arithmetic in the
-// compute warps and no CTA-wide barrier in the key loop.
+//   O_h = softmax_j(q_h k_h^T + p_h . E_h[L-1-i+j], key-padded -> -1000) V_h        (scores in log2 units)
+// Same flash-style mathematics as attn_kernel<16> (zv_attn.cu) with a Blackwell data path:
+//   producer warp : feeds a 4-stage shared-memory ring with TMA (K tile: SWIZZLE_64B tensor box of the fp16 q|k|p
+//                   rows; V tile: 16-column box at column 16 h of the padded value rows; relative-position window:
+//                   one 1-D bulk copy);
+//   MMA warp      : S = Q K^T of every key tile with tcgen05.mma kind::f16 on those fp16 tiles as they lie,
+//                   S[128 x 64] fp32 double-buffered in 128 TMEM columns;
+//   8 compute warps (16 query rows each): tcgen05.ld 16x256b -> the mma.sync accumulator layout -> position term
+//                   on CUDA cores, exp2, P V on mma.sync.  Interior key tiles are exponentiated against the running
+//                   reference maximum (key_tile, SPEC); tile 0, the last tile and repeats are exact.
+// The roles synchronise only through mbarriers -- no CTA-wide barrier in the key loop.
 #include <cuda.h>
 
 #include <type_traits>
@@ -37,11 +42,6 @@ struct alignas(16) Smem {  // the key mask that follows is read with 16-byte loa
   // followed by: uint8_t mask[n_tiles * BKV], uint8_t flag[n_tiles]
 };
 
-ZV_DEVINL void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
-               : "r"(addr));
-}
 ZV_DEVINL void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
@@ -95,8 +95,6 @@ ZV_DEVINL void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, ui
                "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
-// byte offset of 16-byte chunk c of row r in a SWIZZLE_64B tile with 64-byte rows
-ZV_DEVINL uint32_t sw64(int r, int c) { return (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4)); }
 
 }  // namespace sa
 

@@ -91,6 +91,15 @@ ZV_DEVINL void mbar_wait_backoff(uint64_t* bar, uint32_t parity, unsigned ns = 1
   while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
 }
 
+// ------------------------------------------------------------------ programmatic dependent launch
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while its predecessor in
+// the stream is still running: everything before griddep_wait() must not touch global memory that another
+// kernel writes (set-up of barriers, TMEM, descriptor prefetch is fine); griddep_wait() returns once the
+// predecessor grid has completed and its writes are visible.  griddep_launch() lets the successor start its own
+// set-up as soon as SM resources free up.  Both are no-ops for a normally launched kernel.
+ZV_DEVINL void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+ZV_DEVINL void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ------------------------------------------------------------------ TMA
 ZV_DEVINL void tma_prefetch_desc(const void* desc) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(desc)) : "memory");

@@ -344,6 +344,10 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
   if (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = tail->tmem_base;
+  // programmatic dependent launch: the set-up above overlaps the tail of the previous kernel; nothing below reads
+  // global memory before the predecessor has completed
+  griddep_wait();
+  griddep_launch();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -824,18 +828,27 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
       sched.main_units = units - rem, sched.split = split, sched.total_units = units - rem + rem * split;
     }
   }
-  if (!PAIR) {
-    gemm_tc_kernel<MODE, PAIR><<<nunits, threads, smem, stream>>>(maps, m_tiles, n_tiles, k_blocks, kb_split,
-                                                                   p.block_n, stages, ep, sched);
-    return (int)cudaGetLastError();
-  }
+  // Programmatic dependent launch (ZV_PDL=0 switches it off): not while the stream is being captured into a graph.
+  static const int pdl_on = getenv("ZV_PDL") ? atoi(getenv("ZV_PDL")) : 1;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (pdl_on) cudaStreamIsCapturing(stream, &cap);
+  const bool pdl = pdl_on && cap == cudaStreamCaptureStatusNone;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(2 * nunits);
+  cfg.gridDim = dim3(PAIR ? 2 * nunits : nunits);
   cfg.blockDim = dim3(threads), cfg.dynamicSmemBytes = smem, cfg.stream = stream;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = 2, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
-  cfg.attrs = at, cfg.numAttrs = 1;
+  cudaLaunchAttribute at[2];
+  int na = 0;
+  if (PAIR) {
+    at[na].id = cudaLaunchAttributeClusterDimension;
+    at[na].val.clusterDim.x = 2, at[na].val.clusterDim.y = 1, at[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (pdl) {
+    at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = at, cfg.numAttrs = na;
   return (int)cudaLaunchKernelEx(&cfg, gemm_tc_kernel<MODE, PAIR>, maps, m_tiles, n_tiles, k_blocks, kb_split,
                                  p.block_n, stages, ep, sched);
 }
