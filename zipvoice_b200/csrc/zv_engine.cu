@@ -508,20 +508,21 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   ep.L = L, ep.out_bf16 = ws.qkp, ep.ld_bf16 = 288, ep.out_f16 = 1;  // q | k | p kept in fp16
   ZV_TRY(run_gemm(e, ly.attn_in, ws.shadow, D, M, ep, s));
 
+  // shadow = false: nobody reads the bf16 copy of this stream state (the last feed-forward: BiasNorm reads fp32)
   auto residual = [&](const Lin& lin, const __nv_bfloat16* A, int lda, const float* res, const float* resbias,
-                      const float* orig, const float* bscale) {
+                      const float* orig, const float* bscale, bool shadow = true) {
     EpiParams r;
-    r.L = L, r.res = res, r.out_f32 = ws.Y, r.ld_f32 = D, r.out_bf16 = ws.shadow, r.ld_bf16 = D;
+    r.L = L, r.res = res, r.out_f32 = ws.Y, r.ld_f32 = D, r.out_bf16 = shadow ? ws.shadow : nullptr, r.ld_bf16 = D;
     r.resbias = resbias, r.bias_ld = te_ld, r.orig = orig, r.bypass_scale = bscale;
     return run_gemm(e, lin, A, lda, M, r, s);
   };
   auto ff = [&](int i, const float* rowbias, const float* res, const float* resbias, const float* orig,
-                const float* bscale) {
+                const float* bscale, bool shadow = true) {
     EpiParams f;
     f.L = L, f.rowbias = rowbias, f.bias_ld = te_ld, f.out_bf16 = ws.hidden, f.ld_bf16 = ly.ff_in[i].N;
     int rc = run_gemm(e, ly.ff_in[i], ws.shadow, D, M, f, s);
     if (rc) return rc;
-    return residual(ly.ff_out[i], ws.hidden, ly.ff_in[i].N, res, resbias, orig, bscale);
+    return residual(ly.ff_out[i], ws.hidden, ly.ff_in[i].N, res, resbias, orig, bscale, shadow);
   };
   const int ldc = D + 64;  // conv_b row pitch: [conv hidden (D) | SelfAttention output (48) | zeros (16)]
   auto self_attn = [&](int i) {
@@ -566,7 +567,7 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   ZV_TRY(ff(1, nullptr, ws.Y, nullptr, X, ly.bypass_mid_scale));          // :593-598 (FF2 + bypass_mid)
   ZV_TRY(self_attn(1));                                                  // :600-616
   ZV_TRY(conv(1, te_c1, te_stack));                                      // :618-624
-  ZV_TRY(ff(2, nullptr, ws.Y, nullptr, nullptr, nullptr));                // :630-632
+  ZV_TRY(ff(2, nullptr, ws.Y, nullptr, nullptr, nullptr, false));         // :630-632
   // src = bypass(src_orig, BiasNorm(src))  (:635-637), in place on X
   ZV_K(KC_BIASNORM, (double)M * D * 14, s,
        biasnorm_bypass(ws.Y, X, ly.norm_bias, ly.log_scale, ly.bypass_scale, M, D, X, ws.shadow, s));
