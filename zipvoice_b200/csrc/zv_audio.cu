@@ -269,72 +269,100 @@ __global__ void vc_layernorm_kernel(const float* __restrict__ in, const float* _
 }
 
 // ConvNeXt block head: depthwise Conv1d(k=7, pad 3) over time + LayerNorm -> bf16 (GEMM A operand).
-// CTA = 32 frames of one sequence, all 512 channels; the (32 + 6) x 512 fp32 input tile and the taps
-// are staged in shared memory; one warp produces 4 frames, a lane owns 4 x 4 channels of a frame.
-static constexpr int DWT = 32;
-struct DwSmem {
-  float x[DWT + 6][VC_DIM];
-  float w[VC_K][VC_DIM];
-};
-__global__ void __launch_bounds__(256) vc_dwconv_ln_kernel(const float* __restrict__ in, const int* __restrict__ lens,
-                                                           int T, int Tp, const float* __restrict__ dw_w,
-                                                           const float* __restrict__ dw_b,
-                                                           const float* __restrict__ ln_w,
-                                                           const float* __restrict__ ln_b,
-                                                           __nv_bfloat16* __restrict__ out) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
-  DwSmem& sm = *reinterpret_cast<DwSmem*>(smem_raw);
+// HBM-bound (4 B in + 2 B out per element). CTA = 128 threads walking DW_SUB frames at a time along one
+// sequence; a thread owns 4 channels: its 7 x 4 taps and a sliding window of 6 + DW_SUB input rows stay
+// in registers, every row is read from global exactly once per CTA (plus a 6-row halo per run of
+// frames_per_cta) as one coalesced 2 KB line, and the next DW_SUB rows are in flight while the current
+// ones are computed. LayerNorm statistics (two passes, as the reference's F.layer_norm) go through a
+// warp shuffle + 4-warp shared-memory reduction per group of frames.
+static constexpr int DW_SUB = 4;
+__global__ void __launch_bounds__(128, 4) vc_dwconv_ln_kernel(const float* __restrict__ in,
+                                                              const int* __restrict__ lens, int T, int Tp,
+                                                              int frames_per_cta, const float* __restrict__ dw_w,
+                                                              const float* __restrict__ dw_b,
+                                                              const float* __restrict__ ln_w,
+                                                              const float* __restrict__ ln_b,
+                                                              __nv_bfloat16* __restrict__ out) {
+  __shared__ float red_s[4][DW_SUB], red_q[4][DW_SUB];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int b = blockIdx.y, t0 = blockIdx.x * DWT;
+  const int b = blockIdx.y, t0 = blockIdx.x * frames_per_cta;
+  const int t_end = min(t0 + frames_per_cta, T);
   const int len = min(lens[b], T);
-  const float* src = in + (size_t)b * Tp * VC_DIM;
-  for (int idx = tid; idx < (DWT + 6) * (VC_DIM / 4); idx += 256) {
-    const int r = idx / (VC_DIM / 4), c4 = idx % (VC_DIM / 4);
-    const int t = t0 - 3 + r;
+  const int col = tid * 4;
+  const float* src = in + (size_t)b * Tp * VC_DIM + col;
+  auto load_row = [&](int t) {
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (t >= 0 && t < len) v = *reinterpret_cast<const float4*>(src + (size_t)t * VC_DIM + c4 * 4);
-    *reinterpret_cast<float4*>(&sm.x[r][c4 * 4]) = v;
-  }
-  for (int idx = tid; idx < VC_K * VC_DIM; idx += 256) {
-    const int c = idx / VC_K, k = idx % VC_K;  // weight (512, 1, 7): channel-major
-    sm.w[k][c] = dw_w[idx];
-  }
-  __syncthreads();
-  for (int f = warp * 4; f < warp * 4 + 4; ++f) {
-    const int t = t0 + f;
-    if (t >= T) break;
-    float4 acc[4];
-    float s = 0.f;
+    if (t >= 0 && t < len) v = __ldg(reinterpret_cast<const float4*>(src + (size_t)t * VC_DIM));
+    return v;
+  };
+  float4 w[VC_K];  // weight (512, 1, 7): channel-major
+  {
+    float wf[4 * VC_K];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int col = (i * 32 + lane) * 4;
-      float4 a = *reinterpret_cast<const float4*>(dw_b + col);
+    for (int i = 0; i < VC_K; ++i)
+      *reinterpret_cast<float4*>(&wf[4 * i]) = __ldg(reinterpret_cast<const float4*>(dw_w + (size_t)col * VC_K) + i);
+#pragma unroll
+    for (int k = 0; k < VC_K; ++k) w[k] = make_float4(wf[k], wf[VC_K + k], wf[2 * VC_K + k], wf[3 * VC_K + k]);
+  }
+  const float4 cb = __ldg(reinterpret_cast<const float4*>(dw_b + col));
+  const float4 lw = __ldg(reinterpret_cast<const float4*>(ln_w + col));
+  const float4 lb = __ldg(reinterpret_cast<const float4*>(ln_b + col));
+  float4 r[6 + DW_SUB], nxt[DW_SUB];  // r[j] = row tc - 3 + j
+#pragma unroll
+  for (int j = 0; j < 6; ++j) r[j] = load_row(t0 - 3 + j);
+#pragma unroll
+  for (int i = 0; i < DW_SUB; ++i) nxt[i] = load_row(t0 + 3 + i);
+  for (int tc = t0; tc < t_end; tc += DW_SUB) {
+#pragma unroll
+    for (int i = 0; i < DW_SUB; ++i) r[6 + i] = nxt[i];
+    if (tc + DW_SUB < t_end) {
+#pragma unroll
+      for (int i = 0; i < DW_SUB; ++i) nxt[i] = load_row(tc + DW_SUB + 3 + i);
+    }
+    float4 acc[DW_SUB];
+    float s[DW_SUB];
+#pragma unroll
+    for (int f = 0; f < DW_SUB; ++f) {
+      float4 a = cb;
 #pragma unroll
       for (int k = 0; k < VC_K; ++k) {
-        const float4 xv = *reinterpret_cast<const float4*>(&sm.x[f + k][col]);
-        const float4 wv = *reinterpret_cast<const float4*>(&sm.w[k][col]);
-        a.x = fmaf(xv.x, wv.x, a.x), a.y = fmaf(xv.y, wv.y, a.y), a.z = fmaf(xv.z, wv.z, a.z), a.w = fmaf(xv.w, wv.w, a.w);
+        a.x = fmaf(r[f + k].x, w[k].x, a.x), a.y = fmaf(r[f + k].y, w[k].y, a.y);
+        a.z = fmaf(r[f + k].z, w[k].z, a.z), a.w = fmaf(r[f + k].w, w[k].w, a.w);
       }
-      acc[i] = a;
-      s += a.x + a.y + a.z + a.w;
+      acc[f] = a;
+      s[f] = warp_sum((a.x + a.y) + (a.z + a.w));
     }
-    const float mean = warp_sum(s) * (1.0f / VC_DIM);
-    float q = 0.f;
+    if (lane == 0) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float a = acc[i].x - mean, bb = acc[i].y - mean, c = acc[i].z - mean, d = acc[i].w - mean;
-      q += a * a + bb * bb + c * c + d * d;
+      for (int f = 0; f < DW_SUB; ++f) red_s[warp][f] = s[f];
     }
-    const float rstd = rsqrtf(warp_sum(q) * (1.0f / VC_DIM) + 1e-6f);
-    __nv_bfloat16* o = out + ((size_t)b * Tp + t) * VC_DIM;
+    __syncthreads();
+    float mean[DW_SUB], q[DW_SUB];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int col = (i * 32 + lane) * 4;
-      const float4 ww = *reinterpret_cast<const float4*>(ln_w + col), bb = *reinterpret_cast<const float4*>(ln_b + col);
-      const float r0 = (acc[i].x - mean) * rstd * ww.x + bb.x, r1 = (acc[i].y - mean) * rstd * ww.y + bb.y;
-      const float r2 = (acc[i].z - mean) * rstd * ww.z + bb.z, r3 = (acc[i].w - mean) * rstd * ww.w + bb.w;
-      *reinterpret_cast<uint2*>(o + col) = make_uint2(pack_bf16x2(r0, r1), pack_bf16x2(r2, r3));
+    for (int f = 0; f < DW_SUB; ++f) {
+      mean[f] = ((red_s[0][f] + red_s[1][f]) + (red_s[2][f] + red_s[3][f])) * (1.0f / VC_DIM);
+      const float a0 = acc[f].x - mean[f], a1 = acc[f].y - mean[f], a2 = acc[f].z - mean[f], a3 = acc[f].w - mean[f];
+      q[f] = warp_sum((a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3));
     }
+    if (lane == 0) {
+#pragma unroll
+      for (int f = 0; f < DW_SUB; ++f) red_q[warp][f] = q[f];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int f = 0; f < DW_SUB; ++f) {
+      const int t = tc + f;
+      if (t < t_end) {
+        const float var = ((red_q[0][f] + red_q[1][f]) + (red_q[2][f] + red_q[3][f])) * (1.0f / VC_DIM);
+        const float rstd = rsqrtf(var + 1e-6f);
+        const float r0 = (acc[f].x - mean[f]) * rstd * lw.x + lb.x, r1 = (acc[f].y - mean[f]) * rstd * lw.y + lb.y;
+        const float r2 = (acc[f].z - mean[f]) * rstd * lw.z + lb.z, r3 = (acc[f].w - mean[f]) * rstd * lw.w + lb.w;
+        *reinterpret_cast<uint2*>(out + ((size_t)b * Tp + t) * VC_DIM + col) =
+            make_uint2(pack_bf16x2(r0, r1), pack_bf16x2(r2, r3));
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 6; ++j) r[j] = r[j + DW_SUB];
   }
 }
 
@@ -688,7 +716,6 @@ extern "C" int zv_vocos_decode(void* handle, const float* mel, const int64_t* le
   const int Tp = T + 6, M = B * Tp;
   static bool attr = false;
   if (!attr) {
-    cudaFuncSetAttribute(vc_dwconv_ln_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DwSmem));
     cudaFuncSetAttribute(vc_istft_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FftSmem));
     attr = true;
   }
@@ -701,11 +728,15 @@ extern "C" int zv_vocos_decode(void* handle, const float* mel, const int64_t* le
   AU_TRY(run_gemm(e, a.embed, a.melp, VC_MELP, M, p0, s));
   AU_K(KC_VOCODER_ELEM, (double)M * VC_DIM * 8.0, s,
        (vc_layernorm_kernel<<<(M + 7) / 8, 256, 0, s>>>(a.emb, a.norm_w, a.norm_b, M, a.x, nullptr)));
-  dim3 dgrid((T + DWT - 1) / DWT, B);
+  // longest run of frames per CTA that still leaves >= 8 CTAs for each of the 148 SMs (6 halo rows per run)
+  int dw_run = 32;
+  while (dw_run > 8 && (long long)B * ((T + dw_run - 1) / dw_run) < 8ll * 148) dw_run >>= 1;
+  if (const char* ev = getenv("ZV_DW_RUN")) dw_run = atoi(ev);
+  dim3 dgrid((T + dw_run - 1) / dw_run, B);
   for (int i = 0; i < VC_LAYERS; ++i) {
     AU_K(KC_VOCODER_ELEM, (double)B * T * VC_DIM * 6.0, s,
-         (vc_dwconv_ln_kernel<<<dgrid, 256, sizeof(DwSmem), s>>>(a.x, a.lens_dev, T, Tp, a.dw_w[i], a.dw_b[i],
-                                                                 a.ln_w[i], a.ln_b[i], a.h)));
+         (vc_dwconv_ln_kernel<<<dgrid, 128, 0, s>>>(a.x, a.lens_dev, T, Tp, dw_run, a.dw_w[i], a.dw_b[i],
+                                                    a.ln_w[i], a.ln_b[i], a.h)));
     EpiParams p1;
     p1.L = Tp, p1.out_bf16 = a.g, p1.ld_bf16 = VC_INTER;
     AU_TRY(run_gemm(e, a.pw1[i], a.h, VC_DIM, M, p1, s));
