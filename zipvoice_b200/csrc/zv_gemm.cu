@@ -208,9 +208,10 @@ struct TileSched {
   int main_units, total_units, split;
 };
 
+static constexpr int MAX_STAGES = 10;
 struct GemmSmemTail {
-  uint64_t full[8];
-  uint64_t empty[8];
+  uint64_t full[MAX_STAGES];
+  uint64_t empty[MAX_STAGES];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
   uint64_t rbar[MAX_NCG * 4][2];  // per epilogue warp
@@ -768,14 +769,6 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
                      cudaStream_t stream) {
   constexpr int NCG = ncg_for(MODE);
   constexpr int threads = 128 + 128 * NCG;
-  const int w_stage = (PAIR ? p.block_n / 2 : p.block_n) * BK * 2;
-  const int fixed = 1024 + (int)sizeof(GemmSmemTail) + NCG * stg_group_bytes(MODE);
-  int stages = (227 * 1024 - fixed) / (A_STAGE_BYTES + w_stage);
-  if (stages > 8) stages = 8;
-  static const int stages_cap = getenv("ZV_GEMM_STAGES") ? atoi(getenv("ZV_GEMM_STAGES")) : 0;  // measurement aid
-  if (stages_cap >= 2 && stages > stages_cap) stages = stages_cap;
-  if (stages < 2) return 903;
-  const int smem = stages * (A_STAGE_BYTES + w_stage) + fixed;
   static bool attr_set = false;
   static int max_clusters = 0;
   if (!attr_set) {
@@ -798,36 +791,74 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
     }
     attr_set = true;
   }
-  const int m_tiles = (p.M + BM - 1) / BM;
-  const int n_tiles = p.N_pad / p.block_n;
-  const int k_blocks = (p.K + BK - 1) / BK;
-  const int kb_split = p.A2 ? p.k_split / BK : k_blocks;
-  const int units = (PAIR ? (m_tiles + 1) / 2 : m_tiles) * n_tiles;
-  const int nunits = PAIR ? min(units, min(max_clusters, g_num_sms / 2)) : min(units, g_num_sms);
-  // Last wave: R = units % nunits tiles would keep R CTAs busy for a whole tile time while the others idle.  Cut
-  // them into `split` column slices (one slice per CTA, R * split <= nunits).  A slice keeps every epilogue column
-  // group busy (>= 32 NCG columns), is a legal UMMA N, and ends the gated part of EPI_NONLIN on a slice boundary.
-  TileSched sched = {units, units, 1};
-  GemmMaps maps = maps_in;
   const EpiParams& ep = ep_in;
-  static const int tail_split = getenv("ZV_GEMM_TAILSPLIT") ? atoi(getenv("ZV_GEMM_TAILSPLIT")) : 1;
-  const int rem = units % nunits;
-  if (tail_split && units > nunits && rem != 0) {
+  GemmMaps maps = maps_in;
+  const int m_tiles = (p.M + BM - 1) / BM;
+  const int m_units = PAIR ? (m_tiles + 1) / 2 : m_tiles;
+  const int max_units = PAIR ? min(max_clusters, g_num_sms / 2) : g_num_sms;  // co-resident work units
+  // Column slices of a tile must keep every epilogue column group busy (>= 32 NCG columns), be a legal UMMA N
+  // and end the gated part of EPI_NONLIN on a slice boundary; at most `room` of them fit beside each other.
+  auto pick_split = [&](int bn_full, int tiles, int room) {
     int split = 1;
     for (int sp = 2; sp <= 8; sp *= 2) {
-      const int bn = p.block_n / sp;
-      if (p.block_n % sp || bn % 32 || bn < 32 * NCG || rem * sp > nunits) break;
+      const int bn = bn_full / sp;
+      if (bn_full % sp || bn % 32 || bn < 32 * NCG || tiles * sp > room) break;
       if (MODE == EPI_NONLIN_BF16 && ep.gate_cols % bn != 0) break;
       split = sp;
     }
+    return split;
+  };
+  // ZV_GEMM_TAILSPLIT: 0 = off, 1 = last wave of large grids only, 2 (default) = small grids too.
+  static const int tail_split = getenv("ZV_GEMM_TAILSPLIT") ? atoi(getenv("ZV_GEMM_TAILSPLIT")) : 2;
+  // A grid smaller than the machine (single utterances): every tile is "last wave".  Run the whole GEMM on
+  // narrower tiles (any multiple of 32 that divides N_pad) -- more SMs pull W (which streams from HBM: the weights
+  // of all layers exceed L2) and each K step moves fewer bytes through one SM's ~75 GB/s TMA feed.
+  int block_n = p.block_n;
+  if (!PAIR && tail_split >= 2 && m_units * (p.N_pad / p.block_n) < max_units) {
+    for (int bn = 32; bn < p.block_n; bn += 32) {  // narrowest width whose grid still fits the machine
+      if (p.N_pad % bn || m_units * (p.N_pad / bn) > max_units) continue;
+      if (MODE == EPI_NONLIN_BF16 && ep.gate_cols % bn != 0) continue;
+      block_n = bn;
+      break;
+    }
+    if (block_n != p.block_n) {
+      const int rc = make_tmap_impl(&maps.W, W, 0, (uint64_t)p.N_pad, (uint64_t)p.K, (uint64_t)p.ldw,
+                                    (uint32_t)block_n, 64, 128);
+      if (rc) return rc;
+    }
+  }
+  const int w_stage = (PAIR ? block_n / 2 : block_n) * BK * 2;
+  const int fixed = 1024 + (int)sizeof(GemmSmemTail) + NCG * stg_group_bytes(MODE);
+  int stages = (227 * 1024 - fixed) / (A_STAGE_BYTES + w_stage);
+  if (stages > MAX_STAGES) stages = MAX_STAGES;
+  static const int stages_cap = getenv("ZV_GEMM_STAGES") ? atoi(getenv("ZV_GEMM_STAGES")) : 0;  // measurement aid
+  if (stages_cap >= 2 && stages > stages_cap) stages = stages_cap;
+  if (stages < 2) return 903;
+  const int smem = stages * (A_STAGE_BYTES + w_stage) + fixed;
+  const int n_tiles = p.N_pad / block_n;
+  const int k_blocks = (p.K + BK - 1) / BK;
+  const int kb_split = p.A2 ? p.k_split / BK : k_blocks;
+  const int units = m_units * n_tiles;
+  // Last wave of a large grid: R = units % max_units tiles would keep R CTAs busy for a whole tile time while the
+  // others idle.  Cut them into `split` column slices (one slice per CTA, R * split <= max_units).
+  TileSched sched = {units, units, 1};
+  const int rem = units > max_units ? units % max_units : 0;
+  if (tail_split && rem != 0) {
+    const int split = pick_split(block_n, rem, max_units);
     if (split > 1) {
-      const int bn = p.block_n / split;
+      const int bn = block_n / split;
       const int rc = make_tmap_impl(&maps.Wt, W, 0, (uint64_t)p.N_pad, (uint64_t)p.K, (uint64_t)p.ldw,
                                     (uint32_t)(PAIR ? bn / 2 : bn), 64, 128);
       if (rc) return rc;
       sched.main_units = units - rem, sched.split = split, sched.total_units = units - rem + rem * split;
     }
   }
+  const int nunits = min(sched.total_units, max_units);
+  static const bool verbose = getenv("ZV_VERBOSE") != nullptr;
+  if (verbose)
+    fprintf(stderr, "[zv] gemm mode %d M %d N_pad %d K %d bn %d (plan %d), %d stages: %d units, tail split %d -> %d "
+            "work items on %d CTAs\n", MODE, p.M, p.N_pad, p.K, block_n, p.block_n, stages, units, sched.split,
+            sched.total_units, nunits);
   // Programmatic dependent launch (ZV_PDL=0 switches it off): not while the stream is being captured into a graph.
   static const int pdl_on = getenv("ZV_PDL") ? atoi(getenv("ZV_PDL")) : 1;
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
@@ -850,7 +881,7 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
   }
   cfg.attrs = at, cfg.numAttrs = na;
   return (int)cudaLaunchKernelEx(&cfg, gemm_tc_kernel<MODE, PAIR>, maps, m_tiles, n_tiles, k_blocks, kb_split,
-                                 p.block_n, stages, ep, sched);
+                                 block_n, stages, ep, sched);
 }
 
 // impl: 0 = tcgen05, CTA pairs (cta_group::2) for the shapes where they measure faster; 1 = SIMT checker;

@@ -29,34 +29,38 @@ __global__ void time_embed_kernel(const float* __restrict__ t, int t_stride, con
     gemb[half + i] = sinf(gv * f);
   }
   __syncthreads();
-  if (g) {
-    float add = 0.f;
-    // each thread owns output rows i of Wg
-    for (int i = threadIdx.x; i < dim; i += blockDim.x) {
-      add = 0.f;
-      for (int k = 0; k < dim; ++k) add += wg[(size_t)i * dim + k] * gemb[k];
-      h[i] = add;  // temporary
+  // y[i] = W[i][:] . x: one warp per output row, 4 rows in flight per warp (coalesced row reads, shuffle sum)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  auto matvec = [&](const float* __restrict__ W, const float* x, int rows, int K, auto&& store) {
+    for (int i0 = warp * 4; i0 < rows; i0 += nwarps * 4) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int k = lane; k < K; k += 32) {
+        const float xv = x[k];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+          if (i0 + r < rows) acc[r] = fmaf(W[(size_t)(i0 + r) * K + k], xv, acc[r]);
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const float v = warp_sum(acc[r]);
+        if (lane == 0 && i0 + r < rows) store(i0 + r, v);
+      }
     }
+  };
+  if (g) {
+    matvec(wg, gemb, dim, dim, [&](int i, float v) { h[i] = v; });  // temporary
     __syncthreads();
     for (int i = threadIdx.x; i < dim; i += blockDim.x) emb[i] += h[i];
     __syncthreads();
   }
-  for (int i = threadIdx.x; i < 2 * dim; i += blockDim.x) {
-    float acc = b0[i];
-    for (int k = 0; k < dim; ++k) acc += w0[(size_t)i * dim + k] * emb[k];
-    h[i] = swoosh_r(acc);
-  }
+  matvec(w0, emb, 2 * dim, dim, [&](int i, float v) { h[i] = swoosh_r(v + b0[i]); });
   __syncthreads();
-  for (int i = threadIdx.x; i < dim; i += blockDim.x) {
-    float acc = b2[i];
-    for (int k = 0; k < 2 * dim; ++k) acc += w2[(size_t)i * 2 * dim + k] * h[k];
-    a_out[(size_t)b * dim + i] = swoosh_r(acc);
-  }
+  matvec(w2, h, dim, 2 * dim, [&](int i, float v) { a_out[(size_t)b * dim + i] = swoosh_r(v + b2[i]); });
 }
 
 int time_embed(const float* t, int t_stride, const float* g, int g_stride, int nb, int dim, const float* w0, const float* b0, const float* w2,
                const float* b2, const float* wg, float* a_out, cudaStream_t s) {
-  time_embed_kernel<<<nb, 128, 4 * dim * sizeof(float), s>>>(t, t_stride, g, g_stride, dim, w0, b0, w2, b2, wg, a_out);
+  time_embed_kernel<<<nb, 512, 4 * dim * sizeof(float), s>>>(t, t_stride, g, g_stride, dim, w0, b0, w2, b2, wg, a_out);
   return (int)cudaGetLastError();
 }
 
