@@ -354,6 +354,10 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+#ifdef ZV_TRACE
+      long long tr_pw = 0, tr_pi = 0;
+      const long long tr_t0 = clock64();
+#endif
       for (int t = unit0; t < total_tiles; t += nunits) {
         int m_blk, n0t, bn;
         decode(t, m_blk, n0t, bn);
@@ -361,7 +365,14 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         const uint32_t tx = A_STAGE_BYTES + wn * BK * 2;
         const CUtensorMap* mapW = bn == block_n ? &maps.W : &maps.Wt;
         for (int kb = 0; kb < k_blocks; ++kb) {
+#ifdef ZV_TRACE
+          const long long c0 = clock64();
+#endif
           mbar_wait(&tail->empty[stage], phase ^ 1);
+#ifdef ZV_TRACE
+          const long long c1 = clock64();
+          tr_pw += c1 - c0;
+#endif
           const CUtensorMap* mapA = kb < kb_split ? &maps.A : &maps.A2;
           const int ka = (kb < kb_split ? kb : kb - kb_split) * BK;
           if (PAIR) {
@@ -375,9 +386,17 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
             tma_load_2d(sA + stage * A_STAGE_BYTES, mapA, &tail->full[stage], ka, m_blk * BM);
             tma_load_2d(sW + stage * w_stage_bytes, mapW, &tail->full[stage], kb * BK, n0t);
           }
+#ifdef ZV_TRACE
+          tr_pi += clock64() - c1;
+#endif
           if (++stage == stages) stage = 0, phase ^= 1;
         }
       }
+#ifdef ZV_TRACE
+      if (blockIdx.x == 0)
+        printf("[trace] producer: k_blocks %d wait_empty %lld issue %lld total %lld\n", k_blocks, tr_pw, tr_pi,
+               clock64() - tr_t0);
+#endif
     }
     __syncwarp();
   } else if (warp == 1) {
@@ -387,6 +406,10 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+#ifdef ZV_TRACE
+      long long tr_mw = 0, tr_mi = 0, tr_mc = 0;
+      const long long tr_m0 = clock64();
+#endif
       for (int t = unit0; t < total_tiles; t += nunits, ++it) {
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
@@ -395,8 +418,15 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         const uint32_t d_tmem = tmem_base + as * ACC_STAGE_COLS;
         const uint32_t idesc = t < sched.main_units ? idesc_main : idesc_tail;
         for (int kb = 0; kb < k_blocks; ++kb) {
+#ifdef ZV_TRACE
+          const long long m0 = clock64();
+#endif
           mbar_wait(&tail->full[stage], phase);
           tc_fence_after();
+#ifdef ZV_TRACE
+          const long long m1 = clock64();
+          tr_mw += m1 - m0;
+#endif
           const uint64_t da = make_sdesc_sw128(smem_u32(sA + stage * A_STAGE_BYTES));
           const uint64_t dw = make_sdesc_sw128(smem_u32(sW + stage * w_stage_bytes));
 #pragma unroll
@@ -404,6 +434,10 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
             if (PAIR) umma_bf16_pair(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
             else umma_bf16(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
           }
+#ifdef ZV_TRACE
+          const long long m2 = clock64();
+          tr_mi += m2 - m1;
+#endif
           if (PAIR) {
             umma_commit_pair(&tail->empty[stage], 3);
             if (kb == k_blocks - 1) umma_commit_pair(&tail->tmem_full[as], 3);
@@ -411,9 +445,17 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
             umma_commit(&tail->empty[stage]);
             if (kb == k_blocks - 1) umma_commit(&tail->tmem_full[as]);
           }
+#ifdef ZV_TRACE
+          tr_mc += clock64() - m2;
+#endif
           if (++stage == stages) stage = 0, phase ^= 1;
         }
       }
+#ifdef ZV_TRACE
+      if (blockIdx.x == 0)
+        printf("[trace] mma: wait_full %lld issue %lld commit %lld total %lld\n", tr_mw, tr_mi, tr_mc,
+               clock64() - tr_m0);
+#endif
     }
     __syncwarp();
   } else if (warp >= 4) {
