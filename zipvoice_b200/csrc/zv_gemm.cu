@@ -282,7 +282,9 @@ ZV_DEVINL void add_bias32(float (&v)[32], const float* __restrict__ bias, const 
 // tile, each CTA loads its own 128 rows of A and HALF of the W tile, the leader (cluster rank 0) issues
 // the MMAs for both, accumulators land in each CTA's own TMEM, each CTA runs the epilogue of its rows.
 // Per output element this halves the W bytes pulled from L2, which is what bounds the K = 512 GEMMs.
-template <int MODE, bool PAIR>
+// DUAL (own instantiation, so that the large-grid kernels keep their register allocation): every CTA owns one
+// tile and two threads issue the K loop into two accumulators (see warp 3 below).
+template <int MODE, bool PAIR, bool DUAL = false>
 __global__ void __launch_bounds__(128 + 128 * ncg_for(MODE), 1)
 gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, int k_blocks, int kb_split,
                int block_n, int stages, EpiParams ep, TileSched sched) {
@@ -330,7 +332,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       mbar_init(&tail->empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&tail->tmem_full[i], 1);
+      mbar_init(&tail->tmem_full[i], DUAL ? 2 : 1);
       mbar_init(&tail->tmem_empty[i], PAIR ? 2 * EPI_WARPS : EPI_WARPS);
     }
     for (int g = 0; g < NCG * 4; ++g) mbar_init(&tail->rbar[g][0], 1), mbar_init(&tail->rbar[g][1], 1);
@@ -418,6 +420,10 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         const uint32_t d_tmem = tmem_base + as * ACC_STAGE_COLS;
         const uint32_t idesc = t < sched.main_units ? idesc_main : idesc_tail;
         for (int kb = 0; kb < k_blocks; ++kb) {
+          if (DUAL && (kb & 1)) {  // odd K steps belong to the second issuing thread (warp 3)
+            if (++stage == stages) stage = 0, phase ^= 1;
+            continue;
+          }
 #ifdef ZV_TRACE
           const long long m0 = clock64();
 #endif
@@ -443,19 +449,41 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
             if (kb == k_blocks - 1) umma_commit_pair(&tail->tmem_full[as], 3);
           } else {
             umma_commit(&tail->empty[stage]);
-            if (kb == k_blocks - 1) umma_commit(&tail->tmem_full[as]);
+            if (!DUAL && kb == k_blocks - 1) umma_commit(&tail->tmem_full[as]);
           }
 #ifdef ZV_TRACE
           tr_mc += clock64() - m2;
 #endif
           if (++stage == stages) stage = 0, phase ^= 1;
         }
+        if (!PAIR && DUAL) umma_commit(&tail->tmem_full[as]);  // one of the two arrivals (warp 3: the other)
       }
 #ifdef ZV_TRACE
       if (blockIdx.x == 0)
         printf("[trace] mma: wait_full %lld issue %lld commit %lld total %lld\n", tr_mw, tr_mi, tr_mc,
                clock64() - tr_m0);
 #endif
+    }
+    __syncwarp();
+  } else if (warp == 3) {
+    // Second MMA-issuing thread (DUAL): one thread needs ~340 cycles per K step for four tcgen05.mma and the
+    // commit whatever the tile holds, which is all of the K loop when a CTA owns a single narrow tile.  Odd K
+    // steps accumulate into the second (otherwise unused) accumulator stage; the epilogue adds the two.
+    if (DUAL && lane == 0 && rank == 0 && unit0 < total_tiles) {
+      const uint32_t d_tmem = tmem_base + ACC_STAGE_COLS;
+      const uint32_t idesc = make_idesc_bf16(BM, block_n);
+      for (int kb = 1; kb < k_blocks; kb += 2) {
+        const int stage = kb % stages;
+        mbar_wait(&tail->full[stage], (kb / stages) & 1);
+        tc_fence_after();
+        const uint64_t da = make_sdesc_sw128(smem_u32(sA + stage * A_STAGE_BYTES));
+        const uint64_t dw = make_sdesc_sw128(smem_u32(sW + stage * w_stage_bytes));
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k)
+          umma_bf16(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb == 1 && k == 0) ? 0u : 1u);
+        umma_commit(&tail->empty[stage]);
+      }
+      umma_commit(&tail->tmem_full[0]);  // arrives once all MMAs of this thread have completed
     }
     __syncwarp();
   } else if (warp >= 4) {
@@ -509,6 +537,17 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         uint32_t raw[32];
         tmem_ld32(taddr + c * 32, raw);
         tmem_ld_wait();
+        if (DUAL) {  // + the odd K steps (second accumulator), in two halves to bound the live registers
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            uint32_t odd[16];
+            tmem_ld16(taddr + ACC_STAGE_COLS + c * 32 + h * 16, odd);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              raw[h * 16 + i] = __float_as_uint(__uint_as_float(raw[h * 16 + i]) + __uint_as_float(odd[i]));
+          }
+        }
         if (c + NCG >= nchunks) {  // last accumulator read of this tile by this warp
           tc_fence_before();
           __syncwarp();
@@ -896,6 +935,15 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
     }
   }
   const int nunits = min(sched.total_units, max_units);
+  // one tile per CTA and at least two K steps: split the K loop over two issuing threads / accumulators
+  const bool dual = !PAIR && tail_split >= 2 && sched.total_units <= max_units && k_blocks >= 2;
+  if (dual) {
+    static bool attr_dual = false;
+    if (!attr_dual) {
+      cudaFuncSetAttribute(gemm_tc_kernel<MODE, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      attr_dual = true;
+    }
+  }
   static const bool verbose = getenv("ZV_VERBOSE") != nullptr;
   if (verbose)
     fprintf(stderr, "[zv] gemm mode %d M %d N_pad %d K %d bn %d (plan %d), %d stages: %d units, tail split %d -> %d "
@@ -922,6 +970,9 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
     ++na;
   }
   cfg.attrs = at, cfg.numAttrs = na;
+  if (dual)
+    return (int)cudaLaunchKernelEx(&cfg, gemm_tc_kernel<MODE, false, true>, maps, m_tiles, n_tiles, k_blocks,
+                                   kb_split, block_n, stages, ep, sched);
   return (int)cudaLaunchKernelEx(&cfg, gemm_tc_kernel<MODE, PAIR>, maps, m_tiles, n_tiles, k_blocks, kb_split,
                                  block_n, stages, ep, sched);
 }
