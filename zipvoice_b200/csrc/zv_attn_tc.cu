@@ -136,13 +136,15 @@ using namespace natc;
 
 __global__ void __launch_bounds__(natc::THREADS, 1)
 attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmQK,
-                  const __grid_constant__ CUtensorMap tmG, AttnParams p, int nvbox, int n_mma0, int n_mma1) {
+                  const __grid_constant__ CUtensorMap tmG, AttnParams p, int nvbox, int n_mma0, int n_mma1, int dv_slice) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // align inside the shared window (pointer + integer keeps the shared address space: LDS/STS, not generic LD/ST)
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.y;
   const int i0 = blockIdx.x * BQ;
+  // value-channel slice of this CTA (small grids: blockIdx.z slices of nvbox boxes each; nvbox, n_mma* are per slice)
+  const int zc = blockIdx.z * dv_slice;
   const int L = p.L, H = p.H, R = 2 * L - 1;
   const int n_tiles = (L + BKV - 1) / BKV;
   const int kd = min((i0 + BQ / 2) / BKV, n_tiles - 1);  // key tile under the middle of this CTA's diagonal
@@ -223,7 +225,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
       }
       mbar_arrive_expect_tx(&sm.vfull[st], v_stage_bytes);
       for (int cc = 0; cc < nvbox; ++cc)
-        tma_load_2d(&sm.v[st][cc][0][0], &tmV, &sm.vfull[st], cc * 64, b * L + kt * BKV);
+        tma_load_2d(&sm.v[st][cc][0][0], &tmV, &sm.vfull[st], zc + cc * 64, b * L + kt * BKV);
     };
     // The gate tile y[128 queries][<= 384] of the epilogue rides behind the value tiles in the same ring: its two
     // halves (3 boxes of 128 rows x 64 channels = one 48 KB stage each) are uses n_tiles and n_tiles + 1 of the
@@ -239,7 +241,7 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
       mbar_arrive_expect_tx(&sm.vfull[st], (uint32_t)nbox * BQ * 128);
       for (int cc = 0; cc < nbox; ++cc)
         tma_load_2d(reinterpret_cast<uint8_t*>(&sm.v[st][0][0][0]) + cc * (BQ * 128), &tmG, &sm.vfull[st],
-                    (3 * part + cc) * 64, b * L + i0);
+                    zc + (3 * part + cc) * 64, b * L + i0);
     };
     const uint32_t id0 = make_idesc_bf16_bmn(BQ, n_mma0), id1 = make_idesc_bf16_bmn(BQ, max(n_mma1, 16));
     // c0 / v0: P-buffer and X-ring use counters at entry
@@ -416,12 +418,12 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
       uint32_t raw[32];
       tmem_ld32(tmem_base + (static_cast<uint32_t>(q4 * 32) << 16) + c0, raw);
       tmem_ld_wait();
-      if (i < L && c0 < p.dv) {
-        bf16* op = p.out + grow * p.ldo + c0;
+      if (i < L && zc + c0 < p.dv) {
+        bf16* op = p.out + grow * p.ldo + zc + c0;
 #pragma unroll
         for (int j4 = 0; j4 < 4; ++j4) {
           const int jj = j4 * 8;
-          if (c0 + jj >= p.dv) break;
+          if (zc + c0 + jj >= p.dv) break;
           float v[8];
 #pragma unroll
           for (int u = 0; u < 8; ++u) v[u] = __uint_as_float(raw[jj + u]) * inv;
@@ -447,7 +449,16 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
 // Host launcher; returns -1 if the shape is not supported by this kernel (caller falls back to attn_kernel).
 int attention_na_tc(const AttnParams& p, cudaStream_t s) {
   if (p.heads != 1 || p.dv % 8 || p.dv > 384 || p.ldv % 8 || p.ldo % 8 || (p.gate && p.ldg % 8)) return -1;
-  const int nvbox = (p.dv + 63) / 64;
+  int nvbox = (p.dv + 63) / 64;
+  // Single utterances: a handful of (query tile, sequence) CTAs each pull every 48 KB value tile through one SM.
+  // Slices of 128 value channels (blockIdx.z) recompute the scores but spread the A.X product, the value traffic and
+  // the epilogue over 2-3 x as many SMs.  ZV_NA_DVSLICE=0 switches it off.
+  static const int slice_on = getenv("ZV_NA_DVSLICE") ? atoi(getenv("ZV_NA_DVSLICE")) : 1;
+  int slices = 1;
+  if (slice_on && nvbox > 2 && (long long)((p.L + BQ - 1) / BQ) * p.nb * ((nvbox + 1) / 2) <= 148) {
+    slices = (nvbox + 1) / 2;
+    nvbox = 2;
+  }
   const int ncols = nvbox * 64;
   const int n0 = ncols > 256 ? 256 : ncols, n1 = ncols - n0;
   CUtensorMap tmV;
@@ -470,8 +481,8 @@ int attention_na_tc(const AttnParams& p, cudaStream_t s) {
     cudaFuncSetAttribute(attn_na_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     attr = true;
   }
-  dim3 grid((p.L + BQ - 1) / BQ, p.nb);
-  attn_na_tc_kernel<<<grid, THREADS, smem, s>>>(tmV, tmQK, tmG, p, nvbox, n0, n1);
+  dim3 grid((p.L + BQ - 1) / BQ, p.nb, slices);
+  attn_na_tc_kernel<<<grid, THREADS, smem, s>>>(tmV, tmQK, tmG, p, nvbox, n0, n1, ncols);
   return (int)cudaGetLastError();
 }
 
