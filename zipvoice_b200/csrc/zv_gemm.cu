@@ -949,11 +949,12 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
     fprintf(stderr, "[zv] gemm mode %d M %d N_pad %d K %d bn %d (plan %d), %d stages: %d units, tail split %d -> %d "
             "work items on %d CTAs\n", MODE, p.M, p.N_pad, p.K, block_n, p.block_n, stages, units, sched.split,
             sched.total_units, nunits);
-  // Programmatic dependent launch (ZV_PDL=0 switches it off): not while the stream is being captured into a graph.
-  static const int pdl_on = getenv("ZV_PDL") ? atoi(getenv("ZV_PDL")) : 1;
+  // Programmatic dependent launch (ZV_PDL=0 switches it off), also as programmatic edges of a captured graph
+  // (ZV_PDL=1: plain launches only).
+  static const int pdl_on = getenv("ZV_PDL") ? atoi(getenv("ZV_PDL")) : 2;
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-  if (pdl_on) cudaStreamIsCapturing(stream, &cap);
-  const bool pdl = pdl_on && cap == cudaStreamCaptureStatusNone;
+  if (pdl_on == 1) cudaStreamIsCapturing(stream, &cap);
+  const bool pdl = pdl_on && cap == cudaStreamCaptureStatusNone;  // ZV_PDL=1: not inside graph capture
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(PAIR ? 2 * nunits : nunits);
   cfg.blockDim = dim3(threads), cfg.dynamicSmemBytes = smem, cfg.stream = stream;
