@@ -94,6 +94,77 @@ def resample():
     print("wrote resample.npz", {k: v.shape for k, v in out.items()})
 
 
+@torch.inference_mode()
+def headline(which=("zipvoice", "distill", "dialog", "real", "stress")):
+    """Full-size known answers from the UNMODIFIED reference (VERDICT r1 "next" item 1).
+    python -m oracle.make_golden headline [zipvoice|distill|dialog|real|stress ...]
+      zipvoice: 123 M ZipVoice, B = 2 (row 0 full, row 1 ragged), T = 1219, 281-frame prompt, 16 NFE, g = 1.0,
+                t_shift = 0.5 through EulerSolver.sample (solver.py:182-240); final x1 + the x entering every NFE
+                (row 0, every 8th frame) + the guided velocity of NFE 0 and NFE 12 (both t > 0.5 branches).
+      distill:  123 M ZipVoiceDistill, 4 NFE, g = 3.0, T = 1219 (zipvoice_distill.py:27-69).
+      dialog:   123 M ZipVoiceDialog fm_decoder, one guided velocity, B = 1, T = 6563 (52 / 26 / 13 key tiles).
+      real:     small ZipVoice.sample(duration="real") (zipvoice.py:425-437).
+      stress:   123 M stress weights, one guided velocity at B = 1, T = 1219 (settles the per-NFE tolerance)."""
+    from tests.cases import headline_case
+    from zipvoice_b200 import synth
+    torch.set_num_threads(os.cpu_count())
+    base = synth.BASE_MODEL_CFG
+    if "zipvoice" in which:
+        m = _ref_model("zipvoice", base, synth.make_state_dict(base, seed=0))
+        x0, text, speech, mask = headline_case("zipvoice")
+        traj, vel = [], {}
+
+        def pre(mod, args, kwargs):
+            traj.append(kwargs["x"][0, ::8].clone())
+
+        def post(mod, args, kwargs, out):
+            if len(traj) - 1 in (0, 12):
+                vel[len(traj) - 1] = out.clone()
+
+        h1 = m.solver.model.register_forward_pre_hook(pre, with_kwargs=True)
+        h2 = m.solver.model.register_forward_hook(post, with_kwargs=True)
+        x1 = m.solver.sample(x=x0, text_condition=text, speech_condition=speech, padding_mask=mask, num_step=16,
+                             guidance_scale=1.0, t_shift=0.5)
+        h1.remove(), h2.remove()
+        np.savez(os.path.join(OUT, "headline_zipvoice.npz"), x1=x1.numpy(), traj_row0_s8=torch.stack(traj).numpy(),
+                 v_nfe0=vel[0].numpy(), v_nfe12_row0=vel[12][0].numpy())
+        print("headline zipvoice written", x1.shape, len(traj))
+    if "distill" in which:
+        m = _ref_model("distill", base, synth.make_state_dict(base, seed=2, distill=True))
+        x0, text, speech, mask = headline_case("distill")
+        x1 = m.solver.sample(x=x0, text_condition=text, speech_condition=speech, padding_mask=mask, num_step=4,
+                             guidance_scale=3.0, t_shift=0.5)
+        np.savez(os.path.join(OUT, "headline_distill.npz"), x1=x1.numpy())
+        print("headline distill written", x1.shape)
+    if "dialog" in which:
+        m = _ref_model("dialog", base, synth.make_state_dict(base, seed=3, dialog=True))
+        x0, text, speech, mask = headline_case("dialog")
+        v = m.solver.model(t=torch.tensor(0.3), x=x0, text_condition=text, speech_condition=speech,
+                           padding_mask=mask, guidance_scale=1.5)
+        np.savez(os.path.join(OUT, "headline_dialog.npz"), v=v.numpy())
+        print("headline dialog written", v.shape)
+    if "stress" in which:
+        m = _ref_model("zipvoice", base, synth.make_state_dict(base, seed=1, stress=True))
+        x0, text, speech, mask = headline_case("stress")
+        v = m.solver.model(t=torch.tensor(0.3), x=x0, text_condition=text, speech_condition=speech,
+                           padding_mask=mask, guidance_scale=1.0)
+        np.savez(os.path.join(OUT, "headline_stress_velocity.npz"), v=v.numpy())
+        print("headline stress written", v.shape)
+    if "real" in which:
+        small = synth.small_model_cfg()
+        m = _ref_model("zipvoice", small, synth.make_state_dict(small, seed=1, stress=True))
+        tokens, prompt_tokens = synth.make_tokens(3, n_prompt=11, n_text=27, seed=15, ragged=True)
+        pf, pfl = synth.make_prompt_features(3, 19, seed=16, ragged=True)
+        fl = torch.tensor([61, 40, 52], dtype=torch.int64)
+        torch.manual_seed(666)
+        out = m.sample(tokens=tokens, prompt_tokens=prompt_tokens, prompt_features=pf, prompt_features_lens=pfl,
+                       features_lens=fl, t_shift=0.5, duration="real", num_step=3, guidance_scale=1.0)
+        np.savez(os.path.join(OUT, "sample_small_real.npz"), x1_wo=out[0].numpy(), wo_lens=out[1].numpy(),
+                 x1_prompt=out[2].numpy(), prompt_lens=out[3].numpy())
+        print("sample(duration=real) written", out[0].shape, out[1])
+
+
+
 def main():
     from zipvoice_b200 import synth
     os.makedirs(OUT, exist_ok=True)
@@ -181,7 +252,10 @@ def bigvgan():
 
 
 if __name__ == "__main__":
-    if "bigvgan" in sys.argv[1:]:
+    if "headline" in sys.argv[1:]:
+        rest = [a for a in sys.argv[1:] if a != "headline"]
+        headline(tuple(rest) if rest else ("zipvoice", "distill", "dialog", "real", "stress"))
+    elif "bigvgan" in sys.argv[1:]:
         bigvgan()
     elif "stereo" in sys.argv[1:]:
         stereo()

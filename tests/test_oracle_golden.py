@@ -159,3 +159,43 @@ def test_sample_intermediate():
                                     guidance_scale=inp["guidance_scale"])
     assert lens.tolist() == g["lens"].tolist()
     assert rel_l2(x, torch.from_numpy(g["x"])) < 1e-5
+
+
+def test_headline_stress_velocity_T1219():
+    """Full-depth 123 M stress weights at the headline length: one guided NFE of the oracle against the unmodified
+    reference (oracle/make_golden.py headline stress)."""
+    from tests.cases import headline_case
+    torch.set_num_threads(os.cpu_count())
+    sd = synth.make_state_dict(synth.BASE_MODEL_CFG, seed=1, stress=True)
+    x0, text, speech, mask = headline_case("stress")
+    v = O.cfg_velocity(sd, synth.BASE_MODEL_CFG, torch.tensor(0.3), x0, text, speech, mask, guidance_scale=1.0)
+    assert rel_l2(v, _g("headline_stress_velocity.npz")["v"]) < TOL
+
+
+def test_headline_zipvoice_first_nfe_T1219():
+    """NFE 0 of the 16-NFE headline case (B = 2 ragged, T = 1219, t = 0: doubled-guidance branch, solver.py:92-97)."""
+    from tests.cases import headline_case
+    torch.set_num_threads(os.cpu_count())
+    sd = synth.make_state_dict(synth.BASE_MODEL_CFG, seed=0)
+    x0, text, speech, mask = headline_case("zipvoice")
+    ts = O.get_time_steps(0.0, 1.0, 16, 0.5)
+    v = O.cfg_velocity(sd, synth.BASE_MODEL_CFG, ts[0], x0, text, speech, mask, guidance_scale=1.0)
+    g = _g("headline_zipvoice.npz")
+    assert valid_rel_l2(v, g["v_nfe0"], mask) < TOL
+    x_next = x0 + v * (ts[1] - ts[0])
+    assert rel_l2(x_next[0, ::8], g["traj_row0_s8"][1]) < TOL
+
+
+def test_sample_duration_real():
+    cfg = synth.small_model_cfg()
+    sd = synth.make_state_dict(cfg, seed=1, stress=True)
+    tokens, prompt_tokens = synth.make_tokens(3, n_prompt=11, n_text=27, seed=15, ragged=True)
+    pf, pfl = synth.make_prompt_features(3, 19, seed=16, ragged=True)
+    fl = torch.tensor([61, 40, 52], dtype=torch.int64)
+    g = _g("sample_small_real.npz")
+    torch.manual_seed(666)
+    x0 = torch.randn(3, int((pfl + fl).max()), 100)
+    out = O.sample(sd, cfg, tokens, prompt_tokens, pf, pfl, features_lens=fl, t_shift=0.5, duration="real",
+                   num_step=3, guidance_scale=1.0, x0=x0)
+    assert torch.equal(out[1], g["wo_lens"]) and torch.equal(out[3], g["prompt_lens"])
+    assert rel_l2(out[0], g["x1_wo"]) < TOL and rel_l2(out[2], g["x1_prompt"]) < TOL
