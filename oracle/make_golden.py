@@ -121,13 +121,16 @@ def headline(which=("zipvoice", "distill", "dialog", "real", "stress")):
             if len(traj) - 1 in (0, 12):
                 vel[len(traj) - 1] = out.clone()
 
+        raw = []
+        h0 = m.fm_decoder.register_forward_hook(lambda mod, a, out: raw.append(out.clone()) if not raw else None)
         h1 = m.solver.model.register_forward_pre_hook(pre, with_kwargs=True)
         h2 = m.solver.model.register_forward_hook(post, with_kwargs=True)
         x1 = m.solver.sample(x=x0, text_condition=text, speech_condition=speech, padding_mask=mask, num_step=16,
                              guidance_scale=1.0, t_shift=0.5)
-        h1.remove(), h2.remove()
+        h0.remove(), h1.remove(), h2.remove()
+        # c_nfe0: the conditional rows [B, 2B) of the doubled batch as the network returned them (solver.py:99-105)
         np.savez(os.path.join(OUT, "headline_zipvoice.npz"), x1=x1.numpy(), traj_row0_s8=torch.stack(traj).numpy(),
-                 v_nfe0=vel[0].numpy(), v_nfe12_row0=vel[12][0].numpy())
+                 v_nfe0=vel[0].numpy(), v_nfe12_row0=vel[12][0].numpy(), c_nfe0_row0=raw[0][2].numpy())
         print("headline zipvoice written", x1.shape, len(traj))
     if "distill" in which:
         m = _ref_model("distill", base, synth.make_state_dict(base, seed=2, distill=True))
@@ -139,16 +142,22 @@ def headline(which=("zipvoice", "distill", "dialog", "real", "stress")):
     if "dialog" in which:
         m = _ref_model("dialog", base, synth.make_state_dict(base, seed=3, dialog=True))
         x0, text, speech, mask = headline_case("dialog")
+        raw = []
+        h0 = m.fm_decoder.register_forward_hook(lambda mod, a, out: raw.append(out.clone()))
         v = m.solver.model(t=torch.tensor(0.3), x=x0, text_condition=text, speech_condition=speech,
                            padding_mask=mask, guidance_scale=1.5)
-        np.savez(os.path.join(OUT, "headline_dialog.npz"), v=v.numpy())
+        h0.remove()
+        np.savez(os.path.join(OUT, "headline_dialog.npz"), v=v.numpy(), c=raw[0][1:].numpy())
         print("headline dialog written", v.shape)
     if "stress" in which:
         m = _ref_model("zipvoice", base, synth.make_state_dict(base, seed=1, stress=True))
         x0, text, speech, mask = headline_case("stress")
+        raw = []
+        h0 = m.fm_decoder.register_forward_hook(lambda mod, a, out: raw.append(out.clone()))
         v = m.solver.model(t=torch.tensor(0.3), x=x0, text_condition=text, speech_condition=speech,
                            padding_mask=mask, guidance_scale=1.0)
-        np.savez(os.path.join(OUT, "headline_stress_velocity.npz"), v=v.numpy())
+        h0.remove()
+        np.savez(os.path.join(OUT, "headline_stress_velocity.npz"), v=v.numpy(), c=raw[0][1:].numpy())
         print("headline stress written", v.shape)
     if "real" in which:
         small = synth.small_model_cfg()

@@ -50,3 +50,10 @@ def headline_case(name):
     if name == "stress":
         return case_inputs(1, 1219, 281, seed=44)
     raise KeyError(name)
+
+
+def guided_tol(g_eff, tol_raw):
+    """Per-NFE tolerance of a classifier-free-guided velocity v = (1 + g) c - g u (solver.py:100-110): the two network
+    passes carry independent rounding errors of relative size tol_raw and |v| ~ |c| ~ |u|, so the guided bound is
+    tol_raw * sqrt((1 + g)^2 + g^2); g_eff is the guidance actually applied (doubled for t <= 0.5, solver.py:92-97)."""
+    return tol_raw * ((1.0 + g_eff) ** 2 + g_eff ** 2) ** 0.5
