@@ -418,8 +418,12 @@ int engine_finalize(Engine& e) {
 
 // ------------------------------------------------------------------ workspace
 int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
-  const size_t rows = (size_t)nb * T;
+  size_t rows = (size_t)nb * T;
   if (rows <= ws.cap_rows && nb <= ws.cap_nb) return 0;
+  // capacity only ever grows in BOTH dimensions: alternating shapes (many short utterances, then few long ones)
+  // must not shrink one of them and reallocate ~3 GB (and drop every captured graph) on each call
+  if (rows < ws.cap_rows) rows = ws.cap_rows;
+  if (nb < ws.cap_nb) nb = ws.cap_nb;
   cudaDeviceSynchronize();
   for (void* p : ws.allocs) cudaFree(p);
   ws.allocs.clear();
