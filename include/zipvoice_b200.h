@@ -108,6 +108,27 @@ int zv_fbank_bigvgan(void* handle, const float* wav, const int64_t* lens, int B,
 int zv_resample(void* handle, const float* wav, const int64_t* lens, int B, int N, int orig_freq, int new_freq,
                 float* out, int n_out, void* stream);
 
+/* zv_resample without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, results and error codes as zv_resample, which cudaMallocs its polyphase filter
+ * bank ([new][K] fp32, new / K from the reduced rate ratio) the first time it sees a rate pair.  Here the bank is
+ * SCRATCH: every call rebuilds it on the device (double arithmetic, the formula of zv_resample) into a file-scope
+ * `static __device__` array of ZV_RESAMPLE_STATIC_MAX_FLOATS floats (256 KB, held by every GPU that loads the
+ * library until the process exits) and then runs the resampling kernel on it.  The call makes no cudaMalloc /
+ * cudaFree / allocating library call and no host<->device copy; the caller owns wav, lens and out.
+ *  - Limit: new_r * K <= ZV_RESAMPLE_STATIC_MAX_FLOATS, with new_r = new_freq / gcd, orig_r = orig_freq / gcd,
+ *    K = 2 * ceil(6 * orig_r / (0.99 * min(orig_r, new_r))) + orig_r (8 / 11.025 / 16 / 22.05 / 32 / 44.1 / 48 / 96 kHz
+ *    <-> 24 kHz all fit; 44100 -> 24000 needs 13 680).  Larger banks and B > 65535 are rejected with error 967 and a
+ *    message in zv_last_error; nothing is launched.
+ *  - The array is shared by every call on that GPU (all handles, all streams) and keeps the last call's contents.
+ *    Nothing in it has to start at zero: each call overwrites every entry it reads.  Calls that OVERLAP on the GPU
+ *    (different streams, or graph branches without an edge between them) race on it; calls on one stream do not.
+ *  - The first call on a device looks the array's device address up (cudaGetSymbolAddress, once per device, that
+ *    device current); make that first call outside stream capture. */
+#define ZV_RESAMPLE_STATIC_MAX_FLOATS 65536
+int zv_resample_static(void* handle, const float* wav, const int64_t* lens, int B, int N, int orig_freq,
+                       int new_freq, float* out, int n_out, void* stream);
+
 /* Vocos.decode (third-party `vocos`; call site bin/infer_zipvoice.py:378): mel (B,100,T) -> wav (B, 256*(T-1)).
  * Weights are set through zv_set_weight with the "vocoder." prefix (vocos checkpoint names: backbone.*,
  * head.out.*).  lens (B) int64 valid frames per row, or NULL for full rows: frames >= lens[b] are treated

@@ -46,6 +46,7 @@ _SIGS = {
     "zv_fbank_bigvgan": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "zv_vocos_decode": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "zv_resample": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P]),
+    "zv_resample_static": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P]),
     "zv_debug_gemm": (_I, [_I, _I, _I, _I, _I, _I, _I] + [_P] * 12),
     "zv_debug_attention": (_I, [_I, _I, _I, _I, _I, _P, _I, _P, _P, _P, _I, _P, _P, _P]),
     "zv_debug_set_attn_impl": (_I, [_I]),

@@ -785,3 +785,109 @@ extern "C" int zv_resample(void* handle, const float* wav, const int64_t* lens, 
        (resample_kernel<<<grid, 256, 0, s>>>(wav, lens, N, bk->w, bk->orig, bk->nw, bk->width, bk->K, n_out, out)));
   return 0;
 }
+
+// ------------------------------------------------------------------ zv_resample_static (no allocation)
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops).  zv_resample above cudaMallocs + cudaMemcpys its filter bank
+// on the first use of a rate pair; this variant treats the bank as scratch that every call rebuilds on the device
+// into the file-scope array below, so the call allocates nothing and copies nothing.
+//
+// g_resample_static_scratch is a HOST-SIDE STAND-IN in host code, not a device address: handing it to a kernel
+// would fault (or silently use the wrong memory where the GPU can reach host memory).  Host code gets the real
+// address once per device from cudaGetSymbolAddress (resample_static_setup) and passes THAT to the kernels.
+// Every GPU that loads the library holds these 256 KB until the process exits.  All calls on a GPU share the array
+// and it keeps the last call's contents; nothing has to start at zero because resample_bank_static_kernel writes
+// every one of the nw * K entries resample_kernel reads.  Calls that overlap on the GPU race on it.
+namespace zv {
+
+static __device__ __align__(256) float g_resample_static_scratch[ZV_RESAMPLE_STATIC_MAX_FLOATS];
+
+static constexpr int RS_MAX_DEVICES = 64;
+static float* g_resample_static_ptr[RS_MAX_DEVICES];  // device address of the array on device i; null = not set up
+
+// _get_sinc_resample_kernel in double, the expression order of resample_bank() above; one thread per bank entry.
+__global__ void resample_bank_static_kernel(float* __restrict__ bank, int orig, int nw, int width, int K) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nw * K) return;
+  const int p = i / K, j = i - p * K;
+  const double lpw = 6.0, rolloff = 0.99;
+  const double base_freq = (double)(orig < nw ? orig : nw) * rolloff;
+  const double scale = base_freq / orig;
+  const double idx = (double)(j - width) / orig;
+  double t = ((double)(-p) / nw + idx) * base_freq;
+  t = t < -lpw ? -lpw : (t > lpw ? lpw : t);
+  const double c = cos(t * M_PI / lpw / 2.0);
+  const double window = c * c;
+  t *= M_PI;
+  const double sinc = t == 0.0 ? 1.0 : sin(t) / t;
+  bank[i] = (float)(sinc * (window * scale));
+}
+
+// Once per device, with that device current: the device address of the scratch array.
+static int resample_static_setup(Engine& e, float** out) {
+  int dev = -1;
+  AU_TRY((int)cudaGetDevice(&dev));
+  if (dev < 0 || dev >= RS_MAX_DEVICES) {
+    e.err = "zv_resample_static: device ordinal out of range";
+    return 966;
+  }
+  if (!g_resample_static_ptr[dev]) {
+    float* p = nullptr;
+    AU_TRY((int)cudaGetSymbolAddress((void**)&p, g_resample_static_scratch));
+    if (!p) {
+      e.err = "zv_resample_static: cudaGetSymbolAddress returned a null address";
+      return 966;
+    }
+    g_resample_static_ptr[dev] = p;
+  }
+  *out = g_resample_static_ptr[dev];
+  return 0;
+}
+
+}  // namespace zv
+
+extern "C" int zv_resample_static(void* handle, const float* wav, const int64_t* lens, int B, int N, int orig_freq,
+                                  int new_freq, float* out, int n_out, void* stream) {
+  Engine* ep = (Engine*)handle;
+  if (!ep) return 960;
+  Engine& e = *ep;
+  e.err.clear();
+  if (B <= 0 || N <= 0 || orig_freq <= 0 || new_freq <= 0) {
+    e.err = "zv_resample_static: need B, N, orig_freq, new_freq > 0";
+    return 964;
+  }
+  const long long want = ((long long)N * new_freq + orig_freq - 1) / orig_freq;
+  if (n_out != want) {
+    e.err = "zv_resample_static: n_out must be ceil(new_freq * N / orig_freq)";
+    return 964;
+  }
+  int g = orig_freq, h = new_freq;
+  while (h) {
+    const int t = g % h;
+    g = h, h = t;
+  }
+  const int orig = orig_freq / g, nw = new_freq / g;
+  const double base_freq = (double)(orig < nw ? orig : nw) * 0.99;
+  const int width = (int)ceil(6.0 * orig / base_freq);
+  const long long K = 2LL * width + orig;
+  if ((long long)nw * K > (long long)ZV_RESAMPLE_STATIC_MAX_FLOATS || B > 65535) {
+    char msg[320];
+    snprintf(msg, sizeof(msg),
+             "zv_resample_static: %d -> %d Hz needs a filter bank of %d x %lld = %lld floats (B = %d); the static scratch "
+             "holds ZV_RESAMPLE_STATIC_MAX_FLOATS = %d and B <= 65535 -- use zv_resample", orig_freq, new_freq, nw, K,
+             (long long)nw * K, B, ZV_RESAMPLE_STATIC_MAX_FLOATS);
+    e.err = msg;
+    return 967;
+  }
+  float* bank = nullptr;
+  AU_TRY(resample_static_setup(e, &bank));
+  cudaStream_t s = (cudaStream_t)stream;
+  const int n_bank = nw * (int)K;
+  g_launch_count += 2;  // no zv_prof events here: the profiler's event pool allocates
+  resample_bank_static_kernel<<<(n_bank + 255) / 256, 256, 0, s>>>(bank, orig, nw, width, (int)K);
+  AU_TRY((int)cudaGetLastError());
+  dim3 grid((n_out + 255) / 256, B);
+  resample_kernel<<<grid, 256, 0, s>>>(wav, lens, N, bank, orig, nw, width, (int)K, n_out, out);
+  AU_TRY((int)cudaGetLastError());
+  return 0;
+}

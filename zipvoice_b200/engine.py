@@ -192,6 +192,27 @@ class Engine:
                                              _ptr(out), n_out, _stream(self.device)))
         return out
 
+    RESAMPLE_STATIC_MAX_FLOATS = 65536  # ZV_RESAMPLE_STATIC_MAX_FLOATS (include/zipvoice_b200.h)
+
+    def resample_static(self, wav: torch.Tensor, orig_freq: int, new_freq: int, out: torch.Tensor,
+                        lens: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """zv_resample_static: ``resample`` for callers that must not allocate (no counterpart in the reference).
+        The CALLER owns every buffer: ``wav`` (B, N) fp32 and ``out``
+        (B, ceil(new_freq * N / orig_freq)) fp32, contiguous, on this engine's device (``lens`` int64 likewise) --
+        nothing is converted, copied or allocated here or in the library.  The filter bank lives in a 256 KB static
+        device array shared by all calls on the GPU: rate pairs whose bank exceeds RESAMPLE_STATIC_MAX_FLOATS raise,
+        and calls that overlap on the GPU (different streams) race."""
+        for t, dt in ((wav, torch.float32), (out, torch.float32)) + (() if lens is None else ((lens, torch.int64),)):
+            assert t.is_cuda and t.device == self.device and t.dtype == dt and t.is_contiguous(), \
+                "resample_static takes caller-owned contiguous tensors on the engine's device"
+        B, N = wav.shape
+        n_out = (N * new_freq + orig_freq - 1) // orig_freq
+        assert tuple(out.shape) == (B, n_out), f"out must be ({B}, {n_out})"
+        with torch.cuda.device(self.device):
+            self._check(self.lib.zv_resample_static(self._h, _ptr(wav), _ptr(lens), B, N, int(orig_freq),
+                                                    int(new_freq), _ptr(out), n_out, _stream(self.device)))
+        return out
+
     def vocos_decode(self, mel: torch.Tensor, lens: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Vocos.decode: mel (B, 100, T) -> waveform (B, 256 (T - 1)); needs "vocoder.*" weights."""
         m = self._prep(mel)
