@@ -73,6 +73,14 @@ int zv_velocity(void* handle, int variant, float t, const float* x, const float*
                 const float* speech_condition, const uint8_t* padding_mask, int B, int T, const float* guidance,
                 int guidance_len, float* v_out, void* stream);
 
+/* ZipVoice.forward_fm_decoder (zipvoice.py:135-185) -> TTSZipformer.forward (zipformer.py:242-293): the network
+ * itself, without the classifier-free-guidance logic of DiffusionModel.  t: HOST floats, t_len 1 (the 0-dim case,
+ * :168-169) or N (the (N,1,1) case, :165-167: one time step per row); guidance: HOST floats embedded by the distilled
+ * model (:171-178), guidance_len 0 (guidance_scale=None), 1 or N.  x, speech, v_out (N,T,X); text (N,T,feat_dim). */
+int zv_forward_fm_decoder(void* handle, const float* t, int t_len, const float* x, const float* text_condition,
+                          const float* speech_condition, const uint8_t* padding_mask, int N, int T,
+                          const float* guidance, int guidance_len, float* v_out, void* stream);
+
 /* EulerSolver.sample / DistillEulerSolver.sample (solver.py:182-240).  x0 is not modified; x1 receives
  * the solution at t_end.  No host synchronisation inside. */
 int zv_sample(void* handle, int variant, const float* x0, const float* text_condition,
@@ -135,19 +143,6 @@ int zv_resample_static(void* handle, const float* wav, const int64_t* lens, int 
  * as absent (zero-padded convolutions, as if each utterance were decoded alone) and their samples are 0. */
 int zv_vocos_decode(void* handle, const float* mel, const int64_t* lens, int B, int T, float* wav_out, void* stream);
 
-/* Test / bench hooks (not part of the reference-facing surface). */
-int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int gate_cols, const float* A_f32,
-                  const float* W_f32, const float* bias, const float* rowbias, const float* res, const float* resbias,
-                  const float* orig, const float* bypass_scale, const uint8_t* mask, float* out_f32, float* out2_f32,
-                  void* stream);
-int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp_f32, int ldq, const float* E,
-                       const uint8_t* mask, const float* V_f32, int ldv, const float* gate_f32, float* out_f32,
-                       void* stream);
-int zv_debug_set_attn_impl(int impl);
-int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv, int use_mask, int dbg, int iters, float* ms_out);
-int zv_debug_gemm_bench(int mode, int impl, int M, int N, int K, int L, int gate_cols, int block_n, int iters,
-                        float* ms_out);
-int zv_debug_pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E_out, void* stream);
 /* Per-kernel-class device timing: when enabled every launch is bracketed by CUDA events on its stream.
  * zv_prof_read synchronises the device, fills ms / work / launches (arrays of zv_prof_num_classes()) and
  * resets the records.  work = algorithmic FLOPs for tensor-bound classes, algorithmic bytes otherwise. */

@@ -186,3 +186,14 @@ def test_compute_fbank_bulk_equals_single_extraction(tmp_path):
         assert feats[i].shape == want.shape == ((w.numel() + 128) // 256, 100)
         assert float(np.abs(feats[i] - want).max()) < 1e-5
         assert np.array_equal(z[f"feat_{i}"], feats[i])
+
+
+def test_fbank_rejects_rows_shorter_than_the_reflect_padding():
+    """torch.stft's reflect padding raises for inputs not longer than the pad; so does the extractor."""
+    fb, voc, _ = audio()
+    x = torch.zeros(2, 4000, device="cuda")
+    with pytest.raises(ValueError):
+        fb.engine.fbank(x, torch.tensor([4000, 512]))
+    with pytest.raises(ValueError):
+        fb.engine.fbank(x[:, :384], kind="bigvgan")
+    assert fb.engine.fbank(x, torch.tensor([4000, 513])).shape == (2, 16, 100)

@@ -236,3 +236,25 @@ def test_self_attention_reference_repeat(L):
     assert torch.isfinite(out).all()
     r = rel(out, want)
     assert r < 8e-3, f"rel-L2 {r:.3e}"
+
+
+@pytest.mark.parametrize("impl", [1, 2, 3], ids=["simt", "tcgen05", "tcgen05_pair"])
+def test_gemm_fp16_output_is_precise_at_1e3_and_saturates(impl):
+    """The attention q | k | p projection stores IEEE fp16, un-scaled.  At |q| ~ 1e3 the stored value
+    keeps fp16's 11-bit mantissa; beyond the fp16 range it SATURATES at +-65504 (cvt.rn.satfinite) instead of turning
+    into +-inf, which would make a whole softmax row NaN."""
+    g = torch.Generator(device="cuda").manual_seed(5)
+    M, N, K = 300, 272, 512   # the q | k | p projection's shape
+    A = torch.randn(M, K, device="cuda", generator=g)
+    W = torch.randn(N, K, device="cuda", generator=g) * 0.05
+    bias = torch.tensor([0.0, 1e3, -1e3, 1e5, -1e5, 6.6e4, 3e38], device="cuda")[torch.arange(N, device="cuda") % 7].contiguous()
+    out, _ = run_gemm(7, impl, A, W, bias)          # mode 7: EPI_BIAS with the fp16 store
+    ref, _ = ref_gemm(EPI_BIAS, A, W, bias)
+    assert bool(torch.isfinite(out).all()), "fp16 overflow to inf"
+    want = ref.clamp(-65504.0, 65504.0)
+    err = (out - want).abs()
+    assert bool((err <= want.abs() * 2.0 ** -11 + 1e-3).all()), float((err / (want.abs() + 1.0)).max())
+    big = (torch.arange(N, device="cuda") % 7 >= 3)
+    assert bool((out[:, big].abs() == 65504.0).all())
+    k3 = (torch.arange(N, device="cuda") % 7 == 1)
+    assert float((out[:, k3] - ref[:, k3]).abs().max()) <= 0.5 + 1e-3   # spacing of fp16 near 1e3 is 0.5

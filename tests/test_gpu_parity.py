@@ -216,3 +216,140 @@ def test_sample_intermediate_golden():
     mask = torch.arange(x.shape[1])[None, :] >= g["lens"][:, None]
     r = valid_rel_l2(x.cpu(), g["x"], mask)
     assert r < TOL_MEL, f"sample_intermediate rel-L2 {r:.3e}"
+
+
+def test_bounded_graph_and_position_table_caches():
+    """Single-utterance serving sees a new T on almost every request: the captured-graph cache is an LRU of
+    16 keys and every layer keeps the position tables of at most 32 lengths.  40 distinct lengths drive both
+    evictions (a freed table invalidates the graphs that captured its address); every call, eager, captured or
+    replayed, before and after an eviction, must return exactly what the plain loop returns."""
+    m, cfg, sd = engine("zipvoice", "small", 1, True)
+    eng = m.engine
+    kw = dict(num_step=2, guidance_scale=1.0, t_shift=0.5)
+    lengths = list(range(24, 64))
+    cases = {T: case_inputs(1, T, 7, seed=100 + T) for T in lengths}
+    eng.set_option("graph_max_rows", 0)
+    want = {T: eng.sample(*cases[T], **kw).clone() for T in (24, 25, 40, 62, 63)}
+    eng.set_option("graph_max_rows", 32768)
+    for rnd in range(3):            # round 0 eager, round 1 capture + launch, round 2 replay -- as far as the LRU allows
+        for T in lengths:
+            got = eng.sample(*cases[T], **kw)
+            if T in want:
+                assert torch.equal(got, want[T]), f"round {rnd}, T = {T}"
+    for T in (24, 24, 24, 63, 63, 63):   # evicted long ago: eager again, recaptured, replayed
+        assert torch.equal(eng.sample(*cases[T], **kw), want[T]), f"after eviction, T = {T}"
+
+
+def test_forward_fm_decoder_per_sample_time_steps():
+    """forward_fm_decoder(t (N, 1, 1)) with a different time step per row (zipvoice.py:165-167, SURVEY 8b "signatures
+    to honour") and, for the distilled model, a guidance value per row (zipvoice.py:171-178), against the oracle."""
+    from oracle import zipvoice_oracle as O
+    x0, text, speech, mask = case_inputs(3, 45, 12, seed=33)
+    t = torch.tensor([0.15, 0.85, 0.5]).reshape(3, 1, 1)
+    m, cfg, sd = engine("zipvoice", "small", 1, True)
+    v = m.forward_fm_decoder(t, x0, text, speech, mask).cpu()
+    want = O.forward_fm_decoder(sd, cfg, t, x0, text, speech, mask)
+    r = valid_rel_l2(v, want, mask)
+    assert r < TOL_NFE_STRESS, f"per-row t: rel-L2 {r:.3e}"
+    for b in range(3):   # every row equals the scalar-t call with that row's time step
+        vb = m.forward_fm_decoder(t[b, 0, 0], x0[b:b + 1], text[b:b + 1], speech[b:b + 1], mask[b:b + 1]).cpu()
+        rb = valid_rel_l2(v[b:b + 1], vb, mask[b:b + 1])
+        assert rb < 2e-3, f"row {b}: batched per-row t vs scalar call {rb:.3e}"
+    same = m.forward_fm_decoder(torch.full((3, 1, 1), 0.3), x0, text, speech, mask)
+    assert torch.equal(same, m.forward_fm_decoder(torch.tensor(0.3), x0, text, speech, mask))
+    md, cfgd, sdd = engine("distill", "small", 2, True)
+    g = torch.tensor([0.5, 3.0, 1.5]).reshape(3, 1, 1)
+    vd = md.forward_fm_decoder(t, x0, text, speech, mask, guidance_scale=g).cpu()
+    wd = O.forward_fm_decoder(sdd, cfgd, t, x0, text, speech, mask, guidance_scale=g)
+    rd = valid_rel_l2(vd, wd, mask)
+    assert rd < TOL_NFE_STRESS, f"per-row t and guidance (distill): rel-L2 {rd:.3e}"
+    with pytest.raises(Exception):     # zipformer.py:270-272: guidance needs the distilled model's embedding
+        m.forward_fm_decoder(t, x0, text, speech, mask, guidance_scale=g)
+
+
+class _RefShaped:
+    """Stand-in with the shape of the reference nn.Modules that ``install`` patches (zipvoice.py:38-133): a
+    ``state_dict()`` with the reference's tensor names, ``pad_id``, a ``solver`` attribute (the seam at zipvoice.py:133)
+    and a ``sample()`` that calls ``self.solver.sample(...)`` BY KEYWORD exactly as zipvoice.py:460-468 does.  The parts
+    ``install`` does not replace (text encoder, text condition) come from the CPU oracle here, as they would come
+    from the reference's own torch modules."""
+
+    def __init__(self, cfg, sd, pad_id, dialog=None):
+        self.cfg, self._sd, self.pad_id, self._dialog = cfg, sd, pad_id, dialog
+        self.solver = None  # EulerSolver(self, func_name="forward_fm_decoder") in the reference
+        if dialog:
+            self.spk_a_id, self.spk_b_id = dialog
+
+    def state_dict(self):
+        return self._sd
+
+    def sample(self, tokens, prompt_tokens, prompt_features, prompt_features_lens, speed=1.0, t_shift=1.0,
+               num_step=5, guidance_scale=0.5, x0=None):
+        from oracle import zipvoice_oracle as O
+        cat = [p + t for p, t in zip(prompt_tokens, tokens)]
+        embed, cat_lens = O.forward_text_embed(self._sd, self.cfg, cat, self.pad_id, self._dialog)
+        ptl = torch.tensor([len(t) for t in prompt_tokens])
+        tl = torch.tensor([len(t) for t in tokens])
+        total = O.predict_features_lens(prompt_features_lens, ptl, tl, speed)
+        text_condition, padding_mask = O.forward_text_condition(embed, cat_lens, total)     # zipvoice.py:421-437
+        B, T, _ = text_condition.shape
+        speech_condition = torch.nn.functional.pad(prompt_features, (0, 0, 0, T - prompt_features.size(1)))
+        speech_condition = speech_condition * (~O.make_pad_mask(prompt_features_lens, T)).unsqueeze(-1)
+        x1 = self.solver.sample(x=x0, text_condition=text_condition, speech_condition=speech_condition,
+                                padding_mask=padding_mask, num_step=num_step, guidance_scale=guidance_scale,
+                                t_shift=t_shift)                                             # zipvoice.py:460-468
+        wo_lens = (~padding_mask).sum(-1) - prompt_features_lens
+        out = torch.zeros(B, int(wo_lens.max()), x1.size(2))
+        for i in range(B):                                                                   # zipvoice.py:469-486
+            out[i, : int(wo_lens[i])] = x1[i, int(prompt_features_lens[i]): int(prompt_features_lens[i] + wo_lens[i])].cpu()
+        return out, wo_lens
+
+
+def test_install_on_reference_shaped_modules():
+    """``install(ref_model, cfg)``: the solver of a reference-shaped object is replaced and its own
+    ``sample()`` -- unchanged, calling ``self.solver.sample`` by keyword -- reproduces the unmodified reference's
+    golden output; the class NAME selects the solver / engine flavour as it does for the reference classes."""
+    from oracle import zipvoice_oracle as O
+    from zipvoice_b200 import synth
+    from zipvoice_b200.model import install
+    from zipvoice_b200.solver import B200DistillEulerSolver, B200EulerSolver
+    cfg = synth.small_model_cfg()
+    ZipVoice = type("ZipVoice", (_RefShaped,), {})
+    ZipVoiceDistill = type("ZipVoiceDistill", (_RefShaped,), {})
+    ZipVoiceDialog = type("ZipVoiceDialog", (_RefShaped,), {})
+    # ---- ZipVoice: sample() through the patched seam vs the reference golden and vs ZipVoiceB200
+    sd = synth.make_state_dict(cfg, seed=1, stress=True)
+    ref = ZipVoice(cfg, sd, synth.PAD_ID)
+    eng = install(ref, cfg)
+    assert type(ref.solver) is B200EulerSolver and not eng.distill and not eng.dialog
+    tokens, prompt_tokens = synth.make_tokens(2, n_prompt=9, n_text=21, seed=5, ragged=True)
+    pf, pfl = synth.make_prompt_features(2, 14, seed=6, ragged=True)
+    ptl, tl = torch.tensor([len(t) for t in prompt_tokens]), torch.tensor([len(t) for t in tokens])
+    T = int(O.predict_features_lens(pfl, ptl, tl, 1.3).max())
+    torch.manual_seed(666)
+    x0 = torch.randn(2, T, 100)
+    out, wo_lens = ref.sample(tokens, prompt_tokens, pf, pfl, speed=1.3, t_shift=0.5, num_step=3, guidance_scale=1.0, x0=x0)
+    g = _g("sample_small_stress.npz")
+    assert torch.equal(wo_lens, g["wo_lens"])
+    r = rel_l2(out, g["x1_wo"])
+    assert r < TOL_MEL, f"patched reference-shaped sample() vs reference golden: {r:.3e}"
+    m, _, _ = engine("zipvoice", "small", 1, True)
+    mine = m.sample(tokens, prompt_tokens, pf, pfl, speed=1.3, t_shift=0.5, duration="predict", num_step=3,
+                    guidance_scale=1.0, x0=x0.cuda())[0].cpu()
+    assert rel_l2(out, mine) < TOL_MEL
+    # ---- ZipVoiceDistill: the distill solver (guidance embedded) vs the reference golden
+    sdd = synth.make_state_dict(cfg, seed=2, distill=True, stress=True)
+    refd = ZipVoiceDistill(cfg, sdd, synth.PAD_ID)
+    engd = install(refd, cfg)
+    assert type(refd.solver) is B200DistillEulerSolver and engd.distill
+    xs, text, speech, mask = case_inputs(2, 37, 11, seed=10)
+    x1 = refd.solver.sample(x=xs, text_condition=text, speech_condition=speech, padding_mask=mask, num_step=2,
+                            guidance_scale=3.0, t_shift=0.5).cpu()
+    assert valid_rel_l2(x1, _g("euler_small_distill.npz")["x1"], mask) < TOL_MEL
+    # ---- ZipVoiceDialog: speaker ids travel, the engine's text encoder adds the speaker rows
+    sdg = synth.make_state_dict(cfg, seed=3, dialog=True, stress=True)
+    refg = ZipVoiceDialog(cfg, sdg, synth.PAD_ID, dialog=(synth.SPK_A_ID, synth.SPK_B_ID))
+    engg = install(refg, cfg)
+    assert engg.dialog and type(refg.solver) is B200EulerSolver
+    for e in (eng, engd, engg):
+        e.close()

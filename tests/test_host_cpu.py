@@ -20,6 +20,12 @@ def test_library_exports_every_declared_symbol():
     for name in sorted(declared):
         assert hasattr(lib, name), f"{name} declared in include/zipvoice_b200.h but not exported"
     assert declared == set(_lib.EXPORTS), declared ^ set(_lib.EXPORTS)
+    assert not any(n.startswith("zv_debug") for n in declared), "test hooks belong in csrc/zv_debug.h"
+    dbg = open(os.path.join(ROOT, "zipvoice_b200", "csrc", "zv_debug.h")).read()
+    private = set(re.findall(r"\b(zv_[a-z0-9_]+)\s*\(", dbg))
+    assert private == set(_lib.DEBUG_EXPORTS), private ^ set(_lib.DEBUG_EXPORTS)
+    for name in sorted(private):
+        assert hasattr(lib, name), f"{name} declared in csrc/zv_debug.h but not exported"
 
 
 def test_time_steps_match_torch():

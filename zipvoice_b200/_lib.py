@@ -39,6 +39,7 @@ _SIGS = {
     "zv_set_option": (_I, [_P, C.c_char_p, _I]),
     "zv_time_steps": (_I, [_D, _D, _I, _D, C.POINTER(_F)]),
     "zv_velocity": (_I, [_P, _I, _F, _P, _P, _P, _P, _I, _I, C.POINTER(_F), _I, _P, _P]),
+    "zv_forward_fm_decoder": (_I, [_P, C.POINTER(_F), _I, _P, _P, _P, _P, _I, _I, C.POINTER(_F), _I, _P, _P]),
     "zv_sample": (_I, [_P, _I, _P, _P, _P, _P, _I, _I, _I, C.POINTER(_F), _I, _D, _D, _D, _P, _P]),
     "zv_text_embed": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "zv_text_condition": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P, _P]),
@@ -47,12 +48,6 @@ _SIGS = {
     "zv_vocos_decode": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "zv_resample": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P]),
     "zv_resample_static": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P]),
-    "zv_debug_gemm": (_I, [_I, _I, _I, _I, _I, _I, _I] + [_P] * 12),
-    "zv_debug_attention": (_I, [_I, _I, _I, _I, _I, _P, _I, _P, _P, _P, _I, _P, _P, _P]),
-    "zv_debug_set_attn_impl": (_I, [_I]),
-    "zv_debug_attention_bench": (_I, [_I] * 8 + [C.POINTER(_F)]),
-    "zv_debug_gemm_bench": (_I, [_I] * 9 + [C.POINTER(_F)]),
-    "zv_debug_pos_table": (_I, [_P, _I, _I, _I, _I, _P, _P]),
     "zv_prof_enable": (_I, [_P, _I]),
     "zv_prof_num_classes": (_I, []),
     "zv_prof_class_name": (C.c_char_p, [_I]),
@@ -61,7 +56,17 @@ _SIGS = {
     "zv_launch_count": (_LL, []),
     "zv_launch_count_reset": (None, []),
 }
+# private test / bench hooks (zipvoice_b200/csrc/zv_debug.h), not part of the reference-facing surface
+_DEBUG_SIGS = {
+    "zv_debug_gemm": (_I, [_I, _I, _I, _I, _I, _I, _I] + [_P] * 12),
+    "zv_debug_attention": (_I, [_I, _I, _I, _I, _I, _P, _I, _P, _P, _P, _I, _P, _P, _P]),
+    "zv_debug_set_attn_impl": (_I, [_I]),
+    "zv_debug_attention_bench": (_I, [_I] * 8 + [C.POINTER(_F)]),
+    "zv_debug_gemm_bench": (_I, [_I] * 9 + [C.POINTER(_F)]),
+    "zv_debug_pos_table": (_I, [_P, _I, _I, _I, _I, _P, _P]),
+}
 EXPORTS = tuple(_SIGS)
+DEBUG_EXPORTS = tuple(_DEBUG_SIGS)
 
 _lib = None
 
@@ -77,7 +82,7 @@ def load(build_if_missing: bool = True) -> C.CDLL:
         from . import build as _build
         _build.build()
     lib = C.CDLL(LIB_PATH)
-    for name, (res, args) in _SIGS.items():
+    for name, (res, args) in list(_SIGS.items()) + list(_DEBUG_SIGS.items()):
         fn = getattr(lib, name)  # AttributeError if the .so does not export it
         fn.restype, fn.argtypes = res, args
     _lib = lib

@@ -110,6 +110,12 @@ void zv_destroy(void* handle) {
   if (e->gev_in) cudaEventDestroy(e->gev_in);
   if (e->gev_out) cudaEventDestroy(e->gev_out);
   audio_destroy(*e);
+  if (e->pin_host) {
+    cudaFreeHost(e->pin_host);
+    for (int i = 0; i < Engine::kPinSlots; ++i) cudaEventDestroy(e->pin_ev[i]);
+  }
+  free_pos_tables(e->fm);
+  free_pos_tables(e->text);
   for (void* p : e->weight_allocs) cudaFree(p);
   for (void* p : e->ws_fm.allocs) cudaFree(p);
   for (void* p : e->ws_text.allocs) cudaFree(p);
@@ -196,7 +202,23 @@ void zv_launch_count_reset(void) { g_launch_count = 0; }
 }  // extern "C"
 
 static int upload_small(Engine* e, float* dst, const float* host, int n, cudaStream_t s) {
-  return (int)cudaMemcpyAsync(dst, host, (size_t)n * 4, cudaMemcpyHostToDevice, s);
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(s, &cap);
+  if (n > Engine::kPinSlotFloats || cap != cudaStreamCaptureStatusNone)  // oversized / capturing: plain staged copy
+    return (int)cudaMemcpyAsync(dst, host, (size_t)n * 4, cudaMemcpyHostToDevice, s);
+  if (!e->pin_host) {
+    API_TRY((int)cudaHostAlloc((void**)&e->pin_host, (size_t)Engine::kPinSlots * Engine::kPinSlotFloats * 4,
+                               cudaHostAllocDefault));
+    for (int i = 0; i < Engine::kPinSlots; ++i)
+      API_TRY((int)cudaEventCreateWithFlags(&e->pin_ev[i], cudaEventDisableTiming));
+  }
+  const int slot = e->pin_next;
+  e->pin_next = (slot + 1) % Engine::kPinSlots;
+  API_TRY((int)cudaEventSynchronize(e->pin_ev[slot]));  // never recorded: returns at once
+  float* stage = e->pin_host + (size_t)slot * Engine::kPinSlotFloats;
+  memcpy(stage, host, (size_t)n * 4);
+  API_TRY((int)cudaMemcpyAsync(dst, stage, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+  return (int)cudaEventRecord(e->pin_ev[slot], s);
 }
 
 // One DiffusionModel.forward / DistillDiffusionModel.forward.  t_dev points at the device scalar of
@@ -310,10 +332,23 @@ static int sample_graphed(Engine* e, int variant, const float* x0, const float* 
   Engine::SampleGraph* g = nullptr;
   for (auto& c : e->graphs)
     if (c.key == key) g = &c;
+  ++e->graph_tick;
+  if (g) g->last_use = e->graph_tick;
   int rc = 0;
   if (!g) {  // first sighting: eager
+    if (e->graphs.size() >= Engine::kMaxGraphs) {  // bounded cache: evict the least recently used key
+      size_t lru = 0;
+      for (size_t i = 1; i < e->graphs.size(); ++i)
+        if (e->graphs[i].last_use < e->graphs[lru].last_use) lru = i;
+      if (e->graphs[lru].exec) {
+        API_TRY((int)cudaStreamSynchronize(gs));  // a replay of it may still be running
+        cudaGraphExecDestroy(e->graphs[lru].exec);
+      }
+      e->graphs.erase(e->graphs.begin() + lru);
+    }
     Engine::SampleGraph c;
     c.key = key;
+    c.last_use = e->graph_tick;
     e->graphs.push_back(c);
     rc = sample_loop(e, variant, ts, e->gx, e->gtext, e->gspeech, gm, B, T, num_step, all_zero, guidance_len, gs);
   } else if (g->unsupported) {
@@ -364,6 +399,45 @@ extern "C" int zv_velocity(void* handle, int variant, float t, const float* x, c
   API_TRY(upload_small(e, e->ws_fm.guid_dev, guidance, guidance_len, s));
   return velocity_step(e, variant, t, e->ws_fm.t_dev, x, text, speech, mask, B, T, all_zero, guidance_len, v_out,
                        nullptr, 0.f, s);
+}
+
+// ZipVoice.forward_fm_decoder (zipvoice.py:135-185): the raw network call -- no classifier-free-guidance logic.
+extern "C" int zv_forward_fm_decoder(void* handle, const float* t, int t_len, const float* x, const float* text,
+                                     const float* speech, const uint8_t* mask, int N, int T, const float* guidance,
+                                     int guidance_len, float* v_out, void* stream) {
+  Engine* e = (Engine*)handle;
+  if (!e) return 960;
+  e->err.clear();
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!e->finalized) {
+    e->err = "zv_finalize_weights has not been called";
+    return 963;
+  }
+  if (N <= 0 || T <= 0 || !t || !(t_len == 1 || t_len == N) ||
+      !(guidance_len == 0 || guidance_len == 1 || guidance_len == N) || (guidance_len > 0 && !guidance)) {
+    e->err = "bad arguments (N, T > 0; t_len must be 1 or N; guidance_len 0, 1 or N)";
+    return 964;
+  }
+  if (guidance_len > 0 && !e->cfg.use_guidance_scale_embed) {  // zipformer.py:270-272
+    e->err = "guidance_scale needs a model built with use_guidance_scale_embed (ZipVoiceDistill)";
+    return 965;
+  }
+  Net& net = e->fm;
+  Workspace& ws = e->ws_fm;
+  const int Ft = e->cfg.feat_dim, F = e->cfg.stereo ? 2 * Ft : Ft;
+  API_TRY(ws_reserve(*e, net, ws, N, T));
+  API_TRY(upload_small(e, ws.t_dev, t, t_len, s));
+  if (guidance_len > 0) API_TRY(upload_small(e, ws.guid_dev, guidance, guidance_len, s));
+  API_K(KC_PACK, (double)N * T * (2 * F + Ft) * 4.0 + (double)N * T * net.in_pad * 2.0, s,
+        API_TRY(pack_input(x, text, speech, mask, N, T, F, Ft, 0, 0, ws.x_in, net.in_pad, mask ? ws.mask[0] : nullptr,
+                           s)));
+  TimeArgs ta;
+  ta.t = ws.t_dev, ta.t_stride = t_len == 1 ? 0 : 1;
+  if (guidance_len > 0) ta.g = ws.guid_dev, ta.g_stride = guidance_len == 1 ? 0 : 1;
+  API_TRY(net_forward(*e, net, ws, N, T, mask ? ws.mask[0] : nullptr, ta, ws.vel, s));
+  API_K(KC_CFG_EULER, (double)N * T * F * 4.0 * 2, s,
+        API_TRY(cfg_euler_update(nullptr, ws.vel, ws.guid_dev, 1, 1.0f, N, T, F, 0, 0.f, v_out, s)));
+  return 0;
 }
 
 extern "C" int zv_sample(void* handle, int variant, const float* x0, const float* text, const float* speech,

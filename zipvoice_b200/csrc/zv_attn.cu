@@ -280,13 +280,12 @@ __global__ void __launch_bounds__(256, (DV <= 16) ? 2 : 1) attn_kernel(AttnParam
 
 template <int DV>
 static int launch_attn(const AttnParams& p, int chunks, int dv_valid, cudaStream_t s) {
-  static bool attr = false;
+  static unsigned long long attr = 0;
   const int n_tiles = (p.L + BKV - 1) / BKV;
   const int smem = (int)sizeof(AttnSmem<DV>) + n_tiles * BKV + ((n_tiles + 15) & ~15);
   if (smem > 227 * 1024) return 931;  // sequence too long for the in-kernel mask copy
-  if (!attr) {
+  if (first_use_on_device(attr)) {
     cudaFuncSetAttribute(attn_kernel<DV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    attr = true;
   }
   dim3 grid((p.L + BQ - 1) / BQ, p.heads * chunks, p.nb);
   attn_kernel<DV><<<grid, 256, smem, s>>>(p, chunks, dv_valid);

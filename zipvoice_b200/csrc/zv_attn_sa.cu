@@ -370,10 +370,9 @@ int attention_sa_tma(const AttnParams& p, cudaStream_t s) {
   if (rc) return rc;
   rc = make_tmap(&tmV, p.V, 0, (uint64_t)p.nb * p.L, (uint64_t)p.heads * DVP, (uint64_t)p.ldv, BKV, DVP, 0);
   if (rc) return rc;
-  static bool attr = false;
-  if (!attr) {
+  static unsigned long long attr = 0;
+  if (first_use_on_device(attr)) {
     cudaFuncSetAttribute(attn_sa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-    attr = true;
   }
   dim3 grid((p.L + BQ - 1) / BQ, p.heads, p.nb);
   attn_sa_kernel<<<grid, THREADS, smem, s>>>(tmQK, tmV, p);

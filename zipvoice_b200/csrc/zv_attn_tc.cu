@@ -473,13 +473,12 @@ int attention_na_tc(const AttnParams& p, cudaStream_t s) {
     rc = make_tmap(&tmG, p.gate, 0, (uint64_t)p.nb * p.L, (uint64_t)p.dv, (uint64_t)p.ldg, BQ, 64, 128);
     if (rc) return rc;
   }
-  static bool attr = false;
+  static unsigned long long attr = 0;
   const int n_tiles = (p.L + BKV - 1) / BKV;
   const int smem = (int)sizeof(Smem) + 1024 + n_tiles * BKV + ((n_tiles + 15) & ~15);
   if (smem > 227 * 1024) return -1;  // sequence too long for the in-kernel mask copy: mma.sync kernel instead
-  if (!attr) {
+  if (first_use_on_device(attr)) {
     cudaFuncSetAttribute(attn_na_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    attr = true;
   }
   dim3 grid((p.L + BQ - 1) / BQ, p.nb, slices);
   attn_na_tc_kernel<<<grid, THREADS, smem, s>>>(tmV, tmQK, tmG, p, nvbox, n0, n1, ncols);

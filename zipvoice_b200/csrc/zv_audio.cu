@@ -673,10 +673,9 @@ static int fbank_launch(void* handle, const float* wav, const int64_t* lens, int
   AU_TRY(audio_tables(e, a));
   const int T = (N + HOP / 2) / HOP;
   const int fpc = 16;
-  static bool attr = false;
-  if (!attr) {
+  static unsigned long long attr = 0;
+  if (first_use_on_device(attr)) {
     cudaFuncSetAttribute(fbank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FftSmem));
-    attr = true;
   }
   dim3 grid((T + fpc - 1) / fpc, B);
   // algorithmic bytes: 4 B per input sample + 400 B per output frame
@@ -714,10 +713,9 @@ extern "C" int zv_vocos_decode(void* handle, const float* mel, const int64_t* le
   AU_TRY(vocoder_build(e, a));
   AU_TRY(vocoder_reserve(e, a, B, T));
   const int Tp = T + 6, M = B * Tp;
-  static bool attr = false;
-  if (!attr) {
+  static unsigned long long attr = 0;
+  if (first_use_on_device(attr)) {
     cudaFuncSetAttribute(vc_istft_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FftSmem));
-    attr = true;
   }
   AU_K(KC_VOCODER_ELEM, B * 12.0, s, (vc_lens_kernel<<<(B + 127) / 128, 128, 0, s>>>(lens, B, T, a.lens_dev)));
   const size_t tot = (size_t)(M + 6) * VC_MELP;

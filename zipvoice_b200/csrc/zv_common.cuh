@@ -11,6 +11,17 @@
 
 namespace zv {
 
+// Function attributes (the dynamic shared-memory opt-in) and occupancy answers are PER DEVICE: a launcher keeps one
+// bit per device ordinal and runs its set-up the first time it is called with that device current.
+inline bool first_use_on_device(unsigned long long& mask) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (mask & bit) return false;
+  mask |= bit;
+  return true;
+}
+
 typedef __nv_bfloat16 bf16;
 
 // ------------------------------------------------------------------ math
@@ -38,6 +49,17 @@ ZV_DEVINL uint32_t pack_bf16x2(float lo, float hi) {
 ZV_DEVINL uint32_t pack_f16x2(float lo, float hi) {
   __half2 v = __floats2half2_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
+}
+// fp32 pair -> fp16 pair, round to nearest, SATURATING at +-65504 instead of overflowing to +-inf (NaN stays NaN):
+// the attention q | k | p rows are stored in fp16 un-scaled, and an inf there would turn a whole softmax row into NaN.
+ZV_DEVINL uint32_t pack_f16x2_sat(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+ZV_DEVINL __half f2h_sat(float x) {
+  const uint32_t d = pack_f16x2_sat(x, 0.f);
+  return __ushort_as_half((unsigned short)(d & 0xffffu));
 }
 ZV_DEVINL float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 ZV_DEVINL float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }

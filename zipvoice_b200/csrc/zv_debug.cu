@@ -4,6 +4,7 @@
 #include <vector>
 
 #include "zv_common.cuh"
+#include "zv_debug.h"
 #include "zv_engine.h"
 
 using namespace zv;
@@ -28,6 +29,10 @@ static void cvt_pad(const float* in, int rows, int cols, int ld_in, __nv_bfloat1
   const size_t n = (size_t)rows * ld_out;
   cvt_pad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, rows, cols, ld_in, out, ld_out);
 }
+__global__ void cvt_back_f16_kernel(const __half* __restrict__ in, size_t n, float* __restrict__ out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = __half2float(in[i]);
+}
 static void cvt_back(const __nv_bfloat16* in, size_t n, float* out, cudaStream_t s) {
   cvt_back_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, n, out);
 }
@@ -37,6 +42,8 @@ extern "C" int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int
                              const float* resbias, const float* orig, const float* bypass_scale, const uint8_t* mask,
                              float* out_f32, float* out2_f32, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
+  const bool f16 = mode == 7;  // EPI_BIAS_BF16 storing IEEE fp16 (the attention q | k | p projection)
+  if (f16) mode = EPI_BIAS_BF16;
   const int block_n = gemm_pick_block_n(N, mode, gate_cols);
   const int N_pad = (N + block_n - 1) / block_n * block_n;
   const int ld = (K + 63) / 64 * 64;
@@ -59,12 +66,16 @@ extern "C" int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int
   ep.bias_ld = N, ep.out_bf16 = ob, ep.ld_bf16 = n_out, ep.out2_bf16 = ob2, ep.ld2_bf16 = n_out2;
   ep.out_f32 = of, ep.ld_f32 = N, ep.res = res, ep.resbias = resbias, ep.orig = orig, ep.bypass_scale = bypass_scale;
   ep.mask = mask;
+  ep.out_f16 = f16 ? 1 : 0;
   if (mode == EPI_F32) ep.out_bf16 = nullptr;
   int rc = gemm_launch(A, W, p, ep, impl, s);
   if (!rc) {
     if (mode == EPI_RESIDUAL || mode == EPI_F32) {
       cudaMemcpyAsync(out_f32, of, (size_t)M * N * 4, cudaMemcpyDeviceToDevice, s);
       if (mode == EPI_RESIDUAL && out2_f32) cvt_back(ob, (size_t)M * N, out2_f32, s);
+    } else if (f16) {
+      const size_t n = (size_t)M * n_out;
+      cvt_back_f16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(reinterpret_cast<const __half*>(ob), n, out_f32);
     } else {
       cvt_back(ob, (size_t)M * n_out, out_f32, s);
       if (n_out2) cvt_back(ob2, (size_t)M * n_out2, out2_f32, s);

@@ -183,14 +183,13 @@ template <int K, int TT, int FG>
 static int launch_dwconv(const bf16* in, const float* w, const float* bias, int nb, int L, int C, bf16* out, int ldo,
                          cudaStream_t s) {
   constexpr int smem = 2 * (TT + K - 1) * 128 * 4 + 128 + 64;
-  static bool attr = false;
+  static unsigned long long attr = 0;
   static int sms = 0;
-  if (!attr) {
+  if (first_use_on_device(attr)) {
     cudaFuncSetAttribute(dwconv_kernel<K, TT, FG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    attr = true;
   }
   CUtensorMap tm;
   int rc = make_tmap3d_16(&tm, in, (uint64_t)C, (uint64_t)L, (uint64_t)nb, (uint64_t)C, (uint64_t)L * C, 256,

@@ -489,14 +489,40 @@ static int run_dwconv(Engine& e, const __nv_bfloat16* in, const float* w, const 
 static int get_pos_table(Engine& e, Net& net, Layer& ly, int L, cudaStream_t s, float** out) {
   auto it = ly.pos_tab.find(L);
   if (it == ly.pos_tab.end()) {
+    if (ly.pos_tab.size() >= kMaxPosTables) {
+      // single-utterance serving sees a new T on almost every request: drop this layer's tables instead of growing
+      // without bound.  Kernels in flight and captured graphs may still read them.
+      cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+      cudaStreamIsCapturing(s, &cap);
+      if (cap != cudaStreamCaptureStatusNone) {
+        e.err = "position-table cache full during stream capture";
+        return 951;  // the capture fails and zv_sample runs the plain loop, which evicts
+      }
+      ZV_TRY((int)cudaDeviceSynchronize());
+      for (auto& kv : ly.pos_tab) cudaFree(kv.second);
+      ly.pos_tab.clear();
+      ++e.ws_fm.gen;  // captured graphs hold the freed addresses
+    }
     float* E = nullptr;
-    ZV_TRY(dev_alloc(e, e.weight_allocs, (void**)&E, (size_t)net.H * (2 * L - 1) * 4 * sizeof(float)));
+    const cudaError_t mrc = cudaMalloc((void**)&E, (size_t)net.H * (2 * L - 1) * 4 * sizeof(float));
+    if (mrc != cudaSuccess) {
+      e.err = std::string("cudaMalloc failed: ") + cudaGetErrorString(mrc);
+      return (int)mrc;
+    }
     ZV_K(KC_TIME_EMBED, (double)net.H * (2 * L - 1) * 16, s,
          pos_table(ly.w_pos, net.H, e.cfg.pos_head_dim, e.cfg.pos_dim, L, E, s));
     it = ly.pos_tab.emplace(L, E).first;
   }
   *out = it->second;
   return 0;
+}
+
+void free_pos_tables(Net& net) {
+  for (Stack& st : net.stacks)
+    for (Layer& ly : st.layers) {
+      for (auto& kv : ly.pos_tab) cudaFree(kv.second);
+      ly.pos_tab.clear();
+    }
 }
 
 // Zipformer2EncoderLayer.forward in eval mode (zipformer.py:489-642).  X: layer input / output (fp32),

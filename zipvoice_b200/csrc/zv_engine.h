@@ -117,7 +117,10 @@ struct Engine {
     cudaGraphExec_t exec = nullptr;  // null: key seen once (ran eagerly), capture on the next call
     long long launches = 0;          // kernels inside the graph (added to the launch counter per replay)
     bool unsupported = false;        // capture failed once: stay on the eager path
+    unsigned long long last_use = 0; // graph_tick of the last call with this key (least recently used is evicted)
   };
+  static constexpr size_t kMaxGraphs = 16;  // instantiated graphs kept per handle (~350 kernel nodes per NFE each)
+  unsigned long long graph_tick = 0;
   int graph_max_rows = 32768;
   std::vector<SampleGraph> graphs;
   unsigned long long graphs_ws_gen = 0;
@@ -127,6 +130,13 @@ struct Engine {
   size_t g_cap = 0;  // staging capacity in B * T elements
   float *gx = nullptr, *gtext = nullptr, *gspeech = nullptr;
   uint8_t* gmask = nullptr;
+  // Small host -> device uploads (time table, guidance values) go through a ring of PINNED slots so that the copy is
+  // truly asynchronous (a cudaMemcpyAsync from pageable memory stages synchronously).  A slot is reused only after
+  // the event recorded behind its last copy has completed.
+  static constexpr int kPinSlots = 8, kPinSlotFloats = 4096;
+  float* pin_host = nullptr;
+  cudaEvent_t pin_ev[kPinSlots] = {};
+  int pin_next = 0;
   // audio front-end / vocoder state lives in zv_audio.cu
   void* audio = nullptr;
 };
@@ -145,6 +155,11 @@ struct TimeArgs {
 int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t* mask_dev, const TimeArgs& ta,
                 float* out, cudaStream_t s);
 int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T);
+// Position tables E[H][2L-1][4] are cached per (layer, L), at most kMaxPosTables lengths per layer; when a layer is
+// full its tables are freed (after a device synchronise) and ws_fm.gen is bumped so that captured graphs, which hold
+// their addresses, are dropped.  free_pos_tables releases them all (zv_destroy).
+static constexpr size_t kMaxPosTables = 32;
+void free_pos_tables(Net& net);
 void audio_destroy(Engine& e);
 // Shared with the vocoder (zv_audio.cu): pack one Linear from host fp32 (rows optionally permuted for the
 // fused epilogue of `mode`), and launch it.  row_scale (optional, [N]) multiplies weight rows and bias.

@@ -56,7 +56,7 @@ ZV_DEVINL void epi_apply(const EpiParams& ep, int m, int b, int n0, const float 
       __half* oh = reinterpret_cast<__half*>(o);
 #pragma unroll
       for (int i = 0; i < 32; ++i)
-        if (i < nvalid) oh[i] = __float2half_rn(v[i]);
+        if (i < nvalid) oh[i] = f2h_sat(v[i]);
     } else if (nvalid == 32) {
 #pragma unroll
       for (int i = 0; i < 32; i += 8) {
@@ -237,8 +237,8 @@ ZV_DEVINL void stage_row_f16x32(uint8_t* stg, int r, const float (&v)[32]) {
   const int x = (r >> 1) & 3;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    uint4 p = make_uint4(pack_f16x2(v[8 * j], v[8 * j + 1]), pack_f16x2(v[8 * j + 2], v[8 * j + 3]),
-                         pack_f16x2(v[8 * j + 4], v[8 * j + 5]), pack_f16x2(v[8 * j + 6], v[8 * j + 7]));
+    uint4 p = make_uint4(pack_f16x2_sat(v[8 * j], v[8 * j + 1]), pack_f16x2_sat(v[8 * j + 2], v[8 * j + 3]),
+                         pack_f16x2_sat(v[8 * j + 4], v[8 * j + 5]), pack_f16x2_sat(v[8 * j + 6], v[8 * j + 7]));
     *reinterpret_cast<uint4*>(stg + r * 64 + ((j ^ x) << 4)) = p;
   }
 }
@@ -850,9 +850,9 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
                      cudaStream_t stream) {
   constexpr int NCG = ncg_for(MODE);
   constexpr int threads = 128 + 128 * NCG;
-  static bool attr_set = false;
+  static unsigned long long attr_set = 0;
   static int max_clusters = 0;
-  if (!attr_set) {
+  if (first_use_on_device(attr_set)) {
     cudaFuncSetAttribute(gemm_tc_kernel<MODE, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (PAIR) {
       cudaFuncSetAttribute(gemm_tc_kernel<MODE, PAIR>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0);
@@ -870,7 +870,6 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
       if (getenv("ZV_VERBOSE"))
         fprintf(stderr, "[zv] gemm mode %d: %d SMs, %d co-resident CTA pairs\n", MODE, g_num_sms, max_clusters);
     }
-    attr_set = true;
   }
   const EpiParams& ep = ep_in;
   GemmMaps maps = maps_in;
@@ -938,10 +937,9 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
   // one tile per CTA and at least two K steps: split the K loop over two issuing threads / accumulators
   const bool dual = !PAIR && tail_split >= 2 && sched.total_units <= max_units && k_blocks >= 2;
   if (dual) {
-    static bool attr_dual = false;
-    if (!attr_dual) {
+    static unsigned long long attr_dual = 0;
+    if (first_use_on_device(attr_dual)) {
       cudaFuncSetAttribute(gemm_tc_kernel<MODE, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-      attr_dual = true;
     }
   }
   static const bool verbose = getenv("ZV_VERBOSE") != nullptr;

@@ -125,6 +125,29 @@ class Engine:
                                              T, g, glen, _ptr(out), _stream(self.device)))
         return out
 
+    def forward_fm_decoder(self, t, xt, text_condition, speech_condition, padding_mask=None,
+                           guidance_scale=None) -> torch.Tensor:
+        """ZipVoice.forward_fm_decoder (zipvoice.py:135-185): t 0-dim or (N, 1, 1) with one time step per row;
+        guidance_scale None, 0-dim or (N, 1, 1) (embedded by the distilled model).  No CFG logic."""
+        x, tc, sc = self._prep(xt), self._prep(text_condition), self._prep(speech_condition)
+        N, T, F = x.shape
+        assert F == self.x_dim and sc.shape == x.shape and tuple(tc.shape) == (N, T, self.feat_dim), \
+            f"x/speech (N,T,{self.x_dim}) and text (N,T,{self.feat_dim}) expected"
+        tv = torch.as_tensor(t).detach().float().reshape(-1).cpu().tolist()
+        assert len(tv) in (1, N), "t must be 0-dim or (N, 1, 1)"                     # zipvoice.py:165-169
+        if guidance_scale is None:
+            gv = []
+        else:
+            gv = torch.as_tensor(guidance_scale).detach().float().reshape(-1).cpu().tolist()
+            assert len(gv) in (1, N), "guidance_scale must be 0-dim or (N, 1, 1)"    # zipvoice.py:171-178
+        m = None if padding_mask is None else self._prep(padding_mask, torch.uint8)
+        out = torch.empty_like(x)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.zv_forward_fm_decoder(
+                self._h, (C.c_float * len(tv))(*tv), len(tv), _ptr(x), _ptr(tc), _ptr(sc), _ptr(m), N, T,
+                (C.c_float * max(1, len(gv)))(*gv) if gv else None, len(gv), _ptr(out), _stream(self.device)))
+        return out
+
     def sample(self, x, text_condition, speech_condition, padding_mask, num_step=10, guidance_scale=0.0,
                t_start=0.0, t_end=1.0, t_shift=1.0, distill: Optional[bool] = None) -> torch.Tensor:
         """EulerSolver.sample (solver.py:182-240); the input x is not modified."""
@@ -171,6 +194,12 @@ class Engine:
         w = self._prep(wav)
         B, N = w.shape
         ln = None if lens is None else self._prep(lens, torch.int64)
+        # torch.stft's reflect padding (feature.py:47-60 via torchaudio) needs more samples than the pad and raises
+        # otherwise; the kernel would clamp silently, so short rows are rejected here (one host read of lens)
+        pad = 512 if kind == "vocos" else 384
+        shortest = N if ln is None else (int(ln.min()) if ln.numel() else N)
+        if shortest <= pad:
+            raise ValueError(f"fbank: every row needs more than {pad} samples (reflect padding), got {shortest}")
         T = (N + 128) // 256
         out = torch.empty(B, T, 100, device=self.device, dtype=torch.float32)
         with torch.cuda.device(self.device):

@@ -23,10 +23,13 @@ import torch
 from . import parallel
 
 
-def _rms_normalise(wav: torch.Tensor, target_rms: float):
-    """infer_zipvoice.py:340-342: quiet prompts are raised to target_rms; returns (wav, prompt_rms)."""
-    rms = torch.sqrt(torch.mean(torch.square(wav)))
-    if rms < target_rms:
+def _rms_normalise(wav: torch.Tensor, target_rms: float, rms: Optional[torch.Tensor] = None):
+    """infer_zipvoice.py:340-342: quiet prompts are raised to target_rms; returns (wav, prompt_rms).  ``rms`` may be
+    handed in when it was measured on another view of the prompt (the un-mixed channels, generate_list).  A silent
+    prompt (rms == 0) is left as it is: the reference divides by zero there and feeds NaNs to the model."""
+    if rms is None:
+        rms = torch.sqrt(torch.mean(torch.square(wav)))
+    if 0 < rms < target_rms:
         wav = wav * target_rms / rms
     return wav, rms
 
@@ -106,10 +109,17 @@ def generate_sentence_stereo(prompt_tokens: List[int], prompt_wav: torch.Tensor,
 def generate_batch(prompt_tokens: Sequence[List[int]], prompt_wavs: Sequence[torch.Tensor],
                    tokens: Sequence[List[int]], model, vocoder, feature_extractor, num_step: int = 16,
                    guidance_scale: float = 1.0, speed: float = 1.0, t_shift: float = 0.5, target_rms: float = 0.1,
-                   feat_scale: float = 0.1, feat_bias: float = 0.0, distributed: bool = False) -> Optional[list]:
+                   feat_scale: float = 0.1, feat_bias: float = 0.0, distributed: bool = False,
+                   prompt_rms: Optional[Sequence] = None, x0: Optional[torch.Tensor] = None) -> Optional[list]:
     """All utterances of this rank as one padded batch.  With ``distributed`` the list is first sharded by
     (prompt length + text length) over the torchrun ranks and the waveforms are gathered to rank 0, which
-    returns them in the original order (other ranks return None)."""
+    returns them in the original order (other ranks return None).  ``prompt_rms`` (one value per utterance)
+    replaces the RMS of the mono prompt, for callers that measured it on the un-mixed channels as the reference does;
+    ``x0`` (B, T, F) injects the start noise (single-rank only; rows in the order of the arguments).
+
+    Output is tolerance-level, not bit-level, equal to per-utterance ``generate_sentence`` calls: Zipformer's
+    down- and up-sampling mix the last valid frames of an utterance with the padded frames behind it, and the
+    reference draws different noise per call."""
     dev = model.device
     n = len(tokens)
     rank, world = 0, 1
@@ -118,11 +128,16 @@ def generate_batch(prompt_tokens: Sequence[List[int]], prompt_wavs: Sequence[tor
     cost = [int(prompt_wavs[i].numel()) // 256 * (1 + len(tokens[i]) // max(1, len(prompt_tokens[i]))) for i in range(n)]
     shards = [parallel.shard_indices(cost, world, r) for r in range(world)]
     mine = shards[rank]
+    if not mine:  # more ranks than utterances: this rank only takes part in the gather
+        parts = parallel.gather_ragged(torch.zeros(0, 0, device=dev), torch.zeros(0, dtype=torch.int64, device=dev))
+        return parallel.scatter_back(parts, shards, n) if (world == 1 or rank == 0) else None
+    assert x0 is None or world == 1, "x0 is given in argument order: single-rank calls only"
     wav_lens = torch.tensor([int(prompt_wavs[i].numel()) for i in mine], dtype=torch.int64)
     batch = torch.zeros(len(mine), int(wav_lens.max()), device=dev)
     rms = []
     for row, i in enumerate(mine):
-        w, r = _rms_normalise(prompt_wavs[i].to(dev).reshape(-1).float(), target_rms)
+        given = None if prompt_rms is None else torch.as_tensor(prompt_rms[i], dtype=torch.float32, device=dev)
+        w, r = _rms_normalise(prompt_wavs[i].to(dev).reshape(-1).float(), target_rms, given)
         batch[row, : w.numel()] = w
         rms.append(r)
     feats = feature_extractor.extract_batch(batch, wav_lens.to(dev))           # (B, Tp, 100), zeros past each prompt
@@ -132,10 +147,13 @@ def generate_batch(prompt_tokens: Sequence[List[int]], prompt_wavs: Sequence[tor
     pred, pred_lens, _, _ = model.sample(tokens=[tokens[i] for i in mine], prompt_tokens=[prompt_tokens[i] for i in mine],
                                          prompt_features=feats, prompt_features_lens=feats_lens.to(dev), speed=speed,
                                          t_shift=t_shift, duration="predict", num_step=num_step,
-                                         guidance_scale=guidance_scale)
+                                         guidance_scale=guidance_scale,
+                                         **({"x0": x0[mine]} if x0 is not None else {}))  # batch rows are in shard (length-sorted) order
     mel = pred.permute(0, 2, 1) / feat_scale - feat_bias
     wav = vocoder.decode(mel, pred_lens).clamp(-1, 1)
-    scale = torch.stack([torch.clamp(r / target_rms, max=1.0) for r in rms]).to(dev)
+    # infer_zipvoice.py:399-400: only prompts that were raised are lowered again (a silent prompt was not raised)
+    scale = torch.stack([torch.where(r > 0, torch.clamp(r / target_rms, max=1.0), torch.ones_like(r))
+                         for r in rms]).to(dev)
     wav = wav * scale[:, None]
     wlens = (pred_lens - 1).clamp(min=0) * 256
     if world == 1:
@@ -194,9 +212,11 @@ def generate_list(res_dir: str, test_list: str, model, vocoder, tokenizer, featu
     """infer_zipvoice.py:406-466.  ``test_list`` lines: wav_name <tab> prompt_text <tab> prompt_wav <tab> text;
     ``tokenizer`` needs ``texts_to_token_ids`` like the reference's tokenizers.  Writes ``res_dir/<wav_name>.wav``.
 
-    Differences from the reference loop, none of them numerical: utterances run as padded batches of similar
-    length (``max_batch_frames`` bounds batch x frames), prompts of one sampling rate are resampled together on
-    the GPU, multi-channel prompts are down-mixed before the RMS normalisation, and files are written behind the
+    Differences from the reference loop: utterances run as padded batches of similar length (``max_batch_frames``
+    bounds batch x frames) with their own noise, so the output equals the per-utterance loop to tolerance, not bit
+    for bit (see ``generate_batch``); prompts of one sampling rate are resampled together on the GPU (all channels,
+    one row each); the prompt RMS is measured on the resampled un-mixed channels exactly as :340-342 does, and the
+    channel mean that VocosFbank applies (feature.py:84-86) is taken right after it; files are written behind the
     compute.  With ``distributed`` the list is split over the torchrun ranks by estimated cost and every rank
     writes its own files (no collective on the data path).  Returns the totals the reference logs."""
     from .audio import ResampleB200
@@ -215,26 +235,31 @@ def generate_list(res_dir: str, test_list: str, model, vocoder, tokenizer, featu
     # rank split on a cost known before any audio is read: characters to synthesise
     text_cost = [len(t) + len(p) for t, p in zip(tokens, prompt_tokens)]
     mine = parallel.shard_indices(text_cost, world, rank)
-    # ---- prompts: load, down-mix, resample per source rate as one padded GPU batch
+    # ---- prompts: load, resample per source rate as one padded GPU batch (one row per channel), RMS, down-mix
     loaded = {i: load_wav(items[i][2]) for i in mine}
     prompts: Dict[int, torch.Tensor] = {}
+    prompt_rms: Dict[int, torch.Tensor] = {}
     by_rate: Dict[int, List[int]] = {}
     for i, (w, sr) in loaded.items():
         by_rate.setdefault(int(sr), []).append(i)
     for sr, idx in by_rate.items():
-        mono = [loaded[i][0].float().mean(dim=0) if loaded[i][0].dim() == 2 else loaded[i][0].float() for i in idx]
-        if sr == sampling_rate:
-            for i, w in zip(idx, mono):
-                prompts[i] = w.to(dev)
-            continue
-        lens = torch.tensor([w.numel() for w in mono], dtype=torch.int64)
-        batch = torch.zeros(len(idx), int(lens.max()))
-        for r, w in enumerate(mono):
-            batch[r, : w.numel()] = w
-        res = ResampleB200(sr, sampling_rate, engine=feature_extractor.engine)(batch.to(dev), lens.to(dev))
-        out_lens = (lens * sampling_rate + sr - 1) // sr
-        for r, i in enumerate(idx):
-            prompts[i] = res[r, : int(out_lens[r])]
+        chans = {i: loaded[i][0].float().reshape(-1, loaded[i][0].shape[-1]) for i in idx}   # (C_i, N_i)
+        if sr != sampling_rate:
+            rows = [(i, c) for i in idx for c in range(chans[i].shape[0])]
+            lens = torch.tensor([chans[i].shape[1] for i, _ in rows], dtype=torch.int64)
+            batch = torch.zeros(len(rows), int(lens.max()))
+            for r, (i, c) in enumerate(rows):
+                batch[r, : chans[i].shape[1]] = chans[i][c]
+            res = ResampleB200(sr, sampling_rate, engine=feature_extractor.engine)(batch.to(dev), lens.to(dev))
+            out_lens = (lens * sampling_rate + sr - 1) // sr
+            got: Dict[int, List[torch.Tensor]] = {}
+            for r, (i, c) in enumerate(rows):
+                got.setdefault(i, []).append(res[r, : int(out_lens[r])])
+            chans = {i: torch.stack(v) for i, v in got.items()}
+        for i in idx:
+            w = chans[i].to(dev)
+            prompt_rms[i] = torch.sqrt(torch.mean(torch.square(w)))     # :340, on every channel
+            prompts[i] = w.mean(dim=0)                                  # feature.py:84-86 (num_channels = 1)
     # ---- buckets of similar total length (prompt frames scaled by the text / prompt-text ratio)
     frames = {i: max(1, prompts[i].numel() // 256) for i in mine}
     cost = [int(frames[i] * (1 + len(tokens[i]) / max(1, len(prompt_tokens[i])) / max(speed, 1e-3))) for i in mine]
@@ -248,7 +273,7 @@ def generate_list(res_dir: str, test_list: str, model, vocoder, tokenizer, featu
             wavs = generate_batch([prompt_tokens[i] for i in b], [prompts[i] for i in b], [tokens[i] for i in b],
                                   model, vocoder, feature_extractor, num_step=num_step,
                                   guidance_scale=guidance_scale, speed=speed, t_shift=t_shift, target_rms=target_rms,
-                                  feat_scale=feat_scale, feat_bias=feat_bias)
+                                  feat_scale=feat_scale, feat_bias=feat_bias, prompt_rms=[prompt_rms[i] for i in b])
             host = [w.cpu().numpy() for w in wavs]          # device -> host read of the bucket's waveforms
             total_t += time.perf_counter() - t0
             for i, w in zip(b, host):

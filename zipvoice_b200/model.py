@@ -45,13 +45,8 @@ class ZipVoiceB200:
     # ---- zipvoice.py:135-185
     def forward_fm_decoder(self, t, xt, text_condition, speech_condition, padding_mask=None, guidance_scale=None):
         t = torch.as_tensor(t)
-        assert t.dim() in (0, 3)
-        assert t.numel() == 1 or bool((t == t.flatten()[0]).all()), "per-sample time steps are not accelerated"
-        if guidance_scale is None:
-            return self.engine.velocity(float(t.flatten()[0]), xt, text_condition, speech_condition, padding_mask, 0.0,
-                                        distill=False)
-        return self.engine.velocity(float(t.flatten()[0]), xt, text_condition, speech_condition, padding_mask,
-                                    guidance_scale, distill=True)
+        assert t.dim() in (0, 3)  # zipvoice.py:165: a scalar, or (N, 1, 1) with one time step per row
+        return self.engine.forward_fm_decoder(t, xt, text_condition, speech_condition, padding_mask, guidance_scale)
 
     # ---- zipvoice.py:187-212 (+ zipvoice_dialog.py:127-159 inside the library)
     def forward_text_embed(self, tokens: List[List[int]]):
