@@ -11,6 +11,7 @@
 //                   reference maximum (key_tile, SPEC); tile 0, the last tile and repeats are exact.
 // The roles synchronise only through mbarriers -- no CTA-wide barrier in the key loop.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include <type_traits>
 
@@ -356,6 +357,319 @@ attn_sa_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__
   if (warp == MMA_WARP) tmem_dealloc(tmem_base, S_COLS);
 }
 
+// =====================================================================================================================
+// attn_sa2_kernel: the same attention with the relative-position term ON THE TENSOR CORES.
+//
+//   T[m][n] = p_m . W[127 - m + n]          (m: query row of the 128-row tile, n: key of the 64-key tile, W: the
+//                                            window of the projected position table that the tile pair can see)
+// is a Toeplitz form, not a product of a row factor and a column factor.  Write m = 8 a + s and u = n + 120 - 8 a:
+//   T[m][n] = p_m . W[u + s'],  s' = 7 - s   =   sum_{s', c} A[m][4 s' + c] * B[u][4 s' + c]
+//   A[m][4 s' + c] = p_m[c] if s' == 7 - (m % 8) else 0          (128 x 32 fp16, built once per CTA)
+//   B[u][4 s' + c] = W[u + s'][c]  =  Wflat[4 u + k],  k = 4 s' + c
+// so row u of B is nothing but 32 consecutive halves of the flat fp16 window starting at half 4 u: an operand with
+// OVERLAPPING rows, 8 bytes apart.  The no-swizzle K-major UMMA layout wants the 8 rows of a core matrix 16 bytes
+// apart, so the even rows (u = 2 v) are read from the window as it lies (row v at byte 16 v: core matrix = 128
+// contiguous bytes, SBO = 128, LBO = 16) and the odd rows from a second copy shifted by one entry; nothing is
+// materialised.  D_even / D_odd [128 x 96] land in TMEM beside S = Q K^T.  What is left of the skew, 8 a, is the
+// same for the 8 rows a warp reads with one TMEM lane group, i.e. a per-warp COLUMN BASE of tcgen05.ld:
+// shape 16x128b hands thread (g, qd) the columns base + 4 i + qd of rows g and g + 8 -- with the even / odd split
+// exactly the keys 8 nt + 2 qd (+ 1) of the mma.sync fragment that S arrives in.  Per score: one FADD instead of four
+// FMAs and a shared-memory table load (128 of ~300 instructions per thread and tile before).
+// The table is rounded to fp16 for this (q, k, p already are); accumulation is fp32.
+// TMEM: S 64 + D_even 96 + D_odd 96 = 256 columns, two CTAs per SM; one accumulator set, handed back to the MMA warp as
+// soon as the 8 compute warps hold their scores in registers (the speculative / exact decision is taken on the score
+// maxima before any exponential, so a tile never has to be read twice).
+namespace sa2 {
+
+// tile sizes, warp roles and SPEC_LOG2 are those of namespace sa above (two CTAs of 8 compute warps per SM; a layout
+// with one CTA of 16 compute warps, two accumulator sets and two MMA-issuing warps measured 0.62 ms against 0.44 ms)
+static constexpr int EW16 = 200;   // fp16 window entries (8 bytes) per copy: rows u < 96 x 2 read up to entry 197
+static constexpr int D_N = 96;     // columns of D_even / D_odd (u < 184 are used)
+static constexpr int COL_S = 0, COL_DE = 64, COL_DO = 160, TM_COLS = 256;
+
+struct alignas(1024) Smem {
+  __half q[BQ][DQ];            // 8 KB, SWIZZLE_64B (TMA)
+  __half ap[BQ][DQ];           // 8 KB, SWIZZLE_64B: one-hot position operand A
+  __half k[STAGES][BKV][DQ];   // 4 KB each, SWIZZLE_64B (TMA)
+  bf16 v[STAGES][BKV][DVP];    // 2 KB each, SWIZZLE_32B (TMA)
+  uint2 we[STAGES][EW16];      // position window, entries x0 .. x0 + 199
+  uint2 wo[STAGES][EW16];      // ... shifted by one entry
+  uint64_t full[STAGES], empty[STAGES], qbar, sfull, sfree, pad_;
+  uint32_t tmem_base, pad2_[3];
+  // followed by: uint8_t mask[n_tiles * BKV], uint8_t flag[n_tiles]
+};
+
+// K-major operand without swizzle: core matrices of 8 rows x 16 bytes (128 contiguous bytes), `sbo` bytes between
+// core matrices along M / N, `lbo` bytes between the two 16-byte K chunks of one K = 16 instruction
+ZV_DEVINL uint64_t make_sdesc_kmajor_plain(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(lbo >> 4) << 16;
+  d |= static_cast<uint64_t>(sbo >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  return d;
+}
+// 16 TMEM lanes x (4 N) fp32 columns: r[2 i] = lane g, column 4 i + qd; r[2 i + 1] = lane g + 8, same column
+// (cute SM100_TMEM_LOAD_16dp128b8x / 1x); NO wait inside
+ZV_DEVINL void tmem_ld_16x128b_x8(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.16x128b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+ZV_DEVINL void tmem_ld_16x128b_x1(uint32_t taddr, uint32_t (&r)[2]) {
+  asm volatile("tcgen05.ld.sync.aligned.16x128b.x1.b32 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(taddr) : "memory");
+}
+ZV_DEVINL float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+// 2^x on the FMA / ALU pipes for x <= 64 (x below -126, -inf included, gives 2^-126): Cody-Waite split at the nearest
+// integer (magic-number rounding), a cubic for 2^f on [-0.5, 0.5] (max relative error 7.5e-5, P is rounded to bf16
+// at 2e-3 afterwards) and the integer part added to the exponent field.  MUFU.EX2 runs at 16 results / clk / SM for
+// fp32, f16x2 and bf16x2 alike (tools/micro/mufu_f16_rate.cu).  Measurement aid (ZV_SA_SOFT, see the launcher): the
+// default kernel computes every exponential on MUFU.
+ZV_DEVINL float ex2_soft(float x) {
+  x = fmaxf(x, -126.0f);
+  const float xr = x + 12582912.0f;          // 1.5 * 2^23: the low mantissa bits now hold round(x)
+  const float f = x - (xr - 12582912.0f);
+  float pl = fmaf(0.055171654f, f, 0.24261113f);
+  pl = fmaf(pl, f, 0.69326097f);
+  pl = fmaf(pl, f, 0.99992806f);
+  return __int_as_float(__float_as_int(pl) + (__float_as_int(xr) << 23));
+}
+// element e (0, 1: row g; 2, 3: row g + 8) of every 8-key block goes to the FMA pipe when e < SOFT
+template <int SOFT, int E>
+ZV_DEVINL float ex2_sel(float x) {
+  return E < SOFT ? ex2_soft(x) : ex2_approx(x);
+}
+
+}  // namespace sa2
+
+template <int SOFT>
+__global__ void __launch_bounds__(sa::THREADS, 2)
+attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__ CUtensorMap tmV, AttnParams p) {
+  using namespace sa2;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  sa2::Smem& sm = *reinterpret_cast<sa2::Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.z, head = blockIdx.y, i0 = blockIdx.x * BQ;
+  const int L = p.L, H = p.H;
+  const int n_tiles = (L + BKV - 1) / BKV;
+  uint8_t* smask = reinterpret_cast<uint8_t*>(&sm) + sizeof(sa2::Smem);
+  uint8_t* sflag = smask + n_tiles * BKV;
+  const uint8_t* mask = p.mask ? p.mask + (size_t)b * L : nullptr;
+  const __half* qkp = reinterpret_cast<const __half*>(p.qkp) + (size_t)b * L * p.ldq;
+
+  if (tid == 0) {
+    for (int i = 0; i < STAGES; ++i) mbar_init(&sm.full[i], 1), mbar_init(&sm.empty[i], COMPUTE_THREADS / 32);
+    mbar_init(&sm.qbar, 1);
+    mbar_init(&sm.sfull, 1), mbar_init(&sm.sfree, COMPUTE_THREADS / 32);
+    fence_barrier_init();
+  }
+  if (warp == MMA_WARP) tmem_alloc(&sm.tmem_base, TM_COLS);
+  if (tid < BQ) {
+    // row m of A: zeros except the 4 halves of p_m at K position 4 (7 - m % 8); SWIZZLE_64B rows of 64 bytes
+    const int m = tid;
+    uint8_t* row = reinterpret_cast<uint8_t*>(&sm.ap[m][0]);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(row + c * 16) = make_uint4(0u, 0u, 0u, 0u);
+    const uint2 pm = *reinterpret_cast<const uint2*>(qkp + (size_t)min(i0 + m, L - 1) * p.ldq + 2 * H * DQ + head * 4);
+    const int sp = 7 - (m & 7);
+    *reinterpret_cast<uint2*>(row + (((sp >> 1) ^ ((m >> 1) & 3)) << 4) + (sp & 1) * 8) = pm;
+  }
+  for (int j = tid; j < n_tiles * BKV; j += THREADS) smask[j] = (j < L) ? (mask ? mask[j] : 0) : 2;
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  for (int t = tid; t < n_tiles; t += THREADS) {
+    const uint4* mp = reinterpret_cast<const uint4*>(smask + t * BKV);
+    const uint4 a = mp[0], b4 = mp[1], c = mp[2], d = mp[3];
+    sflag[t] =
+        ((a.x | a.y | a.z | a.w | b4.x | b4.y | b4.z | b4.w | c.x | c.y | c.z | c.w | d.x | d.y | d.z | d.w) != 0);
+  }
+  __syncthreads();
+
+  const uint32_t tmem_base = sm.tmem_base;
+  if (warp == MMA_WARP) {
+    if (lane == 0) {
+      const uint32_t idesc_s = sa::make_idesc_f16(BQ, BKV), idesc_d = sa::make_idesc_f16(BQ, D_N);
+      mbar_wait(&sm.qbar, 0);
+      const uint64_t dq = sa::make_sdesc_sw64(smem_u32(&sm.q[0][0]));
+      const uint64_t dap = sa::make_sdesc_sw64(smem_u32(&sm.ap[0][0]));
+      for (int kt = 0; kt < n_tiles; ++kt) {
+        const int st = kt % STAGES;
+        mbar_wait(&sm.full[st], (kt / STAGES) & 1);
+        if (kt >= 1) mbar_wait(&sm.sfree, (kt - 1) & 1);
+        tc_fence_after();
+        const uint64_t dk = sa::make_sdesc_sw64(smem_u32(&sm.k[st][0][0]));
+        const uint64_t dwe = make_sdesc_kmajor_plain(smem_u32(&sm.we[st][0]), 16, 128);
+        const uint64_t dwo = make_sdesc_kmajor_plain(smem_u32(&sm.wo[st][0]), 16, 128);
+#pragma unroll
+        for (int k = 0; k < DQ / 16; ++k) sa::umma_f16(tmem_base + COL_S, dq + 2 * k, dk + 2 * k, idesc_s, k);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) sa::umma_f16(tmem_base + COL_DE, dap + 2 * k, dwe + 2 * k, idesc_d, k);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) sa::umma_f16(tmem_base + COL_DO, dap + 2 * k, dwo + 2 * k, idesc_d, k);
+        umma_commit(&sm.sfull);
+      }
+    }
+    __syncwarp();
+  } else if (warp == PRODUCER_WARP) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmQK);
+      tma_prefetch_desc(&tmV);
+      mbar_arrive_expect_tx(&sm.qbar, BQ * DQ * 2);
+      tma_load_2d(&sm.q[0][0], &tmQK, &sm.qbar, head * DQ, b * L + i0);
+      tma_load_2d(&sm.q[64][0], &tmQK, &sm.qbar, head * DQ, b * L + i0 + 64);
+      const uint2* Ea = reinterpret_cast<const uint2*>(p.E16) + (size_t)head * p.e16_stride;
+      const uint2* Eb = Ea + (size_t)H * p.e16_stride;
+      for (int kt = 0; kt < n_tiles; ++kt) {
+        const int s = kt % STAGES;
+        if (kt >= STAGES) mbar_wait_backoff(&sm.empty[s], ((kt / STAGES) - 1) & 1);
+        const int j0 = kt * BKV;
+        const int x0 = (j0 - i0 - (BQ - 1)) + (L - 1) + POS16_PADL;  // padded-table entry of window entry 0 (>= 1)
+        const uint2* src_e = (x0 & 1) ? Eb + (x0 - 1) : Ea + x0;       // both sources start at an even entry:
+        const uint2* src_o = (x0 & 1) ? Ea + (x0 + 1) : Eb + x0;       // 16-byte aligned
+        mbar_arrive_expect_tx(&sm.full[s], BKV * DQ * 2 + BKV * DVP * 2 + 2 * EW16 * 8);
+        tma_load_2d(&sm.k[s][0][0], &tmQK, &sm.full[s], H * DQ + head * DQ, b * L + j0);
+        tma_load_2d(&sm.v[s][0][0], &tmV, &sm.full[s], head * DVP, b * L + j0);
+        sa::bulk_load_1d(&sm.we[s][0], src_e, EW16 * 8, &sm.full[s]);
+        sa::bulk_load_1d(&sm.wo[s][0], src_o, EW16 * 8, &sm.full[s]);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---------------- compute warps: 16 query rows each (TMEM lanes row0 + g and row0 + 8 + g)
+    const int g = lane >> 2, qd = lane & 3;
+    const int row0 = 32 * (warp & 3) + 16 * (warp >> 2);
+    const int rl0 = row0 + g, rl1 = rl0 + 8;
+    float o[2][4];
+#pragma unroll
+    for (int n = 0; n < 2; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY;
+    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(row0) << 16);
+    // rows g + 8 (a = row0 / 8 + 1) sit at v = 56 - row0 / 2 + 4 nt + qd, rows g four columns further
+    const uint32_t dcol = 56 - (row0 >> 1);
+    for (int kt = 0; kt < n_tiles; ++kt) {
+      const int st = kt % STAGES;
+      const bool mk = sflag[kt] != 0;
+      // ---- scores: S + D_even / D_odd from TMEM, then the accumulators go back to the MMA warp
+      float s[8][4];
+      mbar_wait(&sm.sfull, kt & 1);
+      tc_fence_after();
+      {
+        uint32_t r[32];
+        asm volatile(
+            "tcgen05.ld.sync.aligned.16x256b.x8.b32 "
+            "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+            "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+              "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+              "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+              "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+            : "r"(lane_addr + COL_S)
+            : "memory");
+        uint32_t te[16], te1[2];
+        tmem_ld_16x128b_x8(lane_addr + COL_DE + dcol, te);
+        tmem_ld_16x128b_x1(lane_addr + COL_DE + dcol + 32, te1);
+        tmem_ld_wait();
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          s[nt][0] = __uint_as_float(r[4 * nt]) + __uint_as_float(nt < 7 ? te[2 * (nt + 1)] : te1[0]);
+          s[nt][2] = __uint_as_float(r[4 * nt + 2]) + __uint_as_float(te[2 * nt + 1]);
+          s[nt][1] = __uint_as_float(r[4 * nt + 1]);
+          s[nt][3] = __uint_as_float(r[4 * nt + 3]);
+        }
+        uint32_t to[16], to1[2];
+        tmem_ld_16x128b_x8(lane_addr + COL_DO + dcol, to);
+        tmem_ld_16x128b_x1(lane_addr + COL_DO + dcol + 32, to1);
+        tmem_ld_wait();
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          s[nt][1] += __uint_as_float(nt < 7 ? to[2 * (nt + 1)] : to1[0]);
+          s[nt][3] += __uint_as_float(to[2 * nt + 1]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.sfree);
+      // ---- key mask (padded keys -> -1000 log2 e, keys beyond the sequence -> -inf) and the row maxima
+      if (mk) {
+        const uint8_t* mrow = smask + kt * BKV;
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          const uint8_t k0 = mrow[nt * 8 + 2 * qd], k1 = mrow[nt * 8 + 2 * qd + 1];
+          if (k0) s[nt][0] = s[nt][2] = (k0 == 1 ? ATTN_MASKED : -INFINITY);
+          if (k1) s[nt][1] = s[nt][3] = (k1 == 1 ? ATTN_MASKED : -INFINITY);
+        }
+      }
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) mx0 = fmax3(mx0, s[nt][0], s[nt][1]), mx1 = fmax3(mx1, s[nt][2], s[nt][3]);
+      // Softmax is shift invariant and P is bf16 with fp32 sums: while no score exceeds the running reference by more
+      // than 2^SPEC_LOG2 the reference stays as it is (no maximum reduction, no rescaling of O); otherwise -- always
+      // for tile 0, whose reference is -inf -- the classic online-softmax step.
+      if (!__all_sync(0xffffffffu, (mx0 <= m0 + SPEC_LOG2) && (mx1 <= m1 + SPEC_LOG2))) {
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+        const float sc0 = ex2_approx(m0 - mn0), sc1 = ex2_approx(m1 - mn1);
+#pragma unroll
+        for (int n = 0; n < 2; ++n) o[n][0] *= sc0, o[n][1] *= sc0, o[n][2] *= sc1, o[n][3] *= sc1;
+        m0 = mn0, m1 = mn1;
+      }
+      // ---- P = exp2(S - m) (SOFT of every 4 on the FMA pipe, the rest on MUFU), O += P V  (V tile of this stage;
+      //      its ones column carries the row sums)
+      mbar_wait(&sm.full[st], (kt / STAGES) & 1);  // complete long ago (the MMAs waited for it); orders the V reads
+      const uint32_t vbase = smem_u32(&sm.v[st][0][0]);
+#pragma unroll
+      for (int kk = 0; kk < BKV / 16; ++kk) {
+        uint32_t pa[4];
+        pa[0] = pack_bf16x2(ex2_sel<SOFT, 0>(s[2 * kk][0] - m0), ex2_sel<SOFT, 1>(s[2 * kk][1] - m0));
+        pa[1] = pack_bf16x2(ex2_sel<SOFT, 2>(s[2 * kk][2] - m1), ex2_sel<SOFT, 3>(s[2 * kk][3] - m1));
+        pa[2] = pack_bf16x2(ex2_sel<SOFT, 0>(s[2 * kk + 1][0] - m0), ex2_sel<SOFT, 1>(s[2 * kk + 1][1] - m0));
+        pa[3] = pack_bf16x2(ex2_sel<SOFT, 2>(s[2 * kk + 1][2] - m1), ex2_sel<SOFT, 3>(s[2 * kk + 1][3] - m1));
+        uint32_t vb[4];
+        // V rows are 32 bytes apart: SWIZZLE_32B (16-byte chunk ^= bit 2 of the row) keeps the 8 rows of an
+        // ldmatrix 8 x 8 tile in 8 different bank groups
+        const int vrow = kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+        sa::ldsm_x4_t(vb, vbase + vrow * (DVP * 2) + ((((lane >> 4) ^ (vrow >> 2)) & 1) << 4));
+        sa::mma_bf16(o[0], pa, vb[0], vb[1]);
+        sa::mma_bf16(o[1], pa, vb[2], vb[3]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.empty[st]);
+    }
+    // ---- normalise, store: column dv = 12 of O (n-tile 1, columns 4..5 -> the lane with qd == 2) is the row sum
+    const float l0 = __shfl_sync(0xffffffffu, o[1][0], (lane & ~3) | 2);
+    const float l1 = __shfl_sync(0xffffffffu, o[1][2], (lane & ~3) | 2);
+    const float inv0 = 1.f / l0, inv1 = 1.f / l1;
+    const int ia = i0 + rl0, ib = i0 + rl1;
+    const int vcol0 = head * p.dv;
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+      const int col = n * 8 + 2 * qd;
+      if (col >= p.dv) continue;
+      if (ia < L)
+        *reinterpret_cast<uint32_t*>(p.out + ((size_t)b * L + ia) * p.ldo + vcol0 + col) =
+            pack_bf16x2(o[n][0] * inv0, o[n][1] * inv0);
+      if (ib < L)
+        *reinterpret_cast<uint32_t*>(p.out + ((size_t)b * L + ib) * p.ldo + vcol0 + col) =
+            pack_bf16x2(o[n][2] * inv1, o[n][3] * inv1);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == MMA_WARP) tmem_dealloc(tmem_base, sa2::TM_COLS);
+}
+
 // Host launcher; returns -1 if the shape is not supported (caller falls back to attn_kernel).
 int attention_sa_tma(const AttnParams& p, cudaStream_t s) {
   // V must be in the padded layout (16 columns per head: 12 values, a column of ones, zeros): the TMA box start
@@ -370,11 +684,28 @@ int attention_sa_tma(const AttnParams& p, cudaStream_t s) {
   if (rc) return rc;
   rc = make_tmap(&tmV, p.V, 0, (uint64_t)p.nb * p.L, (uint64_t)p.heads * DVP, (uint64_t)p.ldv, BKV, DVP, 0);
   if (rc) return rc;
+  CUtensorMap tmV32;  // the same box with SWIZZLE_32B (attn_sa2_kernel)
+  rc = make_tmap(&tmV32, p.V, 0, (uint64_t)p.nb * p.L, (uint64_t)p.heads * DVP, (uint64_t)p.ldv, BKV, DVP, 32);
+  if (rc) return rc;
   static unsigned long long attr = 0;
   if (first_use_on_device(attr)) {
     cudaFuncSetAttribute(attn_sa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaFuncSetAttribute(attn_sa2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaFuncSetAttribute(attn_sa2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
   }
   dim3 grid((p.L + BQ - 1) / BQ, p.heads, p.nb);
+  // ZV_SA_IMPL=1: the CUDA-core position term (A/B measurements); default: position term on the tensor cores.
+  // ZV_SA_SOFT=2: half of the exponentials on the FMA pipe instead of MUFU -- measured SLOWER on B200 (nb = 128,
+  // L = 1219: 0.441 ms with none, 0.455 / 0.500 / 0.521 ms with 1 / 2 / 3 of every 4; identical accuracy): the kernel
+  // is bound by issue slots and the per-tile MMA -> TMEM -> release chain, not by the MUFU pipe.  Kept for A/B runs.
+  static const int sa_impl = getenv("ZV_SA_IMPL") ? atoi(getenv("ZV_SA_IMPL")) : 2;
+  static const int sa_soft = getenv("ZV_SA_SOFT") ? atoi(getenv("ZV_SA_SOFT")) : 0;
+  const int smem2 = (int)sizeof(sa2::Smem) + 1024 + n_tiles * BKV + ((n_tiles + 15) & ~15);
+  if (sa_impl == 2 && p.E16 && smem2 <= 100 * 1024) {
+    if (sa_soft == 2) attn_sa2_kernel<2><<<grid, THREADS, smem2, s>>>(tmQK, tmV32, p);
+    else attn_sa2_kernel<0><<<grid, THREADS, smem2, s>>>(tmQK, tmV32, p);
+    return (int)cudaGetLastError();
+  }
   attn_sa_kernel<<<grid, THREADS, smem, s>>>(tmQK, tmV, p);
   return (int)cudaGetLastError();
 }

@@ -138,6 +138,12 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
   a.qkp = q, a.ldq = ldq, a.E = Es, a.mask = mask, a.V = v, a.ldv = ldv, a.gate = g, a.ldg = ldv, a.out = o, a.ldo = ldv;
   a.nb = nb, a.L = L, a.H = H, a.heads = heads, a.dv = dv;
   if (sa_pad) a.ldv = heads * 16, a.vhs = 16;
+  void* E16 = nullptr;
+  if (sa_pad) {  // the SelfAttention kernel takes its position term from the fp16 copies of the table
+    cudaMalloc(&E16, (size_t)2 * H * pos_table_f16_stride(L) * 8);
+    pos_table_f16(Es, H, L, E16, s);
+    a.E16 = E16, a.e16_stride = pos_table_f16_stride(L);
+  }
   int rc = attention(a, s);
   if (!rc) {
     cvt_back(o, rows * ldv, out_f32, s);
@@ -145,6 +151,7 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
   }
   cudaFree(q), cudaFree(v), cudaFree(o), cudaFree(Es);
   if (g) cudaFree(g);
+  if (E16) cudaFree(E16);
   return rc;
 }
 
@@ -185,6 +192,12 @@ extern "C" int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv,
   a.ldv = ldv, a.gate = heads == 1 ? g : nullptr, a.ldg = ldv, a.out = o, a.ldo = ldv, a.nb = nb, a.L = L, a.H = H;
   a.heads = heads, a.dv = dv, a.dbg = dbg, a.vhs = (heads > 1 && dv == 12) ? 16 : 0;
   if (heads > 1) a.ldo = heads * dv;
+  void* E16 = nullptr;
+  if (heads > 1 && dv == 12) {
+    cudaMalloc(&E16, (size_t)2 * H * pos_table_f16_stride(L) * 8);
+    pos_table_f16(E, H, L, E16, 0);
+    a.E16 = E16, a.e16_stride = pos_table_f16_stride(L);
+  }
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0), cudaEventCreate(&e1);
   int rc = attention(a, 0);
@@ -197,7 +210,7 @@ extern "C" int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv,
   cudaEventElapsedTime(&ms, e0, e1);
   *ms_out = ms / (iters > 0 ? iters : 1);
   cudaEventDestroy(e0), cudaEventDestroy(e1);
-  cudaFree(q), cudaFree(v), cudaFree(g), cudaFree(o), cudaFree(E), cudaFree(m);
+  cudaFree(q), cudaFree(v), cudaFree(g), cudaFree(o), cudaFree(E), cudaFree(m), cudaFree(E16);
   return rc;
 }
 

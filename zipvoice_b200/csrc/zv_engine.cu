@@ -486,7 +486,7 @@ static int run_dwconv(Engine& e, const __nv_bfloat16* in, const float* w, const 
   return 0;
 }
 
-static int get_pos_table(Engine& e, Net& net, Layer& ly, int L, cudaStream_t s, float** out) {
+static int get_pos_table(Engine& e, Net& net, Layer& ly, int L, cudaStream_t s, float** out, void** out16) {
   auto it = ly.pos_tab.find(L);
   if (it == ly.pos_tab.end()) {
     if (ly.pos_tab.size() >= kMaxPosTables) {
@@ -500,7 +500,8 @@ static int get_pos_table(Engine& e, Net& net, Layer& ly, int L, cudaStream_t s, 
       }
       ZV_TRY((int)cudaDeviceSynchronize());
       for (auto& kv : ly.pos_tab) cudaFree(kv.second);
-      ly.pos_tab.clear();
+      for (auto& kv : ly.pos_tab16) cudaFree(kv.second);
+      ly.pos_tab.clear(), ly.pos_tab16.clear();
       ++e.ws_fm.gen;  // captured graphs hold the freed addresses
     }
     float* E = nullptr;
@@ -512,8 +513,17 @@ static int get_pos_table(Engine& e, Net& net, Layer& ly, int L, cudaStream_t s, 
     ZV_K(KC_TIME_EMBED, (double)net.H * (2 * L - 1) * 16, s,
          pos_table(ly.w_pos, net.H, e.cfg.pos_head_dim, e.cfg.pos_dim, L, E, s));
     it = ly.pos_tab.emplace(L, E).first;
+    void* E16 = nullptr;
+    const cudaError_t hrc = cudaMalloc(&E16, (size_t)2 * net.H * pos_table_f16_stride(L) * 8);
+    if (hrc != cudaSuccess) {
+      e.err = std::string("cudaMalloc failed: ") + cudaGetErrorString(hrc);
+      return (int)hrc;
+    }
+    ly.pos_tab16.emplace(L, E16);
+    ZV_K(KC_TIME_EMBED, (double)net.H * (2 * L - 1) * 32, s, pos_table_f16(E, net.H, L, E16, s));
   }
   *out = it->second;
+  *out16 = ly.pos_tab16[L];
   return 0;
 }
 
@@ -521,7 +531,8 @@ void free_pos_tables(Net& net) {
   for (Stack& st : net.stacks)
     for (Layer& ly : st.layers) {
       for (auto& kv : ly.pos_tab) cudaFree(kv.second);
-      ly.pos_tab.clear();
+      for (auto& kv : ly.pos_tab16) cudaFree(kv.second);
+      ly.pos_tab.clear(), ly.pos_tab16.clear();
     }
 }
 
@@ -531,7 +542,8 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
                          const uint8_t* mask, const float* te_stack, const float* te_ff1, int te_ld, cudaStream_t s) {
   const int M = nb * L, D = net.D, hn = net.hidden_na;
   float* Etab = nullptr;
-  ZV_TRY(get_pos_table(e, net, ly, L, s, &Etab));
+  void* Etab16 = nullptr;
+  ZV_TRY(get_pos_table(e, net, ly, L, s, &Etab, &Etab16));
   EpiParams ep;
   // attention projections from the layer input (before the time embedding is added) -- :526-531
   ep = EpiParams();
@@ -563,6 +575,7 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
     AttnParams a;
     a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.sa_v, a.ldv = 16 * net.H, a.vhs = 16, a.gate = nullptr, a.ldg = 0;
     a.out = ws.conv_b + D, a.ldo = ldc, a.nb = nb, a.L = L, a.H = net.H, a.heads = net.H, a.dv = 12;
+    a.E16 = Etab16, a.e16_stride = pos_table_f16_stride(L);
     return run_attn(e, KC_ATTN_SELF, a, i == 0 ? net.H - 1 : 0, s);  // out_proj: folded into conv(i)
   };
   // SelfAttention(i).out_proj + time embedding + ConvolutionModule(i) with one pass over the fp32 stream

@@ -38,6 +38,7 @@ struct Layer {
   size_t te_off_ff1 = 0;          // column offset of this layer's FF1 row-bias in the te projection
   size_t te_off_conv[2] = {0, 0}; // ... of the two conv in_proj row-biases (W_in te_stack, accumulator order)
   std::map<int, float*> pos_tab;  // L -> E[H][2L-1][dp]
+  std::map<int, void*> pos_tab16; // L -> pos_table_f16 of it (SelfAttention kernel's tensor-core position term)
 };
 
 struct Stack {

@@ -47,6 +47,11 @@ int sgemm_nn(const float* A, const float* B, float* C, int M, int N, int K, cuda
 // Projected relative-position table E[h][r][dp] = sum_c Wpos[h*dp+?][c] pe[r][c], r in [0, 2L-1)
 // (zipformer.py:983-1056,1215-1219).  W [H*dp][pos_dim].
 int pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E, cudaStream_t s);
+// fp16 copies of E for the tensor-core position term of the SelfAttention kernel: out = [2][H][stride][4] halves
+// (2 * H * stride * 8 bytes), stride = pos_table_f16_stride(L); see zv_time.cu.
+static constexpr int POS16_PADL = 128;
+int pos_table_f16_stride(int L);
+int pos_table_f16(const float* E, int H, int L, void* out, cudaStream_t s);
 
 // The scores arrive in LOG2 units: the producer scales q (the rows of the attention in_proj that make q) and the
 // relative-position table E by log2(e), so that softmax = exp2(S - max) without a multiply per score and the
@@ -57,6 +62,8 @@ struct AttnParams {
   const __nv_bfloat16* qkp;  // IEEE fp16 bit patterns (not bf16) [nb][L][ldq]: q at h*dq, k at H*dq + h*dq, p at 2*H*dq + h*dp
   int ldq;
   const float* E;            // [H][2L-1][4], times log2(e)
+  const void* E16 = nullptr; // pos_table_f16 of E (SelfAttention, tensor-core position term); null: CUDA-core kernel
+  int e16_stride = 0;        // entries per head of E16
   const uint8_t* mask;       // [nb][L] 1 = padded key (may be null)
   const __nv_bfloat16* V;    // [nb][L][ldv]
   int ldv;

@@ -1,6 +1,8 @@
 // Small fp32 kernels: time / guidance embedding MLP, per-batch bias projections, the projected
 // relative-position table, and an fp32 matmul used only when weights are folded at finalize time.
 #include "zv_common.cuh"
+#include <cuda_fp16.h>
+
 #include "zv_kernels.h"
 
 namespace zv {
@@ -147,6 +149,28 @@ __global__ void pos_table_kernel(const float* __restrict__ W, int H, int dp, int
   for (int h = 0; h < H; ++h)
     for (int j = 0; j < dp; ++j) E[((size_t)h * R + r) * dp + j] = acc[h * dp + j];
 }
+// fp16 copies of E for the tensor-core position term of the SelfAttention kernel (zv_attn_sa.cu, attn_sa2_kernel):
+// out = [2][H][stride][4] halves, stride = pos_table_f16_stride(L) entries per head.  Copy 0 holds POS16_PADL zero
+// entries, then the R = 2L - 1 table rows, then zeros (every 200-entry window a key tile can ask for lies inside, so
+// the producer issues whole, unclipped bulk copies); copy 1 is copy 0 shifted by one entry (copy1[x] = copy0[x + 1]):
+// the kernel needs windows that start at odd entries too, and a bulk copy's source must be 16-byte aligned.
+int pos_table_f16_stride(int L) { return 2 * L + 208; }
+__global__ void pos_table_f16_kernel(const float* __restrict__ E, int H, int L, int stride, __half* __restrict__ out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, h = blockIdx.y, copy = blockIdx.z;
+  if (x >= stride) return;
+  const int R = 2 * L - 1;
+  const int r = x + copy - POS16_PADL;
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (r >= 0 && r < R) v = reinterpret_cast<const float4*>(E)[(size_t)h * R + r];
+  __half2* o = reinterpret_cast<__half2*>(out + (((size_t)copy * H + h) * stride + x) * 4);
+  o[0] = __floats2half2_rn(v.x, v.y), o[1] = __floats2half2_rn(v.z, v.w);
+}
+int pos_table_f16(const float* E, int H, int L, void* out, cudaStream_t s) {
+  const int stride = pos_table_f16_stride(L);
+  pos_table_f16_kernel<<<dim3((stride + 127) / 128, H, 2), 128, 0, s>>>(E, H, L, stride, static_cast<__half*>(out));
+  return (int)cudaGetLastError();
+}
+
 int pos_table(const float* W, int H, int dp, int pos_dim, int L, float* E, cudaStream_t s) {
   if (H * dp > 16) return 921;
   const int R = 2 * L - 1;
