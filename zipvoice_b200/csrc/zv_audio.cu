@@ -564,8 +564,12 @@ static int vocoder_build(Engine& e, Audio& a) {
 
 static int vocoder_reserve(Engine& e, Audio& a, int B, int T) {
   const int Tp = T + 6;
-  const size_t rows = (size_t)B * Tp;
+  size_t rows = (size_t)B * Tp;
   if (rows <= a.cap_rows && B <= a.cap_B) return 0;
+  // capacity only grows, in both dimensions: a sweep that alternates many short and few long clips must not
+  // shrink one of them and reallocate (and clear) gigabytes on every call
+  if (rows < a.cap_rows) rows = a.cap_rows;
+  if (B < a.cap_B) B = a.cap_B;
   cudaDeviceSynchronize();
   for (void* p : a.ws_allocs) cudaFree(p);
   a.ws_allocs.clear();
