@@ -219,7 +219,12 @@ def cpu_baseline_obj(k: int, c: dict, threads: int):
     n = 3 if c["target_frames"] < 2000 else 1
     r = cpu_sample_time(c, nfe_timed=n, threads=threads)
     total = r["t_text"] + c["nfe"] * r["t_nfe"] + r["t_voc"]
-    return {"value": r["audio_s"] / total, "unit": "audio-s/s", "cores": threads, "kind": "port",
+    one = {}
+    if k == 1:  # also at 1 thread, the reference CLI's own default (infer_zipvoice.py:637-638)
+        r1 = cpu_sample_time(c, nfe_timed=2, threads=1)
+        one = {"value_1_thread": r1["audio_s"] / (r1["t_text"] + c["nfe"] * r1["t_nfe"] + r1["t_voc"]),
+               "s_per_nfe_1_thread": r1["t_nfe"]}
+    return {"value": r["audio_s"] / total, "unit": "audio-s/s", "cores": threads, "kind": "port", **one,
             "s_per_nfe": r["t_nfe"], "s_text_encoder": r["t_text"], "s_vocoder": r["t_voc"],
             "sample": f"1 utterance of the batch (B=1{' -> CFG batch 2' if c['kind'] != 'distill' else ''}, "
                       f"T={c['prompt_frames'] + c['target_frames']}) through the torch-fp32 CPU oracle port: text encoder + "

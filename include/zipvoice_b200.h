@@ -53,6 +53,9 @@ int zv_finalize_weights(void* handle);
  * kernel (tests only), 2 = tcgen05 single-CTA tiles only, 3 = tcgen05 CTA pairs only;
  * "attn_impl" 0 = NonlinAttention on the tcgen05 kernel (default), 1 = mma.sync flash kernel, 2 = as 0 with the
  * exact-maxima repeat of the NonlinAttention kernel forced (tests) (process-wide);
+ * "stream" (two-stream / stereo models only) 0 = the two-channel projection pair in_proj.0 / out_proj.0 (default; x and
+ * speech 2*feat_dim wide), 1 = the mono pair in_proj.1 / out_proj.1 (x and speech feat_dim wide) -- the choice
+ * TTSZipformerTwoStream.forward makes from the input width (zipformer_two_stream.py:238-244);
  * "graph_max_rows" (default 32768; 0 = off): zv_sample calls whose network batch x frames is at or below this
  * value are launch-bound; from the third call of a (shape, schedule, guidance mode) key on they replay a CUDA
  * graph of the whole NFE loop captured on an engine-owned stream from engine-owned input copies (results are

@@ -55,6 +55,14 @@ def stereo():
     np.savez(os.path.join(OUT, "dialog_stereo.npz"), v=v.numpy(), x1_cfg=x1.numpy(), x1_wo=out[0].numpy(),
              wo_lens=out[1].numpy(), x1_prompt=out[2].numpy())
     print("stereo golden written")
+    # the SECOND projection pair of TTSZipformerTwoStream (zipformer_two_stream.py:238-244: a mono input, width
+    # 3 * feat_dim, goes through in_proj[1] / out_proj[1]): velocity and a 3-step CFG Euler on mono inputs
+    xm, tm, sm_, mm = case_inputs(2, 41, 13, seed=14)
+    vm = m.forward_fm_decoder(torch.tensor(0.6), xm, tm, sm_, mm)
+    x1m = m.solver.sample(x=xm, text_condition=tm, speech_condition=sm_, padding_mask=mm, num_step=3,
+                          guidance_scale=1.0, t_shift=0.5)
+    np.savez(os.path.join(OUT, "dialog_stereo_mono_stream.npz"), v=vm.numpy(), x1_cfg=x1m.numpy())
+    print("stereo model, mono stream golden written", vm.shape)
 
 
 @torch.inference_mode()

@@ -127,8 +127,21 @@ def test_dialog_stereo_golden():
     assert torch.equal(out[1].cpu(), g["wo_lens"])
     r = rel_l2(out[0].cpu(), g["x1_wo"])
     assert r < TOL_MEL, f"stereo sample() generated part rel-L2 {r:.3e}"
-    with pytest.raises(AssertionError):  # zipformer_two_stream.py:240: the width must match an input stream
-        m.forward_fm_decoder(torch.tensor(0.3), x0[..., :100], text, speech[..., :100], mask)
+    with pytest.raises(AssertionError):  # zipformer_two_stream.py:238: the width must match one of the two streams
+        m.forward_fm_decoder(torch.tensor(0.3), x0[..., :150], text, speech[..., :150], mask)
+    # the SECOND projection pair (mono input through in_proj.1 / out_proj.1, zipformer_two_stream.py:238-244) against
+    # the unmodified reference, then back to the two-channel stream on the same handle
+    gm = _g("dialog_stereo_mono_stream.npz")
+    xm, tm, sm_, mm = case_inputs(2, 41, 13, seed=14)
+    vm = m.forward_fm_decoder(torch.tensor(0.6), xm, tm, sm_, mm).cpu()
+    r = valid_rel_l2(vm, gm["v"], mm)
+    assert vm.shape == (2, 41, 100) and r < TOL_NFE_STRESS, f"mono stream of the two-stream decoder: rel-L2 {r:.3e}"
+    x1m = m.solver.sample(x=xm, text_condition=tm, speech_condition=sm_, padding_mask=mm, num_step=3,
+                          guidance_scale=1.0, t_shift=0.5).cpu()
+    r = valid_rel_l2(x1m, gm["x1_cfg"], mm)
+    assert r < TOL_MEL, f"mono stream CFG Euler rel-L2 {r:.3e}"
+    v2 = m.forward_fm_decoder(torch.tensor(0.3), x0, text, speech, mask).cpu()
+    assert torch.equal(v2, v), "switching streams must not disturb the two-channel path"
 
 
 def test_dialog_text_embed_golden():

@@ -3,6 +3,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <utility>
+
 #include "zv_common.cuh"
 #include "zv_engine.h"
 
@@ -153,6 +155,19 @@ int zv_set_option(void* handle, const char* key, int value) {
   if (!strcmp(key, "gemm_impl")) e->gemm_impl = value;
   else if (!strcmp(key, "attn_impl")) zv::g_attn_impl = value;  // process-wide
   else if (!strcmp(key, "graph_max_rows")) e->graph_max_rows = value;
+  else if (!strcmp(key, "stream")) {
+    // TTSZipformerTwoStream: 0 = the two-channel projection pair, 1 = the mono pair (zipformer_two_stream.py:238-244)
+    Net& net = e->fm;
+    if (!net.two_stream || value < 0 || value > 1) {
+      e->err = "option stream needs a two-stream (stereo) model and a value of 0 or 1";
+      return 962;
+    }
+    if (value != net.stream) {
+      std::swap(net.in_proj, net.alt_in_proj), std::swap(net.out_proj, net.alt_out_proj);
+      std::swap(net.in_dim, net.alt_in_dim), std::swap(net.in_pad, net.alt_in_pad), std::swap(net.out_dim, net.alt_out_dim);
+      net.stream = value;
+    }
+  }
   else {
     e->err = std::string("unknown option ") + key;
     return 962;
@@ -229,7 +244,7 @@ static int velocity_step(Engine* e, int variant, float t_host, const float* t_de
                          float* v_out, float* x_update, float dt, cudaStream_t s) {
   Net& net = e->fm;
   Workspace& ws = e->ws_fm;
-  const int Ft = e->cfg.feat_dim, F = e->cfg.stereo ? 2 * Ft : Ft;  // F: width of x / speech / velocity
+  const int Ft = e->cfg.feat_dim, F = e->fm.out_dim;  // F: width of x / speech / velocity (active stream)
   const bool cfg = (variant == 0) && !all_zero_g;
   const int nb = cfg ? 2 * B : B;
   const bool hi = t_host > 0.5f;  // solver.py:90 decided on the host from the precomputed time table
@@ -283,7 +298,7 @@ static int sample_graphed(Engine* e, int variant, const float* x0, const float* 
                           const uint8_t* mask, int B, int T, int num_step, bool all_zero, int guidance_len,
                           double t_start, double t_end, double t_shift, const std::vector<float>& ts, float* x1,
                           cudaStream_t s) {
-  const int Ft = e->cfg.feat_dim, F = e->cfg.stereo ? 2 * Ft : Ft;
+  const int Ft = e->cfg.feat_dim, F = e->fm.out_dim;
   const size_t bt = (size_t)B * T;
   if (!e->gstream) {
     API_TRY((int)cudaStreamCreateWithFlags(&e->gstream, cudaStreamNonBlocking));
@@ -327,7 +342,7 @@ static int sample_graphed(Engine* e, int variant, const float* x0, const float* 
   const std::vector<unsigned long long> key = {(unsigned long long)variant, (unsigned long long)B, (unsigned long long)T,
                                                (unsigned long long)num_step, (unsigned long long)all_zero,
                                                (unsigned long long)guidance_len, bits(t_start), bits(t_end), bits(t_shift),
-                                               (unsigned long long)(mask != nullptr), (unsigned long long)e->gemm_impl,
+                                               (unsigned long long)(mask != nullptr), (unsigned long long)(e->gemm_impl * 2 + e->fm.stream),
                                                (unsigned long long)zv::g_attn_impl};
   Engine::SampleGraph* g = nullptr;
   for (auto& c : e->graphs)
@@ -424,7 +439,7 @@ extern "C" int zv_forward_fm_decoder(void* handle, const float* t, int t_len, co
   }
   Net& net = e->fm;
   Workspace& ws = e->ws_fm;
-  const int Ft = e->cfg.feat_dim, F = e->cfg.stereo ? 2 * Ft : Ft;
+  const int Ft = e->cfg.feat_dim, F = e->fm.out_dim;
   API_TRY(ws_reserve(*e, net, ws, N, T));
   API_TRY(upload_small(e, ws.t_dev, t, t_len, s));
   if (guidance_len > 0) API_TRY(upload_small(e, ws.guid_dev, guidance, guidance_len, s));
@@ -460,7 +475,7 @@ extern "C" int zv_sample(void* handle, int variant, const float* x0, const float
   float* ts_dev = e->ws_fm.ts_dev;  // time table on the device: no host synchronisation inside the loop
   API_TRY(upload_small(e, ts_dev, ts.data(), (int)ts.size(), s));
   API_TRY(upload_small(e, e->ws_fm.guid_dev, guidance, guidance_len, s));
-  const size_t n = (size_t)B * T * e->cfg.feat_dim * (e->cfg.stereo ? 2 : 1);
+  const size_t n = (size_t)B * T * e->fm.out_dim;
   const bool cfg2 = (variant == 0) && !all_zero;
   if (e->graph_max_rows > 0 && !e->prof.on && (size_t)(cfg2 ? 2 : 1) * B * T <= (size_t)e->graph_max_rows)
     return sample_graphed(e, variant, x0, text, speech, mask, B, T, num_step, all_zero, guidance_len, t_start, t_end,

@@ -294,6 +294,17 @@ static int build_net(Engine& e, Net& net, const std::string& prefix, int in_dim,
   const std::string pj = two_stream ? ".0" : "";
   ZV_TRY(pack_linear(e, prefix + ".in_proj" + pj, EPI_F32, &net.in_proj, net.in_pad));
   ZV_TRY(pack_linear(e, prefix + ".out_proj" + pj, EPI_F32, &net.out_proj));
+  net.in_pad_max = net.in_pad, net.out_dim_max = net.out_dim;
+  net.two_stream = two_stream;
+  if (two_stream) {
+    // the mono pair: in_proj.1 (3 feat_dim -> D), out_proj.1 (D -> feat_dim)
+    net.alt_in_dim = 3 * c.feat_dim, net.alt_out_dim = c.feat_dim;
+    net.alt_in_pad = (net.alt_in_dim + 63) / 64 * 64;
+    ZV_TRY(pack_linear(e, prefix + ".in_proj.1", EPI_F32, &net.alt_in_proj, net.alt_in_pad));
+    ZV_TRY(pack_linear(e, prefix + ".out_proj.1", EPI_F32, &net.alt_out_proj));
+    if (net.alt_in_pad > net.in_pad_max) net.in_pad_max = net.alt_in_pad;
+    if (net.alt_out_dim > net.out_dim_max) net.out_dim_max = net.alt_out_dim;
+  }
   const int td = c.time_embed_dim;
   if (use_time) {
     ZV_TRY(upload_named(e, prefix + ".time_embed.0.weight", &net.te_w0));
@@ -436,9 +447,9 @@ int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
   ZV_TRY(A((void**)&ws.X, rows * D * 4));
   ZV_TRY(A((void**)&ws.Xs, rows * D * 4));
   ZV_TRY(A((void**)&ws.Y, rows * D * 4));
-  ZV_TRY(A((void**)&ws.vel, rows * net.out_dim * 4));
-  ZV_TRY(A((void**)&ws.xcur, rows * net.out_dim * 4));
-  ZV_TRY(A((void**)&ws.x_in, rows * net.in_pad * 2));
+  ZV_TRY(A((void**)&ws.vel, rows * net.out_dim_max * 4));
+  ZV_TRY(A((void**)&ws.xcur, rows * net.out_dim_max * 4));
+  ZV_TRY(A((void**)&ws.x_in, rows * net.in_pad_max * 2));
   ZV_TRY(A((void**)&ws.shadow, rows * D * 2));
   ZV_TRY(A((void**)&ws.qkp, rows * 288 * 2));
   ZV_TRY(A((void**)&ws.hidden, rows * Fmax * 2));

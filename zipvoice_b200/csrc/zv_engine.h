@@ -54,6 +54,14 @@ struct Net {
   int in_dim = 0, in_pad = 0, out_dim = 0, D = 0, F = 0, H = 0, hidden_na = 0;
   bool use_time = false, use_guidance = false;
   Lin in_proj, out_proj;
+  // TTSZipformerTwoStream (zipformer_two_stream.py:139-150,238-244) keeps TWO projection pairs and picks one by the
+  // width of its input.  in_proj / out_proj / in_dim / in_pad / out_dim above are the ACTIVE pair; the other one
+  // waits here and zv_set_option("stream", i) swaps them.  Workspaces are sized for the wider pair.
+  bool two_stream = false;
+  int stream = 0;  // index of the active pair (0: two channels, 1: mono)
+  Lin alt_in_proj, alt_out_proj;
+  int alt_in_dim = 0, alt_in_pad = 0, alt_out_dim = 0;
+  int in_pad_max = 0, out_dim_max = 0;
   float *te_w0 = nullptr, *te_b0 = nullptr, *te_w2 = nullptr, *te_b2 = nullptr, *te_wg = nullptr;
   float* te_proj_w = nullptr;  // [N_te][time_dim] folded (stack time_emb, FF1 in_proj . time_emb)
   float* te_proj_b = nullptr;  // [N_te]

@@ -96,6 +96,19 @@ class Engine:
         self._check(self.lib.zv_set_option(self._h, key.encode(), int(value)))
 
     # ------------------------------------------------------------------ helpers
+    def _select_stream(self, width: int):
+        """TTSZipformerTwoStream.forward (zipformer_two_stream.py:238-244): the width of x picks the projection pair --
+        2 * feat_dim: pair 0 (two channels), feat_dim: pair 1 (mono).  Single-stream models: nothing to choose."""
+        if not self.stereo:
+            return
+        assert width in (2 * self.feat_dim, self.feat_dim), \
+            f"{3 * width} not in ({5 * self.feat_dim}, {3 * self.feat_dim})"           # zipformer_two_stream.py:238
+        stream = 0 if width == 2 * self.feat_dim else 1
+        if stream != getattr(self, "_stream", 0):
+            self.set_option("stream", stream)
+            self._stream = stream
+        self.x_dim = width
+
     def _prep(self, t: torch.Tensor, dtype=torch.float32) -> torch.Tensor:
         return t.to(device=self.device, dtype=dtype).contiguous()
 
@@ -112,6 +125,7 @@ class Engine:
                  distill: Optional[bool] = None) -> torch.Tensor:
         """DiffusionModel.forward / DistillDiffusionModel.forward (solver.py:40-110,127-165)."""
         distill = self.distill if distill is None else distill
+        self._select_stream(x.shape[-1])
         x, tc, sc = self._prep(x), self._prep(text_condition), self._prep(speech_condition)
         B, T, F = x.shape
         # zipformer.py:268 / zipformer_two_stream.py:240: the concatenated width must be the in_proj's
@@ -129,6 +143,7 @@ class Engine:
                            guidance_scale=None) -> torch.Tensor:
         """ZipVoice.forward_fm_decoder (zipvoice.py:135-185): t 0-dim or (N, 1, 1) with one time step per row;
         guidance_scale None, 0-dim or (N, 1, 1) (embedded by the distilled model).  No CFG logic."""
+        self._select_stream(xt.shape[-1])
         x, tc, sc = self._prep(xt), self._prep(text_condition), self._prep(speech_condition)
         N, T, F = x.shape
         assert F == self.x_dim and sc.shape == x.shape and tuple(tc.shape) == (N, T, self.feat_dim), \
@@ -152,6 +167,7 @@ class Engine:
                t_start=0.0, t_end=1.0, t_shift=1.0, distill: Optional[bool] = None) -> torch.Tensor:
         """EulerSolver.sample (solver.py:182-240); the input x is not modified."""
         distill = self.distill if distill is None else distill
+        self._select_stream(x.shape[-1])
         x, tc, sc = self._prep(x), self._prep(text_condition), self._prep(speech_condition)
         B, T, F = x.shape
         # zipformer.py:268 / zipformer_two_stream.py:240: the concatenated width must be the in_proj's
