@@ -230,3 +230,91 @@ def test_generate_batch_silent_prompt_and_empty_shard_do_not_crash():
     wavs = [torch.zeros(8000), synth.make_audio(1, 8000, seed=5)[0] * 0.3]
     outs = infer.generate_batch(prompt_tokens, wavs, tokens, model, voc, fb, num_step=2)
     assert len(outs) == 2 and all(bool(torch.isfinite(o).all()) for o in outs)
+
+
+def test_generate_list_dialog_formats_and_prompt_assembly(tmp_path, monkeypatch):
+    """generate_list of the dialog CLI (bin/infer_zipvoice_dialog.py:518-611): the 6-field line (two prompt texts / wavs,
+    "[S1]..[S2].." prompt text) and the 4-field line; prompts are resampled per file, down-mixed and joined along time
+    (:268-279) -- checked against the CPU resampling oracle -- and every written file holds what generate_batch returned.
+    Then the stereo model: two one-channel prompts on the silence template (:436-441), two-channel output files."""
+    import os
+    import numpy as np
+    from oracle import resample_oracle as R
+    from oracle import vocos_oracle as VO
+    from zipvoice_b200 import infer, synth
+    from zipvoice_b200.audio import VocosB200, VocosFbankB200
+    from zipvoice_b200.model import ZipVoiceB200
+
+    class Tok:
+        def texts_to_token_ids(self, texts):
+            return [[synth.SPK_A_ID if t[i:i + 4] == "[S1]" else synth.SPK_B_ID if t[i:i + 4] == "[S2]"
+                     else 1 + (ord(c) % 300) for i, c in enumerate(t) if c not in "S12]" or t[i - 1:i] != "["]
+                    for t in texts]
+
+    cfg = synth.small_model_cfg()
+    vsd = VO.make_vocos_state_dict(0)
+    voc = VocosB200(vsd)
+    w1 = synth.make_audio(1, 6000, seed=41)[0] * 0.3
+    w2 = synth.make_audio(1, 9000, seed=42)[0] * 0.2
+    wm = synth.make_audio(1, 12000, seed=43)[0] * 0.3
+    q = lambda w: torch.round(w * 32768.0).clamp(-32768, 32767) / 32768.0
+    p1, p2, pm = (os.path.join(tmp_path, n) for n in ("p1.wav", "p2.wav", "pm.wav"))
+    infer.write_wav(p1, w1.numpy(), 16000), infer.write_wav(p2, w2.numpy(), 24000), infer.write_wav(pm, wm.numpy(), 24000)
+    lst = os.path.join(tmp_path, "d.tsv")
+    open(lst, "w").write("two\thello there\tfine thanks\t%s\t%s\t[S1]so it goes[S2]yes it does\n"
+                         "one\t[S1]merged prompt[S2]of two\t%s\t[S1]short one\n" % (p1, p2, pm))
+    # ---- mono dialog model
+    model = ZipVoiceB200(cfg, synth.make_state_dict(cfg, seed=3, dialog=True, stress=True), synth.VOCAB_SIZE,
+                         synth.PAD_ID, kind="dialog")
+    fb = VocosFbankB200(engine=voc.engine)
+    calls = []
+    real = infer.generate_batch
+
+    def spy(prompt_tokens, prompt_wavs, tokens, *a, **kw):
+        outs = real(prompt_tokens, prompt_wavs, tokens, *a, **kw)
+        calls.append(dict(prompt_tokens=prompt_tokens, prompt_wavs=[w.cpu() for w in prompt_wavs],
+                          outs=[o.cpu() for o in outs]))
+        return outs
+
+    monkeypatch.setattr(infer, "generate_batch", spy)
+    res = os.path.join(tmp_path, "out")
+    m = infer.generate_list_dialog("zipvoice_dialog", res, lst, model, voc, Tok(), fb, num_step=2)
+    assert m["utterances"] == 2 and m["wav_seconds"] > 0
+    tok = Tok()
+    pt_two = tok.texts_to_token_ids(["[S1]hello there[S2]fine thanks"])[0]
+    assert pt_two[0] == synth.SPK_A_ID and synth.SPK_B_ID in pt_two
+    found = {}
+    for c in calls:
+        for j, pt in enumerate(c["prompt_tokens"]):
+            found["two" if pt == pt_two else "one"] = (c, j)
+    c, j = found["two"]
+    want = torch.cat([torch.from_numpy(R.resample(q(w1).numpy(), 16000, 24000)), q(w2)])
+    assert c["prompt_wavs"][j].shape == want.shape and float((c["prompt_wavs"][j] - want).abs().max()) < 2e-5
+    c1, j1 = found["one"]
+    assert float((c1["prompt_wavs"][j1] - q(wm)).abs().max()) < 1e-6
+    for name in ("two", "one"):
+        cc, jj = found[name]
+        w, sr = infer.read_wav(os.path.join(res, f"{name}.wav"))
+        wantw = torch.round(cc["outs"][jj] * 32768.0).clamp(-32768, 32767) / 32768.0
+        assert sr == 24000 and w.shape == (1, wantw.numel()) and float((w[0] - wantw).abs().max()) <= 1 / 32768 + 1e-7
+    monkeypatch.setattr(infer, "generate_batch", real)
+    with pytest.raises(ValueError):
+        bad = os.path.join(tmp_path, "bad.tsv")
+        open(bad, "w").write("a\tb\tc\n")
+        infer.generate_list_dialog("zipvoice_dialog", res, bad, model, voc, Tok(), fb)
+    # ---- stereo dialog model: two mono prompts -> channel 0 then channel 1 on the silence template
+    sil = os.path.join(tmp_path, "sil.wav")
+    infer.write_wav(sil, np.zeros((2, 40000), dtype=np.float32) + 1e-4, 24000)
+    lst2 = os.path.join(tmp_path, "s.tsv")
+    open(lst2, "w").write("st\thello there\tfine thanks\t%s\t%s\t[S1]so it goes[S2]yes\n" % (p2, pm))
+    models = ZipVoiceB200(cfg, synth.make_state_dict(cfg, seed=4, dialog=True, stress=True, stereo=True),
+                          synth.VOCAB_SIZE, synth.PAD_ID, kind="dialog_stereo")
+    fb2 = VocosFbankB200(engine=voc.engine, num_channels=2)
+    merged = infer.merge_dialog_prompts([q(w2).reshape(1, -1), q(wm).reshape(1, -1)], True, torch.zeros(2, 40000))
+    assert merged.shape == (2, 21000) and bool((merged[0, 9000:] == 0).all()) and bool((merged[1, :9000] == 0).all())
+    assert torch.equal(merged[0, :9000], q(w2)) and torch.equal(merged[1, 9000:], q(wm))
+    ms = infer.generate_list_dialog("zipvoice_dialog_stereo", res, lst2, models, voc, Tok(), fb2, num_step=2,
+                                    silence_wav=sil)
+    w, sr = infer.read_wav(os.path.join(res, "st.wav"))
+    assert ms["utterances"] == 1 and sr == 24000 and w.shape[0] == 2 and w.shape[1] % 256 == 0 and w.shape[1] > 0
+    assert bool(torch.isfinite(w).all()) and float(w.abs().max()) > 0

@@ -180,13 +180,40 @@ def read_wav(path: str):
 
 
 def write_wav(path: str, wav: np.ndarray, sampling_rate: int):
-    """mono float waveform in [-1, 1] -> 16-bit PCM (what torchaudio.save writes for the reference, :401)."""
-    pcm = np.clip(np.round(np.asarray(wav, dtype=np.float32).reshape(-1) * 32768.0), -32768, 32767).astype("<i2")
+    """float waveform in [-1, 1], (N,) mono or (C, N) -> 16-bit PCM with interleaved channels (what torchaudio.save
+    writes for the reference, infer_zipvoice.py:401, infer_zipvoice_dialog.py:346,513)."""
+    w = np.asarray(wav, dtype=np.float32)
+    w = w.reshape(1, -1) if w.ndim == 1 else w
+    pcm = np.clip(np.round(w.T.reshape(-1) * 32768.0), -32768, 32767).astype("<i2")
     with wave.open(path, "wb") as f:
-        f.setnchannels(1)
+        f.setnchannels(int(w.shape[0]))
         f.setsampwidth(2)
         f.setframerate(int(sampling_rate))
         f.writeframes(pcm.tobytes())
+
+
+def merge_dialog_prompts(wavs: Sequence[torch.Tensor], stereo: bool,
+                         silence: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """The prompt assembly of the dialog CLI on waveforms already at the model's sampling rate, each (C, N).
+    Mono model (infer_zipvoice_dialog.py:268-279): every file is down-mixed to one channel, two files are joined
+    along time -> (1, N).  Stereo model (:424-441): one file must have two channels; two two-channel files are joined
+    along time; two one-channel files go to channel 0 / channel 1 one after the other on top of the ``silence``
+    template (2, >= N1 + N2) -> (2, N)."""
+    wavs = [w.reshape(1, -1) if w.dim() == 1 else w for w in wavs]
+    assert len(wavs) in (1, 2)
+    if not stereo:
+        return torch.cat([w.mean(0, keepdim=True) if w.size(0) != 1 else w for w in wavs], dim=1)
+    if len(wavs) == 1:
+        assert wavs[0].size(0) == 2, "Merged prompt wav must be stereo for stereo dialogue generation"
+        return wavs[0]
+    if wavs[0].size(0) == 2:
+        return torch.cat(list(wavs), dim=1)
+    assert wavs[0].size(0) == 1 and silence is not None, "two mono prompts need the silence template (silence_wav)"
+    n1, n2 = wavs[0].size(1), wavs[1].size(1)
+    out = silence[:, : n1 + n2].clone()
+    out[0, :n1] = wavs[0][0]
+    out[1, n1:] = wavs[1][0]
+    return out
 
 
 def length_buckets(cost: Sequence[int], max_batch_cost: int) -> List[List[int]]:
@@ -284,3 +311,96 @@ def generate_list(res_dir: str, test_list: str, model, vocoder, tokenizer, featu
             f.result()
     return {"t": total_t, "wav_seconds": total_sec, "rtf": total_t / max(total_sec, 1e-9), "utterances": n_done,
             "batches": len(buckets)}
+
+
+@torch.inference_mode()
+def generate_list_dialog(model_name: str, res_dir: str, test_list: str, model, vocoder, tokenizer, feature_extractor,
+                         num_step: int = 16, guidance_scale: float = 1.5, speed: float = 1.0, t_shift: float = 0.5,
+                         target_rms: float = 0.1, feat_scale: float = 0.1, sampling_rate: int = 24000,
+                         silence_wav: Optional[str] = None, max_batch_frames: int = 64 * 1300,
+                         load_wav: Callable = read_wav) -> Dict[str, float]:
+    """bin/infer_zipvoice_dialog.py:518-611.  ``test_list`` lines are either
+        wav_name <tab> prompt_text <tab> prompt_wav <tab> text                                   (merged prompt), or
+        wav_name <tab> prompt_text_1 <tab> prompt_text_2 <tab> prompt_wav_1 <tab> prompt_wav_2 <tab> text
+    (the prompt text becomes "[S1]...[S2]...", :546); ``text`` must start with "[S1]" (:552).
+    ``model_name`` "zipvoice_dialog": prompts are resampled per file, down-mixed and joined along time
+    (``merge_dialog_prompts``), the RMS is that of the joined mono prompt (:280-282), and the utterances run as padded
+    length buckets through ``generate_batch`` (tolerance-level equal to the reference's per-utterance loop, see there).
+    "zipvoice_dialog_stereo": two-channel prompts and outputs through ``generate_sentence_stereo`` per utterance.
+    Writes ``res_dir/<wav_name>.wav`` (two channels for the stereo model) and returns the totals the reference logs."""
+    from .audio import ResampleB200
+    assert model_name in ("zipvoice_dialog", "zipvoice_dialog_stereo"), model_name
+    stereo = model_name == "zipvoice_dialog_stereo"
+    dev = model.device
+    names, ptexts, pwavs, texts = [], [], [], []
+    with open(test_list, "r") as fr:
+        for line in fr:
+            if not line.strip():
+                continue
+            items = line.strip().split("\t")
+            if len(items) == 6:
+                wav_name, pt1, pt2, pw1, pw2, text = items
+                ptext, pw = f"[S1]{pt1}[S2]{pt2}", [pw1, pw2]
+            elif len(items) == 4:
+                wav_name, ptext, pw1, text = items
+                pw = [pw1]
+            else:
+                raise ValueError(f"Invalid line: {line}")
+            assert text.startswith("[S1]")
+            names.append(wav_name), ptexts.append(ptext), pwavs.append(pw), texts.append(text)
+    os.makedirs(res_dir, exist_ok=True)
+    tokens = tokenizer.texts_to_token_ids(texts)
+    prompt_tokens = tokenizer.texts_to_token_ids(ptexts)
+    silence = None
+    if stereo and silence_wav is not None:
+        silence, ssr = load_wav(silence_wav)
+        assert ssr == sampling_rate                                              # :436
+    resamplers: Dict[int, ResampleB200] = {}
+
+    def load(path):  # :268-277 / :416-422: load, resample the file as it is (all channels) to the model's rate
+        w, sr = load_wav(path)
+        w = w.float().reshape(-1, w.shape[-1]).to(dev)
+        if int(sr) != sampling_rate:
+            if int(sr) not in resamplers:
+                resamplers[int(sr)] = ResampleB200(int(sr), sampling_rate, engine=feature_extractor.engine)
+            w = resamplers[int(sr)](w)
+        return w
+
+    prompts = [merge_dialog_prompts([load(pth) for pth in pw], stereo, None if silence is None else silence.to(dev))
+               for pw in pwavs]
+    total_t, total_sec = 0.0, 0.0
+    pending = []
+    with ThreadPoolExecutor(max_workers=2) as pool:
+        if stereo:
+            for i, name in enumerate(names):
+                wav, m = generate_sentence_stereo(prompt_tokens[i], prompts[i], tokens[i], model, vocoder,
+                                                  feature_extractor, num_step=num_step, guidance_scale=guidance_scale,
+                                                  speed=speed, t_shift=t_shift, target_rms=target_rms,
+                                                  feat_scale=feat_scale, sampling_rate=sampling_rate)
+                total_t += m["t"]
+                total_sec += m["wav_seconds"]
+                pending.append(pool.submit(write_wav, os.path.join(res_dir, f"{name}.wav"), wav.cpu().numpy(),
+                                           sampling_rate))
+            n_batches = len(names)
+        else:
+            frames = [max(1, p.shape[-1] // 256) for p in prompts]
+            cost = [int(frames[i] * (1 + len(tokens[i]) / max(1, len(prompt_tokens[i])) / max(speed, 1e-3)))
+                    for i in range(len(names))]
+            buckets = length_buckets(cost, max_batch_frames)
+            for b in buckets:
+                torch.cuda.synchronize(dev)
+                t0 = time.perf_counter()
+                wavs = generate_batch([prompt_tokens[i] for i in b], [prompts[i][0] for i in b], [tokens[i] for i in b],
+                                      model, vocoder, feature_extractor, num_step=num_step,
+                                      guidance_scale=guidance_scale, speed=speed, t_shift=t_shift,
+                                      target_rms=target_rms, feat_scale=feat_scale, feat_bias=0.0)
+                host = [w.cpu().numpy() for w in wavs]
+                total_t += time.perf_counter() - t0
+                for i, w in zip(b, host):
+                    total_sec += w.shape[-1] / sampling_rate
+                    pending.append(pool.submit(write_wav, os.path.join(res_dir, f"{names[i]}.wav"), w, sampling_rate))
+            n_batches = len(buckets)
+        for f in pending:
+            f.result()
+    return {"t": total_t, "wav_seconds": total_sec, "rtf": total_t / max(total_sec, 1e-9), "utterances": len(names),
+            "batches": n_batches}
