@@ -258,3 +258,38 @@ def test_gemm_fp16_output_is_precise_at_1e3_and_saturates(impl):
     assert bool((out[:, big].abs() == 65504.0).all())
     k3 = (torch.arange(N, device="cuda") % 7 == 1)
     assert float((out[:, k3] - ref[:, k3]).abs().max()) <= 0.5 + 1e-3   # spacing of fp16 near 1e3 is 0.5
+
+
+@pytest.mark.parametrize("ksplit", [2, 3, 8])
+@pytest.mark.parametrize("L", [130, 611, 1219])
+def test_self_attention_key_split(L, ksplit, monkeypatch):
+    """The SelfAttention kernel's key split (small grids: single utterances, the 60 s dialog): ksplit CTAs per query
+    tile write partial softmax states that a merge kernel combines.  Forced here (the launcher would pick it from the
+    grid size); must equal the unsplit kernel to rounding and the fp32 reference to the attention tolerance."""
+    H, nb, dv = 4, 2, 12
+    g = torch.Generator(device="cuda").manual_seed(L + ksplit)
+    rn = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    qkp = (rn(nb, L, 288) * 0.7).bfloat16().float()
+    qkp[:, L // 2:, H * 32: 2 * H * 32] += 1.0      # later keys score higher: the splits end with different maxima
+    qkp = qkp.bfloat16().float()
+    E = rn(H, 2 * L - 1, 4).contiguous()
+    mask = torch.zeros(nb, L, dtype=torch.uint8, device="cuda")
+    mask[1, L - 7:] = 1
+    V = rn(nb, L, H * dv).bfloat16().float()
+    outs = {}
+    for k in (1, ksplit):
+        out = torch.zeros(nb, L, H * dv, device="cuda")
+        rc = _lib().zv_debug_attention_ksplit(k)
+        assert rc == 0
+        rc = _lib().zv_debug_attention(nb, L, H, H, dv, _p(qkp), 288, _p(E), _p(mask), _p(V), H * dv, None, _p(out), None)
+        assert rc == 0
+        outs[k] = out
+    _lib().zv_debug_attention_ksplit(0)
+    want = ref_attention(qkp, E, mask, V, None, H, H, dv)
+    assert rel(outs[ksplit], want) < 8e-3
+    d = float((outs[ksplit] - outs[1]).abs().max())
+    assert d < 2e-2 and rel(outs[ksplit], outs[1]) < 4e-3, (d, rel(outs[ksplit], outs[1]))
+    nt = (L + 63) // 64
+    per = (nt + ksplit - 1) // ksplit
+    if per >= 2 and (ksplit - 1) * per < nt:   # a legal split (no empty key range) was really taken: not bit-identical
+        assert not torch.equal(outs[ksplit], outs[1])

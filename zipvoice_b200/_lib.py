@@ -61,6 +61,7 @@ _DEBUG_SIGS = {
     "zv_debug_gemm": (_I, [_I, _I, _I, _I, _I, _I, _I] + [_P] * 12),
     "zv_debug_attention": (_I, [_I, _I, _I, _I, _I, _P, _I, _P, _P, _P, _I, _P, _P, _P]),
     "zv_debug_set_attn_impl": (_I, [_I]),
+    "zv_debug_attention_ksplit": (_I, [_I]),
     "zv_debug_attention_bench": (_I, [_I] * 8 + [C.POINTER(_F)]),
     "zv_debug_gemm_bench": (_I, [_I] * 9 + [C.POINTER(_F)]),
     "zv_debug_pos_table": (_I, [_P, _I, _I, _I, _I, _P, _P]),

@@ -451,14 +451,19 @@ ZV_DEVINL float ex2_sel(float x) {
 
 template <int SOFT>
 __global__ void __launch_bounds__(sa::THREADS, 2)
-attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__ CUtensorMap tmV, AttnParams p) {
+attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__ CUtensorMap tmV, AttnParams p,
+                int ksplit) {
   using namespace sa2;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   sa2::Smem& sm = *reinterpret_cast<sa2::Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int b = blockIdx.z, head = blockIdx.y, i0 = blockIdx.x * BQ;
+  const int b = blockIdx.z, head = blockIdx.y;
+  const int qt = blockIdx.x / ksplit, sp = blockIdx.x - qt * ksplit, i0 = qt * BQ;
   const int L = p.L, H = p.H;
   const int n_tiles = (L + BKV - 1) / BKV;
+  // this CTA's key tiles [kt0, kt1): never empty (the launcher keeps (ksplit - 1) * tiles_per < n_tiles)
+  const int tiles_per = (n_tiles + ksplit - 1) / ksplit;
+  const int kt0 = sp * tiles_per, kt1 = min(n_tiles, kt0 + tiles_per);
   uint8_t* smask = reinterpret_cast<uint8_t*>(&sm) + sizeof(sa2::Smem);
   uint8_t* sflag = smask + n_tiles * BKV;
   const uint8_t* mask = p.mask ? p.mask + (size_t)b * L : nullptr;
@@ -501,10 +506,10 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
       mbar_wait(&sm.qbar, 0);
       const uint64_t dq = sa::make_sdesc_sw64(smem_u32(&sm.q[0][0]));
       const uint64_t dap = sa::make_sdesc_sw64(smem_u32(&sm.ap[0][0]));
-      for (int kt = 0; kt < n_tiles; ++kt) {
-        const int st = kt % STAGES;
-        mbar_wait(&sm.full[st], (kt / STAGES) & 1);
-        if (kt >= 1) mbar_wait(&sm.sfree, (kt - 1) & 1);
+      for (int it = 0; it < kt1 - kt0; ++it) {
+        const int st = it % STAGES;
+        mbar_wait(&sm.full[st], (it / STAGES) & 1);
+        if (it >= 1) mbar_wait(&sm.sfree, (it - 1) & 1);
         tc_fence_after();
         const uint64_t dk = sa::make_sdesc_sw64(smem_u32(&sm.k[st][0][0]));
         const uint64_t dwe = make_sdesc_kmajor_plain(smem_u32(&sm.we[st][0]), 16, 128);
@@ -528,9 +533,9 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
       tma_load_2d(&sm.q[64][0], &tmQK, &sm.qbar, head * DQ, b * L + i0 + 64);
       const uint2* Ea = reinterpret_cast<const uint2*>(p.E16) + (size_t)head * p.e16_stride;
       const uint2* Eb = Ea + (size_t)H * p.e16_stride;
-      for (int kt = 0; kt < n_tiles; ++kt) {
-        const int s = kt % STAGES;
-        if (kt >= STAGES) mbar_wait_backoff(&sm.empty[s], ((kt / STAGES) - 1) & 1);
+      for (int kt = kt0; kt < kt1; ++kt) {
+        const int it = kt - kt0, s = it % STAGES;
+        if (it >= STAGES) mbar_wait_backoff(&sm.empty[s], ((it / STAGES) - 1) & 1);
         const int j0 = kt * BKV;
         const int x0 = (j0 - i0 - (BQ - 1)) + (L - 1) + POS16_PADL;  // padded-table entry of window entry 0 (>= 1)
         const uint2* src_e = (x0 & 1) ? Eb + (x0 - 1) : Ea + x0;       // both sources start at an even entry:
@@ -555,12 +560,12 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(row0) << 16);
     // rows g + 8 (a = row0 / 8 + 1) sit at v = 56 - row0 / 2 + 4 nt + qd, rows g four columns further
     const uint32_t dcol = 56 - (row0 >> 1);
-    for (int kt = 0; kt < n_tiles; ++kt) {
-      const int st = kt % STAGES;
+    for (int kt = kt0; kt < kt1; ++kt) {
+      const int it = kt - kt0, st = it % STAGES;
       const bool mk = sflag[kt] != 0;
       // ---- scores: S + D_even / D_odd from TMEM, then the accumulators go back to the MMA warp
       float s[8][4];
-      mbar_wait(&sm.sfull, kt & 1);
+      mbar_wait(&sm.sfull, it & 1);
       tc_fence_after();
       {
         uint32_t r[32];
@@ -627,7 +632,7 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
       }
       // ---- P = exp2(S - m) (SOFT of every 4 on the FMA pipe, the rest on MUFU), O += P V  (V tile of this stage;
       //      its ones column carries the row sums)
-      mbar_wait(&sm.full[st], (kt / STAGES) & 1);  // complete long ago (the MMAs waited for it); orders the V reads
+      mbar_wait(&sm.full[st], (it / STAGES) & 1);  // complete long ago (the MMAs waited for it); orders the V reads
       const uint32_t vbase = smem_u32(&sm.v[st][0][0]);
 #pragma unroll
       for (int kk = 0; kk < BKV / 16; ++kk) {
@@ -647,27 +652,65 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.empty[st]);
     }
-    // ---- normalise, store: column dv = 12 of O (n-tile 1, columns 4..5 -> the lane with qd == 2) is the row sum
-    const float l0 = __shfl_sync(0xffffffffu, o[1][0], (lane & ~3) | 2);
-    const float l1 = __shfl_sync(0xffffffffu, o[1][2], (lane & ~3) | 2);
-    const float inv0 = 1.f / l0, inv1 = 1.f / l1;
     const int ia = i0 + rl0, ib = i0 + rl1;
-    const int vcol0 = head * p.dv;
+    if (ksplit > 1) {
+      // ---- key split: the unnormalised state of this key range (O incl. the row-sum column, reference maximum)
+      float* pa = p.part + ((((size_t)b * H + head) * ksplit + sp) * L) * 17;
 #pragma unroll
-    for (int n = 0; n < 2; ++n) {
-      const int col = n * 8 + 2 * qd;
-      if (col >= p.dv) continue;
-      if (ia < L)
-        *reinterpret_cast<uint32_t*>(p.out + ((size_t)b * L + ia) * p.ldo + vcol0 + col) =
-            pack_bf16x2(o[n][0] * inv0, o[n][1] * inv0);
-      if (ib < L)
-        *reinterpret_cast<uint32_t*>(p.out + ((size_t)b * L + ib) * p.ldo + vcol0 + col) =
-            pack_bf16x2(o[n][2] * inv1, o[n][3] * inv1);
+      for (int n = 0; n < 2; ++n) {
+        const int col = n * 8 + 2 * qd;
+        if (ia < L) pa[(size_t)ia * 17 + 1 + col] = o[n][0], pa[(size_t)ia * 17 + 2 + col] = o[n][1];
+        if (ib < L) pa[(size_t)ib * 17 + 1 + col] = o[n][2], pa[(size_t)ib * 17 + 2 + col] = o[n][3];
+      }
+      if (qd == 0) {
+        if (ia < L) pa[(size_t)ia * 17] = m0;
+        if (ib < L) pa[(size_t)ib * 17] = m1;
+      }
+    } else {
+      // ---- normalise, store: column dv = 12 of O (n-tile 1, columns 4..5 -> the lane with qd == 2) is the row sum
+      const float l0 = __shfl_sync(0xffffffffu, o[1][0], (lane & ~3) | 2);
+      const float l1 = __shfl_sync(0xffffffffu, o[1][2], (lane & ~3) | 2);
+      const float inv0 = 1.f / l0, inv1 = 1.f / l1;
+      const int vcol0 = head * p.dv;
+#pragma unroll
+      for (int n = 0; n < 2; ++n) {
+        const int col = n * 8 + 2 * qd;
+        if (col >= p.dv) continue;
+        if (ia < L)
+          *reinterpret_cast<uint32_t*>(p.out + ((size_t)b * L + ia) * p.ldo + vcol0 + col) =
+              pack_bf16x2(o[n][0] * inv0, o[n][1] * inv0);
+        if (ib < L)
+          *reinterpret_cast<uint32_t*>(p.out + ((size_t)b * L + ib) * p.ldo + vcol0 + col) =
+              pack_bf16x2(o[n][2] * inv1, o[n][3] * inv1);
+      }
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == MMA_WARP) tmem_dealloc(tmem_base, sa2::TM_COLS);
+}
+
+// Merge of the key-split partial states: one thread per (sequence, head, query row).
+__global__ void attn_sa_merge_kernel(const float* __restrict__ part, int nb, int H, int L, int ksplit, int dv,
+                                     __nv_bfloat16* __restrict__ out, int ldo) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)nb * H * L) return;
+  const int row = (int)(gid % L), head = (int)((gid / L) % H), b = (int)(gid / ((size_t)L * H));
+  const float* pa = part + (((size_t)b * H + head) * ksplit * L + row) * 17;
+  const size_t sstride = (size_t)L * 17;
+  float m = -INFINITY;
+  for (int s = 0; s < ksplit; ++s) m = fmaxf(m, pa[s * sstride]);
+  float acc[13];
+#pragma unroll
+  for (int c = 0; c < 13; ++c) acc[c] = 0.f;
+  for (int s = 0; s < ksplit; ++s) {
+    const float w = ex2_approx(pa[s * sstride] - m);
+#pragma unroll
+    for (int c = 0; c < 13; ++c) acc[c] += w * pa[s * sstride + 1 + c];
+  }
+  const float inv = 1.f / acc[12];  // column dv = 12 of the padded V is the constant 1: the softmax row sum
+  __nv_bfloat16* o = out + ((size_t)b * L + row) * ldo + head * dv;
+  for (int c = 0; c < dv; ++c) o[c] = __float2bfloat16(acc[c] * inv);
 }
 
 // Host launcher; returns -1 if the shape is not supported (caller falls back to attn_kernel).
@@ -702,9 +745,51 @@ int attention_sa_tma(const AttnParams& p, cudaStream_t s) {
   static const int sa_soft = getenv("ZV_SA_SOFT") ? atoi(getenv("ZV_SA_SOFT")) : 0;
   const int smem2 = (int)sizeof(sa2::Smem) + 1024 + n_tiles * BKV + ((n_tiles + 15) & ~15);
   if (sa_impl == 2 && p.E16 && smem2 <= 100 * 1024) {
-    if (sa_soft == 2) attn_sa2_kernel<2><<<grid, THREADS, smem2, s>>>(tmQK, tmV32, p);
-    else attn_sa2_kernel<0><<<grid, THREADS, smem2, s>>>(tmQK, tmV32, p);
-    return (int)cudaGetLastError();
+    // Key split for grids that leave SMs idle or end in a mostly empty wave.  Cost of a launch in key-tile times:
+    // waves x (key tiles per CTA + 4 for a CTA's prologue: mask copy, operand A, TMEM, Q load) + 2 for the partial
+    // stores and the merge kernel.  Large grids (B = 64) stay unsplit: halving a 5-tile CTA doubles its prologue share
+    // (measured: nb = 128, L = 305 0.052 -> 0.109 ms when split).
+    static int slots = 0;
+    if (!slots) {
+      int dev = 0, sms = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      slots = 2 * sms;
+    }
+    static const int ks_env = getenv("ZV_SA_KSPLIT") ? atoi(getenv("ZV_SA_KSPLIT")) : 0;
+    int ksplit = p.ksplit > 0 ? p.ksplit : ks_env;
+    const long long base = (long long)grid.x * grid.y * grid.z;
+    auto fits = [&](int k) {
+      const int per = (n_tiles + k - 1) / k;
+      return k == 1 || (p.part && per >= 2 && (long long)(k - 1) * per < n_tiles &&
+                        (size_t)p.nb * p.H * k * p.L * 17 * sizeof(float) <= p.part_cap);
+    };
+    if (ksplit <= 0) {
+      // automatic: long sequences only (every CTA keeps >= 8 key tiles: a single utterance of 8 s is a 15 us launch and
+      // the extra merge launch costs more than the split saves -- measured) and a predicted gain of >= 15 %
+      auto cost = [&](int k) {
+        return (double)((base * k + slots - 1) / slots) * ((n_tiles + k - 1) / k + 4) + (k > 1 ? 2 : 0);
+      };
+      double best = 0.85 * cost(1);
+      ksplit = 1;
+      for (int k = 2; k <= 8; ++k) {
+        if (!fits(k) || (n_tiles + k - 1) / k < 8) continue;
+        if (cost(k) < best - 1e-9) best = cost(k), ksplit = k;
+      }
+    } else if (!fits(ksplit)) {
+      ksplit = 1;
+    }
+    grid.x *= ksplit;
+    if (sa_soft == 2) attn_sa2_kernel<2><<<grid, THREADS, smem2, s>>>(tmQK, tmV32, p, ksplit);
+    else attn_sa2_kernel<0><<<grid, THREADS, smem2, s>>>(tmQK, tmV32, p, ksplit);
+    int lrc = (int)cudaGetLastError();
+    if (!lrc && ksplit > 1) {
+      const size_t n = (size_t)p.nb * p.H * p.L;
+      attn_sa_merge_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(p.part, p.nb, p.H, p.L, ksplit, p.dv, p.out,
+                                                                      p.ldo);
+      lrc = (int)cudaGetLastError();
+    }
+    return lrc;
   }
   attn_sa_kernel<<<grid, THREADS, smem, s>>>(tmQK, tmV, p);
   return (int)cudaGetLastError();

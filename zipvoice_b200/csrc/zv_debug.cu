@@ -1,6 +1,7 @@
 // Test hooks: run a single GEMM / attention / position-table kernel on fp32 inputs supplied by the
 // caller (converted to the bf16 operand layout here).  Used by tests/ only.
 #include <cuda_fp16.h>
+#include <algorithm>
 #include <vector>
 
 #include "zv_common.cuh"
@@ -106,6 +107,12 @@ __global__ void scale_f32_kernel(const float* __restrict__ in, size_t n, float s
   if (i < n) out[i] = in[i] * sc;
 }
 
+static int g_dbg_ksplit = 0;
+extern "C" int zv_debug_attention_ksplit(int ksplit) {
+  g_dbg_ksplit = ksplit;
+  return 0;
+}
+
 extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp_f32, int ldq,
                                   const float* E, const uint8_t* mask, const float* V_f32, int ldv,
                                   const float* gate_f32, float* out_f32, void* stream) {
@@ -143,6 +150,9 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
     cudaMalloc(&E16, (size_t)2 * H * pos_table_f16_stride(L) * 8);
     pos_table_f16(Es, H, L, E16, s);
     a.E16 = E16, a.e16_stride = pos_table_f16_stride(L);
+    a.part_cap = (size_t)nb * H * 8 * L * 17 * sizeof(float);
+    cudaMalloc(&a.part, a.part_cap);
+    a.ksplit = g_dbg_ksplit;
   }
   int rc = attention(a, s);
   if (!rc) {
@@ -152,6 +162,7 @@ extern "C" int zv_debug_attention(int nb, int L, int H, int heads, int dv, const
   cudaFree(q), cudaFree(v), cudaFree(o), cudaFree(Es);
   if (g) cudaFree(g);
   if (E16) cudaFree(E16);
+  if (a.part) cudaFree(a.part);
   return rc;
 }
 
@@ -197,6 +208,8 @@ extern "C" int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv,
     cudaMalloc(&E16, (size_t)2 * H * pos_table_f16_stride(L) * 8);
     pos_table_f16(E, H, L, E16, 0);
     a.E16 = E16, a.e16_stride = pos_table_f16_stride(L);
+    a.part_cap = std::min<size_t>((size_t)64 << 20, (size_t)nb * H * 8 * L * 17 * sizeof(float));
+    cudaMalloc(&a.part, a.part_cap);
   }
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0), cudaEventCreate(&e1);
@@ -211,6 +224,7 @@ extern "C" int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv,
   *ms_out = ms / (iters > 0 ? iters : 1);
   cudaEventDestroy(e0), cudaEventDestroy(e1);
   cudaFree(q), cudaFree(v), cudaFree(g), cudaFree(o), cudaFree(E), cudaFree(m), cudaFree(E16);
+  if (a.part) cudaFree(a.part);
   return rc;
 }
 

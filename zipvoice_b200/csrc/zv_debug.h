@@ -14,6 +14,8 @@ int zv_debug_attention(int nb, int L, int H, int heads, int dv, const float* qkp
                        const uint8_t* mask, const float* V_f32, int ldv, const float* gate_f32, float* out_f32,
                        void* stream);
 int zv_debug_set_attn_impl(int impl);
+/* force the key split of the SelfAttention kernel in zv_debug_attention (0 = let the launcher choose) */
+int zv_debug_attention_ksplit(int ksplit);
 int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv, int use_mask, int dbg, int iters, float* ms_out);
 int zv_debug_gemm_bench(int mode, int impl, int M, int N, int K, int L, int gate_cols, int block_n, int iters,
                         float* ms_out);

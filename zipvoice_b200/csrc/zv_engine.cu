@@ -3,6 +3,8 @@
 #include "zv_engine.h"
 
 #include <math.h>
+
+#include <algorithm>
 #include <stdio.h>
 #include <string.h>
 
@@ -461,6 +463,10 @@ int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
   // conv hidden state (D columns) + SelfAttention output (48 of the 64 extra columns; the rest stays zero)
   ZV_TRY(A((void**)&ws.conv_b, rows * (D + 64) * 2));
   ZV_TRY((int)cudaMemset(ws.conv_b, 0, rows * (D + 64) * 2));
+  // key split of the SelfAttention kernel: only small grids use it, so the buffer is capped (8 splits of every row
+  // of a small batch fit; the launcher falls back to fewer splits or none when they would not)
+  ws.sa_part_cap = std::min<size_t>((size_t)64 << 20, rows * net.H * 8 * 17 * sizeof(float));
+  ZV_TRY(A((void**)&ws.sa_part, ws.sa_part_cap));
   for (int i = 0; i < 3; ++i) ZV_TRY(A((void**)&ws.mask[i], rows));
   ZV_TRY(A((void**)&ws.t_dev, nb * 4));
   ZV_TRY(A((void**)&ws.ts_dev, 1025 * 4));
@@ -587,6 +593,7 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
     a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.sa_v, a.ldv = 16 * net.H, a.vhs = 16, a.gate = nullptr, a.ldg = 0;
     a.out = ws.conv_b + D, a.ldo = ldc, a.nb = nb, a.L = L, a.H = net.H, a.heads = net.H, a.dv = 12;
     a.E16 = Etab16, a.e16_stride = pos_table_f16_stride(L);
+    a.part = ws.sa_part, a.part_cap = ws.sa_part_cap;
     return run_attn(e, KC_ATTN_SELF, a, i == 0 ? net.H - 1 : 0, s);  // out_proj: folded into conv(i)
   };
   // SelfAttention(i).out_proj + time embedding + ConvolutionModule(i) with one pass over the fp32 stream

@@ -78,6 +78,8 @@ struct Workspace {
   __nv_bfloat16 *x_in = nullptr, *shadow = nullptr, *qkp = nullptr, *hidden = nullptr, *na_v = nullptr,
                 *na_y = nullptr, *na_o = nullptr, *sa_v = nullptr, *conv_a = nullptr,
                 *conv_b = nullptr;
+  float* sa_part = nullptr;   // key-split partial states of the SelfAttention kernel (AttnParams::part)
+  size_t sa_part_cap = 0;     // bytes
   uint8_t* mask[3] = {nullptr, nullptr, nullptr};  // per distinct downsampling rate (1, 2, 4)
   float *t_dev = nullptr, *ts_dev = nullptr /* time table of one sample(): 1025 floats */, *g_dev = nullptr, *te_a = nullptr, *te_out = nullptr, *guid_dev = nullptr;
   std::vector<void*> allocs;

@@ -64,6 +64,13 @@ struct AttnParams {
   const float* E;            // [H][2L-1][4], times log2(e)
   const void* E16 = nullptr; // pos_table_f16 of E (SelfAttention, tensor-core position term); null: CUDA-core kernel
   int e16_stride = 0;        // entries per head of E16
+  // Key split of the SelfAttention kernel for grids smaller than the machine (single utterances, the 60 s dialog):
+  // ksplit CTAs share a query tile, each takes a contiguous range of key tiles and writes its unnormalised state
+  // (16 fp32 columns of O -- column dv is the row sum -- and the row's reference maximum) to `part`; a merge
+  // kernel combines them.  part: [nb][H][ksplit][L][17] floats; 0 / null: chosen by the launcher from part_cap.
+  float* part = nullptr;
+  size_t part_cap = 0;       // bytes available at `part`
+  int ksplit = 0;            // 0: let the launcher choose; tests force a value
   const uint8_t* mask;       // [nb][L] 1 = padded key (may be null)
   const __nv_bfloat16* V;    // [nb][L][ldv]
   int ldv;
