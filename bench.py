@@ -257,7 +257,7 @@ def run_reference(args):
         ms_step, extra = dt * 1e3, {}
     else:
         probe = cpu_sample_time(c, nfe_timed=1, threads=threads, warm=1)
-        budget = 240.0
+        budget = 150.0
         n = int(max(1, min(c["nfe"], (budget / (K + min(W, 1)) - probe["t_text"] - probe["t_voc"]) / probe["t_nfe"])))
         steps = []
         for _ in range(min(W, 1) + K):
