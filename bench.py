@@ -303,6 +303,19 @@ def residual_bytes(model_cfg: dict, nb: int, T: int, nfe: int) -> float:
     return by * nfe
 
 
+def attention_exps(model_cfg: dict, nb: int, T: int, nfe: int):
+    """Softmax exponentials of one sample() call, the irreducible MUFU work of the attention kernels: per layer the two
+    SelfAttention launches exponentiate H x L x L scores per sequence, the NonlinAttention launch head 0's L x L."""
+    H = model_cfg["fm_decoder_num_heads"]
+    pairs = 0.0
+    for ds, nl in zip(model_cfg["fm_decoder_downsampling_factor"], model_cfg["fm_decoder_num_layers"]):
+        L = (T + ds - 1) // ds
+        pairs += nl * float(nb) * L * L
+    return {"attn_self": 2.0 * H * pairs * nfe, "attn_nonlin": pairs * nfe}
+
+
+MUFU_PER_CLK_PER_SM, NUM_SMS = 16.0, 148   # measured: tools/micro/mufu_f16_rate.cu (fp32, f16x2 and bf16x2 alike)
+
 TRAFFIC_PREFIX = {"gemm_residual": ["gemm_tc_kernel<4,"], "gemm_swooshl": ["gemm_tc_kernel<1,"],
                   "gemm_glu": ["gemm_tc_kernel<2,"], "gemm_nonlin": ["gemm_tc_kernel<3,"],
                   "gemm_gelu": ["gemm_tc_kernel<6,"], "attn_self": ["attn_sa_kernel"],
@@ -332,7 +345,7 @@ def ncu_traffic(kernel_class: str):
     return None, None
 
 
-def kernel_table(table, pk, res_bytes=None):
+def kernel_table(table, pk, res_bytes=None, exps=None, sm_mhz=None):
     tot_ms = sum(r["ms"] for r in table) or 1.0
     kernels = []
     for r in sorted(table, key=lambda r: -r["ms"]):
@@ -348,6 +361,13 @@ def kernel_table(table, pk, res_bytes=None):
             row["tensor_view"] = {"achieved": row["achieved"], "peak": peak, "unit": "TFLOP/s", "frac": row["frac"]}
             row.update({"bound": "hbm", "achieved": round(hb, 1), "unit": "GB/s", "frac": round(hb / pk["hbm"], 4),
                         "algorithmic_bytes_per_launch": round(res_bytes / max(1, r["launches"]))})
+        if exps and r["name"] in exps and r["ms"] > 0 and sm_mhz:
+            # the attention kernels do little tensor work by construction (dq = 32, dv = 12 / 384): what bounds them from
+            # below is the softmax exponential on the MUFU pipe, 16 results / clk / SM at the clock the step ran at
+            ach = exps[r["name"]] / (r["ms"] * 1e-3) / 1e9
+            peak = MUFU_PER_CLK_PER_SM * NUM_SMS * sm_mhz * 1e6 / 1e9
+            row["mufu_view"] = {"achieved": round(ach, 1), "peak": round(peak, 1), "unit": "Gexp/s",
+                                "frac": round(ach / peak, 4), "sm_mhz": sm_mhz}
         kernels.append(row)
     return kernels
 
@@ -566,7 +586,13 @@ def main():
     step_device()
     table = eng.prof_read()
     eng.prof_enable(False)
-    kernels = kernel_table(table, pk, res_bytes)
+    exps = attention_exps(cfg, nb, T, nfe) if c["kind"] != "audio" else None
+    clk = (clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz")
+    if world > 1:  # the clock sampler runs on rank 0 only
+        ct = torch.tensor([float(clk or 0.0)], device=dev)
+        dist.broadcast(ct, src=0)
+        clk = float(ct.item()) or None
+    kernels = kernel_table(table, pk, res_bytes, exps, clk)
     top = kernels[0]
     roofline = {"kernel": top["name"], "bound": top["bound"], "achieved": top["achieved"],
                 "peak": pk["tf_sustained"] if top["bound"] == "tensor" else pk["hbm"], "unit": top["unit"],
