@@ -366,3 +366,23 @@ def test_install_on_reference_shaped_modules():
     assert engg.dialog and type(refg.solver) is B200EulerSolver
     for e in (eng, engd, engg):
         e.close()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_second_engine_on_another_device_in_the_same_process():
+    """function attributes (the > 48 KB dynamic shared-memory opt-in) are per DEVICE.  A handle created on
+    cuda:1 after cuda:0 has run must launch the same kernels and return the same numbers."""
+    from zipvoice_b200 import synth
+    from zipvoice_b200.model import ZipVoiceB200
+    m0, cfg, sd = engine("zipvoice", "small", 1, True)
+    x0, text, speech, mask = case_inputs(2, 37, 11, seed=10)
+    v0 = m0.forward_fm_decoder(torch.tensor(0.3), x0, text, speech, mask).cpu()
+    m1 = ZipVoiceB200(cfg, sd, synth.VOCAB_SIZE, synth.PAD_ID, kind="zipvoice", device="cuda:1")
+    v1 = m1.forward_fm_decoder(torch.tensor(0.3), x0, text, speech, mask)
+    assert v1.device == torch.device("cuda:1")
+    assert torch.equal(v1.cpu(), v0)
+    x1 = m1.solver.sample(x=x0, text_condition=text, speech_condition=speech, padding_mask=mask, num_step=4,
+                          guidance_scale=1.0, t_shift=0.5).cpu()
+    assert valid_rel_l2(x1, _g("euler_small_stress.npz")["x1_cfg"], mask) < TOL_MEL
+    assert torch.equal(m0.forward_fm_decoder(torch.tensor(0.3), x0, text, speech, mask).cpu(), v0)
+    m1.engine.close()
