@@ -65,3 +65,19 @@ def test_gather_ragged_world2_gloo():
         p.join(120)
         assert p.exitcode == 0
     assert q.get(timeout=10) is True
+
+
+def test_gather_ragged_with_an_empty_shard_gloo():
+    """More ranks than utterances: one rank holds nothing and only takes part in the collectives (the empty-shard path of
+    infer.generate_batch); rank 0 still gets every row back in the original order."""
+    lengths = [9]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, lengths, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert q.get(timeout=10) is True
