@@ -292,14 +292,15 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------ GPU arm
 def residual_bytes(model_cfg: dict, nb: int, T: int, nfe: int) -> float:
     """Algorithmic HBM bytes of the residual-GEMM class for one sample() call: per output row the A operand (K bf16)
-    + fp32 stream read + fp32 stream write + bf16 shadow write = 2 K + 10 D (2 K + 8 D for the last feed-forward of a
-    layer, whose shadow nobody reads) -- DESIGN.md 3.1."""
+    + the residual stream read and written in its s24 storage format (bf16 hi plane + byte lo plane = 3 bytes per
+    element each way; the hi plane is the next GEMM's A operand, there is no separate bf16 copy) = 2 K + 6 D, plus
+    3 D for the layer input the second feed-forward's bypass reads -- DESIGN.md 3.1."""
     D, Fd = model_cfg["fm_decoder_dim"], model_cfg["fm_decoder_feedforward_dim"]
     ks = [Fd * 3 // 4, Fd, Fd * 5 // 4, 3 * D // 4, D + 64, D + 64]
     by = 0.0
     for ds, nl in zip(model_cfg["fm_decoder_downsampling_factor"], model_cfg["fm_decoder_num_layers"]):
         rows = nb * ((T + ds - 1) // ds)
-        by += nl * sum(rows * (kk * 2.0 + D * (8.0 if i == 2 else 10.0)) for i, kk in enumerate(ks))
+        by += nl * sum(rows * (kk * 2.0 + D * (9.0 if i == 1 else 6.0)) for i, kk in enumerate(ks))
     return by * nfe
 
 
@@ -316,7 +317,7 @@ def attention_exps(model_cfg: dict, nb: int, T: int, nfe: int):
 
 MUFU_PER_CLK_PER_SM, NUM_SMS = 16.0, 148   # measured: tools/micro/mufu_f16_rate.cu (fp32, f16x2 and bf16x2 alike)
 
-TRAFFIC_PREFIX = {"gemm_residual": ["gemm_tc_kernel<4,"], "gemm_swooshl": ["gemm_tc_kernel<1,"],
+TRAFFIC_PREFIX = {"gemm_residual": ["gemm_tc_kernel<7,", "gemm_tc_kernel<4,"], "gemm_swooshl": ["gemm_tc_kernel<1,"],
                   "gemm_glu": ["gemm_tc_kernel<2,"], "gemm_nonlin": ["gemm_tc_kernel<3,"],
                   "gemm_gelu": ["gemm_tc_kernel<6,"], "attn_self": ["attn_sa_kernel"],
                   "attn_nonlin": ["attn_na_tc_kernel"], "dwconv_swooshr": ["dwconv_kernel"],

@@ -9,6 +9,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 EPI_BIAS, EPI_SWOOSHL, EPI_GLU, EPI_NONLIN, EPI_RESIDUAL, EPI_F32 = range(6)
+EPI_RES24 = 8  # debug-hook number of the residual epilogue on the s24 stream (hi bf16 plane + lo byte plane)
 
 
 def _lib():
@@ -42,7 +43,7 @@ def ref_gemm(mode, A, W, bias, L=1, gate_cols=0, rowbias=None, res=None, resbias
     M = A.shape[0]
     acc = A.bfloat16().float() @ W.bfloat16().float().T + bias
     b = torch.arange(M, device="cuda") // L
-    if rowbias is not None and mode != EPI_RESIDUAL:
+    if rowbias is not None and mode not in (EPI_RESIDUAL, EPI_RES24):
         acc = acc + rowbias[b]
     if mode == EPI_BIAS or mode == EPI_F32:
         return acc, None
@@ -57,8 +58,8 @@ def ref_gemm(mode, A, W, bias, L=1, gate_cols=0, rowbias=None, res=None, resbias
     if mode == EPI_NONLIN:
         g = acc[:, :gate_cols].reshape(M, -1, 2, 16)
         return (g[:, :, 1] * torch.tanh(g[:, :, 0])).reshape(M, -1), acc[:, gate_cols:]
-    if mode == EPI_RESIDUAL:
-        v = acc + res
+    if mode in (EPI_RESIDUAL, EPI_RES24):
+        v = acc + res if res is not None else acc
         if resbias is not None:
             v = v + resbias[b]
         if orig is not None:
@@ -97,6 +98,14 @@ CASES = [
     # the quarter-rate residual shape of the bench, 610 tiles -> 18 leftover tiles in 4 slices
     (EPI_SWOOSHL, 3823, 1152, 512, {"rowbias": True, "L": 1000}),
     (EPI_RESIDUAL, 39040, 512, 576, {"resbias": True, "L": 305}),
+    # the same residual epilogue on the s24 stream planes (the Zipformer layers); "nores": stack in_proj, no input
+    (EPI_RES24, 900, 512, 1536, {"resbias": True, "orig": True, "L": 300}),
+    (EPI_RES24, 333, 512, 48, {}),
+    (EPI_RES24, 129, 192, 640, {}),
+    (EPI_RES24, 300, 512, 320, {"nores": True}),
+    (EPI_RES24, 20000, 512, 384, {"resbias": True, "L": 1219}),
+    (EPI_RES24, 38300, 512, 1920, {"orig": True}),
+    (EPI_RES24, 39040, 512, 576, {"resbias": True, "L": 305}),
 ]
 
 
@@ -114,8 +123,8 @@ def test_gemm(case, impl):
     kw = dict(L=L, gate_cols=ex.get("gate_cols", 0))
     if ex.get("rowbias"):
         kw["rowbias"] = rn(nb, N)
-    if mode == EPI_RESIDUAL:
-        kw["res"] = rn(M, N)
+    if mode in (EPI_RESIDUAL, EPI_RES24):
+        kw["res"] = None if ex.get("nores") else rn(M, N)
         if ex.get("resbias"):
             kw["resbias"] = rn(nb, N)
         if ex.get("orig"):
@@ -124,11 +133,12 @@ def test_gemm(case, impl):
         kw["mask"] = (torch.rand(nb * L, device="cuda", generator=g) < 0.3).to(torch.uint8)[: nb * L].contiguous()
     out, out2 = run_gemm(mode, impl, A, W, bias, **kw)
     want, want2 = ref_gemm(mode, A, W, bias, **kw)
-    tol = 2e-5 if mode in (EPI_F32, EPI_RESIDUAL) else 6e-3  # bf16 outputs: 2^-9 rounding
+    # bf16 outputs: 2^-9 rounding; s24: 16 significant bits (2^-17 per value, on the residual input and the output)
+    tol = 2e-5 if mode in (EPI_F32, EPI_RESIDUAL, EPI_RES24) else 6e-3
     assert rel(out, want) < tol, f"rel-L2 {rel(out, want):.3e} max-abs {float((out - want).abs().max()):.3e}"
     if mode == EPI_NONLIN:
         assert rel(out2, want2) < 6e-3, f"out2 rel-L2 {rel(out2, want2):.3e}"
-    if mode == EPI_RESIDUAL:
+    if mode in (EPI_RESIDUAL, EPI_RES24):
         assert rel(out2, want2) < 6e-3, f"bf16 shadow rel-L2 {rel(out2, want2):.3e}"
 
 

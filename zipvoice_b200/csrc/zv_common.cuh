@@ -64,6 +64,43 @@ ZV_DEVINL __half f2h_sat(float x) {
 ZV_DEVINL float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 ZV_DEVINL float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 
+// ------------------------------------------------------------------ s24: the residual stream's storage format
+// The residual stream of a Zipformer stack is an fp32 quantity that every module reads and rewrites.  It is kept in
+// HBM as TWO planes of the same [rows][D] shape: `hi`, the value rounded to bf16 -- which is also the A operand of the
+// next in_proj GEMM, so no separate bf16 copy of the stream exists -- and `lo`, one more byte of mantissa.  3 bytes per
+// element instead of 4 (fp32) + 2 (bf16 copy); 16 significant bits (relative rounding error 2^-17 per rewrite, against
+// 2^-9 for the bf16 operands of the GEMMs that produce the increments).
+//   w  = bits(v) + 0x8080        (round the magnitude to 24 bits, half up, and pre-add half a bf16 ulp)
+//   hi = w >> 16                 (bf16 of v, rounded half up)
+//   lo = (w >> 8) & 0xff         (biased: the rounding of hi is undone by the - 0x8000 below)
+//   v' = bits^-1(((hi << 16) | (lo << 8)) - 0x8000)  =  v rounded to 24 bits
+ZV_DEVINL uint32_t s24_w(float v) { return __float_as_uint(v) + 0x8080u; }
+ZV_DEVINL float s24_dec(uint32_t hi16, uint32_t lo8) {
+  return __uint_as_float(((hi16 << 16) | (lo8 << 8)) - 0x8000u);
+}
+// 8 consecutive elements: hi = 8 bf16 (16 bytes), lo = 8 bytes
+ZV_DEVINL void s24_dec8(const uint4& hi, const uint2& lo, float (&v)[8]) {
+  const uint32_t h[4] = {hi.x, hi.y, hi.z, hi.w};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t lw = k < 2 ? lo.x : lo.y;
+    // bytes [x, lo(2k), h.b0, h.b1] and [x, lo(2k+1), h.b2, h.b3]; byte 0 is cleared by the mask
+    const uint32_t e = __byte_perm(h[k], lw, 0x1040u | (((2 * k) & 3) << 4));
+    const uint32_t o = __byte_perm(h[k], lw, 0x3240u | (((2 * k + 1) & 3) << 4));
+    v[2 * k] = __uint_as_float((e & 0xffffff00u) - 0x8000u);
+    v[2 * k + 1] = __uint_as_float((o & 0xffffff00u) - 0x8000u);
+  }
+}
+ZV_DEVINL void s24_enc8(const float (&v)[8], uint4& hi, uint2& lo) {
+  uint32_t w[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) w[i] = s24_w(v[i]);
+  hi.x = __byte_perm(w[0], w[1], 0x7632u), hi.y = __byte_perm(w[2], w[3], 0x7632u);
+  hi.z = __byte_perm(w[4], w[5], 0x7632u), hi.w = __byte_perm(w[6], w[7], 0x7632u);
+  lo.x = __byte_perm(__byte_perm(w[0], w[1], 0x0051u), __byte_perm(w[2], w[3], 0x0051u), 0x5410u);
+  lo.y = __byte_perm(__byte_perm(w[4], w[5], 0x0051u), __byte_perm(w[6], w[7], 0x0051u), 0x5410u);
+}
+
 ZV_DEVINL float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

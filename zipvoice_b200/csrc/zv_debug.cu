@@ -34,6 +34,19 @@ __global__ void cvt_back_f16_kernel(const __half* __restrict__ in, size_t n, flo
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = __half2float(in[i]);
 }
+// fp32 <-> the s24 storage format of the residual stream (zv_common.cuh)
+__global__ void f32_to_s24_kernel(const float* __restrict__ in, size_t n, uint16_t* __restrict__ hi,
+                                  uint8_t* __restrict__ lo) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t w = s24_w(in[i]);
+  hi[i] = (uint16_t)(w >> 16), lo[i] = (uint8_t)(w >> 8);
+}
+__global__ void s24_to_f32_kernel(const uint16_t* __restrict__ hi, const uint8_t* __restrict__ lo, size_t n,
+                                  float* __restrict__ out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = s24_dec(hi[i], lo[i]);
+}
 static void cvt_back(const __nv_bfloat16* in, size_t n, float* out, cudaStream_t s) {
   cvt_back_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, n, out);
 }
@@ -45,6 +58,10 @@ extern "C" int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int
   cudaStream_t s = (cudaStream_t)stream;
   const bool f16 = mode == 7;  // EPI_BIAS_BF16 storing IEEE fp16 (the attention q | k | p projection)
   if (f16) mode = EPI_BIAS_BF16;
+  // 8: EPI_RES24 -- res / orig are converted to the s24 planes here, the result is decoded into out_f32 and the
+  // hi plane alone into out2_f32; res == nullptr: no residual input (the stack in_proj)
+  const bool s24 = mode == 8;
+  if (s24) mode = EPI_RES24;
   const int block_n = gemm_pick_block_n(N, mode, gate_cols);
   const int N_pad = (N + block_n - 1) / block_n * block_n;
   const int ld = (K + 63) / 64 * 64;
@@ -57,6 +74,20 @@ extern "C" int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int
   cudaMalloc(&ob, (size_t)M * (n_out + 8) * 2);
   cudaMalloc(&ob2, (size_t)M * (n_out2 + 8) * 2);
   cudaMalloc(&of, (size_t)M * N * 4);
+  uint16_t *res_hi = nullptr, *orig_hi = nullptr;
+  uint8_t *res_lo = nullptr, *orig_lo = nullptr, *out_lo = nullptr;
+  const size_t mn = (size_t)M * N;
+  if (s24) {
+    cudaMalloc(&out_lo, mn);
+    if (res) {
+      cudaMalloc(&res_hi, mn * 2), cudaMalloc(&res_lo, mn);
+      f32_to_s24_kernel<<<(unsigned)((mn + 255) / 256), 256, 0, s>>>(res, mn, res_hi, res_lo);
+    }
+    if (orig) {
+      cudaMalloc(&orig_hi, mn * 2), cudaMalloc(&orig_lo, mn);
+      f32_to_s24_kernel<<<(unsigned)((mn + 255) / 256), 256, 0, s>>>(orig, mn, orig_hi, orig_lo);
+    }
+  }
   cudaMemsetAsync(W, 0, (size_t)N_pad * ld * 2, s);
   cvt_pad(A_f32, M, K, K, A, ld, s);
   cvt_pad(W_f32, N, K, K, W, ld, s);
@@ -69,9 +100,18 @@ extern "C" int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int
   ep.mask = mask;
   ep.out_f16 = f16 ? 1 : 0;
   if (mode == EPI_F32) ep.out_bf16 = nullptr;
+  if (s24) {
+    ep.res = ep.orig = nullptr, ep.out_f32 = nullptr;
+    ep.res_hi = reinterpret_cast<const __nv_bfloat16*>(res_hi), ep.res_lo = res_lo;
+    ep.orig_hi = reinterpret_cast<const __nv_bfloat16*>(orig_hi), ep.orig_lo = orig_lo, ep.out_lo = out_lo;
+  }
   int rc = gemm_launch(A, W, p, ep, impl, s);
   if (!rc) {
-    if (mode == EPI_RESIDUAL || mode == EPI_F32) {
+    if (s24) {
+      s24_to_f32_kernel<<<(unsigned)((mn + 255) / 256), 256, 0, s>>>(reinterpret_cast<const uint16_t*>(ob), out_lo, mn,
+                                                                    out_f32);
+      if (out2_f32) cvt_back(ob, mn, out2_f32, s);
+    } else if (mode == EPI_RESIDUAL || mode == EPI_F32) {
       cudaMemcpyAsync(out_f32, of, (size_t)M * N * 4, cudaMemcpyDeviceToDevice, s);
       if (mode == EPI_RESIDUAL && out2_f32) cvt_back(ob, (size_t)M * N, out2_f32, s);
     } else if (f16) {
@@ -84,6 +124,7 @@ extern "C" int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int
     rc = (int)cudaStreamSynchronize(s);
   }
   cudaFree(A), cudaFree(W), cudaFree(ob), cudaFree(ob2), cudaFree(of);
+  cudaFree(res_hi), cudaFree(res_lo), cudaFree(orig_hi), cudaFree(orig_lo), cudaFree(out_lo);
   return rc;
 }
 
@@ -232,6 +273,8 @@ extern "C" int zv_debug_attention_bench(int nb, int L, int H, int heads, int dv,
 // block_n <= 0 picks the production tile width.  Returns mean milliseconds per launch.
 extern "C" int zv_debug_gemm_bench(int mode, int impl, int M, int N, int K, int L, int gate_cols, int block_n,
                                    int iters, float* ms_out) {
+  const bool s24 = mode == 8;  // EPI_RES24 updating its stream in place, like the layer's residual GEMMs
+  if (s24) mode = EPI_RES24;
   if (block_n <= 0) block_n = gemm_pick_block_n(N, mode, gate_cols);
   const int N_pad = (N + block_n - 1) / block_n * block_n;
   const int ld = (K + 63) / 64 * 64;
@@ -249,10 +292,15 @@ extern "C" int zv_debug_gemm_bench(int mode, int impl, int M, int N, int K, int 
   p.M = M, p.N_pad = N_pad, p.K = K, p.lda = ld, p.ldw = ld, p.block_n = block_n;
   EpiParams ep;
   ep.mode = mode, ep.M = M, ep.N = N, ep.L = L, ep.gate_cols = gate_cols, ep.bias = bias;
-  ep.rowbias = (mode == EPI_SWOOSHL_BF16) ? rowb : nullptr, ep.resbias = (mode == EPI_RESIDUAL) ? rowb : nullptr;
+  ep.rowbias = (mode == EPI_SWOOSHL_BF16) ? rowb : nullptr;
+  ep.resbias = (mode == EPI_RESIDUAL || mode == EPI_RES24) ? rowb : nullptr;
   ep.bias_ld = N_pad, ep.out_bf16 = ob, ep.ld_bf16 = (n_out + 7) / 8 * 8, ep.out2_bf16 = ob2, ep.ld2_bf16 = (n_out2 + 7) / 8 * 8;
   ep.out_f32 = of, ep.ld_f32 = N, ep.res = of;
   if (mode == EPI_F32) ep.out_bf16 = nullptr;
+  if (s24) {  // hi plane = ob (pitch N), lo plane inside the fp32 scratch
+    ep.res = nullptr, ep.ld_bf16 = N;
+    ep.res_hi = ob, ep.out_lo = reinterpret_cast<uint8_t*>(of), ep.res_lo = ep.out_lo;
+  }
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0), cudaEventCreate(&e1);
   int rc = gemm_launch(A, W, p, ep, impl, 0);

@@ -222,78 +222,99 @@ int dwconv_swooshr(const bf16* in, const float* w, const float* bias, int nb, in
 }
 
 // ------------------------------------------------------------------ BiasNorm + bypass (one warp per row)
-__global__ void biasnorm_bypass_kernel(const float* __restrict__ src, const float* __restrict__ orig,
-                                       const float* __restrict__ nbias, float scale_exp,
-                                       const float* __restrict__ bscale, int M, int D, float* __restrict__ out,
-                                       bf16* __restrict__ out_bf16) {
+// All three kernels below read and write the residual stream in its s24 storage format (zv_common.cuh): a bf16 `hi`
+// plane and a byte `lo` plane per tensor, 8 elements (16 + 8 bytes) per thread and access.
+struct S24Ld {
+  const bf16* hi;
+  const uint8_t* lo;
+  ZV_DEVINL void load8(size_t off, float (&v)[8]) const {
+    s24_dec8(*reinterpret_cast<const uint4*>(hi + off), *reinterpret_cast<const uint2*>(lo + off), v);
+  }
+};
+ZV_DEVINL void s24_store8(bf16* hi, uint8_t* lo, size_t off, const float (&v)[8]) {
+  uint4 h;
+  uint2 l;
+  s24_enc8(v, h, l);
+  *reinterpret_cast<uint4*>(hi + off) = h;
+  *reinterpret_cast<uint2*>(lo + off) = l;
+}
+
+__global__ void biasnorm_bypass_kernel(S24Ld src, S24Ld orig, const float* __restrict__ nbias, float scale_exp,
+                                       const float* __restrict__ bscale, int M, int D, bf16* __restrict__ out_hi,
+                                       uint8_t* __restrict__ out_lo) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= M) return;
-  const float* s = src + (size_t)row * D;
-  const float* o = orig + (size_t)row * D;
-  float4 v[4];  // up to D = 512: 4 float4 per lane
+  const size_t base = (size_t)row * D;
+  float v[2][8];  // up to D = 512: two groups of 8 per lane
   float ss = 0.f;
-  const int nvec = D >> 7;  // float4 groups per lane (D multiple of 128... handled below for 192)
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int col = (i * 32 + lane) * 4;
+  for (int i = 0; i < 2; ++i) {
+    const int col = (i * 32 + lane) * 8;
     if (col < D) {
-      v[i] = *reinterpret_cast<const float4*>(s + col);
-      const float4 nb = *reinterpret_cast<const float4*>(nbias + col);
-      const float d0 = v[i].x - nb.x, d1 = v[i].y - nb.y, d2 = v[i].z - nb.z, d3 = v[i].w - nb.w;
-      ss += d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
+      src.load8(base + col, v[i]);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const float4 nb = *reinterpret_cast<const float4*>(nbias + col + 4 * h);
+        const float d0 = v[i][4 * h] - nb.x, d1 = v[i][4 * h + 1] - nb.y, d2 = v[i][4 * h + 2] - nb.z,
+                    d3 = v[i][4 * h + 3] - nb.w;
+        ss += d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
+      }
     }
   }
-  (void)nvec;
   ss = warp_sum(ss);
   const float sc = rsqrtf(ss / (float)D) * scale_exp;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int col = (i * 32 + lane) * 4;
+  for (int i = 0; i < 2; ++i) {
+    const int col = (i * 32 + lane) * 8;
     if (col < D) {
-      const float4 og = *reinterpret_cast<const float4*>(o + col);
-      const float4 bs = *reinterpret_cast<const float4*>(bscale + col);
-      float4 r;
-      r.x = og.x + (v[i].x * sc - og.x) * bs.x;
-      r.y = og.y + (v[i].y * sc - og.y) * bs.y;
-      r.z = og.z + (v[i].z * sc - og.z) * bs.z;
-      r.w = og.w + (v[i].w * sc - og.w) * bs.w;
-      *reinterpret_cast<float4*>(out + (size_t)row * D + col) = r;
-      *reinterpret_cast<uint2*>(out_bf16 + (size_t)row * D + col) =
-          make_uint2(pack_bf16x2(r.x, r.y), pack_bf16x2(r.z, r.w));
+      float og[8], r[8];
+      orig.load8(base + col, og);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const float4 bs = *reinterpret_cast<const float4*>(bscale + col + 4 * h);
+        r[4 * h] = og[4 * h] + (v[i][4 * h] * sc - og[4 * h]) * bs.x;
+        r[4 * h + 1] = og[4 * h + 1] + (v[i][4 * h + 1] * sc - og[4 * h + 1]) * bs.y;
+        r[4 * h + 2] = og[4 * h + 2] + (v[i][4 * h + 2] * sc - og[4 * h + 2]) * bs.z;
+        r[4 * h + 3] = og[4 * h + 3] + (v[i][4 * h + 3] * sc - og[4 * h + 3]) * bs.w;
+      }
+      s24_store8(out_hi, out_lo, base + col, r);
     }
   }
 }
 
-int biasnorm_bypass(const float* src, const float* orig, const float* nbias, float log_scale, const float* bscale,
-                    int M, int D, float* out, bf16* out_bf16, cudaStream_t s) {
-  if (D > 512 || (D & 3)) return 911;
+int biasnorm_bypass(const bf16* src_hi, const uint8_t* src_lo, const bf16* orig_hi, const uint8_t* orig_lo,
+                    const float* nbias, float log_scale, const float* bscale, int M, int D, bf16* out_hi,
+                    uint8_t* out_lo, cudaStream_t s) {
+  if (D > 512 || (D & 7)) return 911;
   const int warps = 8;
-  biasnorm_bypass_kernel<<<(M + warps - 1) / warps, warps * 32, 0, s>>>(src, orig, nbias, expf(log_scale), bscale, M,
-                                                                        D, out, out_bf16);
+  biasnorm_bypass_kernel<<<(M + warps - 1) / warps, warps * 32, 0, s>>>(
+      S24Ld{src_hi, src_lo}, S24Ld{orig_hi, orig_lo}, nbias, expf(log_scale), bscale, M, D, out_hi, out_lo);
   return (int)cudaGetLastError();
 }
 
 // ------------------------------------------------------------------ SimpleDownsample / SimpleUpsample
-__global__ void downsample_kernel(const float* __restrict__ src, float4 w, int L, int L2, int D, int ds,
-                                  float* __restrict__ out, bf16* __restrict__ out_bf16, size_t total4) {
+__global__ void downsample_kernel(S24Ld src, float4 w, int L, int L2, int D, int ds, bf16* __restrict__ out_hi,
+                                  uint8_t* __restrict__ out_lo, size_t total8) {
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= total4) return;
-  const int d4 = D >> 2;
-  const int c = (int)(gid % d4) * 4;
-  const size_t row = gid / d4;  // b * L2 + j
+  if (gid >= total8) return;
+  const int d8 = D >> 3;
+  const int c = (int)(gid % d8) * 8;
+  const size_t row = gid / d8;  // b * L2 + j
   const int j = (int)(row % L2);
   const int b = (int)(row / L2);
   const float ws[4] = {w.x, w.y, w.z, w.w};
-  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
   for (int k = 0; k < ds; ++k) {
     const int t = min(j * ds + k, L - 1);
-    const float4 v = *reinterpret_cast<const float4*>(src + ((size_t)b * L + t) * D + c);
-    acc.x += v.x * ws[k], acc.y += v.y * ws[k], acc.z += v.z * ws[k], acc.w += v.w * ws[k];
+    float v[8];
+    src.load8(((size_t)b * L + t) * D + c, v);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] += v[i] * ws[k];
   }
-  *reinterpret_cast<float4*>(out + row * D + c) = acc;
-  *reinterpret_cast<uint2*>(out_bf16 + row * D + c) =
-      make_uint2(pack_bf16x2(acc.x, acc.y), pack_bf16x2(acc.z, acc.w));
+  s24_store8(out_hi, out_lo, row * D + c, acc);
 }
 __global__ void mask_subsample_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int nb, int L, int L2,
                                       int ds) {
@@ -303,41 +324,47 @@ __global__ void mask_subsample_kernel(const uint8_t* __restrict__ in, uint8_t* _
   out[gid] = in[(size_t)b * L + j * ds];  // padding_mask[..., ::ds] (zipformer.py:857-858)
 }
 
-int downsample(const float* src, const float* w, int nb, int L, int D, int ds, float* out, bf16* out_bf16,
-               uint8_t* mask_out, const uint8_t* mask_in, cudaStream_t s) {
-  if (ds > 4 || (D & 3)) return 912;
+int downsample(const bf16* src_hi, const uint8_t* src_lo, const float* w, int nb, int L, int D, int ds, bf16* out_hi,
+               uint8_t* out_lo, uint8_t* mask_out, const uint8_t* mask_in, cudaStream_t s) {
+  if (ds > 4 || (D & 7)) return 912;
   const int L2 = (L + ds - 1) / ds;
   float4 wv = make_float4(w[0], ds > 1 ? w[1] : 0.f, ds > 2 ? w[2] : 0.f, ds > 3 ? w[3] : 0.f);
-  const size_t total4 = (size_t)nb * L2 * (D >> 2);
-  downsample_kernel<<<blocks_for(total4, 256), 256, 0, s>>>(src, wv, L, L2, D, ds, out, out_bf16, total4);
+  const size_t total8 = (size_t)nb * L2 * (D >> 3);
+  downsample_kernel<<<blocks_for(total8, 256), 256, 0, s>>>(S24Ld{src_hi, src_lo}, wv, L, L2, D, ds, out_hi, out_lo,
+                                                            total8);
   if (mask_out) mask_subsample_kernel<<<blocks_for((size_t)nb * L2, 256), 256, 0, s>>>(mask_in, mask_out, nb, L, L2, ds);
   return (int)cudaGetLastError();
 }
 
-__global__ void upsample_combine_kernel(float* __restrict__ orig, const float* __restrict__ y,
-                                        const float* __restrict__ bscale, int L, int L2, int D, int ds,
-                                        bf16* __restrict__ out_bf16, size_t total4) {
+__global__ void upsample_combine_kernel(bf16* __restrict__ orig_hi, uint8_t* __restrict__ orig_lo, S24Ld y,
+                                        const float* __restrict__ bscale, int L, int L2, int D, int ds, size_t total8) {
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= total4) return;
-  const int d4 = D >> 2;
-  const int c = (int)(gid % d4) * 4;
-  const size_t row = gid / d4;  // b * L + t
+  if (gid >= total8) return;
+  const int d8 = D >> 3;
+  const int c = (int)(gid % d8) * 8;
+  const size_t row = gid / d8;  // b * L + t
   const int t = (int)(row % L);
   const int b = (int)(row / L);
-  const float4 o = *reinterpret_cast<const float4*>(orig + row * D + c);
-  const float4 v = *reinterpret_cast<const float4*>(y + ((size_t)b * L2 + t / ds) * D + c);
-  const float4 sc = *reinterpret_cast<const float4*>(bscale + c);
-  float4 r;
-  r.x = o.x + (v.x - o.x) * sc.x, r.y = o.y + (v.y - o.y) * sc.y;
-  r.z = o.z + (v.z - o.z) * sc.z, r.w = o.w + (v.w - o.w) * sc.w;
-  *reinterpret_cast<float4*>(orig + row * D + c) = r;
-  *reinterpret_cast<uint2*>(out_bf16 + row * D + c) = make_uint2(pack_bf16x2(r.x, r.y), pack_bf16x2(r.z, r.w));
+  float o[8], v[8], r[8];
+  S24Ld{orig_hi, orig_lo}.load8(row * D + c, o);
+  y.load8(((size_t)b * L2 + t / ds) * D + c, v);
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const float4 sc = *reinterpret_cast<const float4*>(bscale + c + 4 * h);
+    r[4 * h] = o[4 * h] + (v[4 * h] - o[4 * h]) * sc.x;
+    r[4 * h + 1] = o[4 * h + 1] + (v[4 * h + 1] - o[4 * h + 1]) * sc.y;
+    r[4 * h + 2] = o[4 * h + 2] + (v[4 * h + 2] - o[4 * h + 2]) * sc.z;
+    r[4 * h + 3] = o[4 * h + 3] + (v[4 * h + 3] - o[4 * h + 3]) * sc.w;
+  }
+  s24_store8(orig_hi, orig_lo, row * D + c, r);
 }
 
-int upsample_combine(float* orig, const float* y, const float* bscale, int nb, int L, int L2, int D, int ds,
-                     bf16* out_bf16, cudaStream_t s) {
-  const size_t total4 = (size_t)nb * L * (D >> 2);
-  upsample_combine_kernel<<<blocks_for(total4, 256), 256, 0, s>>>(orig, y, bscale, L, L2, D, ds, out_bf16, total4);
+int upsample_combine(bf16* orig_hi, uint8_t* orig_lo, const bf16* y_hi, const uint8_t* y_lo, const float* bscale,
+                     int nb, int L, int L2, int D, int ds, cudaStream_t s) {
+  if (D & 7) return 912;
+  const size_t total8 = (size_t)nb * L * (D >> 3);
+  upsample_combine_kernel<<<blocks_for(total8, 256), 256, 0, s>>>(orig_hi, orig_lo, S24Ld{y_hi, y_lo}, bscale, L, L2, D,
+                                                                  ds, total8);
   return (int)cudaGetLastError();
 }
 

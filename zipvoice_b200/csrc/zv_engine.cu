@@ -206,7 +206,7 @@ static int fold_self_attn_into_conv(Engine& e, const std::string& so, const std:
   }
   ZV_TRY(pack_linear_host(e, wi.data(), bi.data(), N2, Ke, EPI_GLU_BF16, conv_in, D + 64, nullptr));
   conv_in->K_valid = D;  // algorithmic FLOPs of the reference in_proj; the folded 48 columns are counted below
-  ZV_TRY(pack_linear_host(e, wo.data(), bo.data(), D, Ke, EPI_RESIDUAL, conv_out, D + 64, nullptr));
+  ZV_TRY(pack_linear_host(e, wo.data(), bo.data(), D, Ke, EPI_RES24, conv_out, D + 64, nullptr));
   return 0;
 }
 
@@ -233,10 +233,10 @@ static int build_layer(Engine& e, Net& net, const std::string& p, int kernel, La
   for (int i = 0; i < 3; ++i) {
     const std::string f = p + ".feed_forward" + std::to_string(i + 1);
     ZV_TRY(pack_linear(e, f + ".in_proj", EPI_SWOOSHL_BF16, &L->ff_in[i]));
-    ZV_TRY(pack_linear(e, f + ".out_proj", EPI_RESIDUAL, &L->ff_out[i]));
+    ZV_TRY(pack_linear(e, f + ".out_proj", EPI_RES24, &L->ff_out[i]));
   }
   ZV_TRY(pack_linear(e, p + ".nonlin_attention.in_proj", EPI_NONLIN_BF16, &L->na_in));
-  ZV_TRY(pack_linear(e, p + ".nonlin_attention.out_proj", EPI_RESIDUAL, &L->na_out));
+  ZV_TRY(pack_linear(e, p + ".nonlin_attention.out_proj", EPI_RES24, &L->na_out));
   for (int i = 0; i < 2; ++i) {
     const std::string a = p + ".self_attn" + std::to_string(i + 1);
     {  // value projection padded to 16 columns per head (12 + 4 zero rows): 16-byte aligned TMA boxes per head
@@ -294,7 +294,7 @@ static int build_net(Engine& e, Net& net, const std::string& prefix, int in_dim,
   // TTSZipformerTwoStream keeps two projection pairs in ModuleLists; inference of the stereo dialog model
   // goes through the first one (zipformer_two_stream.py:240-263, x.size(2) == in_dim[0])
   const std::string pj = two_stream ? ".0" : "";
-  ZV_TRY(pack_linear(e, prefix + ".in_proj" + pj, EPI_F32, &net.in_proj, net.in_pad));
+  ZV_TRY(pack_linear(e, prefix + ".in_proj" + pj, EPI_RES24, &net.in_proj, net.in_pad));
   ZV_TRY(pack_linear(e, prefix + ".out_proj" + pj, EPI_F32, &net.out_proj));
   net.in_pad_max = net.in_pad, net.out_dim_max = net.out_dim;
   net.two_stream = two_stream;
@@ -302,7 +302,7 @@ static int build_net(Engine& e, Net& net, const std::string& prefix, int in_dim,
     // the mono pair: in_proj.1 (3 feat_dim -> D), out_proj.1 (D -> feat_dim)
     net.alt_in_dim = 3 * c.feat_dim, net.alt_out_dim = c.feat_dim;
     net.alt_in_pad = (net.alt_in_dim + 63) / 64 * 64;
-    ZV_TRY(pack_linear(e, prefix + ".in_proj.1", EPI_F32, &net.alt_in_proj, net.alt_in_pad));
+    ZV_TRY(pack_linear(e, prefix + ".in_proj.1", EPI_RES24, &net.alt_in_proj, net.alt_in_pad));
     ZV_TRY(pack_linear(e, prefix + ".out_proj.1", EPI_F32, &net.alt_out_proj));
     if (net.alt_in_pad > net.in_pad_max) net.in_pad_max = net.alt_in_pad;
     if (net.alt_out_dim > net.out_dim_max) net.out_dim_max = net.alt_out_dim;
@@ -446,13 +446,15 @@ int ws_reserve(Engine& e, Net& net, Workspace& ws, int nb, int T) {
   const size_t Fmax = (size_t)net.F * 5 / 4;
   const size_t td = e.cfg.time_embed_dim;
   auto A = [&](void** p, size_t bytes) { return dev_alloc(e, ws.allocs, p, bytes); };
-  ZV_TRY(A((void**)&ws.X, rows * D * 4));
-  ZV_TRY(A((void**)&ws.Xs, rows * D * 4));
-  ZV_TRY(A((void**)&ws.Y, rows * D * 4));
+  ZV_TRY(A((void**)&ws.X_hi, rows * D * 2));
+  ZV_TRY(A((void**)&ws.Xs_hi, rows * D * 2));
+  ZV_TRY(A((void**)&ws.Y_hi, rows * D * 2));
+  ZV_TRY(A((void**)&ws.X_lo, rows * D));
+  ZV_TRY(A((void**)&ws.Xs_lo, rows * D));
+  ZV_TRY(A((void**)&ws.Y_lo, rows * D));
   ZV_TRY(A((void**)&ws.vel, rows * net.out_dim_max * 4));
   ZV_TRY(A((void**)&ws.xcur, rows * net.out_dim_max * 4));
   ZV_TRY(A((void**)&ws.x_in, rows * net.in_pad_max * 2));
-  ZV_TRY(A((void**)&ws.shadow, rows * D * 2));
   ZV_TRY(A((void**)&ws.qkp, rows * 288 * 2));
   ZV_TRY(A((void**)&ws.hidden, rows * Fmax * 2));
   ZV_TRY(A((void**)&ws.na_v, rows * net.hidden_na * 2));
@@ -483,8 +485,9 @@ int run_gemm(Engine& e, const Lin& lin, const __nv_bfloat16* A, int lda, int M, 
   p.M = M, p.N_pad = lin.N_pad, p.K = lin.K, p.lda = lda, p.ldw = lin.ldw, p.block_n = lin.block_n;
   p.A2 = A2, p.lda2 = lda2, p.k_split = k_split;
   ep.mode = lin.mode, ep.M = M, ep.N = lin.N, ep.gate_cols = lin.gate_cols, ep.bias = lin.bias;
-  ZV_K(KC_GEMM_BIAS + lin.mode, 2.0 * M * lin.N * (double)lin.K_valid, s,
-       gemm_launch(A, lin.w, p, ep, e.gemm_impl, s));
+  // the s24 residual GEMMs are timed with the residual class; without a residual input (stack in_proj) with EPI_F32's
+  const int cls = lin.mode == EPI_RES24 ? (ep.res_hi ? KC_GEMM_RESIDUAL : KC_GEMM_F32) : KC_GEMM_BIAS + lin.mode;
+  ZV_K(cls, 2.0 * M * lin.N * (double)lin.K_valid, s, gemm_launch(A, lin.w, p, ep, e.gemm_impl, s));
   return 0;
 }
 
@@ -553,9 +556,10 @@ void free_pos_tables(Net& net) {
     }
 }
 
-// Zipformer2EncoderLayer.forward in eval mode (zipformer.py:489-642).  X: layer input / output (fp32),
-// ws.Y: working residual stream, ws.shadow: bf16 copy of the current stream (GEMM A operand).
-static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kernel, float* X, int nb, int L,
+// Zipformer2EncoderLayer.forward in eval mode (zipformer.py:489-642).  X: layer input / output, ws.Y: working
+// residual stream, both in the s24 storage format (hi plane = bf16 GEMM A operand, lo plane = 8 more mantissa bits).
+static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kernel, __nv_bfloat16* X_hi,
+                         uint8_t* X_lo, int nb, int L,
                          const uint8_t* mask, const float* te_stack, const float* te_ff1, int te_ld, cudaStream_t s) {
   const int M = nb * L, D = net.D, hn = net.hidden_na;
   float* Etab = nullptr;
@@ -565,29 +569,31 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   // attention projections from the layer input (before the time embedding is added) -- :526-531
   ep = EpiParams();
   ep.L = L, ep.out_bf16 = ws.qkp, ep.ld_bf16 = 288, ep.out_f16 = 1;  // q | k | p kept in fp16
-  ZV_TRY(run_gemm(e, ly.attn_in, ws.shadow, D, M, ep, s));
+  ZV_TRY(run_gemm(e, ly.attn_in, X_hi, D, M, ep, s));
 
-  // shadow = false: nobody reads the bf16 copy of this stream state (the last feed-forward: BiasNorm reads fp32)
-  auto residual = [&](const Lin& lin, const __nv_bfloat16* A, int lda, const float* res, const float* resbias,
-                      const float* orig, const float* bscale, bool shadow = true) {
+  // src: the stream state the module reads (X for the first feed-forward, ws.Y afterwards); every module writes ws.Y
+  // from_x: the residual input is the layer input X (first module), else ws.Y updated in place
+  auto residual = [&](const Lin& lin, const __nv_bfloat16* A, int lda, bool from_x, const float* resbias,
+                      bool bypass_x, const float* bscale) {
     EpiParams r;
-    r.L = L, r.res = res, r.out_f32 = ws.Y, r.ld_f32 = D, r.out_bf16 = shadow ? ws.shadow : nullptr, r.ld_bf16 = D;
-    r.resbias = resbias, r.bias_ld = te_ld, r.orig = orig, r.bypass_scale = bscale;
+    r.L = L, r.res_hi = from_x ? X_hi : ws.Y_hi, r.res_lo = from_x ? X_lo : ws.Y_lo;
+    r.out_bf16 = ws.Y_hi, r.out_lo = ws.Y_lo, r.ld_bf16 = D;
+    r.resbias = resbias, r.bias_ld = te_ld, r.bypass_scale = bscale;
+    if (bypass_x) r.orig_hi = X_hi, r.orig_lo = X_lo;
     return run_gemm(e, lin, A, lda, M, r, s);
   };
-  auto ff = [&](int i, const float* rowbias, const float* res, const float* resbias, const float* orig,
-                const float* bscale, bool shadow = true) {
+  auto ff = [&](int i, const float* rowbias, bool from_x, const float* resbias, bool bypass_x, const float* bscale) {
     EpiParams f;
     f.L = L, f.rowbias = rowbias, f.bias_ld = te_ld, f.out_bf16 = ws.hidden, f.ld_bf16 = ly.ff_in[i].N;
-    int rc = run_gemm(e, ly.ff_in[i], ws.shadow, D, M, f, s);
+    int rc = run_gemm(e, ly.ff_in[i], from_x ? X_hi : ws.Y_hi, D, M, f, s);
     if (rc) return rc;
-    return residual(ly.ff_out[i], ws.hidden, ly.ff_in[i].N, res, resbias, orig, bscale, shadow);
+    return residual(ly.ff_out[i], ws.hidden, ly.ff_in[i].N, from_x, resbias, bypass_x, bscale);
   };
   const int ldc = D + 64;  // conv_b row pitch: [conv hidden (D) | SelfAttention output (48) | zeros (16)]
   auto self_attn = [&](int i) {
     EpiParams v;
     v.L = L, v.out_bf16 = ws.sa_v, v.ld_bf16 = 16 * net.H;
-    int rc = run_gemm(e, ly.sa_in[i], ws.shadow, D, M, v, s);
+    int rc = run_gemm(e, ly.sa_in[i], ws.Y_hi, D, M, v, s);
     if (rc) return rc;
     AttnParams a;
     a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.sa_v, a.ldv = 16 * net.H, a.vhs = 16, a.gate = nullptr, a.ldg = 0;
@@ -600,38 +606,38 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   auto conv = [&](int i, const float* te_conv, const float* resbias) {
     EpiParams c;
     c.L = L, c.mask = mask, c.out_bf16 = ws.conv_a, c.ld_bf16 = D, c.rowbias = te_conv, c.bias_ld = te_ld;
-    int rc = run_gemm(e, ly.conv_in[i], ws.shadow, D, M, c, s, ws.conv_b + D, ldc, D);
+    int rc = run_gemm(e, ly.conv_in[i], ws.Y_hi, D, M, c, s, ws.conv_b + D, ldc, D);
     if (rc) return rc;
     rc = run_dwconv(e, ws.conv_a, ly.dw_w[i], ly.dw_b[i], nb, L, D, kernel, ws.conv_b, ldc, s);
     if (rc) return rc;
-    return residual(ly.conv_out[i], ws.conv_b, ldc, ws.Y, resbias, nullptr, nullptr);
+    return residual(ly.conv_out[i], ws.conv_b, ldc, false, resbias, false, nullptr);
   };
 
   // src += time_emb; src += FF1(src)  (:532-536): FF1 input bias folded, time_emb added to the stream here
-  ZV_TRY(ff(0, te_ff1, X, te_stack, nullptr, nullptr));
+  ZV_TRY(ff(0, te_ff1, true, te_stack, false, nullptr));
   // src += NonlinAttention(src, A[0:1])  (:542,558-562)
   ep = EpiParams();
   ep.L = L, ep.out_bf16 = ws.na_v, ep.ld_bf16 = hn, ep.out2_bf16 = ws.na_y, ep.ld2_bf16 = hn;
-  ZV_TRY(run_gemm(e, ly.na_in, ws.shadow, D, M, ep, s));
+  ZV_TRY(run_gemm(e, ly.na_in, ws.Y_hi, D, M, ep, s));
   {
     AttnParams a;
     a.qkp = ws.qkp, a.ldq = 288, a.E = Etab, a.mask = mask, a.V = ws.na_v, a.ldv = hn, a.gate = ws.na_y, a.ldg = hn;
     a.out = ws.na_o, a.ldo = hn, a.nb = nb, a.L = L, a.H = net.H, a.heads = 1, a.dv = hn;
     ZV_TRY(run_attn(e, KC_ATTN_NONLIN, a, 1, s));
   }
-  ZV_TRY(residual(ly.na_out, ws.na_o, hn, ws.Y, nullptr, nullptr, nullptr));
+  ZV_TRY(residual(ly.na_out, ws.na_o, hn, false, nullptr, false, nullptr));
   // src += SelfAttn1(src, A); src += time_emb  (:564-579)
   const float* te_c0 = te_stack ? ws.te_out + ly.te_off_conv[0] : nullptr;
   const float* te_c1 = te_stack ? ws.te_out + ly.te_off_conv[1] : nullptr;
   ZV_TRY(self_attn(0));
   ZV_TRY(conv(0, te_c0, te_stack));                                      // :581-587
-  ZV_TRY(ff(1, nullptr, ws.Y, nullptr, X, ly.bypass_mid_scale));          // :593-598 (FF2 + bypass_mid)
+  ZV_TRY(ff(1, nullptr, false, nullptr, true, ly.bypass_mid_scale));      // :593-598 (FF2 + bypass_mid)
   ZV_TRY(self_attn(1));                                                  // :600-616
   ZV_TRY(conv(1, te_c1, te_stack));                                      // :618-624
-  ZV_TRY(ff(2, nullptr, ws.Y, nullptr, nullptr, nullptr, false));         // :630-632
+  ZV_TRY(ff(2, nullptr, false, nullptr, false, nullptr));                 // :630-632
   // src = bypass(src_orig, BiasNorm(src))  (:635-637), in place on X
-  ZV_K(KC_BIASNORM, (double)M * D * 14, s,
-       biasnorm_bypass(ws.Y, X, ly.norm_bias, ly.log_scale, ly.bypass_scale, M, D, X, ws.shadow, s));
+  ZV_K(KC_BIASNORM, (double)M * D * 9, s,
+       biasnorm_bypass(ws.Y_hi, ws.Y_lo, X_hi, X_lo, ly.norm_bias, ly.log_scale, ly.bypass_scale, M, D, X_hi, X_lo, s));
   return 0;
 }
 
@@ -645,7 +651,7 @@ int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t
   const int nb_te = te_shared ? 1 : nb;
   const int te_ld = te_shared ? 0 : net.N_te;
   EpiParams ep;
-  ep.L = T, ep.out_f32 = ws.X, ep.ld_f32 = D, ep.out_bf16 = ws.shadow, ep.ld_bf16 = D;
+  ep.L = T, ep.out_bf16 = ws.X_hi, ep.out_lo = ws.X_lo, ep.ld_bf16 = D;  // no residual input: X = in_proj(x)
   ZV_TRY(run_gemm(e, net.in_proj, ws.x_in, net.in_pad, M, ep, s));
   if (net.use_time) {
     if (!ta.t) {
@@ -661,28 +667,29 @@ int net_forward(Engine& e, Net& net, Workspace& ws, int nb, int T, const uint8_t
   for (Stack& st : net.stacks) {
     const int ds = st.ds;
     const int L = (T + ds - 1) / ds;
-    float* X = ws.X;
+    __nv_bfloat16* X_hi = ws.X_hi;
+    uint8_t* X_lo = ws.X_lo;
     const uint8_t* mask = mask_dev;
     if (ds != 1) {
       uint8_t* msub = mask_dev ? ws.mask[ds == 2 ? 1 : 2] : nullptr;
       g_launch_count += msub ? 1 : 0;  // mask subsampling rides in the same launcher
-      ZV_K(KC_RESAMPLE, (double)nb * D * (4.0 * T + 6.0 * L), s,
-           downsample(ws.X, st.ds_w, nb, T, D, ds, ws.Xs, ws.shadow, msub, mask_dev, s));
-      X = ws.Xs, mask = msub;
+      ZV_K(KC_RESAMPLE, (double)nb * D * (3.0 * T + 3.0 * L), s,
+           downsample(ws.X_hi, ws.X_lo, st.ds_w, nb, T, D, ds, ws.Xs_hi, ws.Xs_lo, msub, mask_dev, s));
+      X_hi = ws.Xs_hi, X_lo = ws.Xs_lo, mask = msub;
     }
     const float* te_stack = net.use_time ? ws.te_out + st.te_off : nullptr;
     for (Layer& ly : st.layers) {
       const float* te_ff1 = net.use_time ? ws.te_out + ly.te_off_ff1 : nullptr;
       // row pitch of the time-embedding projections is N_te for every layer of this net
-      ZV_TRY(layer_forward(e, net, ws, ly, st.kernel, X, nb, L, mask, te_stack, te_ff1, te_ld, s));
+      ZV_TRY(layer_forward(e, net, ws, ly, st.kernel, X_hi, X_lo, nb, L, mask, te_stack, te_ff1, te_ld, s));
     }
     if (ds != 1)
-      ZV_K(KC_RESAMPLE, (double)nb * D * (10.0 * T + 4.0 * L), s,
-           upsample_combine(ws.X, ws.Xs, st.out_comb_scale, nb, T, L, D, ds, ws.shadow, s));
+      ZV_K(KC_RESAMPLE, (double)nb * D * (6.0 * T + 3.0 * L), s,
+           upsample_combine(ws.X_hi, ws.X_lo, ws.Xs_hi, ws.Xs_lo, st.out_comb_scale, nb, T, L, D, ds, s));
   }
   ep = EpiParams();
   ep.L = T, ep.out_f32 = out, ep.ld_f32 = net.out_dim;
-  ZV_TRY(run_gemm(e, net.out_proj, ws.shadow, D, M, ep, s));
+  ZV_TRY(run_gemm(e, net.out_proj, ws.X_hi, D, M, ep, s));
   return 0;
 }
 

@@ -74,8 +74,12 @@ struct Workspace {
   unsigned long long gen = 0;  // bumped whenever the buffers are reallocated (captured graphs hold their addresses)
   int cap_nb = 0;
   int D = 0;
-  float *X = nullptr, *Xs = nullptr, *Y = nullptr, *vel = nullptr, *xcur = nullptr;
-  __nv_bfloat16 *x_in = nullptr, *shadow = nullptr, *qkp = nullptr, *hidden = nullptr, *na_v = nullptr,
+  float *vel = nullptr, *xcur = nullptr;
+  // residual streams in the s24 storage format (zv_common.cuh): X = stack input / output at full rate, Xs = the
+  // same at the stack's frame rate, Y = working stream inside a layer.  The hi planes are the GEMM A operands.
+  __nv_bfloat16 *X_hi = nullptr, *Xs_hi = nullptr, *Y_hi = nullptr;
+  uint8_t *X_lo = nullptr, *Xs_lo = nullptr, *Y_lo = nullptr;
+  __nv_bfloat16 *x_in = nullptr, *qkp = nullptr, *hidden = nullptr, *na_v = nullptr,
                 *na_y = nullptr, *na_o = nullptr, *sa_v = nullptr, *conv_a = nullptr,
                 *conv_b = nullptr;
   float* sa_part = nullptr;   // key-split partial states of the SelfAttention kernel (AttnParams::part)

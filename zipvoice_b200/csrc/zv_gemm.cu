@@ -38,7 +38,8 @@ ZV_DEVINL void epi_apply(const EpiParams& ep, int m, int b, int n0, const float 
     float x = acc[i];
     if (i < nvalid) {
       x += __ldg(ep.bias + n0 + i);
-      if (MODE != EPI_RESIDUAL && ep.rowbias) x += __ldg(ep.rowbias + (size_t)b * ep.bias_ld + n0 + i);
+      if (MODE != EPI_RESIDUAL && MODE != EPI_RES24 && ep.rowbias)
+        x += __ldg(ep.rowbias + (size_t)b * ep.bias_ld + n0 + i);
     }
     v[i] = x;
   }
@@ -160,6 +161,26 @@ ZV_DEVINL void epi_apply(const EpiParams& ep, int m, int b, int n0, const float 
         if (ob) ob[i] = __float2bfloat16(x);
       }
     }
+  } else if (MODE == EPI_RES24) {
+    // checker path: element by element through the scalar forms of the s24 format
+    const size_t off = (size_t)m * ep.ld_bf16 + n0;
+    const uint16_t* rh = reinterpret_cast<const uint16_t*>(ep.res_hi);
+    const uint16_t* oh = reinterpret_cast<const uint16_t*>(ep.orig_hi);
+    uint16_t* wh = reinterpret_cast<uint16_t*>(ep.out_bf16);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      if (i >= nvalid) continue;
+      float x = v[i];
+      if (rh) x += s24_dec(rh[off + i], ep.res_lo[off + i]);
+      if (ep.resbias) x += ep.resbias[(size_t)b * ep.bias_ld + n0 + i];
+      if (oh) {
+        const float oo = s24_dec(oh[off + i], ep.orig_lo[off + i]);
+        x = oo + (x - oo) * ep.bypass_scale[n0 + i];
+      }
+      const uint32_t w = s24_w(x);
+      wh[off + i] = (uint16_t)(w >> 16);
+      ep.out_lo[off + i] = (uint8_t)(w >> 8);
+    }
   } else {  // EPI_F32
     float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + n0;
     if (nvalid == 32 && (ep.ld_f32 & 3) == 0) {
@@ -189,6 +210,8 @@ __host__ __device__ constexpr int ncg_for(int mode) {
 }
 static constexpr int STG_BF16_BYTES = BM * 64;   // 128 rows x 32 bf16
 static constexpr int STG_F32_BYTES = BM * 128;   // 128 rows x 32 fp32
+static constexpr int STG_LO_BYTES = BM * 32;     // 128 rows x 32 bytes (lo plane of the s24 stream)
+static constexpr int STG_S24_BYTES = STG_BF16_BYTES + STG_LO_BYTES;  // one s24 staging buffer: hi rows, then lo rows
 
 struct GemmMaps {
   CUtensorMap A, W;
@@ -197,6 +220,9 @@ struct GemmMaps {
   CUtensorMap O0;  // bf16 output (box 32 cols, SWIZZLE_64B; GLU / gated NONLIN: box 16 cols, SWIZZLE_32B)
   CUtensorMap O1;  // EPI_NONLIN plain part: bf16 (box 32, SWIZZLE_64B); EPI_RESIDUAL: fp32 out (box 32, SWIZZLE_128B)
   CUtensorMap R;   // EPI_RESIDUAL: fp32 residual input (box 32, SWIZZLE_128B)
+  // EPI_RES24: O0 / O1 = hi / lo plane of the output (bf16 box 32, SWIZZLE_64B / byte box 32, SWIZZLE_32B),
+  //            R / R2 = hi / lo plane of the residual input, same boxes
+  CUtensorMap R2;
 };
 
 // Work schedule of one launch.  Units [0, main_units) are full tiles (128 x block_n; 256 x block_n for CTA pairs)
@@ -220,7 +246,9 @@ struct GemmSmemTail {
 
 // bytes of epilogue staging per column group
 __host__ __device__ constexpr int stg_group_bytes(int mode) {
-  return (mode == EPI_RESIDUAL || mode == EPI_F32) ? 2 * STG_F32_BYTES + STG_BF16_BYTES : 2 * STG_BF16_BYTES;
+  return (mode == EPI_RESIDUAL || mode == EPI_F32) ? 2 * STG_F32_BYTES + STG_BF16_BYTES
+         : mode == EPI_RES24                        ? 2 * STG_S24_BYTES
+                                                    : 2 * STG_BF16_BYTES;
 }
 
 // 32 fp32 values of one row -> 32 bf16 in a 64-byte staging row (SWIZZLE_64B pattern of the TMA store)
@@ -509,6 +537,14 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       mbar_arrive_expect_tx(&rbar[0], STG_F32_BYTES / 4);
       tma_load_2d(stg + q * (STG_F32_BYTES / 4), &maps.R, &rbar[0], n0t + cg * 32, m_blk * BM + q * 32);
     }
+    if (MODE == EPI_RES24 && ep.res_hi && lane == 0 && unit0 < total_tiles) {
+      int m_blk, n0t, bn;
+      decode(unit0, m_blk, n0t, bn);
+      mbar_arrive_expect_tx(&rbar[0], STG_S24_BYTES / 4);
+      tma_load_2d(stg + q * (STG_BF16_BYTES / 4), &maps.R, &rbar[0], n0t + cg * 32, m_blk * BM + q * 32);
+      tma_load_2d(stg + STG_BF16_BYTES + q * (STG_LO_BYTES / 4), &maps.R2, &rbar[0], n0t + cg * 32,
+                  m_blk * BM + q * 32);
+    }
     int it = 0;
     for (int t = unit0; t < total_tiles; t += nunits, ++it) {
       int m_blk, n0t, bn;
@@ -520,11 +556,12 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       const int mm = min(m, ep.M - 1);
       const int b = mm / ep.L;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * ACC_STAGE_COLS;
-      const float* rowb = (MODE != EPI_RESIDUAL && ep.rowbias) ? ep.rowbias + (size_t)b * ep.bias_ld : nullptr;
+      const float* rowb =
+          (MODE != EPI_RESIDUAL && MODE != EPI_RES24 && ep.rowbias) ? ep.rowbias + (size_t)b * ep.bias_ld : nullptr;
       // chunks that lie entirely in the padded columns of the last n-tile are skipped (never for EPI_RESIDUAL,
       // whose prefetch chain assumes full tiles: its N is a multiple of block_n)
-      const int nchunks = (MODE == EPI_RESIDUAL) ? nchunks_tile
-                                                 : min(nchunks_tile, (ep.N - n0t + 31) >> 5);
+      const int nchunks = (MODE == EPI_RESIDUAL || MODE == EPI_RES24) ? nchunks_tile
+                                                                      : min(nchunks_tile, (ep.N - n0t + 31) >> 5);
       mbar_wait(&tail->tmem_full[as], aphase);
       tc_fence_after();
       if (cg >= nchunks) {  // this group owns no chunk of the tile: release the accumulator right away
@@ -640,6 +677,88 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           }
           continue;
         }
+        if (MODE == EPI_RES24) {
+          // s24 stream: the hi / lo rows of the residual chunk arrive by TMA one chunk ahead, are decoded, updated and
+          // re-encoded in registers and leave through the same staging rows
+          const int sb = nq & 1;
+          uint8_t* hb = stg + sb * STG_S24_BYTES;
+          uint8_t* lb = hb + STG_BF16_BYTES;
+          if (lane == 0) {
+            tma_store_wait_read<0>();  // the previous chunk's stores have read buffer sb ^ 1
+            if (ep.res_hi) {
+              int c2 = c + NCG, t2 = t;
+              if (c2 >= nchunks) c2 = cg, t2 = t + nunits;
+              if (t2 < total_tiles) {
+                int mb2 = m_blk, n02 = n0t, bn2;
+                if (t2 != t) decode(t2, mb2, n02, bn2);
+                uint8_t* nb2 = stg + (sb ^ 1) * STG_S24_BYTES;
+                mbar_arrive_expect_tx(&rbar[sb ^ 1], STG_S24_BYTES / 4);
+                tma_load_2d(nb2 + q * (STG_BF16_BYTES / 4), &maps.R, &rbar[sb ^ 1], n02 + c2 * 32, mb2 * BM + q * 32);
+                tma_load_2d(nb2 + STG_BF16_BYTES + q * (STG_LO_BYTES / 4), &maps.R2, &rbar[sb ^ 1], n02 + c2 * 32,
+                            mb2 * BM + q * 32);
+              }
+            }
+          }
+          add_bias32(v, ep.bias, ep.resbias ? ep.resbias + (size_t)b * ep.bias_ld : nullptr, n0, ep.N);
+          const int xh = (r >> 1) & 3, xl = (r >> 2) & 1;
+          if (ep.res_hi) {
+            mbar_wait(&rbar[sb], (nq >> 1) & 1);
+            const uint4 l0 = *reinterpret_cast<const uint4*>(lb + r * 32 + ((0 ^ xl) << 4));
+            const uint4 l1 = *reinterpret_cast<const uint4*>(lb + r * 32 + ((1 ^ xl) << 4));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 hh = *reinterpret_cast<const uint4*>(hb + r * 64 + ((j ^ xh) << 4));
+              const uint4 lw = j < 2 ? l0 : l1;
+              float d[8];
+              s24_dec8(hh, (j & 1) ? make_uint2(lw.z, lw.w) : make_uint2(lw.x, lw.y), d);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) v[8 * j + i] += d[i];
+            }
+          }
+          if (ep.orig_hi) {
+            const uint4* oh = reinterpret_cast<const uint4*>(ep.orig_hi + (size_t)mm * ep.ld_bf16 + n0);
+            const uint4* ol = reinterpret_cast<const uint4*>(ep.orig_lo + (size_t)mm * ep.ld_bf16 + n0);
+            const uint4 l0 = ol[0], l1 = ol[1];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 lw = j < 2 ? l0 : l1;
+              float d[8];
+              s24_dec8(oh[j], (j & 1) ? make_uint2(lw.z, lw.w) : make_uint2(lw.x, lw.y), d);
+#pragma unroll
+              for (int i = 0; i < 8; i += 4) {
+                const float4 bs = __ldg(reinterpret_cast<const float4*>(ep.bypass_scale + n0 + 8 * j + i));
+                v[8 * j + i] = d[i] + (v[8 * j + i] - d[i]) * bs.x;
+                v[8 * j + i + 1] = d[i + 1] + (v[8 * j + i + 1] - d[i + 1]) * bs.y;
+                v[8 * j + i + 2] = d[i + 2] + (v[8 * j + i + 2] - d[i + 2]) * bs.z;
+                v[8 * j + i + 3] = d[i + 3] + (v[8 * j + i + 3] - d[i + 3]) * bs.w;
+              }
+            }
+          }
+          __syncwarp();  // lane 0 has waited for the stores that read this buffer; every lane has read its row
+          uint4 lo4[2];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float d[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) d[i] = v[8 * j + i];
+            uint4 hh;
+            uint2 l2;
+            s24_enc8(d, hh, l2);
+            *reinterpret_cast<uint4*>(hb + r * 64 + ((j ^ xh) << 4)) = hh;
+            if (j & 1) lo4[j >> 1].z = l2.x, lo4[j >> 1].w = l2.y;
+            else lo4[j >> 1].x = l2.x, lo4[j >> 1].y = l2.y;
+          }
+          *reinterpret_cast<uint4*>(lb + r * 32 + ((0 ^ xl) << 4)) = lo4[0];
+          *reinterpret_cast<uint4*>(lb + r * 32 + ((1 ^ xl) << 4)) = lo4[1];
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&maps.O0, hb + q * (STG_BF16_BYTES / 4), n0, m_blk * BM + q * 32);
+            tma_store_2d(&maps.O1, lb + q * (STG_LO_BYTES / 4), n0, m_blk * BM + q * 32);
+            tma_store_commit();
+          }
+          continue;
+        }
         // ---- bf16 outputs
         add_bias32(v, ep.bias, rowb, n0, ep.N);
         uint8_t* sbuf = stg + (nq & 1) * STG_BF16_BYTES;
@@ -750,7 +869,7 @@ struct TmapKeyHash {
 };
 static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
 
-static int make_tmap_impl(CUtensorMap* tm, const void* ptr, int dtype /*0 bf16, 1 fp32*/, uint64_t rows, uint64_t cols,
+static int make_tmap_impl(CUtensorMap* tm, const void* ptr, int dtype /*0 bf16, 1 fp32, 2 u8*/, uint64_t rows, uint64_t cols,
                      uint64_t ld, uint32_t box_rows, uint32_t box_cols, int swizzle /*32, 64, 128*/) {
   const TmapKey key{ptr, rows, cols, ld, box_rows, box_cols, dtype, swizzle};
   auto it = g_tmap_cache.find(key);
@@ -760,7 +879,7 @@ static int make_tmap_impl(CUtensorMap* tm, const void* ptr, int dtype /*0 bf16, 
   }
   PFN_encodeTiled enc = get_encode_fn();
   if (!enc) return 901;
-  const uint64_t esz = dtype == 0 ? 2 : 4;
+  const uint64_t esz = dtype == 0 ? 2 : (dtype == 2 ? 1 : 4);
   if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld * esz) & 15)) return 906;  // TMA alignment rules
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {ld * esz};
@@ -770,7 +889,10 @@ static int make_tmap_impl(CUtensorMap* tm, const void* ptr, int dtype /*0 bf16, 
                                 : swizzle == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
                                 : swizzle == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
                                                 : CU_TENSOR_MAP_SWIZZLE_NONE;
-  CUresult r = enc(tm, dtype == 0 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+  const CUtensorMapDataType dt = dtype == 0   ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                 : dtype == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                              : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  CUresult r = enc(tm, dt, 2,
                    const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return 902;
@@ -1000,7 +1122,7 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
   // with K >= 1024 (246 vs 261 us at K = 1536) -- and lose or tie for the SwooshL / GLU / tanh-gate epilogues
   // and the short-K HBM-bound residual GEMMs, which stay on single-CTA tiles.
   const bool big = (long long)m_tiles_all * (p.N_pad / p.block_n) >= 2LL * g_num_sms;
-  const bool pair = impl == 3 || (impl == 0 && big && MODE == EPI_RESIDUAL && p.K >= 1024);
+  const bool pair = impl == 3 || (impl == 0 && big && (MODE == EPI_RESIDUAL || MODE == EPI_RES24) && p.K >= 1024);
   GemmMaps maps;
   memset(&maps, 0, sizeof(maps));
   const int k_a = p.A2 ? p.k_split : p.K;
@@ -1021,6 +1143,15 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
     rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.gate_cols / 2, (uint64_t)ep.ld_bf16, 32, 16, 32);
     if (!rc && ep.N > ep.gate_cols)
       rc = make_tmap_impl(&maps.O1, ep.out2_bf16, 0, Mu, (uint64_t)(ep.N - ep.gate_cols), (uint64_t)ep.ld2_bf16, 32, 32, 64);
+  } else if (MODE == EPI_RES24) {
+    if (!ep.out_bf16 || !ep.out_lo || (ep.res_hi && !ep.res_lo) || (ep.orig_hi && !(ep.orig_lo && ep.bypass_scale)) ||
+        ep.N % 32 || ep.ld_bf16 % 16)
+      return 908;
+    const uint64_t ld = (uint64_t)ep.ld_bf16;
+    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, ld, 32, 32, 64);
+    if (!rc) rc = make_tmap_impl(&maps.O1, ep.out_lo, 2, Mu, (uint64_t)ep.N, ld, 32, 32, 32);
+    if (!rc && ep.res_hi) rc = make_tmap_impl(&maps.R, ep.res_hi, 0, Mu, (uint64_t)ep.N, ld, 32, 32, 64);
+    if (!rc && ep.res_hi) rc = make_tmap_impl(&maps.R2, ep.res_lo, 2, Mu, (uint64_t)ep.N, ld, 32, 32, 32);
   } else if (MODE == EPI_RESIDUAL) {
     rc = make_tmap_impl(&maps.O1, ep.out_f32, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, 32, 32, 128);
     if (!rc) rc = make_tmap_impl(&maps.R, ep.res, 1, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_f32, 32, 32, 128);
@@ -1057,6 +1188,7 @@ int gemm_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const GemmPlan& 
     case EPI_RESIDUAL: return launch_mode<EPI_RESIDUAL>(A, W, plan, ep, impl, stream);
     case EPI_F32: return launch_mode<EPI_F32>(A, W, plan, ep, impl, stream);
     case EPI_GELU_BF16: return launch_mode<EPI_GELU_BF16>(A, W, plan, ep, impl, stream);
+    case EPI_RES24: return launch_mode<EPI_RES24>(A, W, plan, ep, impl, stream);
   }
   return 905;
 }

@@ -16,6 +16,8 @@ enum EpiMode : int {
   EPI_RESIDUAL = 4,      // v = res + acc + bias (+ resbias[b]); optional bypass vs orig; writes fp32 + bf16
   EPI_F32 = 5,           // out_f32 = acc + bias (+ rowbias[b])
   EPI_GELU_BF16 = 6,     // out_bf16 = GELU_erf(acc + bias)                          (Vocos ConvNeXt pwconv1)
+  EPI_RES24 = 7,         // EPI_RESIDUAL on the s24 residual stream (zv_common.cuh): v = res + acc + bias (+ resbias[b]),
+                         // optional bypass vs orig; res may be absent (stack input).  Writes the hi and lo planes.
 };
 
 struct EpiParams {
@@ -38,6 +40,12 @@ struct EpiParams {
   const float* resbias = nullptr;  // [B][bias_ld] optional (time embedding folded into the residual)
   const float* orig = nullptr;     // optional bypass: v = orig + (v - orig) * bypass_scale[n]
   const float* bypass_scale = nullptr;
+  // EPI_RES24: s24 planes, all with row pitch ld_bf16 (elements); the output hi plane is out_bf16
+  const __nv_bfloat16* res_hi = nullptr;   // may alias out_bf16 / out_lo (in-place update)
+  const uint8_t* res_lo = nullptr;
+  const __nv_bfloat16* orig_hi = nullptr;  // with bypass_scale, like orig
+  const uint8_t* orig_lo = nullptr;
+  uint8_t* out_lo = nullptr;
   const uint8_t* mask = nullptr;   // [B][L] 1 = padded frame (EPI_GLU_BF16)
   int f32_direct = 0;              // EPI_F32: set by the launcher when the output cannot be a TMA tensor (pitch % 4)
 };
@@ -61,7 +69,7 @@ int gemm_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const GemmPlan& 
 int gemm_pick_block_n(int n_valid, int mode, int gate_cols);
 
 // Cached cuTensorMapEncodeTiled for a row-major [rows][cols] tensor with row pitch ld (elements):
-// dtype 0 = 16-bit, 1 = fp32; box [box_rows][box_cols]; swizzle 0 (none) / 32 / 64 / 128 bytes.  `tm` is a CUtensorMap*.
+// dtype 0 = 16-bit, 1 = fp32, 2 = bytes; box [box_rows][box_cols]; swizzle 0 (none) / 32 / 64 / 128 bytes.  `tm` is a CUtensorMap*.
 int make_tmap(void* tm, const void* ptr, int dtype, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
               uint32_t box_cols, int swizzle);
 

@@ -21,17 +21,20 @@ int cfg_euler_update(float* x, const float* v, const float* guidance, int guidan
 int dwconv_swooshr(const __nv_bfloat16* in, const float* w, const float* bias, int nb, int L, int C, int k,
                    __nv_bfloat16* out, int ld_out, cudaStream_t s);
 
-// out = orig + (BiasNorm(src) - orig) * scale   (scaling.py:345-348, zipformer.py:635-637); fp32 + bf16 shadow.
-int biasnorm_bypass(const float* src, const float* orig, const float* nbias, float log_scale, const float* bscale,
-                    int M, int D, float* out, __nv_bfloat16* out_bf16, cudaStream_t s);
+// The next three read and write the residual stream in its s24 storage format (zv_common.cuh): a bf16 `hi` plane
+// (the GEMM A operand) and a byte `lo` plane of the same [rows][D] shape.
+// out = orig + (BiasNorm(src) - orig) * scale   (scaling.py:345-348, zipformer.py:635-637); out may alias orig.
+int biasnorm_bypass(const __nv_bfloat16* src_hi, const uint8_t* src_lo, const __nv_bfloat16* orig_hi,
+                    const uint8_t* orig_lo, const float* nbias, float log_scale, const float* bscale, int M, int D,
+                    __nv_bfloat16* out_hi, uint8_t* out_lo, cudaStream_t s);
 
 // SimpleDownsample (zipformer.py:887-913): out[b][j] = sum_k w[k] * src[b][min(j*ds+k, L-1)]
-int downsample(const float* src, const float* w, int nb, int L, int D, int ds, float* out, __nv_bfloat16* out_bf16,
-               uint8_t* mask_out, const uint8_t* mask_in, cudaStream_t s);
+int downsample(const __nv_bfloat16* src_hi, const uint8_t* src_lo, const float* w, int nb, int L, int D, int ds,
+               __nv_bfloat16* out_hi, uint8_t* out_lo, uint8_t* mask_out, const uint8_t* mask_in, cudaStream_t s);
 
 // SimpleUpsample + out_combiner (zipformer.py:866-870): x = orig + (y[t/ds] - orig) * scale, in place on orig.
-int upsample_combine(float* orig, const float* y, const float* bscale, int nb, int L, int L2, int D, int ds,
-                     __nv_bfloat16* out_bf16, cudaStream_t s);
+int upsample_combine(__nv_bfloat16* orig_hi, uint8_t* orig_lo, const __nv_bfloat16* y_hi, const uint8_t* y_lo,
+                     const float* bscale, int nb, int L, int L2, int D, int ds, cudaStream_t s);
 
 int f32_to_bf16(const float* in, __nv_bfloat16* out, size_t n, cudaStream_t s);
 
