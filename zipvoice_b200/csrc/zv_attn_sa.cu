@@ -15,6 +15,8 @@
 
 #include <type_traits>
 
+#include <stdio.h>
+
 #include "zv_common.cuh"
 #include "zv_gemm.h"
 #include "zv_kernels.h"
@@ -560,15 +562,31 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(row0) << 16);
     // rows g + 8 (a = row0 / 8 + 1) sit at v = 56 - row0 / 2 + 4 nt + qd, rows g four columns further
     const uint32_t dcol = 56 - (row0 >> 1);
+#ifdef ZV_SA_TRACE  // measurement build: cycles of one warp per phase of the key-tile loop
+    long long tr_w = 0, tr_l = 0, tr_m = 0, tr_v = 0, tr_e = 0;
+    const long long tr_0 = clock64();
+#define ZV_SA_TR(acc) { const long long c_ = clock64(); acc += c_ - tr_c; tr_c = c_; }
+#else
+#define ZV_SA_TR(acc)
+#endif
     for (int kt = kt0; kt < kt1; ++kt) {
       const int it = kt - kt0, st = it % STAGES;
       const bool mk = sflag[kt] != 0;
+#ifdef ZV_SA_TRACE
+      long long tr_c = clock64();
+#endif
       // ---- scores: S + D_even / D_odd from TMEM, then the accumulators go back to the MMA warp
       float s[8][4];
       mbar_wait(&sm.sfull, it & 1);
       tc_fence_after();
+      ZV_SA_TR(tr_w)
       {
         uint32_t r[32];
+#if defined(ZV_SA_ABL) && (ZV_SA_ABL & 2)  // measurement build: no score load (wrong results)
+#pragma unroll
+        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint((float)((lane + i + kt) & 7));
+        if (false)
+#endif
         asm volatile(
             "tcgen05.ld.sync.aligned.16x256b.x8.b32 "
             "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
@@ -580,8 +598,14 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
             : "r"(lane_addr + COL_S)
             : "memory");
         uint32_t te[16], te1[2];
+#if defined(ZV_SA_ABL) && (ZV_SA_ABL & 1)  // measurement build: no position-term loads (wrong results)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) te[i] = r[i];
+        te1[0] = te1[1] = r[5];
+#else
         tmem_ld_16x128b_x8(lane_addr + COL_DE + dcol, te);
         tmem_ld_16x128b_x1(lane_addr + COL_DE + dcol + 32, te1);
+#endif
         tmem_ld_wait();
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
@@ -591,9 +615,15 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
           s[nt][3] = __uint_as_float(r[4 * nt + 3]);
         }
         uint32_t to[16], to1[2];
+#if defined(ZV_SA_ABL) && (ZV_SA_ABL & 1)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) to[i] = r[16 + i];
+        to1[0] = to1[1] = r[7];
+#else
         tmem_ld_16x128b_x8(lane_addr + COL_DO + dcol, to);
         tmem_ld_16x128b_x1(lane_addr + COL_DO + dcol + 32, to1);
         tmem_ld_wait();
+#endif
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
           s[nt][1] += __uint_as_float(nt < 7 ? to[2 * (nt + 1)] : to1[0]);
@@ -603,6 +633,7 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.sfree);
+      ZV_SA_TR(tr_l)
       // ---- key mask (padded keys -> -1000 log2 e, keys beyond the sequence -> -inf) and the row maxima
       if (mk) {
         const uint8_t* mrow = smask + kt * BKV;
@@ -632,7 +663,9 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
       }
       // ---- P = exp2(S - m) (SOFT of every 4 on the FMA pipe, the rest on MUFU), O += P V  (V tile of this stage;
       //      its ones column carries the row sums)
+      ZV_SA_TR(tr_m)
       mbar_wait(&sm.full[st], (it / STAGES) & 1);  // complete long ago (the MMAs waited for it); orders the V reads
+      ZV_SA_TR(tr_v)
       const uint32_t vbase = smem_u32(&sm.v[st][0][0]);
 #pragma unroll
       for (int kk = 0; kk < BKV / 16; ++kk) {
@@ -651,7 +684,14 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.empty[st]);
+      ZV_SA_TR(tr_e)
     }
+#ifdef ZV_SA_TRACE
+    if (lane == 0 && (warp == 0 || warp == 5) && blockIdx.x == 1 && blockIdx.y == 1 && (blockIdx.z == 3 || blockIdx.z == 100))
+      printf("[sa trace] z %d warp %d tiles %d: wait_S %lld  ld %lld  max %lld  wait_V %lld  exp_pv %lld  loop %lld  since_start %lld\n",
+             (int)blockIdx.z, warp, kt1 - kt0, tr_w, tr_l, tr_m, tr_v, tr_e, tr_w + tr_l + tr_m + tr_v + tr_e,
+             clock64() - tr_0);
+#endif
     const int ia = i0 + rl0, ib = i0 + rl1;
     if (ksplit > 1) {
       // ---- key split: the unnormalised state of this key range (O incl. the row-sum column, reference maximum)

@@ -212,6 +212,14 @@ static constexpr int STG_BF16_BYTES = BM * 64;   // 128 rows x 32 bf16
 static constexpr int STG_F32_BYTES = BM * 128;   // 128 rows x 32 fp32
 static constexpr int STG_LO_BYTES = BM * 32;     // 128 rows x 32 bytes (lo plane of the s24 stream)
 static constexpr int STG_S24_BYTES = STG_BF16_BYTES + STG_LO_BYTES;  // one s24 staging buffer: hi rows, then lo rows
+// s24 staging buffers per column group: while chunk n is updated the residual rows of chunks n + 1 .. n + S24_BUFS - 1
+// are in flight.  Measured on B200 (tools/res24_bench.py, M = 156 k): 3 or 4 buffers change nothing for K = 384 / 576
+// (121 us either way: the residual prefetch is not what holds the short-K shapes at 0.77 of the HBM roofline) and
+// cost the K >= 1152 shapes a stage of the operand ring (181 -> 200 us at K = 1536), so two it is.
+#ifndef ZV_S24_BUFS
+#define ZV_S24_BUFS 2
+#endif
+static constexpr int S24_BUFS = ZV_S24_BUFS;
 
 struct GemmMaps {
   CUtensorMap A, W;
@@ -240,14 +248,14 @@ struct GemmSmemTail {
   uint64_t empty[MAX_STAGES];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
-  uint64_t rbar[MAX_NCG * 4][2];  // per epilogue warp
+  uint64_t rbar[MAX_NCG * 4][4];  // per epilogue warp (EPI_RESIDUAL: 2 in use, EPI_RES24: S24_BUFS)
   uint32_t tmem_base;
 };
 
 // bytes of epilogue staging per column group
 __host__ __device__ constexpr int stg_group_bytes(int mode) {
   return (mode == EPI_RESIDUAL || mode == EPI_F32) ? 2 * STG_F32_BYTES + STG_BF16_BYTES
-         : mode == EPI_RES24                        ? 2 * STG_S24_BYTES
+         : mode == EPI_RES24                        ? S24_BUFS * STG_S24_BYTES
                                                     : 2 * STG_BF16_BYTES;
 }
 
@@ -363,7 +371,8 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       mbar_init(&tail->tmem_full[i], DUAL ? 2 : 1);
       mbar_init(&tail->tmem_empty[i], PAIR ? 2 * EPI_WARPS : EPI_WARPS);
     }
-    for (int g = 0; g < NCG * 4; ++g) mbar_init(&tail->rbar[g][0], 1), mbar_init(&tail->rbar[g][1], 1);
+    for (int g = 0; g < NCG * 4; ++g)
+      for (int i = 0; i < 4; ++i) mbar_init(&tail->rbar[g][i], 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -537,13 +546,25 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       mbar_arrive_expect_tx(&rbar[0], STG_F32_BYTES / 4);
       tma_load_2d(stg + q * (STG_F32_BYTES / 4), &maps.R, &rbar[0], n0t + cg * 32, m_blk * BM + q * 32);
     }
-    if (MODE == EPI_RES24 && ep.res_hi && lane == 0 && unit0 < total_tiles) {
-      int m_blk, n0t, bn;
-      decode(unit0, m_blk, n0t, bn);
-      mbar_arrive_expect_tx(&rbar[0], STG_S24_BYTES / 4);
-      tma_load_2d(stg + q * (STG_BF16_BYTES / 4), &maps.R, &rbar[0], n0t + cg * 32, m_blk * BM + q * 32);
-      tma_load_2d(stg + STG_BF16_BYTES + q * (STG_LO_BYTES / 4), &maps.R2, &rbar[0], n0t + cg * 32,
-                  m_blk * BM + q * 32);
+    // EPI_RES24: prefetch cursor of this warp -- the next chunk whose residual rows are to be requested (lane 0)
+    int pf_c = cg, pf_t = unit0;
+    uint32_t pf_n = 0;
+    auto pf_issue = [&]() {
+      if (pf_t >= total_tiles) return;
+      int mb2, n02, bn2;
+      decode(pf_t, mb2, n02, bn2);
+      const uint32_t sb2 = pf_n % S24_BUFS;
+      uint8_t* nb2 = stg + sb2 * STG_S24_BYTES;
+      mbar_arrive_expect_tx(&rbar[sb2], STG_S24_BYTES / 4);
+      tma_load_2d(nb2 + q * (STG_BF16_BYTES / 4), &maps.R, &rbar[sb2], n02 + pf_c * 32, mb2 * BM + q * 32);
+      tma_load_2d(nb2 + STG_BF16_BYTES + q * (STG_LO_BYTES / 4), &maps.R2, &rbar[sb2], n02 + pf_c * 32,
+                  mb2 * BM + q * 32);
+      pf_c += NCG, ++pf_n;
+      if (pf_c >= (bn2 >> 5)) pf_c = cg, pf_t += nunits;
+    };
+    if (MODE == EPI_RES24 && ep.res_hi && lane == 0) {
+#pragma unroll
+      for (int i = 0; i < S24_BUFS - 1; ++i) pf_issue();
     }
     int it = 0;
     for (int t = unit0; t < total_tiles; t += nunits, ++it) {
@@ -680,29 +701,18 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         if (MODE == EPI_RES24) {
           // s24 stream: the hi / lo rows of the residual chunk arrive by TMA one chunk ahead, are decoded, updated and
           // re-encoded in registers and leave through the same staging rows
-          const int sb = nq & 1;
+          const uint32_t sb = nq % S24_BUFS;
           uint8_t* hb = stg + sb * STG_S24_BYTES;
           uint8_t* lb = hb + STG_BF16_BYTES;
           if (lane == 0) {
-            tma_store_wait_read<0>();  // the previous chunk's stores have read buffer sb ^ 1
-            if (ep.res_hi) {
-              int c2 = c + NCG, t2 = t;
-              if (c2 >= nchunks) c2 = cg, t2 = t + nunits;
-              if (t2 < total_tiles) {
-                int mb2 = m_blk, n02 = n0t, bn2;
-                if (t2 != t) decode(t2, mb2, n02, bn2);
-                uint8_t* nb2 = stg + (sb ^ 1) * STG_S24_BYTES;
-                mbar_arrive_expect_tx(&rbar[sb ^ 1], STG_S24_BYTES / 4);
-                tma_load_2d(nb2 + q * (STG_BF16_BYTES / 4), &maps.R, &rbar[sb ^ 1], n02 + c2 * 32, mb2 * BM + q * 32);
-                tma_load_2d(nb2 + STG_BF16_BYTES + q * (STG_LO_BYTES / 4), &maps.R2, &rbar[sb ^ 1], n02 + c2 * 32,
-                            mb2 * BM + q * 32);
-              }
-            }
+            // the previous chunk's stores have read their buffer, (nq - 1) % S24_BUFS: the one the next prefetch fills
+            tma_store_wait_read<0>();
+            if (ep.res_hi) pf_issue();
           }
           add_bias32(v, ep.bias, ep.resbias ? ep.resbias + (size_t)b * ep.bias_ld : nullptr, n0, ep.N);
           const int xh = (r >> 1) & 3, xl = (r >> 2) & 1;
           if (ep.res_hi) {
-            mbar_wait(&rbar[sb], (nq >> 1) & 1);
+            mbar_wait(&rbar[sb], (nq / S24_BUFS) & 1);
             const uint4 l0 = *reinterpret_cast<const uint4*>(lb + r * 32 + ((0 ^ xl) << 4));
             const uint4 l1 = *reinterpret_cast<const uint4*>(lb + r * 32 + ((1 ^ xl) << 4));
 #pragma unroll
