@@ -5,6 +5,7 @@ import ctypes as C
 import os
 import re
 
+import numpy as np
 import pytest
 import torch
 
@@ -68,3 +69,36 @@ def test_synth_state_dict_is_deterministic():
     assert a.keys() == b.keys() and all(torch.equal(a[k], b[k]) for k in a)
     full = synth.make_state_dict(distill=True)
     assert len(full) == 890 and abs(sum(v.numel() for v in full.values()) / 1e6 - 122.7) < 0.1
+
+
+def test_s24_stream_format_restated_in_numpy():
+    """The residual stream's storage format (csrc/zv_common.cuh: bf16 `hi` plane + byte `lo` plane): restated here in
+    numpy integer arithmetic and checked for what the kernels rely on -- decode(encode(v)) is v rounded to 24 bits
+    (relative error <= 2^-16), and `hi` alone is a correctly rounded bf16 of v (half up instead of half to even: it
+    differs from torch's bf16 by at most one bf16 ulp and only where the discarded bits sit within 2^-8 of a tie).
+    The CUDA side is checked against the same fp32 references through the GEMM tests (`EPI_RES24` cases)."""
+    rng = np.random.default_rng(24)
+    v = np.concatenate([rng.standard_normal(200000).astype(np.float32) * 3.0,
+                        (rng.standard_normal(50000) * 1e-6).astype(np.float32),
+                        (rng.standard_normal(50000) * 1e6).astype(np.float32),
+                        np.array([0.0, -0.0, 1.0, -1.0, 65504.0, 2.0 ** -126, np.inf, -np.inf], np.float32)])
+    bits = v.view(np.uint32)
+    w = bits + np.uint32(0x8080)
+    hi = (w >> np.uint32(16)).astype(np.uint16)
+    lo = ((w >> np.uint32(8)) & np.uint32(0xff)).astype(np.uint8)
+    dec = (((hi.astype(np.uint32) << np.uint32(16)) | (lo.astype(np.uint32) << np.uint32(8))) - np.uint32(0x8000)).view(np.float32)
+    fin = np.isfinite(v)
+    assert np.array_equal(dec[~fin], v[~fin])
+    err = np.abs(dec[fin].astype(np.float64) - v[fin].astype(np.float64))
+    assert np.all(err <= np.abs(v[fin]).astype(np.float64) * 2.0 ** -16)
+    assert np.array_equal(dec.view(np.uint32) & np.uint32(0xff), np.zeros_like(bits))  # 24 bits: the low byte is clear
+    # re-encoding a decoded value is the identity (in-place updates of unchanged elements do not drift)
+    w2 = dec.view(np.uint32) + np.uint32(0x8080)
+    assert np.array_equal((w2 >> np.uint32(16)).astype(np.uint16), hi) and \
+        np.array_equal(((w2 >> np.uint32(8)) & np.uint32(0xff)).astype(np.uint8), lo)
+    # hi against torch's round-to-nearest-even bf16
+    tb = torch.from_numpy(v[fin]).bfloat16().view(torch.int16).numpy().view(np.uint16)
+    d = hi[fin].astype(np.int64) - tb.astype(np.int64)
+    assert np.all(np.abs(d) <= 1)
+    low16 = bits[fin] & np.uint32(0xffff)
+    assert np.all((d == 0) | ((low16 >= 0x7f80) & (low16 <= 0x8000))), "hi differs from bf16 RNE away from a tie"
