@@ -446,14 +446,20 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       uint32_t phase = 0;
       int it = 0;
 #ifdef ZV_TRACE
-      long long tr_mw = 0, tr_mi = 0, tr_mc = 0;
+      long long tr_mw = 0, tr_mi = 0, tr_mc = 0, tr_me = 0;
       const long long tr_m0 = clock64();
 #endif
       for (int t = unit0; t < total_tiles; t += nunits, ++it) {
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
+#ifdef ZV_TRACE
+        const long long e0 = clock64();
+#endif
         mbar_wait(&tail->tmem_empty[as], aphase ^ 1);
         tc_fence_after();
+#ifdef ZV_TRACE
+        tr_me += clock64() - e0;
+#endif
         const uint32_t d_tmem = tmem_base + as * ACC_STAGE_COLS;
         const uint32_t idesc = t < sched.main_units ? idesc_main : idesc_tail;
         for (int kb = 0; kb < k_blocks; ++kb) {
@@ -497,8 +503,8 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       }
 #ifdef ZV_TRACE
       if (blockIdx.x == 0)
-        printf("[trace] mma: wait_full %lld issue %lld commit %lld total %lld\n", tr_mw, tr_mi, tr_mc,
-               clock64() - tr_m0);
+        printf("[trace] mma: wait_acc_free %lld wait_full %lld issue %lld commit %lld total %lld\n", tr_me, tr_mw, tr_mi,
+               tr_mc, clock64() - tr_m0);
 #endif
     }
     __syncwarp();
