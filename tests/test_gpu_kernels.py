@@ -29,9 +29,10 @@ def run_gemm(mode, impl, A, W, bias, L=1, gate_cols=0, rowbias=None, res=None, r
              mask=None):
     M, K = A.shape
     N = W.shape[0]
-    n_out = N // 2 if mode == EPI_GLU else (gate_cols // 2 if mode == EPI_NONLIN else N)
+    split = mode == EPI_SWOOSHL and gate_cols > 0   # FF1 in_proj + attention q | k | p in one launch
+    n_out = N // 2 if mode == EPI_GLU else (gate_cols // 2 if mode == EPI_NONLIN else (gate_cols if split else N))
     out = torch.zeros(M, n_out, device="cuda")
-    out2 = torch.zeros(M, max(N - gate_cols, 1) if mode == EPI_NONLIN else N, device="cuda")
+    out2 = torch.zeros(M, max(N - gate_cols, 1) if (mode == EPI_NONLIN or split) else N, device="cuda")
     rc = _lib().zv_debug_gemm(mode, impl, M, N, K, L, gate_cols, _p(A), _p(W), _p(bias), _p(rowbias), _p(res),
                               _p(resbias), _p(orig), _p(bscale), _p(mask), _p(out), _p(out2), None)
     assert rc == 0, f"zv_debug_gemm rc={rc}"
@@ -47,6 +48,10 @@ def ref_gemm(mode, A, W, bias, L=1, gate_cols=0, rowbias=None, res=None, resbias
         acc = acc + rowbias[b]
     if mode == EPI_BIAS or mode == EPI_F32:
         return acc, None
+    if mode == EPI_SWOOSHL and gate_cols > 0:
+        # columns >= gate_cols: plain bias, no row bias, stored as fp16
+        tail = A.bfloat16().float() @ W.bfloat16().float().T[:, gate_cols:] + bias[gate_cols:]
+        return swoosh_l(acc[:, :gate_cols]), tail
     if mode == EPI_SWOOSHL:
         return swoosh_l(acc), None
     if mode == EPI_GLU:
@@ -80,6 +85,9 @@ CASES = [
     (EPI_BIAS, 130, 48, 512, {}),
     (EPI_SWOOSHL, 777, 1152, 512, {"rowbias": True, "L": 111}),
     (EPI_SWOOSHL, 640, 1920, 512, {}),
+    (EPI_SWOOSHL, 700, 1424, 512, {"rowbias": True, "L": 100, "gate_cols": 1152}),
+    (EPI_SWOOSHL, 40000, 1424, 512, {"rowbias": True, "L": 1219, "gate_cols": 1152}),
+    (EPI_SWOOSHL, 333, 656, 192, {"gate_cols": 384}),
     (EPI_GLU, 500, 1024, 512, {"mask": True, "L": 125}),
     (EPI_GLU, 200, 384, 192, {}),
     (EPI_NONLIN, 400, 1152, 512, {"gate_cols": 768}),
@@ -136,7 +144,7 @@ def test_gemm(case, impl):
     # bf16 outputs: 2^-9 rounding; s24: 16 significant bits (2^-17 per value, on the residual input and the output)
     tol = 2e-5 if mode in (EPI_F32, EPI_RESIDUAL, EPI_RES24) else 6e-3
     assert rel(out, want) < tol, f"rel-L2 {rel(out, want):.3e} max-abs {float((out - want).abs().max()):.3e}"
-    if mode == EPI_NONLIN:
+    if mode == EPI_NONLIN or (mode == EPI_SWOOSHL and ex.get("gate_cols")):
         assert rel(out2, want2) < 6e-3, f"out2 rel-L2 {rel(out2, want2):.3e}"
     if mode in (EPI_RESIDUAL, EPI_RES24):
         assert rel(out2, want2) < 6e-3, f"bf16 shadow rel-L2 {rel(out2, want2):.3e}"

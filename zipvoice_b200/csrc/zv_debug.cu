@@ -65,8 +65,10 @@ extern "C" int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int
   const int block_n = gemm_pick_block_n(N, mode, gate_cols);
   const int N_pad = (N + block_n - 1) / block_n * block_n;
   const int ld = (K + 63) / 64 * 64;
-  const int n_out = (mode == EPI_GLU_BF16) ? N / 2 : (mode == EPI_NONLIN_BF16 ? gate_cols / 2 : N);
-  const int n_out2 = mode == EPI_NONLIN_BF16 ? N - gate_cols : 0;
+  // EPI_SWOOSHL_BF16 with gate_cols > 0: columns >= gate_cols are the plain fp16 tail (out2)
+  const bool sw_split = mode == EPI_SWOOSHL_BF16 && gate_cols > 0;
+  const int n_out = (mode == EPI_GLU_BF16) ? N / 2 : (mode == EPI_NONLIN_BF16 ? gate_cols / 2 : (sw_split ? gate_cols : N));
+  const int n_out2 = (mode == EPI_NONLIN_BF16 || sw_split) ? N - gate_cols : 0;
   __nv_bfloat16 *A = nullptr, *W = nullptr, *ob = nullptr, *ob2 = nullptr;
   float* of = nullptr;
   cudaMalloc(&A, (size_t)M * ld * 2);
@@ -119,7 +121,12 @@ extern "C" int zv_debug_gemm(int mode, int impl, int M, int N, int K, int L, int
       cvt_back_f16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(reinterpret_cast<const __half*>(ob), n, out_f32);
     } else {
       cvt_back(ob, (size_t)M * n_out, out_f32, s);
-      if (n_out2) cvt_back(ob2, (size_t)M * n_out2, out2_f32, s);
+      if (n_out2 && sw_split) {
+        const size_t n2 = (size_t)M * n_out2;
+        cvt_back_f16_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(reinterpret_cast<const __half*>(ob2), n2, out2_f32);
+      } else if (n_out2) {
+        cvt_back(ob2, (size_t)M * n_out2, out2_f32, s);
+      }
     }
     rc = (int)cudaStreamSynchronize(s);
   }

@@ -229,6 +229,18 @@ static int build_layer(Engine& e, Net& net, const std::string& p, int kernel, La
     for (float& v : wps) v *= ATTN_LOG2E;
     ZV_TRY(pack_linear_host(e, ws.data(), bs.data(), N, K, EPI_BIAS_BF16, &L->attn_in, 0, nullptr));
     ZV_TRY(upload_f32(e, wps, &L->w_pos));
+    // [feed_forward1.in_proj | attention in_proj] as one weight matrix (Layer::ff1_qkp)
+    const HostTensor* w1 = find(e, p + ".feed_forward1.in_proj.weight");
+    const HostTensor* b1 = find(e, p + ".feed_forward1.in_proj.bias");
+    if (!w1 || !b1) return 940;
+    const int N1 = (int)w1->shape[0];
+    if ((int)w1->shape[1] == K && N1 % 32 == 0) {
+      std::vector<float> wc(w1->data), bc(b1->data);
+      wc.insert(wc.end(), ws.begin(), ws.end());
+      bc.insert(bc.end(), bs.begin(), bs.end());
+      ZV_TRY(pack_linear_host(e, wc.data(), bc.data(), N1 + N, K, EPI_SWOOSHL_BF16, &L->ff1_qkp, 0, nullptr));
+      L->ff1_qkp.gate_cols = N1;
+    }
   }
   for (int i = 0; i < 3; ++i) {
     const std::string f = p + ".feed_forward" + std::to_string(i + 1);
@@ -567,9 +579,14 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   ZV_TRY(get_pos_table(e, net, ly, L, s, &Etab, &Etab16));
   EpiParams ep;
   // attention projections from the layer input (before the time embedding is added) -- :526-531
-  ep = EpiParams();
-  ep.L = L, ep.out_bf16 = ws.qkp, ep.ld_bf16 = 288, ep.out_f16 = 1;  // q | k | p kept in fp16
-  ZV_TRY(run_gemm(e, ly.attn_in, X_hi, D, M, ep, s));
+  // ZV_MERGE_QKP=0: separate launches (A/B measurements)
+  static const bool merge_qkp = !(getenv("ZV_MERGE_QKP") && atoi(getenv("ZV_MERGE_QKP")) == 0);
+  const bool merged = merge_qkp && ly.ff1_qkp.w != nullptr;
+  if (!merged) {
+    ep = EpiParams();
+    ep.L = L, ep.out_bf16 = ws.qkp, ep.ld_bf16 = 288, ep.out_f16 = 1;  // q | k | p kept in fp16
+    ZV_TRY(run_gemm(e, ly.attn_in, X_hi, D, M, ep, s));
+  }
 
   // src: the stream state the module reads (X for the first feed-forward, ws.Y afterwards); every module writes ws.Y
   // from_x: the residual input is the layer input X (first module), else ws.Y updated in place
@@ -585,7 +602,13 @@ static int layer_forward(Engine& e, Net& net, Workspace& ws, Layer& ly, int kern
   auto ff = [&](int i, const float* rowbias, bool from_x, const float* resbias, bool bypass_x, const float* bscale) {
     EpiParams f;
     f.L = L, f.rowbias = rowbias, f.bias_ld = te_ld, f.out_bf16 = ws.hidden, f.ld_bf16 = ly.ff_in[i].N;
-    int rc = run_gemm(e, ly.ff_in[i], from_x ? X_hi : ws.Y_hi, D, M, f, s);
+    int rc;
+    if (i == 0 && merged) {  // + q | k | p (fp16, pitch 288) from the same rows, before the time embedding is added:
+      f.out2_bf16 = ws.qkp, f.ld2_bf16 = 288;  // the row bias (W_ff1 . time_emb) applies to the first part only
+      rc = run_gemm(e, ly.ff1_qkp, X_hi, D, M, f, s);
+    } else {
+      rc = run_gemm(e, ly.ff_in[i], from_x ? X_hi : ws.Y_hi, D, M, f, s);
+    }
     if (rc) return rc;
     return residual(ly.ff_out[i], ws.hidden, ly.ff_in[i].N, from_x, resbias, bypass_x, bscale);
   };

@@ -28,6 +28,10 @@ struct Lin {
 
 struct Layer {
   Lin attn_in, ff_in[3], ff_out[3], na_in, na_out, sa_in[2], conv_in[2], conv_out[2];  // SelfAttention.out_proj lives inside conv_in / conv_out
+  // feed_forward1.in_proj and the attention q | k | p projection read the same rows (the layer input): one launch,
+  // weight rows [FF1 in_proj | attention in_proj], EPI_SWOOSHL_BF16 with gate_cols = FF1's width.  attn_in and
+  // ff_in[0] above stay packed for the measurement switch ZV_MERGE_QKP=0.
+  Lin ff1_qkp;
   float* w_pos = nullptr;  // [H*dp][pos_dim]
   float* dw_w[2] = {nullptr, nullptr};
   float* dw_b[2] = {nullptr, nullptr};

@@ -38,12 +38,19 @@ ZV_DEVINL void epi_apply(const EpiParams& ep, int m, int b, int n0, const float 
     float x = acc[i];
     if (i < nvalid) {
       x += __ldg(ep.bias + n0 + i);
-      if (MODE != EPI_RESIDUAL && MODE != EPI_RES24 && ep.rowbias)
+      if (MODE != EPI_RESIDUAL && MODE != EPI_RES24 && ep.rowbias &&
+          !(MODE == EPI_SWOOSHL_BF16 && ep.gate_cols > 0 && n0 >= ep.gate_cols))
         x += __ldg(ep.rowbias + (size_t)b * ep.bias_ld + n0 + i);
     }
     v[i] = x;
   }
-  if (MODE == EPI_BIAS_BF16 || MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GELU_BF16) {
+  if (MODE == EPI_SWOOSHL_BF16 && ep.gate_cols > 0 && n0 >= ep.gate_cols) {
+    // plain fp16 tail of a split launch (see the tcgen05 epilogue): no row bias, no activation
+    __half* oh = reinterpret_cast<__half*>(ep.out2_bf16) + (size_t)m * ep.ld2_bf16 + (n0 - ep.gate_cols);
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < nvalid) oh[i] = f2h_sat(acc[i] + __ldg(ep.bias + n0 + i));
+  } else if (MODE == EPI_BIAS_BF16 || MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GELU_BF16) {
     __nv_bfloat16* o = ep.out_bf16 + (size_t)m * ep.ld_bf16 + n0;
     if (MODE == EPI_SWOOSHL_BF16) {
 #pragma unroll
@@ -776,13 +783,18 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           continue;
         }
         // ---- bf16 outputs
-        add_bias32(v, ep.bias, rowb, n0, ep.N);
+        // EPI_SWOOSHL_BF16 with gate_cols > 0: columns >= gate_cols are a second, plain projection of the same A rows
+        // (the attention q | k | p of the layer beside the first feed-forward's in_proj): bias only, saturating fp16
+        const bool tail16 = MODE == EPI_SWOOSHL_BF16 && ep.gate_cols > 0 && n0 >= ep.gate_cols;
+        add_bias32(v, ep.bias, tail16 ? nullptr : rowb, n0, ep.N);
         uint8_t* sbuf = stg + (nq & 1) * STG_BF16_BYTES;
         const bool gated = (MODE == EPI_GLU_BF16) || (MODE == EPI_NONLIN_BF16 && n0 < ep.gate_cols);
         float o16[16];
         if (MODE == EPI_SWOOSHL_BF16) {
+          if (!tail16) {
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) swoosh_l_fast2(v[i], v[i + 1]);
+            for (int i = 0; i < 32; i += 2) swoosh_l_fast2(v[i], v[i + 1]);
+          }
         } else if (MODE == EPI_GELU_BF16) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
@@ -800,13 +812,14 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         __syncwarp();
         // every warp owns bytes [q * 2048, q * 2048 + 2048) of the buffer for both row widths (gated rows use half)
         if (gated) stage_row_bf16x16(sbuf + q * 2048, lane, o16);
-        else if (MODE == EPI_BIAS_BF16 && ep.out_f16) stage_row_f16x32(sbuf, r, v);
+        else if ((MODE == EPI_BIAS_BF16 && ep.out_f16) || tail16) stage_row_f16x32(sbuf, r, v);
         else stage_row_bf16x32(sbuf, r, v);
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
           const uint8_t* src = sbuf + q * 2048;
-          if (MODE == EPI_NONLIN_BF16 && !gated) tma_store_2d(&maps.O1, src, n0 - ep.gate_cols, m_blk * BM + q * 32);
+          if ((MODE == EPI_NONLIN_BF16 && !gated) || tail16)
+            tma_store_2d(&maps.O1, src, n0 - ep.gate_cols, m_blk * BM + q * 32);
           else tma_store_2d(&maps.O0, src, gated ? (n0 >> 1) : n0, m_blk * BM + q * 32);
           tma_store_commit();
         }
@@ -1151,7 +1164,12 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
                       (uint32_t)(pair ? p.block_n / 2 : p.block_n), 64, 128);
   if (rc) return rc;
   const uint64_t Mu = (uint64_t)ep.M;
-  if (MODE == EPI_BIAS_BF16 || MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GELU_BF16) {
+  if (MODE == EPI_SWOOSHL_BF16 && ep.gate_cols > 0) {
+    if (ep.gate_cols % 32 || ep.gate_cols >= ep.N || !ep.out2_bf16) return 909;
+    rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.gate_cols, (uint64_t)ep.ld_bf16, 32, 32, 64);
+    if (!rc)
+      rc = make_tmap_impl(&maps.O1, ep.out2_bf16, 0, Mu, (uint64_t)(ep.N - ep.gate_cols), (uint64_t)ep.ld2_bf16, 32, 32, 64);
+  } else if (MODE == EPI_BIAS_BF16 || MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GELU_BF16) {
     rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N, (uint64_t)ep.ld_bf16, 32, 32, 64);
   } else if (MODE == EPI_GLU_BF16) {
     rc = make_tmap_impl(&maps.O0, ep.out_bf16, 0, Mu, (uint64_t)ep.N / 2, (uint64_t)ep.ld_bf16, 32, 16, 32);

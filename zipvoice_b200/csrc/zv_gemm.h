@@ -10,6 +10,8 @@ namespace zv {
 enum EpiMode : int {
   EPI_BIAS_BF16 = 0,  // out_bf16 = acc + bias (+ rowbias[b])
   EPI_SWOOSHL_BF16 = 1,  // out_bf16 = SwooshL(acc + bias + rowbias[b])            (FF in_proj)
+                         // with gate_cols > 0 (multiple of 32): columns >= gate_cols are a second projection of the
+                         // same rows, out2 = fp16(acc + bias), saturating  (attention q | k | p beside FF1's in_proj)
   EPI_GLU_BF16 = 2,      // cols come in groups of 32 = [16 x | 16 s]; out = x*sigmoid(s), masked frames -> 0
   EPI_NONLIN_BF16 = 3,   // cols < gate_cols: groups of 32 = [16 s | 16 x] -> out = x*tanh(s);
                          // cols >= gate_cols: out2 = acc + bias                     (NonlinAttention in_proj)
