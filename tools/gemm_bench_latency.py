@@ -6,7 +6,7 @@ import torch
 from zipvoice_b200 import _lib
 lib = _lib.load()
 torch.zeros(1, device="cuda")
-MODES = {"bias": 0, "swooshl": 1, "glu": 2, "nonlin": 3, "residual": 4}
+MODES = {"bias": 0, "swooshl": 1, "glu": 2, "nonlin": 3, "residual": 8}   # 8: the s24 residual epilogue of the layers
 def run(name, M, N, K, iters=50):
     ms = C.c_float()
     rc = lib.zv_debug_gemm_bench(MODES[name], 0, M, N, K, M, 0, 0, iters, C.byref(ms))
@@ -16,7 +16,9 @@ def run_nl(M, iters=50):
     rc = lib.zv_debug_gemm_bench(3, 0, M, 1152, 512, M, 768, 0, iters, C.byref(ms))
     print(f"nonlin    M={M:5d} N=1152 K= 512 rc={rc} {ms.value*1e3:7.2f} us")
 for M in (750, 1500, 3000):
+    run("residual", M, 512, 1920)
     run("residual", M, 512, 1536)
+    run("residual", M, 512, 1152)
     run("residual", M, 512, 576)
     run("residual", M, 512, 384)
     run("swooshl", M, 1536, 512)
