@@ -325,10 +325,11 @@ TRAFFIC_PREFIX = {"gemm_residual": ["gemm_tc_kernel<7,", "gemm_tc_kernel<4,"], "
 
 
 def ncu_traffic(kernel_class: str):
-    """DRAM bytes per launch of the dominant kernel from the newest committed `ncu --set full` capture
+    """DRAM bytes per launch of the dominant kernel from the latest committed `ncu --set full` capture
     (profiles/r*_traffic.json, keys = demangled kernel names; matched by prefix so that added template
     arguments do not break the lookup)."""
-    tfiles = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")), key=os.path.getmtime)
+    # newest set = highest pass tag (r1e < r1k < r2j < r2r ...): file times are meaningless after a checkout
+    tfiles = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")), key=os.path.basename)
     prefixes = TRAFFIC_PREFIX.get(kernel_class, [])
     for tpath in reversed(tfiles):
         tj = json.load(open(tpath))
