@@ -373,6 +373,12 @@ ZV_DEVINL uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
 ZV_DEVINL void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// The same without release semantics: for hand-overs that carry no generic-proxy memory (a TMEM accumulator stage
+// whose reads are ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync).  The cluster-scope release of the
+// form above costs ~1000 cycles per arrive inside a busy epilogue warp (measured, ZV_TRACE).
+ZV_DEVINL void mbar_arrive_cluster_relaxed(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 // 2D tiled load into THIS CTA's shared memory whose completion bytes are signalled on an mbarrier of
 // either CTA of the pair (cluster address): both CTAs of a pair feed the leader's full barrier.
 ZV_DEVINL void tma_load_2d_pair(void* smem_dst, const void* desc, uint32_t bar_cluster_addr, int c0, int c1) {

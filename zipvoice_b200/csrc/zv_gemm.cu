@@ -546,7 +546,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     // EPI_RESIDUAL: the leader prefetches the first residual chunk of this group
     // tmem_empty lives in the leader CTA of a pair
     auto release_acc = [&](int as) {
-      if (PAIR) mbar_arrive_cluster(mapa_shared(smem_u32(&tail->tmem_empty[as]), 0));
+      if (PAIR) mbar_arrive_cluster_relaxed(mapa_shared(smem_u32(&tail->tmem_empty[as]), 0));
       else mbar_arrive(&tail->tmem_empty[as]);
     };
     // Every epilogue warp is its own pipeline: it stages, loads and stores only its 32 rows (TMA boxes of
@@ -1146,12 +1146,21 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
     cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
   }
   const int m_tiles_all = (p.M + BM - 1) / BM;
-  // CTA pairs (cta_group::2) halve the W bytes each SM pulls from L2.  Measured per shape at M = 156 k
-  // (tools/gemm_bench.py): they win where the epilogue is light relative to the main loop -- residual GEMMs
-  // with K >= 1024 (246 vs 261 us at K = 1536) -- and lose or tie for the SwooshL / GLU / tanh-gate epilogues
-  // and the short-K HBM-bound residual GEMMs, which stay on single-CTA tiles.
+  // CTA pairs (cta_group::2) halve the W bytes each SM pulls from L2 (a single-CTA 128 x 256 tile at K = 512 pulls
+  // 384 KB through its SM's L2 port and its MMA thread waits for operands 22-27 % of the time) and halve the number of
+  // tcgen05.mma / commit issues per FLOP.  Measured per shape at M = 156 k (tools/gemm_bench.py, after the accumulator
+  // release of a pair stopped using a cluster-scope RELEASE arrive -- ~1000 cycles each inside a busy epilogue warp):
+  // pairs against single-CTA tiles, SwooshL N = 1152 / 1536 / 1920 165 / 200 / 265 against 174 / 210 / 271 us, GLU 118
+  // against 132, tanh gate 140 against 143, s24 residual K = 1152 / 1536 / 1920 149 / 181 / 214 against 177 / 218 /
+  // 261; a tie for the short-K residual shapes (K = 384 / 576) and the narrow q | k | p projection, which stay on
+  // single-CTA tiles.
   const bool big = (long long)m_tiles_all * (p.N_pad / p.block_n) >= 2LL * g_num_sms;
-  const bool pair = impl == 3 || (impl == 0 && big && (MODE == EPI_RESIDUAL || MODE == EPI_RES24) && p.K >= 1024);
+  // ZV_GEMM_PAIR_INPROJ=0: single-CTA tiles for the in-proj epilogues (A/B measurements)
+  static const bool pair_inproj = !(getenv("ZV_GEMM_PAIR_INPROJ") && atoi(getenv("ZV_GEMM_PAIR_INPROJ")) == 0);
+  const bool pair = impl == 3 ||
+                    (impl == 0 && big &&
+                     (((MODE == EPI_RESIDUAL || MODE == EPI_RES24) && p.K >= 1024) ||
+                      (pair_inproj && (MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GLU_BF16 || MODE == EPI_NONLIN_BF16))));
   GemmMaps maps;
   memset(&maps, 0, sizeof(maps));
   const int k_a = p.A2 ? p.k_split : p.K;
