@@ -542,6 +542,10 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     const int r = q * 32 + lane;       // row within the tile
     uint8_t* stg = sStg + cg * stg_group_bytes(MODE);
     uint32_t nq = 0;  // chunks processed by this group (selects the staging buffer / residual barrier phase)
+#ifdef ZV_TRACE  // cycles of one epilogue warp per phase (bf16-output modes)
+    long long et_acc = 0, et_ld = 0, et_math = 0, et_stw = 0, et_stg = 0;
+    const long long et_0 = clock64();
+#endif
 
     // EPI_RESIDUAL: the leader prefetches the first residual chunk of this group
     // tmem_empty lives in the leader CTA of a pair
@@ -596,8 +600,15 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       // whose prefetch chain assumes full tiles: its N is a multiple of block_n)
       const int nchunks = (MODE == EPI_RESIDUAL || MODE == EPI_RES24) ? nchunks_tile
                                                                       : min(nchunks_tile, (ep.N - n0t + 31) >> 5);
+#ifdef ZV_TRACE
+      long long et_c = clock64();
+#define ZV_ET(acc) { const long long c_ = clock64(); acc += c_ - et_c; et_c = c_; }
+#else
+#define ZV_ET(acc)
+#endif
       mbar_wait(&tail->tmem_full[as], aphase);
       tc_fence_after();
+      ZV_ET(et_acc)
       if (cg >= nchunks) {  // this group owns no chunk of the tile: release the accumulator right away
         tc_fence_before();
         __syncwarp();
@@ -783,6 +794,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           continue;
         }
         // ---- bf16 outputs
+        ZV_ET(et_ld)
         // EPI_SWOOSHL_BF16 with gate_cols > 0: columns >= gate_cols are a second, plain projection of the same A rows
         // (the attention q | k | p of the layer beside the first feed-forward's in_proj): bias only, saturating fp16
         const bool tail16 = MODE == EPI_SWOOSHL_BF16 && ep.gate_cols > 0 && n0 >= ep.gate_cols;
@@ -808,8 +820,10 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
             for (int i = 0; i < 16; ++i) o16[i] = v[16 + i] * tanh_approx(v[i]);
           }
         }
+        ZV_ET(et_math)
         if (lane == 0) tma_store_wait_read<1>();  // the store that last used this staging buffer has read it
         __syncwarp();
+        ZV_ET(et_stw)
         // every warp owns bytes [q * 2048, q * 2048 + 2048) of the buffer for both row widths (gated rows use half)
         if (gated) stage_row_bf16x16(sbuf + q * 2048, lane, o16);
         else if ((MODE == EPI_BIAS_BF16 && ep.out_f16) || tail16) stage_row_f16x32(sbuf, r, v);
@@ -823,9 +837,15 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           else tma_store_2d(&maps.O0, src, gated ? (n0 >> 1) : n0, m_blk * BM + q * 32);
           tma_store_commit();
         }
+        ZV_ET(et_stg)
       }
     }
     if (lane == 0) tma_store_wait_all<0>();
+#ifdef ZV_TRACE
+    if (blockIdx.x == 0 && lane == 0 && (warp == 4 || warp == 13))
+      printf("[trace] epilogue warp %d: chunks %u wait_acc %lld tmem_ld+release %lld math %lld wait_store %lld "
+             "stage+store %lld total %lld\n", warp, nq, et_acc, et_ld, et_math, et_stw, et_stg, clock64() - et_0);
+#endif
   }
   tc_fence_before();
   __syncthreads();
