@@ -1180,7 +1180,8 @@ static int launch_mode(const __nv_bfloat16* A, const __nv_bfloat16* W, const Gem
   const bool pair = impl == 3 ||
                     (impl == 0 && big &&
                      (((MODE == EPI_RESIDUAL || MODE == EPI_RES24) && p.K >= 1024) ||
-                      (pair_inproj && (MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GLU_BF16 || MODE == EPI_NONLIN_BF16))));
+                      (pair_inproj && (MODE == EPI_SWOOSHL_BF16 || MODE == EPI_GLU_BF16 || MODE == EPI_NONLIN_BF16 ||
+                                      MODE == EPI_GELU_BF16))));
   GemmMaps maps;
   memset(&maps, 0, sizeof(maps));
   const int k_a = p.A2 ? p.k_split : p.K;
