@@ -503,7 +503,8 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
 
   const uint32_t tmem_base = sm.tmem_base;
   if (warp == MMA_WARP) {
-    if (lane == 0) {
+    const bool issuer = elect_one();  // uniform loop, one elected lane issues: operands stay in uniform registers
+    {
       const uint32_t idesc_s = sa::make_idesc_f16(BQ, BKV), idesc_d = sa::make_idesc_f16(BQ, D_N);
       mbar_wait(&sm.qbar, 0);
       const uint64_t dq = sa::make_sdesc_sw64(smem_u32(&sm.q[0][0]));
@@ -516,23 +517,29 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
         const uint64_t dk = sa::make_sdesc_sw64(smem_u32(&sm.k[st][0][0]));
         const uint64_t dwe = make_sdesc_kmajor_plain(smem_u32(&sm.we[st][0]), 16, 128);
         const uint64_t dwo = make_sdesc_kmajor_plain(smem_u32(&sm.wo[st][0]), 16, 128);
+        if (issuer) {
 #pragma unroll
-        for (int k = 0; k < DQ / 16; ++k) sa::umma_f16(tmem_base + COL_S, dq + 2 * k, dk + 2 * k, idesc_s, k);
+          for (int k = 0; k < DQ / 16; ++k) sa::umma_f16(tmem_base + COL_S, dq + 2 * k, dk + 2 * k, idesc_s, k);
 #pragma unroll
-        for (int k = 0; k < 2; ++k) sa::umma_f16(tmem_base + COL_DE, dap + 2 * k, dwe + 2 * k, idesc_d, k);
+          for (int k = 0; k < 2; ++k) sa::umma_f16(tmem_base + COL_DE, dap + 2 * k, dwe + 2 * k, idesc_d, k);
 #pragma unroll
-        for (int k = 0; k < 2; ++k) sa::umma_f16(tmem_base + COL_DO, dap + 2 * k, dwo + 2 * k, idesc_d, k);
-        umma_commit(&sm.sfull);
+          for (int k = 0; k < 2; ++k) sa::umma_f16(tmem_base + COL_DO, dap + 2 * k, dwo + 2 * k, idesc_d, k);
+          umma_commit(&sm.sfull);
+        }
+        __syncwarp();
       }
     }
     __syncwarp();
   } else if (warp == PRODUCER_WARP) {
-    if (lane == 0) {
-      tma_prefetch_desc(&tmQK);
-      tma_prefetch_desc(&tmV);
-      mbar_arrive_expect_tx(&sm.qbar, BQ * DQ * 2);
-      tma_load_2d(&sm.q[0][0], &tmQK, &sm.qbar, head * DQ, b * L + i0);
-      tma_load_2d(&sm.q[64][0], &tmQK, &sm.qbar, head * DQ, b * L + i0 + 64);
+    const bool issuer = elect_one();
+    {
+      if (issuer) {
+        tma_prefetch_desc(&tmQK);
+        tma_prefetch_desc(&tmV);
+        mbar_arrive_expect_tx(&sm.qbar, BQ * DQ * 2);
+        tma_load_2d(&sm.q[0][0], &tmQK, &sm.qbar, head * DQ, b * L + i0);
+        tma_load_2d(&sm.q[64][0], &tmQK, &sm.qbar, head * DQ, b * L + i0 + 64);
+      }
       const uint2* Ea = reinterpret_cast<const uint2*>(p.E16) + (size_t)head * p.e16_stride;
       const uint2* Eb = Ea + (size_t)H * p.e16_stride;
       for (int kt = kt0; kt < kt1; ++kt) {
@@ -542,11 +549,14 @@ attn_sa2_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant_
         const int x0 = (j0 - i0 - (BQ - 1)) + (L - 1) + POS16_PADL;  // padded-table entry of window entry 0 (>= 1)
         const uint2* src_e = (x0 & 1) ? Eb + (x0 - 1) : Ea + x0;       // both sources start at an even entry:
         const uint2* src_o = (x0 & 1) ? Ea + (x0 + 1) : Eb + x0;       // 16-byte aligned
-        mbar_arrive_expect_tx(&sm.full[s], BKV * DQ * 2 + BKV * DVP * 2 + 2 * EW16 * 8);
-        tma_load_2d(&sm.k[s][0][0], &tmQK, &sm.full[s], H * DQ + head * DQ, b * L + j0);
-        tma_load_2d(&sm.v[s][0][0], &tmV, &sm.full[s], head * DVP, b * L + j0);
-        sa::bulk_load_1d(&sm.we[s][0], src_e, EW16 * 8, &sm.full[s]);
-        sa::bulk_load_1d(&sm.wo[s][0], src_o, EW16 * 8, &sm.full[s]);
+        if (issuer) {
+          mbar_arrive_expect_tx(&sm.full[s], BKV * DQ * 2 + BKV * DVP * 2 + 2 * EW16 * 8);
+          tma_load_2d(&sm.k[s][0][0], &tmQK, &sm.full[s], H * DQ + head * DQ, b * L + j0);
+          tma_load_2d(&sm.v[s][0][0], &tmV, &sm.full[s], head * DVP, b * L + j0);
+          sa::bulk_load_1d(&sm.we[s][0], src_e, EW16 * 8, &sm.full[s]);
+          sa::bulk_load_1d(&sm.wo[s][0], src_o, EW16 * 8, &sm.full[s]);
+        }
+        __syncwarp();
       }
     }
     __syncwarp();

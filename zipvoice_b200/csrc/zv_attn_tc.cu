@@ -184,6 +184,8 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
 
   if (warp == LOAD_WARP) {
     // ---------------- producer: Q once, then K tile + position window of every key tile of every sweep
+    // (the whole warp walks the loops, one elected lane issues: operands stay in uniform registers, see elect_one)
+    const bool issuer = elect_one();
     int g = 0;
     auto load_k = [&](int kt) {
       const int st = g % KSTAGES;
@@ -192,40 +194,49 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
       const int rr0 = (j0 - i0 - (BQ - 1)) + (L - 1);  // table row of window entry 0
       const int lo = max(rr0, 0), hi = min(rr0 + EWIN, R);
       const uint32_t ebytes = hi > lo ? (uint32_t)(hi - lo) * 16u : 0u;
-      mbar_arrive_expect_tx(&sm.kfull[st], BKV * DQ * 2 + ebytes);
-      tma_load_2d(&sm.k[st][0][0], &tmQK, &sm.kfull[st], H * DQ, b * L + j0);
-      if (ebytes) bulk_load_1d(&sm.e[st][lo - rr0], E + lo, ebytes, &sm.kfull[st]);
+      if (issuer) {
+        mbar_arrive_expect_tx(&sm.kfull[st], BKV * DQ * 2 + ebytes);
+        tma_load_2d(&sm.k[st][0][0], &tmQK, &sm.kfull[st], H * DQ, b * L + j0);
+        if (ebytes) bulk_load_1d(&sm.e[st][lo - rr0], E + lo, ebytes, &sm.kfull[st]);
+      }
+      __syncwarp();
       ++g;
     };
-    if (lane == 0) {
-      tma_prefetch_desc(&tmQK);
-      mbar_arrive_expect_tx(&sm.qbar, BQ * DQ * 2);
-      tma_load_2d(&sm.q[0][0], &tmQK, &sm.qbar, 0, b * L + i0);
-      tma_load_2d(&sm.q[64][0], &tmQK, &sm.qbar, 0, b * L + i0 + 64);
+    {
+      if (issuer) {
+        tma_prefetch_desc(&tmQK);
+        mbar_arrive_expect_tx(&sm.qbar, BQ * DQ * 2);
+        tma_load_2d(&sm.q[0][0], &tmQK, &sm.qbar, 0, b * L + i0);
+        tma_load_2d(&sm.q[64][0], &tmQK, &sm.qbar, 0, b * L + i0 + 64);
+      }
       load_k(0);
       if (kd != 0) load_k(kd);
       for (int kt = 0; kt < n_tiles; ++kt) load_k(kt);
     }
     __syncwarp();
     named_bar_sync(2, THREADS);
-    if (sm.redo != 0 && lane == 0) {
+    if (sm.redo != 0) {
       for (int kt = 0; kt < 2 * n_tiles; ++kt) load_k(kt < n_tiles ? kt : kt - n_tiles);
     }
     __syncwarp();
   } else if (warp == MMA_WARP) {
     // ---------------- producer: X tiles by TMA, P.X by tcgen05.mma.  c counts tiles over both value sweeps.
+    const bool issuer = elect_one();  // uniform loops, one elected lane issues
     // v counts the uses of the X ring (value tiles, then the two halves of the gate tile of every sweep)
     auto load_v = [&](int v, int kt) {
       const int c = v;
       const int st = c % VSTAGES;
       if (c >= VSTAGES) mbar_wait(&sm.vfree[st], ((c / VSTAGES) - 1) & 1);  // tile c - VSTAGES consumed
       if (p.dbg & 1) {
-        mbar_arrive(&sm.vfull[st]);
+        if (issuer) mbar_arrive(&sm.vfull[st]);
         return;
       }
-      mbar_arrive_expect_tx(&sm.vfull[st], v_stage_bytes);
-      for (int cc = 0; cc < nvbox; ++cc)
-        tma_load_2d(&sm.v[st][cc][0][0], &tmV, &sm.vfull[st], zc + cc * 64, b * L + kt * BKV);
+      if (issuer) {
+        mbar_arrive_expect_tx(&sm.vfull[st], v_stage_bytes);
+        for (int cc = 0; cc < nvbox; ++cc)
+          tma_load_2d(&sm.v[st][cc][0][0], &tmV, &sm.vfull[st], zc + cc * 64, b * L + kt * BKV);
+      }
+      __syncwarp();
     };
     // The gate tile y[128 queries][<= 384] of the epilogue rides behind the value tiles in the same ring: its two
     // halves (3 boxes of 128 rows x 64 channels = one 48 KB stage each) are uses n_tiles and n_tiles + 1 of the
@@ -235,13 +246,16 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
       if (v >= VSTAGES) mbar_wait(&sm.vfree[st], ((v / VSTAGES) - 1) & 1);
       const int nbox = min(3, nvbox - 3 * part);
       if (!p.gate || nbox <= 0) {
-        mbar_arrive(&sm.vfull[st]);
+        if (issuer) mbar_arrive(&sm.vfull[st]);
         return;
       }
-      mbar_arrive_expect_tx(&sm.vfull[st], (uint32_t)nbox * BQ * 128);
-      for (int cc = 0; cc < nbox; ++cc)
-        tma_load_2d(reinterpret_cast<uint8_t*>(&sm.v[st][0][0][0]) + cc * (BQ * 128), &tmG, &sm.vfull[st],
-                    zc + (3 * part + cc) * 64, b * L + i0);
+      if (issuer) {
+        mbar_arrive_expect_tx(&sm.vfull[st], (uint32_t)nbox * BQ * 128);
+        for (int cc = 0; cc < nbox; ++cc)
+          tma_load_2d(reinterpret_cast<uint8_t*>(&sm.v[st][0][0][0]) + cc * (BQ * 128), &tmG, &sm.vfull[st],
+                      zc + (3 * part + cc) * 64, b * L + i0);
+      }
+      __syncwarp();
     };
     const uint32_t id0 = make_idesc_bf16_bmn(BQ, n_mma0), id1 = make_idesc_bf16_bmn(BQ, max(n_mma1, 16));
     // c0 / v0: P-buffer and X-ring use counters at entry
@@ -261,32 +275,39 @@ attn_na_tc_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant
         tc_fence_after();
         const uint64_t da = make_sdesc_sw128(smem_u32(&sm.p[pb][0][0]));
         const uint32_t vaddr = smem_u32(&sm.v[st][0][0][0]);
+        if (issuer) {
 #pragma unroll
-        for (int k = 0; k < ((p.dbg & 2) ? 0 : BKV / 16); ++k) {
-          const uint64_t db0 = make_sdesc_mn_sw128(vaddr + k * 2048, BKV * 128, 1024);
-          umma_bf16(tmem_base, da + 2 * k, db0, id0, (kt | k) != 0 ? 1u : 0u);
-          if (n_mma1 > 0) {
-            const uint64_t db1 = make_sdesc_mn_sw128(vaddr + (n_mma0 / 64) * (BKV * 128) + k * 2048, BKV * 128, 1024);
-            umma_bf16(tmem_base + n_mma0, da + 2 * k, db1, id1, (kt | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < ((p.dbg & 2) ? 0 : BKV / 16); ++k) {
+            const uint64_t db0 = make_sdesc_mn_sw128(vaddr + k * 2048, BKV * 128, 1024);
+            umma_bf16(tmem_base, da + 2 * k, db0, id0, (kt | k) != 0 ? 1u : 0u);
+            if (n_mma1 > 0) {
+              const uint64_t db1 =
+                  make_sdesc_mn_sw128(vaddr + (n_mma0 / 64) * (BKV * 128) + k * 2048, BKV * 128, 1024);
+              umma_bf16(tmem_base + n_mma0, da + 2 * k, db1, id1, (kt | k) != 0 ? 1u : 0u);
+            }
           }
+          umma_commit(&sm.vfree[st]);
+          umma_commit(&sm.pfree[pb]);
+          if (kt == n_tiles - 1) umma_commit(&sm.obar);
         }
-        umma_commit(&sm.vfree[st]);
-        umma_commit(&sm.pfree[pb]);
-        if (kt == n_tiles - 1) umma_commit(&sm.obar);
+        __syncwarp();
       }
     };
-    if (lane == 0) {
-      tma_prefetch_desc(&tmV);
-      if (p.gate) tma_prefetch_desc(&tmG);
+    {
+      if (issuer) {
+        tma_prefetch_desc(&tmV);
+        if (p.gate) tma_prefetch_desc(&tmG);
+      }
       value_sweep(0, 0);
     }
     __syncwarp();
     named_bar_sync(2, THREADS);
-    if (sm.redo != 0 && lane == 0) {
+    if (sm.redo != 0) {
       // the gate halves of the abandoned sweep are not consumed by any MMA: retire them by hand
       for (int v = n_tiles; v < n_tiles + 2; ++v) {
         mbar_wait(&sm.vfull[v % VSTAGES], (v / VSTAGES) & 1);
-        mbar_arrive(&sm.vfree[v % VSTAGES]);
+        if (issuer) mbar_arrive(&sm.vfree[v % VSTAGES]);
+        __syncwarp();
       }
       value_sweep(n_tiles, n_tiles + 2);
     }

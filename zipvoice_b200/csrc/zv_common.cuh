@@ -326,6 +326,20 @@ ZV_DEVINL float swoosh_r_fast(float x) {
 ZV_DEVINL float sigmoid_fast(float x) { return rcp_approx(1.0f + ex2_approx(-1.4426950408889634f * x)); }
 
 // ------------------------------------------------------------------ tcgen05 / TMEM
+// One lane of a converged warp (always the same one for the full mask).  The single-thread tcgen05 / TMA instructions
+// take their operands from UNIFORM registers: issued from `if (lane == 0)` code every operand is a per-lane value for
+// the compiler and each instruction is preceded by seven R2UR broadcasts inside a waterfall loop (~90 cycles per
+// tcgen05.mma, measured with ZV_TRACE); issued by an elected lane of warp-uniform code the operands stay in uniform
+// registers.
+ZV_DEVINL bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 ZV_DEVINL void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 ZV_DEVINL void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
