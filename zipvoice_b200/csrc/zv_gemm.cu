@@ -1124,7 +1124,8 @@ static int launch_tc(const GemmMaps& maps_in, const __nv_bfloat16* W, const Gemm
   }
   const int nunits = min(sched.total_units, max_units);
   // one tile per CTA and at least two K steps: split the K loop over two issuing threads / accumulators
-  const bool dual = !PAIR && tail_split >= 2 && sched.total_units <= max_units && k_blocks >= 2;
+  static const bool dual_on = !(getenv("ZV_GEMM_DUAL") && atoi(getenv("ZV_GEMM_DUAL")) == 0);  // A/B measurements
+  const bool dual = dual_on && !PAIR && tail_split >= 2 && sched.total_units <= max_units && k_blocks >= 2;
   if (dual) {
     static unsigned long long attr_dual = 0;
     if (first_use_on_device(attr_dual)) {
