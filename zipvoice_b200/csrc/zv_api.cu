@@ -1,6 +1,7 @@
 // extern "C" surface of libzipvoice_b200.so (declared in include/zipvoice_b200.h).
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <utility>
@@ -477,7 +478,9 @@ extern "C" int zv_sample(void* handle, int variant, const float* x0, const float
   API_TRY(upload_small(e, e->ws_fm.guid_dev, guidance, guidance_len, s));
   const size_t n = (size_t)B * T * e->fm.out_dim;
   const bool cfg2 = (variant == 0) && !all_zero;
-  if (e->graph_max_rows > 0 && !e->prof.on && (size_t)(cfg2 ? 2 : 1) * B * T <= (size_t)e->graph_max_rows)
+  static const bool graph_off = getenv("ZV_GRAPH") && atoi(getenv("ZV_GRAPH")) == 0;  // ZV_GRAPH=0: debugging
+  if (!graph_off && e->graph_max_rows > 0 && !e->prof.on &&
+      (size_t)(cfg2 ? 2 : 1) * B * T <= (size_t)e->graph_max_rows)
     return sample_graphed(e, variant, x0, text, speech, mask, B, T, num_step, all_zero, guidance_len, t_start, t_end,
                           t_shift, ts, x1, s);
   if (x1 != x0) API_TRY((int)cudaMemcpyAsync(x1, x0, n * 4, cudaMemcpyDeviceToDevice, s));

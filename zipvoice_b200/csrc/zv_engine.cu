@@ -23,13 +23,19 @@ long long g_launch_count = 0;
     }                                                                                 \
   } while (0)
 // One kernel launch of class `cls` doing `work` algorithmic FLOPs / bytes.
+// ZV_SYNC_EACH=1 (debugging): synchronise after every launch outside stream capture and name the class that failed
+static const bool g_sync_each = getenv("ZV_SYNC_EACH") && atoi(getenv("ZV_SYNC_EACH")) != 0;
+static int sync_each_check(Engine& e, int cls, cudaStream_t s);
+const char* kclass_name(int c);
 #define ZV_K(cls, work, s, expr)              \
   do {                                        \
     ++g_launch_count;                         \
     if (e.prof.on) e.prof.begin(cls, work, s); \
     int _krc = (expr);                        \
     if (e.prof.on) e.prof.end(s);             \
+    if (_krc) fprintf(stderr, "[zv] launch %lld (class %s) returned %d\n", (long long)g_launch_count, kclass_name(cls), _krc); \
     ZV_TRY(_krc);                             \
+    if (g_sync_each) ZV_TRY(sync_each_check(e, cls, s)); \
   } while (0)
 
 static const char* kNames[KC_COUNT] = {"gemm_bias", "gemm_swooshl", "gemm_glu", "gemm_nonlin", "gemm_residual",
@@ -37,6 +43,19 @@ static const char* kNames[KC_COUNT] = {"gemm_bias", "gemm_swooshl", "gemm_glu", 
                                        "resample", "pack_input", "cfg_euler", "time_embed", "text_glue", "fbank",
                                        "vocoder_elem"};
 const char* kclass_name(int c) { return c >= 0 && c < KC_COUNT ? kNames[c] : "?"; }
+static int sync_each_check(Engine& e, int cls, cudaStream_t s) {
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(s, &cap);
+  if (cap != cudaStreamCaptureStatusNone) return 0;
+  const cudaError_t rc = cudaStreamSynchronize(s);
+  if (rc != cudaSuccess) {
+    fprintf(stderr, "[zv] ZV_SYNC_EACH: launch %lld of class %s failed: %s\n", (long long)g_launch_count,
+            kclass_name(cls), cudaGetErrorString(rc));
+    e.err = std::string("kernel of class ") + kclass_name(cls) + " failed: " + cudaGetErrorString(rc);
+    return (int)rc;
+  }
+  return 0;
+}
 bool kclass_is_tensor(int c) { return c <= KC_ATTN_NONLIN; }
 
 cudaEvent_t Prof::get() {

@@ -397,8 +397,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
   griddep_launch();
 
   if (warp == 0) {
-    const bool issuer = elect_one();  // uniform loops, one elected lane issues (see elect_one)
-    {
+    if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
 #ifdef ZV_TRACE
@@ -425,17 +424,14 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           if (PAIR) {
             // both CTAs' bytes complete on the leader's full barrier
             const uint32_t fb = mapa_shared(smem_u32(&tail->full[stage]), 0);
-            if (issuer) {
-              if (rank == 0) mbar_arrive_expect_tx(&tail->full[stage], 2 * tx);
-              tma_load_2d_pair(sA + stage * A_STAGE_BYTES, mapA, fb, ka, m_blk * BM);
-              tma_load_2d_pair(sW + stage * w_stage_bytes, mapW, fb, kb * BK, n0t + (int)rank * wn);
-            }
-          } else if (issuer) {
+            if (rank == 0) mbar_arrive_expect_tx(&tail->full[stage], 2 * tx);
+            tma_load_2d_pair(sA + stage * A_STAGE_BYTES, mapA, fb, ka, m_blk * BM);
+            tma_load_2d_pair(sW + stage * w_stage_bytes, mapW, fb, kb * BK, n0t + (int)rank * wn);
+          } else {
             mbar_arrive_expect_tx(&tail->full[stage], tx);
             tma_load_2d(sA + stage * A_STAGE_BYTES, mapA, &tail->full[stage], ka, m_blk * BM);
             tma_load_2d(sW + stage * w_stage_bytes, mapW, &tail->full[stage], kb * BK, n0t);
           }
-          __syncwarp();
 #ifdef ZV_TRACE
           tr_pi += clock64() - c1;
 #endif
@@ -443,16 +439,14 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         }
       }
 #ifdef ZV_TRACE
-      if (blockIdx.x == 0 && issuer)
+      if (blockIdx.x == 0)
         printf("[trace] producer: k_blocks %d wait_empty %lld issue %lld total %lld\n", k_blocks, tr_pw, tr_pi,
                clock64() - tr_t0);
 #endif
     }
     __syncwarp();
   } else if (warp == 1) {
-    // the whole warp walks the loops (uniform control flow and operands), one elected lane issues
-    const bool issuer = elect_one();
-    if (rank == 0) {
+    if (lane == 0 && rank == 0) {
       const uint32_t idesc_main = make_idesc_bf16(PAIR ? 2 * BM : BM, block_n);
       const uint32_t idesc_tail = make_idesc_bf16(PAIR ? 2 * BM : BM, bn_tail);
       int stage = 0;
@@ -491,36 +485,31 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
 #endif
           const uint64_t da = make_sdesc_sw128(smem_u32(sA + stage * A_STAGE_BYTES));
           const uint64_t dw = make_sdesc_sw128(smem_u32(sW + stage * w_stage_bytes));
-          if (issuer) {
 #pragma unroll
-            for (int k = 0; k < BK / 16; ++k) {
-              if (PAIR) umma_bf16_pair(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-              else umma_bf16(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-            }
+          for (int k = 0; k < BK / 16; ++k) {
+            if (PAIR) umma_bf16_pair(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            else umma_bf16(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
           }
 #ifdef ZV_TRACE
           const long long m2 = clock64();
           tr_mi += m2 - m1;
 #endif
-          if (issuer) {
-            if (PAIR) {
-              umma_commit_pair(&tail->empty[stage], 3);
-              if (kb == k_blocks - 1) umma_commit_pair(&tail->tmem_full[as], 3);
-            } else {
-              umma_commit(&tail->empty[stage]);
-              if (!DUAL && kb == k_blocks - 1) umma_commit(&tail->tmem_full[as]);
-            }
+          if (PAIR) {
+            umma_commit_pair(&tail->empty[stage], 3);
+            if (kb == k_blocks - 1) umma_commit_pair(&tail->tmem_full[as], 3);
+          } else {
+            umma_commit(&tail->empty[stage]);
+            if (!DUAL && kb == k_blocks - 1) umma_commit(&tail->tmem_full[as]);
           }
-          __syncwarp();
 #ifdef ZV_TRACE
           tr_mc += clock64() - m2;
 #endif
           if (++stage == stages) stage = 0, phase ^= 1;
         }
-        if (!PAIR && DUAL && issuer) umma_commit(&tail->tmem_full[as]);  // one of the two arrivals (warp 3: the other)
+        if (!PAIR && DUAL) umma_commit(&tail->tmem_full[as]);  // one of the two arrivals (warp 3: the other)
       }
 #ifdef ZV_TRACE
-      if (blockIdx.x == 0 && issuer)
+      if (blockIdx.x == 0)
         printf("[trace] mma: wait_acc_free %lld wait_full %lld issue %lld commit %lld total %lld\n", tr_me, tr_mw, tr_mi,
                tr_mc, clock64() - tr_m0);
 #endif
@@ -530,8 +519,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     // Second MMA-issuing thread (DUAL): one thread needs ~340 cycles per K step for four tcgen05.mma and the
     // commit whatever the tile holds, which is all of the K loop when a CTA owns a single narrow tile.  Odd K
     // steps accumulate into the second (otherwise unused) accumulator stage; the epilogue adds the two.
-    const bool issuer = elect_one();
-    if (DUAL && rank == 0 && unit0 < total_tiles) {
+    if (DUAL && lane == 0 && rank == 0 && unit0 < total_tiles) {
       const uint32_t d_tmem = tmem_base + ACC_STAGE_COLS;
       const uint32_t idesc = make_idesc_bf16(BM, block_n);
       for (int kb = 1; kb < k_blocks; kb += 2) {
@@ -540,21 +528,15 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         tc_fence_after();
         const uint64_t da = make_sdesc_sw128(smem_u32(sA + stage * A_STAGE_BYTES));
         const uint64_t dw = make_sdesc_sw128(smem_u32(sW + stage * w_stage_bytes));
-        if (issuer) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            umma_bf16(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb == 1 && k == 0) ? 0u : 1u);
-          umma_commit(&tail->empty[stage]);
-        }
-        __syncwarp();
+        for (int k = 0; k < BK / 16; ++k)
+          umma_bf16(d_tmem, da + 2 * k, dw + 2 * k, idesc, (kb == 1 && k == 0) ? 0u : 1u);
+        umma_commit(&tail->empty[stage]);
       }
-      if (issuer) umma_commit(&tail->tmem_full[0]);  // arrives once all MMAs of this thread have completed
+      umma_commit(&tail->tmem_full[0]);  // arrives once all MMAs of this thread have completed
     }
     __syncwarp();
   } else if (warp >= 4) {
-    // one elected lane per epilogue warp issues its TMA loads / stores and barrier arrives (bulk-group waits are per
-    // thread: always the same lane); elected, not `lane == 0`, so that the operands stay in uniform registers
-    const bool el = elect_one();
     const int q = warp & 3;            // TMEM lane quarter == warp % 4
     const int cg = (warp - 4) >> 2;    // column group
     const int r = q * 32 + lane;       // row within the tile
@@ -575,7 +557,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
     // 32 rows), so the only synchronisation inside the epilogue is __syncwarp.
     uint64_t* rbar = &tail->rbar[cg * 4 + q][0];
     // (every unit of an EPI_RESIDUAL launch is at least 32 * NCG columns wide: each group owns a chunk of it)
-    if (MODE == EPI_RESIDUAL && el && unit0 < total_tiles) {
+    if (MODE == EPI_RESIDUAL && lane == 0 && unit0 < total_tiles) {
       int m_blk, n0t, bn;
       decode(unit0, m_blk, n0t, bn);
       mbar_arrive_expect_tx(&rbar[0], STG_F32_BYTES / 4);
@@ -597,7 +579,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       pf_c += NCG, ++pf_n;
       if (pf_c >= (bn2 >> 5)) pf_c = cg, pf_t += nunits;
     };
-    if (MODE == EPI_RES24 && ep.res_hi && el) {
+    if (MODE == EPI_RES24 && ep.res_hi && lane == 0) {
 #pragma unroll
       for (int i = 0; i < S24_BUFS - 1; ++i) pf_issue();
     }
@@ -630,7 +612,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
       if (cg >= nchunks) {  // this group owns no chunk of the tile: release the accumulator right away
         tc_fence_before();
         __syncwarp();
-        if (el) release_acc(as);
+        if (lane == 0) release_acc(as);
       }
       for (int c = cg; c < nchunks; c += NCG, ++nq) {
         const int n0 = n0t + c * 32;
@@ -651,7 +633,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         if (c + NCG >= nchunks) {  // last accumulator read of this tile by this warp
           tc_fence_before();
           __syncwarp();
-          if (el) release_acc(as);
+          if (lane == 0) release_acc(as);
         }
         float v[32];
 #pragma unroll
@@ -666,7 +648,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           float* fb = reinterpret_cast<float*>(stg + (nq & 1) * STG_F32_BYTES);
           uint8_t* shadow = stg + 2 * STG_F32_BYTES;
           add_bias32(v, ep.bias, rowb, n0, ep.N);
-          if (el) tma_store_wait_read<0>();
+          if (lane == 0) tma_store_wait_read<0>();
           __syncwarp();
           const int x = r & 7;
 #pragma unroll
@@ -676,7 +658,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           if (ep.out_bf16) stage_row_bf16x32(shadow, r, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (el) {
+          if (lane == 0) {
             tma_store_2d(&maps.O1, fb + q * 32 * 32, n0, m_blk * BM + q * 32);
             if (ep.out_bf16) tma_store_2d(&maps.O0, shadow + q * 32 * 64, n0, m_blk * BM + q * 32);
             tma_store_commit();
@@ -687,7 +669,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           const int sb = nq & 1;
           float* fb = reinterpret_cast<float*>(stg + sb * STG_F32_BYTES);
           uint8_t* shadow = stg + 2 * STG_F32_BYTES;
-          if (el) {
+          if (lane == 0) {
             // the previous chunk's stores must have finished reading buffer sb^1 and the shadow buffer
             tma_store_wait_read<0>();
             // prefetch the residual of the next chunk of this group (possibly in the next tile)
@@ -733,7 +715,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           if (ep.out_bf16) stage_row_bf16x32(shadow, r, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (el) {
+          if (lane == 0) {
             tma_store_2d(&maps.O1, fb + q * 32 * 32, n0, m_blk * BM + q * 32);
             if (ep.out_bf16) tma_store_2d(&maps.O0, shadow + q * 32 * 64, n0, m_blk * BM + q * 32);
             tma_store_commit();
@@ -746,7 +728,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           const uint32_t sb = nq % S24_BUFS;
           uint8_t* hb = stg + sb * STG_S24_BYTES;
           uint8_t* lb = hb + STG_BF16_BYTES;
-          if (el) {
+          if (lane == 0) {
             // the previous chunk's stores have read their buffer, (nq - 1) % S24_BUFS: the one the next prefetch fills
             tma_store_wait_read<0>();
             if (ep.res_hi) pf_issue();
@@ -804,7 +786,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           *reinterpret_cast<uint4*>(lb + r * 32 + ((1 ^ xl) << 4)) = lo4[1];
           fence_proxy_async_smem();
           __syncwarp();
-          if (el) {
+          if (lane == 0) {
             tma_store_2d(&maps.O0, hb + q * (STG_BF16_BYTES / 4), n0, m_blk * BM + q * 32);
             tma_store_2d(&maps.O1, lb + q * (STG_LO_BYTES / 4), n0, m_blk * BM + q * 32);
             tma_store_commit();
@@ -839,7 +821,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
           }
         }
         ZV_ET(et_math)
-        if (el) tma_store_wait_read<1>();  // the store that last used this staging buffer has read it
+        if (lane == 0) tma_store_wait_read<1>();  // the store that last used this staging buffer has read it
         __syncwarp();
         ZV_ET(et_stw)
         // every warp owns bytes [q * 2048, q * 2048 + 2048) of the buffer for both row widths (gated rows use half)
@@ -848,7 +830,7 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         else stage_row_bf16x32(sbuf, r, v);
         fence_proxy_async_smem();
         __syncwarp();
-        if (el) {
+        if (lane == 0) {
           const uint8_t* src = sbuf + q * 2048;
           if ((MODE == EPI_NONLIN_BF16 && !gated) || tail16)
             tma_store_2d(&maps.O1, src, n0 - ep.gate_cols, m_blk * BM + q * 32);
@@ -858,9 +840,9 @@ gemm_tc_kernel(const __grid_constant__ GemmMaps maps, int m_tiles, int n_tiles, 
         ZV_ET(et_stg)
       }
     }
-    if (el) tma_store_wait_all<0>();
+    if (lane == 0) tma_store_wait_all<0>();
 #ifdef ZV_TRACE
-    if (blockIdx.x == 0 && el && (warp == 4 || warp == 13))
+    if (blockIdx.x == 0 && lane == 0 && (warp == 4 || warp == 13))
       printf("[trace] epilogue warp %d: chunks %u wait_acc %lld tmem_ld+release %lld math %lld wait_store %lld "
              "stage+store %lld total %lld\n", warp, nq, et_acc, et_ld, et_math, et_stw, et_stg, clock64() - et_0);
 #endif
